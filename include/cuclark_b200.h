@@ -1,0 +1,115 @@
+/*
+ * cuclark_b200.h -- C ABI of the B200-native cuCLARK / cuCLARK-l device layer.
+ *
+ * This is the drop-in seam for the reference's `class CuClarkDB<HKMERr>`
+ * (reference src/CuClarkDB.cuh:99-151), the only thing its host engine
+ * (src/CuCLARK_hh.hh) calls to reach the GPU.  Each entry point names the
+ * reference method it replaces.  Differences by design:
+ *   - opaque handle, plain pointers and sizes, int return codes (0 = ok,
+ *     otherwise see ccb_last_error); the library never calls exit()
+ *     (reference: CUERR -> exit(1), src/CuClarkDB.cu:45-53);
+ *   - one handle drives ONE device; multi-GPU = one handle (thread or
+ *     process) per GPU over a replicated table, reads partitioned by the caller;
+ *   - the key width (reference template HKMERr) is a run-time argument.
+ *
+ * Batch data layout is the reference's (src/CuCLARK_hh.hh:1615-1715):
+ *   offsets[n_reads+1]  u32, in units of u16 containers
+ *   containers[]        per read: parts  [len:u16][ceil(len/8) x u16], 8 bases
+ *                       per u16, first base in the top two bits, A=3 C=2 G=1 T=0
+ * Result layout is the reference's (src/CuClarkDB.cu:1401-1405):
+ *   final5[n_reads*5]   u16 {sumN, idxBest, best, idxSecond, second}; idx = target+1, 0 = none
+ *   rows[n_reads*(2*max_hits+2)] u16 {n,(target,count)*n} targets ascending
+ *                       (src/CuClarkDB.cu:1122-1182), only when extended
+ */
+#ifndef CUCLARK_B200_H
+#define CUCLARK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ccb_handle ccb_handle;
+
+typedef struct ccb_config {
+    int    device;        /* CUDA device ordinal                                           */
+    int    k;             /* k-mer length, 2..32 (src/main.cc:106-110)                      */
+    int    n_targets;     /* number of targets = labels 0..n_targets-1 (<= 65534)           */
+    int    max_hits;      /* MAXHITS of the variant: 15 full / 23 light (parameters.hh:44)  */
+    int    n_slots;       /* batch slots (reference: -b batches); >= 1, 2+ overlaps copies  */
+    double load_factor;   /* table fill, 0 = default 0.5                                    */
+    int    verbose;
+} ccb_config;
+
+typedef struct ccb_db_info {
+    uint64_t entries;       /* occupied slots (incl. tombstones)        */
+    uint64_t buckets;       /* home buckets                             */
+    uint64_t bytes;         /* device bytes of the table                */
+    uint64_t tombstones;    /* k-mers seen under more than one label    */
+    uint32_t max_displacement;
+} ccb_db_info;
+
+typedef struct ccb_stats {
+    uint64_t reads;         /* reads submitted                          */
+    uint64_t lookups;       /* k-mers probed   (only with CCB_STATS)    */
+    uint64_t sectors;       /* 32-byte table sectors read (CCB_STATS)   */
+    uint64_t dense_reads;   /* reads re-done by the dense exact path    */
+} ccb_stats;
+
+enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4 };
+
+/* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
+int  ccb_create(const ccb_config* cfg, ccb_handle** out);
+void ccb_destroy(ccb_handle* h);
+/* message of the last failing call on this handle (or of ccb_create when h == NULL) */
+const char* ccb_last_error(const ccb_handle* h);
+
+/* CuClarkDB::read + swapDbParts (src/CuClarkDB.cu:464-770, 776-815): load
+ * <prefix>.sz/.ky/.lb (reference on-disk format, src/hashTable_hh.hh:474-546)
+ * into the device table.  sampling = -s factor (1 = all buckets). */
+int  ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t htsize, int key_bytes,
+                       unsigned sampling, uint64_t* n_loaded);
+/* Same table from (canonical k-mer, label) pairs; a k-mer added under two
+ * different labels becomes non-discriminative (HashTableStorage_hh.hh:244). */
+int  ccb_db_begin(ccb_handle* h, uint64_t expected_entries);
+int  ccb_db_add_pairs(ccb_handle* h, const uint64_t* canon, const uint16_t* labels, uint64_t n);
+int  ccb_db_add_pairs_device(ccb_handle* h, const void* d_canon, const void* d_labels, uint64_t n);
+int  ccb_db_end(ccb_handle* h);
+int  ccb_db_get_info(const ccb_handle* h, ccb_db_info* info);
+
+/* CuClarkDB::malloc (src/CuClarkDB.cu:322-421): pinned host + device buffers for
+ * every slot, owned by the library; the caller fills offsets/containers in
+ * place and reads final5/rows in place after ccb_batch_wait. */
+int  ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended);
+int  ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers,
+                       uint16_t** final5, uint16_t** rows);
+/* CuClarkDB::readyBatch + queryBatch (src/CuClarkDB.cu:821-828, 836-987):
+ * async H2D, query, D2H on the slot's stream; returns immediately. */
+int  ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint64_t n_containers, int flags);
+/* CuClarkDB::waitForBatch / checkBatch (src/CuClarkDB.cu:442-456) */
+int  ccb_batch_wait(ccb_handle* h, int slot);
+int  ccb_batch_poll(ccb_handle* h, int slot);          /* 0 = finished, 1 = still running */
+/* CuClarkDB::freeBatchMemory (src/CuClarkDB.cu:285-316) */
+int  ccb_batch_free(ccb_handle* h);
+/* CuClarkDB::sync (src/CuClarkDB.cu:427-436) */
+int  ccb_sync(ccb_handle* h);
+
+/* Device-resident variant of queryBatch for callers that already hold the batch
+ * in HBM (multi-GPU pipelines, kernel-only timing): all pointers are device
+ * pointers, stream is a cudaStream_t (NULL = default stream).  d_rows may be NULL.
+ * d_stats (optional) = 2 x u64 device counters {lookups, sectors}, accumulated. */
+int  ccb_query_device(ccb_handle* h, const void* d_offsets, const void* d_containers,
+                      uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
+                      int flags, void* stream);
+
+int  ccb_get_stats(const ccb_handle* h, ccb_stats* out);
+
+/* library / build identification, e.g. "cuclark_b200 0.1 sm_100a" */
+const char* ccb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,449 @@
+// capi.cu -- C ABI (include/cuclark_b200.h) over the table + query kernels.
+#include "../../include/cuclark_b200.h"
+#include "query.cuh"
+#include "table.cuh"
+
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+using namespace ccb;
+
+namespace {
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  done = nullptr;
+    // pinned host
+    uint32_t* h_offsets = nullptr; uint16_t* h_cont = nullptr;
+    uint16_t* h_final5 = nullptr;  uint16_t* h_rows = nullptr;
+    // device
+    uint32_t* d_offsets = nullptr; uint16_t* d_cont = nullptr;
+    uint16_t* d_final5 = nullptr;  uint16_t* d_rows = nullptr;
+    uint32_t* d_ovf_list = nullptr; uint32_t* d_ovf_count = nullptr;
+    uint32_t* d_dense_scratch = nullptr;
+    unsigned long long* d_stats = nullptr;     // lookups, sectors
+    uint32_t* h_ovf_count = nullptr;           // pinned
+    unsigned long long* h_stats = nullptr;     // pinned
+    bool      in_flight = false;
+    uint32_t  n_reads = 0;
+    int       flags = 0;
+};
+
+constexpr uint32_t kDenseBlocks = 64;
+thread_local std::string g_create_error;
+
+}  // namespace
+
+struct ccb_handle {
+    ccb_config cfg{};
+    Table      table;
+    bool       db_ready = false, db_building = false;
+    cudaStream_t db_stream = nullptr;
+    std::vector<Slot> slots;
+    uint32_t   max_reads = 0; uint64_t max_cont = 0; bool batch_extended = false;
+    int        row_stride = 0;
+    ccb_stats  stats{};
+    uint64_t   tombstones = 0; uint32_t max_disp = 0;
+    std::string err;
+    // scratch for ccb_query_device
+    uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
+    uint32_t  q_ovf_cap = 0;
+};
+
+static int fail(ccb_handle* h, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (h) h->err = buf; else g_create_error = buf;
+    return code ? code : -1;
+}
+#define CU(h, x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) \
+    return fail(h, (int)e_, "%s failed: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define USE_DEV(h) CU(h, cudaSetDevice((h)->cfg.device))
+
+extern "C" const char* ccb_version(void) { return "cuclark_b200 0.1 sm_100a"; }
+
+extern "C" const char* ccb_last_error(const ccb_handle* h)
+{
+    return h ? h->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
+{
+    if (!cfg || !out) return fail(nullptr, -1, "ccb_create: null argument");
+    if (cfg->k < 2 || cfg->k > 32) return fail(nullptr, -2, "The k-mer length should be in [2,32].");
+    if (cfg->n_targets < 1 || cfg->n_targets > 65534) return fail(nullptr, -3, "n_targets must be in [1,65534]");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0)
+        return fail(nullptr, -4, "No CUDA devices found. Abort. (%s)", cudaGetErrorString(e));   // src/CuClarkDB.cu:128
+    if (cfg->device < 0 || cfg->device >= ndev)
+        return fail(nullptr, -5, "%d CUDA devices requested. Insufficient devices found. Abort.", cfg->device + 1);
+    ccb_handle* h = new ccb_handle();
+    h->cfg = *cfg;
+    if (h->cfg.n_slots < 1) h->cfg.n_slots = 1;
+    if (h->cfg.max_hits < 1) h->cfg.max_hits = 15;
+    if (h->cfg.load_factor <= 0) h->cfg.load_factor = 0.5;
+    h->row_stride = 2 * h->cfg.max_hits + 2;
+    if (cudaSetDevice(cfg->device) != cudaSuccess || cudaStreamCreateWithFlags(&h->db_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));
+        delete h; return -6;
+    }
+    *out = h;
+    return 0;
+}
+
+static void free_slots(ccb_handle* h)
+{
+    for (Slot& s : h->slots) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        cudaFreeHost(s.h_offsets); cudaFreeHost(s.h_cont); cudaFreeHost(s.h_final5); cudaFreeHost(s.h_rows);
+        cudaFreeHost(s.h_ovf_count); cudaFreeHost(s.h_stats);
+        cudaFree(s.d_offsets); cudaFree(s.d_cont); cudaFree(s.d_final5); cudaFree(s.d_rows);
+        cudaFree(s.d_ovf_list); cudaFree(s.d_ovf_count); cudaFree(s.d_dense_scratch); cudaFree(s.d_stats);
+        if (s.done) cudaEventDestroy(s.done);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    h->slots.clear();
+    cudaGetLastError();
+}
+
+extern "C" void ccb_destroy(ccb_handle* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    free_slots(h);
+    table_destroy(h->table);
+    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense);
+    if (h->db_stream) cudaStreamDestroy(h->db_stream);
+    delete h;
+}
+
+// ---------------------------------------------------------------------------
+// database
+// ---------------------------------------------------------------------------
+extern "C" int ccb_db_begin(ccb_handle* h, uint64_t expected_entries)
+{
+    if (!h) return -1;
+    USE_DEV(h);
+    if (h->db_building || h->db_ready) { table_destroy(h->table); h->db_ready = h->db_building = false; }
+    int rc = table_create(h->table, h->cfg.k, expected_entries, h->cfg.load_factor, h->db_stream);
+    if (rc) {
+        table_destroy(h->table);
+        if (rc == (int)cudaErrorMemoryAllocation)
+            return fail(h, rc, "ERROR: Out of GPU memory for the k-mer table (%llu entries).", (unsigned long long)expected_entries);
+        return fail(h, rc, "table_create failed (%d)", rc);
+    }
+    h->db_building = true;
+    return 0;
+}
+
+extern "C" int ccb_db_add_pairs_device(ccb_handle* h, const void* d_canon, const void* d_labels, uint64_t n)
+{
+    if (!h || !h->db_building) return fail(h, -1, "ccb_db_add_pairs_device: call ccb_db_begin first");
+    USE_DEV(h);
+    int rc = table_insert_device(h->table, (const uint64_t*)d_canon, (const uint16_t*)d_labels, n, h->db_stream);
+    if (rc) return fail(h, rc, "table insert failed (%d)", rc);
+    return 0;
+}
+
+extern "C" int ccb_db_add_pairs(ccb_handle* h, const uint64_t* canon, const uint16_t* labels, uint64_t n)
+{
+    if (!h || !h->db_building) return fail(h, -1, "ccb_db_add_pairs: call ccb_db_begin first");
+    USE_DEV(h);
+    const uint64_t chunk = 1ull << 24;
+    uint64_t* dc = nullptr; uint16_t* dl = nullptr;
+    uint64_t cap = n < chunk ? n : chunk;
+    if (cap == 0) return 0;
+    CU(h, cudaMalloc(&dc, cap * 8)); CU(h, cudaMalloc(&dl, cap * 2));
+    int rc = 0;
+    for (uint64_t o = 0; o < n && !rc; o += chunk) {
+        uint64_t m = n - o < chunk ? n - o : chunk;
+        cudaMemcpyAsync(dc, canon + o, m * 8, cudaMemcpyHostToDevice, h->db_stream);
+        cudaMemcpyAsync(dl, labels + o, m * 2, cudaMemcpyHostToDevice, h->db_stream);
+        rc = table_insert_device(h->table, dc, dl, m, h->db_stream);
+        cudaStreamSynchronize(h->db_stream);
+    }
+    cudaFree(dc); cudaFree(dl);
+    if (rc) return fail(h, rc, "table insert failed (%d)", rc);
+    CU(h, cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ccb_db_end(ccb_handle* h)
+{
+    if (!h || !h->db_building) return fail(h, -1, "ccb_db_end: no table under construction");
+    USE_DEV(h);
+    uint32_t st[2] = {0, 0}; unsigned long long cnt[3] = {0, 0, 0};
+    cudaMemcpyAsync(st, h->table.d_status, sizeof st, cudaMemcpyDeviceToHost, h->db_stream);
+    cudaMemcpyAsync(cnt, h->table.d_counts, sizeof cnt, cudaMemcpyDeviceToHost, h->db_stream);
+    int rc = table_finalize(h->table, h->db_stream);
+    h->db_building = false;
+    h->max_disp = st[1]; h->tombstones = cnt[2];
+    if (rc == -13) { table_destroy(h->table); return fail(h, rc, "k-mer table too full: an entry moved more than %d buckets; lower load_factor", kMaxDisp); }
+    if (rc) { table_destroy(h->table); return fail(h, rc, "table finalize failed (%d): %s", rc, rc > 0 ? cudaGetErrorString((cudaError_t)rc) : ""); }
+    h->db_ready = true;
+    return 0;
+}
+
+extern "C" int ccb_db_get_info(const ccb_handle* h, ccb_db_info* info)
+{
+    if (!h || !info || !h->db_ready) return -1;
+    info->entries = h->table.n_inserted; info->buckets = h->table.nb; info->bytes = h->table.bytes();
+    info->tombstones = h->tombstones; info->max_displacement = h->max_disp;
+    return 0;
+}
+
+// Reference files (A9): .sz = HTSIZE bucket sizes, .ky/.lb = keys/labels in
+// bucket order.  Streamed in chunks; the device rebuilds canonical = key*HTSIZE
+// + bucket and inserts (table.cu:k_insert_ref_chunk).
+extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t htsize, int key_bytes,
+                                 unsigned sampling, uint64_t* n_loaded)
+{
+    if (!h || !prefix) return -1;
+    USE_DEV(h);
+    if (key_bytes != 2 && key_bytes != 4 && key_bytes != 8) return fail(h, -2, "key_bytes must be 2, 4 or 8");
+    std::string p = prefix;
+    FILE* fs = fopen((p + ".sz").c_str(), "rb");
+    if (!fs) return fail(h, -20, "Failed to open %s.sz", prefix);          // src/CuClarkDB.cu:483-488
+    FILE* fk = fopen((p + ".ky").c_str(), "rb");
+    if (!fk) { fclose(fs); return fail(h, -20, "Failed to open %s.ky", prefix); }
+    FILE* fl = fopen((p + ".lb").c_str(), "rb");
+    if (!fl) { fclose(fs); fclose(fk); return fail(h, -20, "Failed to open %s.lb", prefix); }
+
+    std::vector<uint8_t> sz(htsize);
+    if (fread(sz.data(), 1, htsize, fs) != htsize) { fclose(fs); fclose(fk); fclose(fl); return fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
+    fclose(fs);
+    // choose buckets (src/CuClarkDB.cu:503-513): keep every sampling-th non-empty bucket
+    const bool all = sampling <= 1;
+    uint64_t n_keep = 0; uint32_t nonzero = 0;
+    std::vector<uint8_t> keep;                 // size used on device (0 = skipped)
+    if (!all) keep.assign(htsize, 0);
+    for (uint64_t b = 0; b < htsize; b++) if (sz[b]) {
+        nonzero++;
+        bool k2 = all || (nonzero % sampling) == 0;
+        if (k2) n_keep += sz[b];
+        if (!all && k2) keep[b] = sz[b];
+    }
+    const uint8_t* ksz = all ? sz.data() : keep.data();
+    int rc = ccb_db_begin(h, n_keep);
+    if (rc) { fclose(fk); fclose(fl); return rc; }
+
+    const uint32_t CB = 1u << 24;               // buckets per chunk
+    const uint64_t CK = 1ull << 25;             // max keys per chunk
+    uint8_t* d_sz = nullptr; uint32_t* d_off = nullptr; void* d_keys = nullptr; uint16_t* d_lab = nullptr;
+    uint32_t* h_off = nullptr; void* h_keys = nullptr; uint16_t* h_lab = nullptr;
+    CU(h, cudaMalloc(&d_sz, CB)); CU(h, cudaMalloc(&d_off, CB * 4ull));
+    CU(h, cudaMalloc(&d_keys, (CK + 256) * key_bytes)); CU(h, cudaMalloc(&d_lab, (CK + 256) * 2));
+    CU(h, cudaMallocHost(&h_off, CB * 4ull));
+    CU(h, cudaMallocHost(&h_keys, (CK + 256) * key_bytes)); CU(h, cudaMallocHost(&h_lab, (CK + 256) * 2));
+    uint64_t b = 0; rc = 0;
+    while (b < htsize && !rc) {
+        uint32_t nb = 0; uint64_t nk = 0;       // nk counts ALL keys of the chunk (file order)
+        while (b + nb < htsize && nb < CB && nk + sz[b + nb] <= CK + 255) {
+            h_off[nb] = (uint32_t)nk; nk += sz[b + nb]; nb++;
+            if (nk >= CK) break;
+        }
+        if (nk) {
+            if (fread(h_keys, (size_t)key_bytes, nk, fk) != nk || fread(h_lab, 2, nk, fl) != nk) { rc = -22; break; }
+            cudaMemcpyAsync(d_keys, h_keys, nk * key_bytes, cudaMemcpyHostToDevice, h->db_stream);
+            cudaMemcpyAsync(d_lab, h_lab, nk * 2, cudaMemcpyHostToDevice, h->db_stream);
+            cudaMemcpyAsync(d_sz, ksz + b, nb, cudaMemcpyHostToDevice, h->db_stream);
+            cudaMemcpyAsync(d_off, h_off, nb * 4ull, cudaMemcpyHostToDevice, h->db_stream);
+            rc = table_insert_ref_chunk(h->table, htsize, b, nb, d_sz, d_off, d_keys, key_bytes, d_lab, h->db_stream);
+            cudaStreamSynchronize(h->db_stream);
+        }
+        b += nb;
+    }
+    fclose(fk); fclose(fl);
+    cudaFree(d_sz); cudaFree(d_off); cudaFree(d_keys); cudaFree(d_lab);
+    cudaFreeHost(h_off); cudaFreeHost(h_keys); cudaFreeHost(h_lab);
+    if (rc == -22) { table_destroy(h->table); h->db_building = false; return fail(h, rc, "%s.ky/.lb are shorter than the bucket sizes in .sz announce", prefix); }
+    if (rc) { table_destroy(h->table); h->db_building = false; return fail(h, rc, "table insert failed (%d)", rc); }
+    rc = ccb_db_end(h);
+    if (rc) return rc;
+    if (n_loaded) *n_loaded = n_keep;
+    if (h->cfg.verbose) fprintf(stderr, "DB loaded on device %d: %llu k-mers, %.3f GB table\n", h->cfg.device,
+                                (unsigned long long)n_keep, h->table.bytes() / 1e9);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// batches
+// ---------------------------------------------------------------------------
+extern "C" int ccb_batch_free(ccb_handle* h)
+{
+    if (!h) return -1;
+    cudaSetDevice(h->cfg.device);
+    free_slots(h);
+    h->max_reads = 0; h->max_cont = 0;
+    return 0;
+}
+
+extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended)
+{
+    if (!h) return -1;
+    USE_DEV(h);
+    if (max_containers > 0xFFFFFFFFull)
+        return fail(h, -30, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>).");  // CuCLARK_hh.hh:1709-1713
+    free_slots(h);
+    h->max_reads = max_reads; h->max_cont = max_containers; h->batch_extended = extended != 0;
+    h->slots.resize((size_t)h->cfg.n_slots);
+    const size_t so = ((size_t)max_reads + 1) * 4, sc = (size_t)(max_containers ? max_containers : 1) * 2,
+                 sf = (size_t)(max_reads ? max_reads : 1) * 10, sr = (size_t)(max_reads ? max_reads : 1) * h->row_stride * 2;
+    for (Slot& s : h->slots) {
+        cudaError_t e = cudaSuccess;
+        auto ok = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
+        ok(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        ok(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        ok(cudaMallocHost(&s.h_offsets, so)); ok(cudaMallocHost(&s.h_cont, sc)); ok(cudaMallocHost(&s.h_final5, sf));
+        ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 16));
+        ok(cudaMalloc(&s.d_offsets, so)); ok(cudaMalloc(&s.d_cont, sc)); ok(cudaMalloc(&s.d_final5, sf));
+        ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 4)); ok(cudaMalloc(&s.d_ovf_count, 4));
+        ok(cudaMalloc(&s.d_dense_scratch, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
+        ok(cudaMalloc(&s.d_stats, 16));
+        if (extended) { ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
+        if (e != cudaSuccess) {
+            free_slots(h);
+            if (e == cudaErrorMemoryAllocation)   // src/CuClarkDB.cu:65-73
+                return fail(h, (int)e, "ERROR: Out of GPU memory.\nPlease increase the number of batches (-b <numberofbatches>).");
+            return fail(h, (int)e, "batch allocation failed: %s", cudaGetErrorString(e));
+        }
+        *s.h_ovf_count = 0; s.h_stats[0] = s.h_stats[1] = 0;
+    }
+    return 0;
+}
+
+extern "C" int ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers,
+                                 uint16_t** final5, uint16_t** rows)
+{
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    Slot& s = h->slots[(size_t)slot];
+    if (offsets) *offsets = s.h_offsets;
+    if (containers) *containers = s.h_cont;
+    if (final5) *final5 = s.h_final5;
+    if (rows) *rows = s.h_rows;
+    return 0;
+}
+
+static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uint32_t* ovf_count,
+                     uint32_t* dense_scratch, int flags, cudaStream_t st)
+{
+    QueryArgs a = a0;
+    a.ovf_list = ovf_list; a.ovf_count = ovf_count;
+    TableView tv = h->table.view();
+    cudaMemsetAsync(ovf_count, 0, 4, st);
+    int rc;
+    if (flags & CCB_FORCE_DENSE) {
+        // every read through the dense exact path (cross-check of the fast path)
+        QueryArgs d = a; d.stats = nullptr;
+        rc = launch_query_dense(tv, d, nullptr, nullptr, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);
+        return rc;
+    }
+    rc = launch_query(tv, a, st);
+    if (rc) return rc;
+    QueryArgs d = a; d.stats = nullptr;
+    return launch_query_dense(tv, d, ovf_list, ovf_count, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);
+}
+
+extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint64_t n_containers, int flags)
+{
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    if (!h->db_ready) return fail(h, -32, "Failed to find the database.");
+    if (n_reads > h->max_reads || n_containers > h->max_cont) return fail(h, -33, "batch larger than allocated (%u reads, %llu containers)", n_reads, (unsigned long long)n_containers);
+    if ((flags & CCB_EXTENDED) && !h->batch_extended) return fail(h, -34, "extended results requested but ccb_batch_alloc(extended=0)");
+    USE_DEV(h);
+    Slot& s = h->slots[(size_t)slot];
+    if (s.in_flight) { CU(h, cudaEventSynchronize(s.done)); s.in_flight = false; }
+    s.n_reads = n_reads; s.flags = flags;
+    if (n_reads == 0) { CU(h, cudaEventRecord(s.done, s.stream)); s.in_flight = true; return 0; }
+    CU(h, cudaMemcpyAsync(s.d_offsets, s.h_offsets, ((size_t)n_reads + 1) * 4, cudaMemcpyHostToDevice, s.stream));
+    if (n_containers) CU(h, cudaMemcpyAsync(s.d_cont, s.h_cont, (size_t)n_containers * 2, cudaMemcpyHostToDevice, s.stream));
+    QueryArgs a{};
+    a.offsets = s.d_offsets; a.containers = s.d_cont; a.n_reads = n_reads;
+    a.out5 = s.d_final5; a.rows = (flags & CCB_EXTENDED) ? s.d_rows : nullptr; a.row_stride = h->row_stride;
+    a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr;
+    if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 16, s.stream));
+    int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, s.d_dense_scratch, flags, s.stream);
+    if (rc) return fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    CU(h, cudaMemcpyAsync(s.h_final5, s.d_final5, (size_t)n_reads * 10, cudaMemcpyDeviceToHost, s.stream));
+    if (flags & CCB_EXTENDED) CU(h, cudaMemcpyAsync(s.h_rows, s.d_rows, (size_t)n_reads * h->row_stride * 2, cudaMemcpyDeviceToHost, s.stream));
+    CU(h, cudaMemcpyAsync(s.h_ovf_count, s.d_ovf_count, 4, cudaMemcpyDeviceToHost, s.stream));
+    if (flags & CCB_STATS) CU(h, cudaMemcpyAsync(s.h_stats, s.d_stats, 16, cudaMemcpyDeviceToHost, s.stream));
+    CU(h, cudaEventRecord(s.done, s.stream));
+    s.in_flight = true;
+    return 0;
+}
+
+static void harvest(ccb_handle* h, Slot& s)
+{
+    h->stats.reads += s.n_reads;
+    h->stats.dense_reads += (s.flags & CCB_FORCE_DENSE) ? s.n_reads : *s.h_ovf_count;
+    if (s.flags & CCB_STATS) { h->stats.lookups += s.h_stats[0]; h->stats.sectors += s.h_stats[1]; }
+    s.in_flight = false;
+}
+
+extern "C" int ccb_batch_wait(ccb_handle* h, int slot)
+{
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    Slot& s = h->slots[(size_t)slot];
+    if (!s.in_flight) return 0;
+    USE_DEV(h);
+    CU(h, cudaEventSynchronize(s.done));
+    harvest(h, s);
+    return 0;
+}
+
+extern "C" int ccb_batch_poll(ccb_handle* h, int slot)
+{
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    Slot& s = h->slots[(size_t)slot];
+    if (!s.in_flight) return 0;
+    cudaError_t e = cudaEventQuery(s.done);
+    if (e == cudaErrorNotReady) return 1;
+    if (e != cudaSuccess) return fail(h, (int)e, "cudaEventQuery: %s", cudaGetErrorString(e));
+    harvest(h, s);
+    return 0;
+}
+
+extern "C" int ccb_sync(ccb_handle* h)
+{
+    if (!h) return -1;
+    USE_DEV(h);
+    CU(h, cudaDeviceSynchronize());
+    return 0;
+}
+
+extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void* d_containers,
+                                uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
+                                int flags, void* stream)
+{
+    if (!h) return -1;
+    if (!h->db_ready) return fail(h, -32, "Failed to find the database.");
+    USE_DEV(h);
+    if (h->q_ovf_cap < n_reads || !h->q_ovf_list) {
+        cudaFree(h->q_ovf_list); h->q_ovf_list = nullptr;
+        CU(h, cudaMalloc(&h->q_ovf_list, (size_t)(n_reads ? n_reads : 1) * 4));
+        h->q_ovf_cap = n_reads;
+    }
+    if (!h->q_ovf_count) CU(h, cudaMalloc(&h->q_ovf_count, 4));
+    if (!h->q_dense) CU(h, cudaMalloc(&h->q_dense, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
+    QueryArgs a{};
+    a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
+    a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
+    a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr;
+    int rc = run_query(h, a, h->q_ovf_list, h->q_ovf_count, h->q_dense, flags, (cudaStream_t)stream);
+    if (rc) return fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    return 0;
+}
+
+extern "C" int ccb_get_stats(const ccb_handle* h, ccb_stats* out)
+{
+    if (!h || !out) return -1;
+    *out = h->stats;
+    return 0;
+}

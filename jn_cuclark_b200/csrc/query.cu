@@ -1,0 +1,324 @@
+// query.cu -- fused k-mer extraction -> canonicalise -> probe -> vote.
+//
+// Replaces the reference's queryKernel + mergeKernel + resultKernel
+// (src/CuClarkDB.cu:1000-1183, 1261-1355, 1361-1411) by one kernel:
+//
+//  * one warp per read, the read is walked in tiles of 512 k-mer start
+//    positions; each lane owns a CONTIGUOUS chunk of positions, so forward and
+//    reverse-complement words roll (4 ALU ops per k-mer instead of the
+//    reference's per-k-mer assembly + 5-stage bit reversal);
+//  * the reference's packed batch layout is consumed as is: the container
+//    stream IS the 2-bit stream, part headers / tail padding / part breaks
+//    become an invalid-position bitmask, so N handling costs one AND per k-mer;
+//  * 4 independent 32-byte probes are in flight per lane before any is
+//    consumed (memory-level parallelism for the HBM random-access bound);
+//  * votes never touch shared or global memory: labels are reduced with
+//    warp shuffles into <=32 register accumulators (one (target,count) per
+//    lane), then best / second best are two warp max-reductions on the key
+//    (count desc, target asc) == the reference's ascending scan
+//    (src/CuClarkDB.cu:1380-1399).
+#include "query.cuh"
+
+namespace ccb {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kTilePos     = 512;          // k-mer start positions per tile
+constexpr int kTileSlots   = kTilePos / 8; // containers per tile
+constexpr int kLoadSlots   = 72;           // 64 + halo (k-1 <= 31 bases -> 4 slots) rounded up
+constexpr int kBaseWords   = kLoadSlots / 2;       // 36 x 16 bases
+constexpr int kMaskWords   = 20;                   // 18 used + pad
+
+struct WarpSmem {
+    uint32_t base[kBaseWords];   // MSB-first: base p at word p>>4, bits 31-2(p&15)..
+    uint32_t mask[kMaskWords];   // LSB-first: position p valid <=> bit p&31 of word p>>5
+};
+
+__device__ __forceinline__ uint32_t slot_of(const WarpSmem& w, int j)
+{   // u16 container j of the tile
+    return (w.base[j >> 1] >> (16 * (1 - (j & 1)))) & 0xFFFFu;
+}
+
+// Fold up to four labels per lane into the warp's register accumulators.
+__device__ __forceinline__ void vote4(const uint32_t (&lab)[4], uint32_t& acc_lab, uint32_t& acc_cnt,
+                                      int& nacc, bool& overflow, int lane)
+{
+    uint32_t pend = (lab[0] != kLabelNone ? 1u : 0u) | (lab[1] != kLabelNone ? 2u : 0u) |
+                    (lab[2] != kLabelNone ? 4u : 0u) | (lab[3] != kLabelNone ? 8u : 0u);
+    for (;;) {
+        uint32_t b = __ballot_sync(0xFFFFFFFFu, pend != 0);
+        if (b == 0) break;
+        int src = __ffs(b) - 1;
+        uint32_t mine = (pend & 1u) ? lab[0] : (pend & 2u) ? lab[1] : (pend & 4u) ? lab[2] : lab[3];
+        uint32_t L = __shfl_sync(0xFFFFFFFFu, mine, src);
+        uint32_t c = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if (((pend >> j) & 1u) && lab[j] == L) { c++; pend &= ~(1u << j); }
+        uint32_t total = __reduce_add_sync(0xFFFFFFFFu, c);
+        uint32_t hit = __ballot_sync(0xFFFFFFFFu, lane < nacc && acc_lab == L);
+        if (hit) {
+            if (lane == __ffs(hit) - 1) acc_cnt += total;
+        } else if (nacc < 32) {
+            if (lane == nacc) { acc_lab = L; acc_cnt = total; }
+            nacc++;
+        } else {
+            overflow = true;
+        }
+    }
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_query(const TableView t, const QueryArgs a)
+{
+    __shared__ WarpSmem smem[kWarpsPerCta];
+    const int lane = threadIdx.x & 31;
+    const int wid  = threadIdx.x >> 5;
+    WarpSmem& sw = smem[wid];
+    const int k = t.hp.k;
+    const uint64_t kmsk = t.hp.mask;
+    const uint64_t validk = (k >= 64) ? ~0ull : ((1ull << k) - 1);
+    const int s2 = 2 * (k - 1);
+    const uint32_t total_warps = gridDim.x * kWarpsPerCta;
+
+    for (uint32_t r = blockIdx.x * kWarpsPerCta + wid; r < a.n_reads; r += total_warps) {
+        const uint32_t beg = a.offsets[r];
+        const int nslots = (int)(a.offsets[r + 1] - beg);
+        const uint16_t* c = a.containers + beg;
+        uint32_t acc_lab = kLabelNone, acc_cnt = 0;
+        int nacc = 0; bool overflow = false;
+        unsigned long long st_lookups = 0; uint32_t st_sectors = 0;
+
+        const int total_pos = 8 * (nslots - 1) - (k - 1);
+        if (total_pos > 0) {
+            int ps = 0, pl = (int)c[0];              // current part: header slot, length
+            const int ntiles = (total_pos + kTilePos - 1) / kTilePos;
+            for (int tile = 0; tile < ntiles; tile++) {
+                const int slot0 = 1 + tile * kTileSlots;        // first container of the tile
+                // ---- stage the tile's containers: 2 x u16 -> one MSB-first word ----
+                __syncwarp();
+                for (int w = lane; w < kBaseWords; w += 32) {
+                    int s = slot0 + 2 * w;
+                    uint32_t v0 = s < nslots ? (uint32_t)c[s] : 0u;
+                    uint32_t v1 = s + 1 < nslots ? (uint32_t)c[s + 1] : 0u;
+                    sw.base[w] = (v0 << 16) | v1;
+                }
+                __syncwarp();
+                // ---- valid-position mask from the part walk (src/CuClarkDB.cu:1042-1047) ----
+                {
+                    uint32_t m = 0;
+                    const int next_tile_slot0 = slot0 + kTileSlots;
+                    const int w0 = 32 * lane;            // tile-relative position of my mask word
+                    int cs = ps, cl = pl; bool have_c = false;
+                    for (;;) {
+                        int lo = 8 * ps - kTilePos * tile, hi = lo + pl;   // valid range, tile-relative
+                        int x0 = max(lo, w0) - w0, x1 = min(hi, w0 + 32) - w0;
+                        if (x0 < x1) m |= (x1 - x0 == 32) ? 0xFFFFFFFFu : (((1u << (x1 - x0)) - 1u) << x0);
+                        int next = ps + 1 + ((pl + 7) >> 3);
+                        if (!have_c && next > next_tile_slot0) { cs = ps; cl = pl; have_c = true; }
+                        if (next >= slot0 + kLoadSlots || next >= nslots) break;
+                        ps = next; pl = (int)slot_of(sw, next - slot0);
+                    }
+                    if (have_c) { ps = cs; pl = cl; }
+                    if (lane < kMaskWords) sw.mask[lane] = m;
+                }
+                __syncwarp();
+                // ---- my chunk of positions ----
+                const int npos = min(kTilePos, total_pos - tile * kTilePos);
+                const int chunk = 4 * ((npos + 127) >> 7);       // multiple of 4, <= 16
+                const int p0 = lane * chunk;
+                uint64_t hi, lo, vm;
+                {
+                    int j = p0 >> 4, sh = 2 * (p0 & 15);
+                    uint32_t a0 = sw.base[j], a1 = sw.base[j + 1], a2 = sw.base[j + 2],
+                             a3 = sw.base[j + 3], a4 = sw.base[min(j + 4, kBaseWords - 1)];
+                    uint32_t b0 = __funnelshift_l(a1, a0, sh), b1 = __funnelshift_l(a2, a1, sh),
+                             b2 = __funnelshift_l(a3, a2, sh), b3 = __funnelshift_l(a4, a3, sh);
+                    hi = ((uint64_t)b0 << 32) | b1; lo = ((uint64_t)b2 << 32) | b3;
+                    int jm = p0 >> 5, shm = p0 & 31;
+                    uint32_t m0 = sw.mask[jm], m1 = sw.mask[jm + 1], m2 = sw.mask[jm + 2];
+                    vm = ((uint64_t)__funnelshift_r(m1, m2, shm) << 32) | __funnelshift_r(m0, m1, shm);
+                }
+                uint64_t x = hi >> (64 - s2);                       // first k-1 bases
+                uint64_t rc = revcomp(x, k);
+                uint64_t rest_hi = (hi << s2) | (lo >> (64 - s2)), rest_lo = lo << s2;
+                const int ngroups = chunk >> 2;
+                for (int g = 0; g < ngroups; g++) {
+                    uint64_t e[4][4]; uint64_t home[4], q[4]; bool ok[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int i = 4 * g + j;
+                        uint64_t code = rest_hi >> 62;
+                        rest_hi = (rest_hi << 2) | (rest_lo >> 62); rest_lo <<= 2;
+                        x = ((x << 2) | code) & kmsk;
+                        rc = (rc >> 2) | ((3ull - code) << s2);
+                        ok[j] = (p0 + i < npos) && (((vm >> i) & validk) == validk);
+                        uint64_t cn = x < rc ? x : rc;
+                        uint64_t h = mix2k(cn, k, kmsk);
+                        home[j] = home_of(h, t.hp);
+                        q[j] = key48_of(h) << 16;
+                        if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
+                    }
+                    uint32_t lab[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        lab[j] = kLabelNone;
+                        if (ok[j]) {
+                            uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &st_sectors : nullptr);
+                            lab[j] = l >= kLabelTomb ? kLabelNone : l;
+                            if (STATS) { st_lookups++; st_sectors++; }
+                        }
+                    }
+                    vote4(lab, acc_lab, acc_cnt, nacc, overflow, lane);
+                }
+            }
+        }
+        // ---- result: {sumN, idxBest, best, idxSecond, second} (src/CuClarkDB.cu:1370-1405) ----
+        const uint32_t cnt16 = lane < nacc ? (acc_cnt & 0xFFFFu) : 0u;   // reference counters are u16
+        const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, cnt16);
+        const uint32_t key = cnt16 ? ((cnt16 << 16) | (0xFFFFu - acc_lab)) : 0u;
+        const uint32_t k1 = __reduce_max_sync(0xFFFFFFFFu, key);
+        const uint32_t k2 = __reduce_max_sync(0xFFFFFFFFu, key == k1 ? 0u : key);
+        if (lane < 5) {
+            uint32_t v;
+            if (lane == 0) v = sum;
+            else if (lane == 1) v = k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u;
+            else if (lane == 2) v = k1 >> 16;
+            else if (lane == 3) v = k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u;
+            else v = k2 >> 16;
+            a.out5[(size_t)r * 5 + lane] = (uint16_t)v;
+        }
+        if (a.rows) {
+            uint16_t* row = a.rows + (size_t)r * a.row_stride;
+            int rank = 0;
+            for (int j = 0; j < nacc; j++) {
+                uint32_t l = __shfl_sync(0xFFFFFFFFu, acc_lab, j);
+                rank += (l < acc_lab) ? 1 : 0;
+            }
+            if (lane == 0) row[0] = (uint16_t)min(nacc, (a.row_stride - 1) / 2);
+            if (lane < nacc && 2 * rank + 2 < a.row_stride) {
+                row[1 + 2 * rank] = (uint16_t)acc_lab;
+                row[2 + 2 * rank] = (uint16_t)acc_cnt;
+            }
+        }
+        if (overflow && lane == 0 && a.ovf_list) {
+            uint32_t i = atomicAdd(a.ovf_count, 1u);
+            a.ovf_list[i] = r;
+        }
+        if (STATS) {
+            unsigned long long l = st_lookups, s = st_sectors;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                l += __shfl_xor_sync(0xFFFFFFFFu, l, o);
+                s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+            }
+            if (lane == 0) { atomicAdd(a.stats + 0, l); atomicAdd(a.stats + 1, s); }
+        }
+    }
+}
+
+int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s)
+{
+    if (a.n_reads == 0) return 0;
+    uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
+    uint32_t cap = 148u * 8u;                       // persistent-style: 8 CTAs per SM, grid-stride over reads
+    if (ctas > cap) ctas = cap;
+    if (a.stats) k_query<true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a);
+    else         k_query<false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a);
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// dense exact path (rare): the reference's own counting scheme
+// (one counter per target, src/CuClarkDB.cu:1017-1027,1104-1108) but with the
+// counters in global scratch, so any number of distinct targets is exact.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t kmer_at(const uint16_t* data, int j, int k, uint64_t mask)
+{   // bases j..j+k-1 of a part whose containers start at data (src/CuClarkDB.cu:1063-1083)
+    uint64_t x = 0;
+    for (int b = 0; b < k; b++) {
+        int p = j + b;
+        x = (x << 2) | ((data[p >> 3] >> (2 * (7 - (p & 7)))) & 3u);
+    }
+    return x & mask;
+}
+
+__global__ void __launch_bounds__(256)
+k_query_dense(const TableView t, const QueryArgs a, const uint32_t* read_list, const uint32_t* d_n_list,
+              uint32_t max_list, uint32_t n_targets, uint32_t* scratch)
+{
+    __shared__ uint32_t s_key[2][256];
+    __shared__ uint32_t s_sum[256];
+    uint32_t n_list = d_n_list ? min(*d_n_list, max_list) : max_list;
+    uint32_t* cnt = scratch + (size_t)blockIdx.x * n_targets;
+    const int k = t.hp.k;
+    for (uint32_t li = blockIdx.x; li < n_list; li += gridDim.x) {
+        const uint32_t r = read_list ? read_list[li] : li;
+        for (uint32_t i = threadIdx.x; i < n_targets; i += blockDim.x) cnt[i] = 0;
+        __syncthreads();
+        const uint32_t beg = a.offsets[r], end = a.offsets[r + 1];
+        uint32_t p = beg;
+        while (p < end) {
+            int len = a.containers[p];
+            const uint16_t* data = a.containers + p + 1;
+            p += 1 + ((len + 7) >> 3);
+            for (int j = threadIdx.x; j + k <= len; j += blockDim.x) {
+                uint64_t x = kmer_at(data, j, k, t.hp.mask);
+                uint32_t lab = lookup(t, canonical(x, k));
+                if (lab != kLabelNone) atomicAdd(cnt + lab, 1u);
+            }
+        }
+        __syncthreads();
+        // top-2 under (count desc, target asc) + sum
+        uint32_t k1 = 0, k2 = 0, sum = 0;
+        for (uint32_t i = threadIdx.x; i < n_targets; i += blockDim.x) {
+            uint32_t c16 = cnt[i] & 0xFFFFu;
+            if (!c16) continue;
+            sum += c16;
+            uint32_t key = (c16 << 16) | (0xFFFFu - i);
+            if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
+        }
+        s_key[0][threadIdx.x] = k1; s_key[1][threadIdx.x] = k2; s_sum[threadIdx.x] = sum;
+        __syncthreads();
+        for (int o = 128; o; o >>= 1) {
+            if ((int)threadIdx.x < o) {
+                uint32_t a1 = s_key[0][threadIdx.x], a2 = s_key[1][threadIdx.x];
+                uint32_t b1 = s_key[0][threadIdx.x + o], b2 = s_key[1][threadIdx.x + o];
+                uint32_t m1 = max(a1, b1);
+                uint32_t m2 = max(min(a1, b1), max(a2, b2));
+                s_key[0][threadIdx.x] = m1; s_key[1][threadIdx.x] = m2;
+                s_sum[threadIdx.x] += s_sum[threadIdx.x + o];
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {
+            k1 = s_key[0][0]; k2 = s_key[1][0];
+            uint16_t* o5 = a.out5 + (size_t)r * 5;
+            o5[0] = (uint16_t)s_sum[0];
+            o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
+            o5[2] = (uint16_t)(k1 >> 16);
+            o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
+            o5[4] = (uint16_t)(k2 >> 16);
+            if (a.rows) {
+                uint16_t* row = a.rows + (size_t)r * a.row_stride;
+                int n = 0, fit = (a.row_stride - 1) / 2;
+                for (uint32_t i = 0; i < n_targets && n < fit; i++)
+                    if (cnt[i] & 0xFFFFu) { row[1 + 2 * n] = (uint16_t)i; row[2 + 2 * n] = (uint16_t)cnt[i]; n++; }
+                row[0] = (uint16_t)n;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+int launch_query_dense(const TableView& t, const QueryArgs& a, const uint32_t* read_list,
+                       const uint32_t* d_n_list, uint32_t max_list, uint32_t n_targets,
+                       uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s)
+{
+    if (max_list == 0 || n_scratch_blocks == 0) return 0;
+    uint32_t g = max_list < n_scratch_blocks ? max_list : n_scratch_blocks;
+    k_query_dense<<<g, 256, 0, s>>>(t, a, read_list, d_n_list, max_list, n_targets, scratch);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace ccb

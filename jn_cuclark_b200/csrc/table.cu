@@ -1,0 +1,205 @@
+// table.cu -- building the bucketed table on the device (see table.cuh).
+#include "table.cuh"
+#include <stdio.h>
+
+namespace ccb {
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return (int)e_; } while (0)
+
+// ---------------------------------------------------------------------------
+// insertion
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t ld_volatile(const uint64_t* p)
+{
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+
+// Insert (canonical, label).  Slots of a bucket fill front to back and never
+// change key afterwards, so every inserter of the same key meets either the
+// key itself or the same first empty slot: no duplicates under concurrency.
+__device__ void insert_one(uint64_t* buckets, uint32_t* flags, uint32_t* status,
+                           unsigned long long* counts, const HashParams hp,
+                           uint64_t canon, uint32_t label)
+{
+    const uint64_t h = mix2k(canon, hp.k, hp.mask);
+    const uint64_t home = home_of(h, hp);
+    const uint64_t q = key48_of(h) << 16;
+    const uint64_t mine = q | label;
+    for (int d = 0; d <= kMaxDisp; d++) {
+        uint64_t* b = buckets + (home + d) * kSlots;
+#pragma unroll 1
+        for (int s = 0; s < kSlots; s++) {
+            uint64_t e = ld_volatile(b + s);
+            if (e == kEmpty) {
+                e = atomicCAS((unsigned long long*)(b + s), (unsigned long long)kEmpty, (unsigned long long)mine);
+                if (e == kEmpty) {
+                    atomicMax(status + 1, (uint32_t)d);
+                    atomicAdd(counts + 0, 1ull);
+                    return;
+                }
+            }
+            if ((e ^ q) < 0x10000ull) {                    // same k-mer already present
+                uint32_t have = (uint32_t)(e & 0xFFFF);
+                if (have == label || have == kLabelTomb) { atomicAdd(counts + 1, 1ull); return; }
+                // seen under two labels: not discriminative (reference
+                // HashTableStorage_hh.hh:244, Multiplicity != 1)
+                uint64_t tomb = q | kLabelTomb;
+                for (;;) {
+                    uint64_t old = atomicCAS((unsigned long long*)(b + s), (unsigned long long)e, (unsigned long long)tomb);
+                    if (old == e || (old & 0xFFFF) == kLabelTomb) break;
+                    e = old;
+                }
+                atomicAdd(counts + 2, 1ull);
+                return;
+            }
+        }
+        // bucket full and key absent: leave a breadcrumb for the finalize pass
+        uint64_t bi = home + d;
+        atomicOr(flags + (bi >> 4), (d == 0 ? 1u : 2u) << (2 * (bi & 15)));
+    }
+    atomicExch(status + 0, 1u);                            // displacement limit exceeded
+}
+
+__global__ void k_fill_empty(ulonglong4* b, uint64_t n)
+{
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    const ulonglong4 v = make_ulonglong4(kEmpty, kEmpty, kEmpty, kEmpty);
+    for (; i < n; i += stride) b[i] = v;
+}
+
+__global__ void k_insert_pairs(uint64_t* buckets, uint32_t* flags, uint32_t* status,
+                               unsigned long long* counts, HashParams hp,
+                               const uint64_t* canon, const uint16_t* labels, uint64_t n)
+{
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    for (; i < n; i += stride) insert_one(buckets, flags, status, counts, hp, canon[i], labels[i]);
+}
+
+// Reference layout (A9): canonical = key * HTSIZE + bucket (src/hashTable_hh.hh:469).
+template <typename KEY>
+__global__ void k_insert_ref_chunk(uint64_t* buckets, uint32_t* flags, uint32_t* status,
+                                   unsigned long long* counts, HashParams hp,
+                                   uint64_t htsize, uint64_t r0, uint32_t nbk,
+                                   const uint8_t* sz, const uint32_t* off,
+                                   const KEY* keys, const uint16_t* labels)
+{
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    for (; i < nbk; i += stride) {
+        uint32_t n = sz[i];
+        uint32_t o = off[i];
+        for (uint32_t j = 0; j < n; j++) {
+            uint64_t c = (uint64_t)keys[o + j] * htsize + (r0 + i);
+            insert_one(buckets, flags, status, counts, hp, c, labels[o + j]);
+        }
+    }
+}
+
+// Order the entries of every full bucket so that (e0 > e1) == A, (e2 > e3) == B.
+__global__ void k_finalize(ulonglong4* b, const uint32_t* flags, uint64_t n)
+{
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    for (; i < n; i += stride) {
+        ulonglong4 v = b[i];
+        if (v.w == kEmpty) continue;                         // not full: flags are never set
+        uint32_t f = (flags[i >> 4] >> (2 * (i & 15))) & 3u;
+        bool A = f & 1u, B = f & 2u;
+        if ((v.x > v.y) != A) { unsigned long long t = v.x; v.x = v.y; v.y = t; }
+        if ((v.z > v.w) != B) { unsigned long long t = v.z; v.z = v.w; v.w = t; }
+        b[i] = v;
+    }
+}
+
+static int grid_for(uint64_t n, int block)
+{
+    uint64_t g = (n + block - 1) / block;
+    uint64_t cap = 148ull * 32;
+    if (g > cap) g = cap;
+    if (g == 0) g = 1;
+    return (int)g;
+}
+
+int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s)
+{
+    if (k < 2 || k > 32) return -10;
+    if (!(load_factor > 0.0 && load_factor <= 0.95)) load_factor = 0.5;
+    uint64_t nb = (uint64_t)((double)expected_entries / (kSlots * load_factor)) + 1;
+    uint64_t mn = min_buckets_for_k(k);
+    if (nb < mn) nb = mn;
+    t.nb = nb;
+    t.n_phys = nb + kPadBuckets;
+    t.hp.nb = nb; t.hp.k = k; t.hp.shift = 64 - 2 * k; t.hp.mask = kmask(k);
+    t.finalized = false; t.n_inserted = 0;
+    CK(cudaMalloc(&t.d_buckets, t.n_phys * sizeof(Bucket)));
+    size_t fw = (t.n_phys + 15) / 16;
+    CK(cudaMalloc(&t.d_flags, fw * sizeof(uint32_t)));
+    CK(cudaMalloc(&t.d_status, 2 * sizeof(uint32_t)));
+    CK(cudaMalloc(&t.d_counts, 3 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(t.d_flags, 0, fw * sizeof(uint32_t), s));
+    CK(cudaMemsetAsync(t.d_status, 0, 2 * sizeof(uint32_t), s));
+    CK(cudaMemsetAsync(t.d_counts, 0, 3 * sizeof(unsigned long long), s));
+    k_fill_empty<<<grid_for(t.n_phys, 256), 256, 0, s>>>((ulonglong4*)t.d_buckets, t.n_phys);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_labels, uint64_t n, cudaStream_t s)
+{
+    if (t.finalized || !t.d_buckets) return -11;
+    if (n == 0) return 0;
+    k_insert_pairs<<<grid_for(n, 256), 256, 0, s>>>((uint64_t*)t.d_buckets, t.d_flags, t.d_status, t.d_counts,
+                                                    t.hp, d_canon, d_labels, n);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
+                           const uint8_t* d_sz, const uint32_t* d_off,
+                           const void* d_keys, int key_bytes, const uint16_t* d_labels, cudaStream_t s)
+{
+    if (t.finalized || !t.d_buckets) return -11;
+    if (nbk == 0) return 0;
+    int g = grid_for(nbk, 256);
+    uint64_t* b = (uint64_t*)t.d_buckets;
+    if (key_bytes == 2)
+        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint16_t*)d_keys, d_labels);
+    else if (key_bytes == 4)
+        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint32_t*)d_keys, d_labels);
+    else if (key_bytes == 8)
+        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint64_t*)d_keys, d_labels);
+    else return -12;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int table_finalize(Table& t, cudaStream_t s)
+{
+    if (t.finalized || !t.d_buckets) return -11;
+    k_finalize<<<grid_for(t.n_phys, 256), 256, 0, s>>>((ulonglong4*)t.d_buckets, t.d_flags, t.n_phys);
+    CK(cudaGetLastError());
+    uint32_t st[2]; unsigned long long cnt[3];
+    CK(cudaMemcpyAsync(st, t.d_status, sizeof st, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(cnt, t.d_counts, sizeof cnt, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    CK(cudaFree(t.d_flags)); t.d_flags = nullptr;
+    t.n_inserted = cnt[0];
+    t.finalized = true;
+    if (st[0]) return -13;                                  // table too full: displacement > kMaxDisp
+    return 0;
+}
+
+void table_destroy(Table& t)
+{
+    if (t.d_buckets) cudaFree(t.d_buckets);
+    if (t.d_flags) cudaFree(t.d_flags);
+    if (t.d_status) cudaFree(t.d_status);
+    if (t.d_counts) cudaFree(t.d_counts);
+    t = Table{};
+}
+
+}  // namespace ccb

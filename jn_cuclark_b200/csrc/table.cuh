@@ -1,0 +1,109 @@
+// table.cuh -- device-resident table of discriminative k-mers.
+//
+// Replaces the reference's three-array layout (bucket pointers + keys + labels,
+// src/CuClarkDB.cu:567-633,671-741) whose probe needs 2-4 dependent global
+// loads (src/CuClarkDB.cu:1216-1247) by a bucketed open-addressing table in
+// which a probe is ONE aligned 32-byte sector:
+//
+//   bucket  = 4 entries x 8 B, 32-byte aligned
+//   entry   = key48 << 16 | label16         (kEmpty = all ones)
+//   h       = mix2k(canonical)              (bijection on 2k bits)
+//   home    = floor(h * nb / 2^2k), key48 = h & (2^48-1)
+//
+// Overflow: an entry whose home bucket is full goes to the next bucket that has
+// room (at most kMaxDisp further; the table carries kPadBuckets extra buckets,
+// there is no wrap-around).  Two flags per FULL bucket are encoded in the ORDER
+// of its (pairwise distinct) entries, so they cost no bits:
+//   A = e0 > e1 : some entry whose home is this bucket lives in a later bucket
+//   B = e2 > e3 : some entry passes through this bucket (home < b < stored)
+// A miss therefore stops after one sector unless the home bucket is full AND
+// has A set.
+#pragma once
+#include <cuda_runtime.h>
+#include "kmer.cuh"
+
+namespace ccb {
+
+struct TableView {
+    const ulonglong4* buckets;   // nb + kPadBuckets
+    HashParams        hp;
+};
+
+struct alignas(32) Bucket { uint64_t e[4]; };
+
+__device__ __forceinline__ void load_bucket(const ulonglong4* p, uint64_t (&e)[4])
+{
+    // one 256-bit read-only load = one 32-byte sector
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+}
+
+// Match the 4 entries of a bucket against q = key48 << 16.
+// returns label (0..0xFFFD), kLabelTomb, or kLabelNone when absent.
+__device__ __forceinline__ uint32_t match_bucket(const uint64_t (&e)[4], uint64_t q)
+{
+    uint32_t lab = kLabelNone;
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        uint64_t d = e[s] ^ q;
+        if (d < 0x10000ull && e[s] != kEmpty) lab = (uint32_t)d;   // d == label when key bits agree
+    }
+    return lab;
+}
+
+// Resolve a probe whose home bucket is already in registers (e); follows the
+// overflow chain only when the flags demand it.  probes (optional) counts sectors.
+__device__ __forceinline__ uint32_t resolve(const TableView& t, uint64_t home, uint64_t q,
+                                            uint64_t (&e)[4], uint32_t* probes = nullptr)
+{
+    uint32_t lab = match_bucket(e, q);
+    if (lab != kLabelNone) return lab;
+    if (e[3] == kEmpty || !(e[0] > e[1])) return kLabelNone;
+    for (int d = 1; d <= kMaxDisp; d++) {
+        load_bucket(t.buckets + home + d, e);
+        if (probes) (*probes)++;
+        lab = match_bucket(e, q);
+        if (lab != kLabelNone) return lab;
+        if (e[3] == kEmpty || !(e[2] > e[3])) return kLabelNone;
+    }
+    return kLabelNone;
+}
+
+__device__ __forceinline__ uint32_t lookup(const TableView& t, uint64_t canon)
+{
+    uint64_t h = mix2k(canon, t.hp.k, t.hp.mask);
+    uint64_t home = home_of(h, t.hp);
+    uint64_t e[4];
+    load_bucket(t.buckets + home, e);
+    uint32_t lab = resolve(t, home, key48_of(h) << 16, e);
+    return lab >= kLabelTomb ? kLabelNone : lab;
+}
+
+// ---- host-side owner --------------------------------------------------------
+struct Table {
+    Bucket*   d_buckets = nullptr;
+    uint32_t* d_flags   = nullptr;   // 2 bits per bucket while building
+    uint32_t* d_status  = nullptr;   // [0] error (displacement overflow) [1] max displacement seen
+    unsigned long long* d_counts = nullptr; // [0] inserted new [1] duplicates same label [2] tombstoned
+    uint64_t  nb = 0;                // home buckets
+    uint64_t  n_phys = 0;            // nb + kPadBuckets
+    HashParams hp{};
+    bool      finalized = false;
+    uint64_t  n_inserted = 0;        // entries occupying a slot (incl. tombstones)
+
+    TableView view() const { return TableView{reinterpret_cast<const ulonglong4*>(d_buckets), hp}; }
+    size_t bytes() const { return n_phys * sizeof(Bucket); }
+};
+
+// All return cudaError_t-compatible ints (0 = ok) or negative library codes.
+int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s);
+int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_labels, uint64_t n, cudaStream_t s);
+// reference on-disk layout chunk (A9): buckets [r0, r0+nbk) with per-bucket
+// size (0 when skipped by -s sampling) and key offset relative to d_keys.
+int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
+                           const uint8_t* d_sz, const uint32_t* d_off,
+                           const void* d_keys, int key_bytes, const uint16_t* d_labels, cudaStream_t s);
+int table_finalize(Table& t, cudaStream_t s);   // orders entries (flags), frees build scratch, checks status
+void table_destroy(Table& t);
+
+}  // namespace ccb

@@ -1,0 +1,234 @@
+"""ctypes binding of ``libcuclark_b200.so`` (include/cuclark_b200.h).
+
+``CuClarkDB`` mirrors the public interface of the reference's
+``class CuClarkDB<HKMERr>`` (reference src/CuClarkDB.cuh:99-151) method for
+method -- ``read / malloc / readyBatch / queryBatch / waitForBatch /
+checkBatch / sync / freeBatchMemory`` -- so the parity tests read like the
+reference's host engine (src/CuCLARK_hh.hh:599-632, 1599-1605, 1734-1741,
+2081-2091).  All computing happens in the CUDA library; there is no Python or
+CPU implementation behind these calls.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE = 1, 2, 4
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def lib_path() -> str:
+    return os.path.join(_HERE, "libcuclark_b200.so")
+
+
+class CcbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"[ccb {code}] {msg}")
+        self.code = code
+        self.msg = msg
+
+
+class _Config(C.Structure):
+    _fields_ = [("device", C.c_int), ("k", C.c_int), ("n_targets", C.c_int), ("max_hits", C.c_int),
+                ("n_slots", C.c_int), ("load_factor", C.c_double), ("verbose", C.c_int)]
+
+
+class DbInfo(C.Structure):
+    _fields_ = [("entries", C.c_uint64), ("buckets", C.c_uint64), ("bytes", C.c_uint64),
+                ("tombstones", C.c_uint64), ("max_displacement", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("reads", C.c_uint64), ("lookups", C.c_uint64), ("sectors", C.c_uint64),
+                ("dense_reads", C.c_uint64)]
+
+
+_lib = None
+
+# every symbol include/cuclark_b200.h declares: (restype, argtypes)
+_VP, _H = C.c_void_p, C.c_void_p
+SYMBOLS = {
+    "ccb_create": (C.c_int, [C.POINTER(_Config), C.POINTER(_H)]),
+    "ccb_destroy": (None, [_H]),
+    "ccb_last_error": (C.c_char_p, [_H]),
+    "ccb_db_load_files": (C.c_int, [_H, C.c_char_p, C.c_uint64, C.c_int, C.c_uint, C.POINTER(C.c_uint64)]),
+    "ccb_db_begin": (C.c_int, [_H, C.c_uint64]),
+    "ccb_db_add_pairs": (C.c_int, [_H, _VP, _VP, C.c_uint64]),
+    "ccb_db_add_pairs_device": (C.c_int, [_H, _VP, _VP, C.c_uint64]),
+    "ccb_db_end": (C.c_int, [_H]),
+    "ccb_db_get_info": (C.c_int, [_H, C.POINTER(DbInfo)]),
+    "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
+    "ccb_batch_buffers": (C.c_int, [_H, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
+    "ccb_batch_submit": (C.c_int, [_H, C.c_int, C.c_uint32, C.c_uint64, C.c_int]),
+    "ccb_batch_wait": (C.c_int, [_H, C.c_int]),
+    "ccb_batch_poll": (C.c_int, [_H, C.c_int]),
+    "ccb_batch_free": (C.c_int, [_H]),
+    "ccb_sync": (C.c_int, [_H]),
+    "ccb_query_device": (C.c_int, [_H, _VP, _VP, C.c_uint32, _VP, _VP, _VP, C.c_int, _VP]),
+    "ccb_get_stats": (C.c_int, [_H, C.POINTER(Stats)]),
+    "ccb_version": (C.c_char_p, []),
+}
+
+
+def load_library() -> C.CDLL:
+    """Load the CUDA library; fail loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = lib_path()
+    if not os.path.exists(p):
+        raise ImportError(
+            f"{p} is missing: the CUDA extension has not been built "
+            "(run `make -C jn_cuclark_b200` or __graft_entry__.build()). There is no CPU fallback.")
+    lib = C.CDLL(p)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the ABI lost a symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _np_view(ptr: int, n: int, dtype) -> np.ndarray:
+    if n == 0 or not ptr:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype, count=n)
+
+
+class CuClarkDB:
+    """Device database + batch scheduler; same method names as the reference class."""
+
+    def __init__(self, numDevices: int = 1, k: int = 31, numBatches: int = 1, numTargets: int = 1,
+                 verbose: bool = False, *, device: int = 0, max_hits: int = 15, load_factor: float = 0.0):
+        # reference ctor: CuClarkDB(numDevices, k, numBatches, numTargets, verbose)
+        # (src/CuClarkDB.cu:95); one handle drives one device here, so numDevices
+        # must be 1 and `device` picks the ordinal.
+        if numDevices not in (0, 1):
+            raise ValueError("one CuClarkDB drives one GPU; create one per device")
+        self._lib = load_library()
+        self._h = _H()
+        cfg = _Config(device, k, numTargets, max_hits, numBatches, load_factor, int(verbose))
+        rc = self._lib.ccb_create(C.byref(cfg), C.byref(self._h))
+        if rc:
+            raise CcbError(rc, self._lib.ccb_last_error(None).decode())
+        self.k, self.numTargets, self.numBatches, self.max_hits = k, numTargets, numBatches, max_hits
+        self.row_stride = 2 * max_hits + 2
+        self._max_reads = 0
+        self._n = {}
+
+    # -- helpers ------------------------------------------------------------
+    def _ck(self, rc: int):
+        if rc:
+            raise CcbError(rc, self._lib.ccb_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.ccb_destroy(self._h)
+            self._h = _H()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- database -----------------------------------------------------------
+    def read(self, filename: str, htsize: int, key_bytes: int, modCollision: int = 1) -> int:
+        """CuClarkDB::read + swapDbParts (src/CuClarkDB.cu:464, 776). Returns #k-mers loaded."""
+        n = C.c_uint64(0)
+        self._ck(self._lib.ccb_db_load_files(self._h, filename.encode(), htsize, key_bytes, modCollision, C.byref(n)))
+        return n.value
+
+    def load_pairs(self, canon: np.ndarray, labels: np.ndarray):
+        canon = np.ascontiguousarray(canon, dtype=np.uint64)
+        labels = np.ascontiguousarray(labels, dtype=np.uint16)
+        assert canon.shape == labels.shape
+        self._ck(self._lib.ccb_db_begin(self._h, canon.size))
+        self._ck(self._lib.ccb_db_add_pairs(self._h, canon.ctypes.data, labels.ctypes.data, canon.size))
+        self._ck(self._lib.ccb_db_end(self._h))
+
+    def db_begin(self, expected: int):
+        self._ck(self._lib.ccb_db_begin(self._h, expected))
+
+    def db_add_device(self, d_canon: int, d_labels: int, n: int):
+        self._ck(self._lib.ccb_db_add_pairs_device(self._h, d_canon, d_labels, n))
+
+    def db_end(self):
+        self._ck(self._lib.ccb_db_end(self._h))
+
+    def db_info(self) -> DbInfo:
+        info = DbInfo()
+        self._ck(self._lib.ccb_db_get_info(self._h, C.byref(info)))
+        return info
+
+    # -- batches --------------------------------------------------------------
+    def malloc(self, maxReads: int, maxContainers: int, isExtended: bool = False):
+        """CuClarkDB::malloc (src/CuClarkDB.cu:322): library-owned pinned buffers."""
+        self._ck(self._lib.ccb_batch_alloc(self._h, maxReads, maxContainers, int(isExtended)))
+        self._max_reads, self._max_cont, self._ext = maxReads, maxContainers, isExtended
+
+    def buffers(self, batchId: int):
+        """(offsets u32[maxReads+1], containers u16[maxContainers], final5 u16[maxReads,5], rows|None)"""
+        o, c, f, r = _VP(), _VP(), _VP(), _VP()
+        self._ck(self._lib.ccb_batch_buffers(self._h, batchId, C.byref(o), C.byref(c), C.byref(f), C.byref(r)))
+        offs = _np_view(o.value, self._max_reads + 1, np.uint32)
+        cont = _np_view(c.value, self._max_cont, np.uint16)
+        fin = _np_view(f.value, self._max_reads * 5, np.uint16).reshape(-1, 5)
+        rows = _np_view(r.value, self._max_reads * self.row_stride, np.uint16).reshape(-1, self.row_stride) if r.value else None
+        return offs, cont, fin, rows
+
+    def readyBatch(self, batchId: int, numReads: int, containerCount: int):
+        """CuClarkDB::readyBatch (src/CuClarkDB.cu:821)."""
+        self._n[batchId] = (numReads, containerCount)
+
+    def queryBatch(self, batchId: int, isExtended: bool = False, flags: int = 0) -> bool:
+        """CuClarkDB::queryBatch (src/CuClarkDB.cu:836); asynchronous."""
+        n, c = self._n[batchId]
+        self._ck(self._lib.ccb_batch_submit(self._h, batchId, n, c, flags | (CCB_EXTENDED if isExtended else 0)))
+        return True
+
+    def waitForBatch(self, batchId: int) -> bool:
+        self._ck(self._lib.ccb_batch_wait(self._h, batchId))
+        return True
+
+    def checkBatch(self, batchId: int) -> bool:
+        rc = self._lib.ccb_batch_poll(self._h, batchId)
+        if rc not in (0, 1):
+            self._ck(rc)
+        return rc == 0
+
+    def sync(self) -> bool:
+        self._ck(self._lib.ccb_sync(self._h))
+        return True
+
+    def freeBatchMemory(self):
+        self._ck(self._lib.ccb_batch_free(self._h))
+
+    def query_device(self, d_offsets: int, d_containers: int, n_reads: int, d_final5: int,
+                     d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
+        self._ck(self._lib.ccb_query_device(self._h, d_offsets, d_containers, n_reads, d_final5,
+                                            d_rows or None, d_stats or None, flags, stream or None))
+
+    def stats(self) -> Stats:
+        s = Stats()
+        self._ck(self._lib.ccb_get_stats(self._h, C.byref(s)))
+        return s
+
+    # -- convenience used by tests/bench: one whole batch, synchronously ------
+    def classify_packed(self, offsets: np.ndarray, containers: np.ndarray, extended: bool = False,
+                        flags: int = 0, slot: int = 0):
+        n = offsets.size - 1
+        nc = int(offsets[-1])
+        if n > self._max_reads or nc > getattr(self, "_max_cont", 0) or extended != getattr(self, "_ext", None):
+            self.malloc(max(n, 1), max(nc, 1), extended)
+        o, c, f, r = self.buffers(slot)
+        o[: n + 1] = offsets
+        c[:nc] = containers[:nc]
+        self.readyBatch(slot, n, nc)
+        self.queryBatch(slot, extended, flags)
+        self.waitForBatch(slot)
+        return f[:n].copy(), (r[:n].copy() if extended else None)

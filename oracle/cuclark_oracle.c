@@ -260,10 +260,6 @@ int ccbo_db_from_occ(ccbo_occ_vec *occ, int k, uint64_t htsize, unsigned min_t,
         db->keys[i] = e[i].q; db->labels[i] = e[i].label;
     }
     free(e);
-    db->ptr = malloc(sizeof(uint64_t) * (htsize + 1));
-    uint64_t acc = 0;
-    for (uint64_t b = 0; b < htsize; b++) { db->ptr[b] = acc; acc += db->sz[b]; }
-    db->ptr[htsize] = acc;
     return 0;
 }
 
@@ -344,10 +340,6 @@ int ccbo_db_read(const char *prefix, uint64_t htsize, int key_bytes, int k,
         }
     }
     fclose(fk); fclose(fl); free(fsz);
-    db->ptr = malloc(sizeof(uint64_t) * (htsize + 1));
-    uint64_t acc = 0;
-    for (uint64_t b = 0; b < htsize; b++) { db->ptr[b] = acc; acc += db->sz[b]; }
-    db->ptr[htsize] = acc;
     return 0;
 }
 
@@ -360,8 +352,20 @@ void ccbo_db_free(ccbo_db *db)
 /* src/hashTable_hh.hh:359-396 == src/CuClarkDB.cu:1190-1254: canonicalise,
  * q = c / HTSIZE, r = c % HTSIZE, early-out on the bucket's first/last key,
  * ascending linear scan. */
+/* bucket pointers = exclusive prefix sum of the sizes (src/CuClarkDB.cu:589-617);
+ * built on first use because it is 4 B x HTSIZE (6.4 GB in full mode). */
+void ccbo_db_index(ccbo_db *db)
+{
+    if (db->ptr) return;
+    db->ptr = malloc(sizeof(uint32_t) * (db->htsize + 1));
+    uint32_t acc = 0;
+    for (uint64_t b = 0; b < db->htsize; b++) { db->ptr[b] = acc; acc += db->sz[b]; }
+    db->ptr[db->htsize] = acc;
+}
+
 int ccbo_db_find(const ccbo_db *db, uint64_t x, uint16_t *label)
 {
+    if (!db->ptr) ccbo_db_index((ccbo_db *)db);
     uint64_t c = ccbo_canonical(x, db->k);
     uint64_t q = c / db->htsize, r = c - q * db->htsize;
     uint64_t b = db->ptr[r], e = db->ptr[r + 1];
@@ -603,6 +607,7 @@ int ccbo_query_packed(const ccbo_db *db, int k, const uint32_t *offsets,
                       uint64_t *n_lookups, int threads)
 {
     (void)n_targets;
+    ccbo_db_index((ccbo_db *)db);
     return ccbo_query_packed_cb(db_find_cb, (void *)db, k, offsets, containers, n_reads,
                                 out5, rows, row_stride, n_lookups, threads);
 }

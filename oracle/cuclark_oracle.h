@@ -54,7 +54,7 @@ typedef struct {
     uint8_t  *sz;          /* [htsize] bucket sizes (.sz)                    */
     uint64_t *keys;        /* [n] quotient c / htsize, bucket order (.ky)    */
     uint16_t *labels;      /* [n] 0-based target index (.lb)                 */
-    uint64_t *ptr;         /* [htsize+1] exclusive prefix of sz              */
+    uint32_t *ptr;         /* [htsize+1] exclusive prefix of sz, built lazily  */
 } ccbo_db;
 
 typedef struct {
@@ -97,6 +97,7 @@ int  ccbo_db_write(const ccbo_db *db, const char *prefix);
 int  ccbo_db_read(const char *prefix, uint64_t htsize, int key_bytes, int k,
                   unsigned sampling, ccbo_db *db);
 void ccbo_db_free(ccbo_db *db);
+void ccbo_db_index(ccbo_db *db);   /* build ptr (idempotent; call before threaded finds) */
 /* src/hashTable_hh.hh:359-396 == src/CuClarkDB.cu:1190-1254; x = x-encoded k-mer */
 int  ccbo_db_find(const ccbo_db *db, uint64_t x, uint16_t *label);
 /* canonical value of stored entry i in bucket r: key*htsize + r (A9) */

@@ -1,0 +1,112 @@
+#!/usr/bin/env python
+"""Generates the golden fixtures under tests/golden/ by running the UNMODIFIED reference
+(oracle/_ref/cuCLARK, cuCLARK-l built by oracle/Makefile from /root/reference).
+
+  python tests/golden/make_golden.py world     # deterministic inputs (numpy) -> tests/golden/world/
+  python tests/golden/make_golden.py db        # reference CPU database build (runs anywhere; the
+                                               # binary stops at its CUDA probe after writing the DB)
+                                               # -> tests/golden/ref_db/{light,full}.npz
+  python tests/golden/make_golden.py gpu OUT   # on a GPU box: reference classification CSVs -> OUT/
+                                               # (copied to tests/golden/ref_gpu/ afterwards)
+"""
+import hashlib
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import synth  # noqa: E402
+
+WORLD = os.path.join(HERE, "world")
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+
+def make_world():
+    shutil.rmtree(WORLD, ignore_errors=True)
+    tp, genomes, labels = synth.make_genomes(os.path.join(WORLD, "genomes"), 6, 12000, seed=21)
+    os.remove(tp)                                    # absolute paths: regenerated where used
+    with open(os.path.join(WORLD, "labels.txt"), "w") as f:
+        f.write("\n".join(labels) + "\n")
+    reads = synth.make_reads(genomes, 400, 150, seed=22, k=31)
+    synth.write_reads_fasta(os.path.join(WORLD, "reads.fa"), reads)
+    synth.write_reads_fasta(os.path.join(WORLD, "reads_ml.fa"), reads, width=60)
+    synth.write_reads_fastq(os.path.join(WORLD, "reads.fq"), [r for r in reads if " " not in r[0] and len(r[1])])
+    r1, r2 = synth.make_pairs(genomes, 150, seed=23)
+    synth.write_reads_fastq(os.path.join(WORLD, "p1.fq"), r1, "/1")
+    synth.write_reads_fastq(os.path.join(WORLD, "p2.fq"), r2, "/2")
+
+
+def write_targets(dst_dir):
+    labels = open(os.path.join(WORLD, "labels.txt")).read().split()
+    tp = os.path.join(dst_dir, "targets.txt")
+    with open(tp, "w") as f:
+        for i, lab in enumerate(labels):
+            f.write(f"{os.path.join(WORLD, 'genomes', f'g{i}.fa')}\t{lab}\n")
+    return tp
+
+
+def run_ref(binary, args, cwd):
+    return subprocess.run([os.path.join(REF, binary)] + args, cwd=cwd, capture_output=True, text=True)
+
+
+def make_db():
+    out = os.path.join(HERE, "ref_db")
+    os.makedirs(out, exist_ok=True)
+    for mode, binary, k in (("light", "cuCLARK-l", 27), ("full", "cuCLARK", 31)):
+        with tempfile.TemporaryDirectory() as d:
+            tp = write_targets(d)
+            os.makedirs(os.path.join(d, "db"))
+            r = run_ref(binary, ["-k", str(k), "-T", tp, "-D", os.path.join(d, "db") + "/", "-O",
+                                 os.path.join(WORLD, "reads.fa"), "-R", os.path.join(d, "out")], d)
+            files = sorted(os.listdir(os.path.join(d, "db")))
+            assert len(files) == 3, (files, r.stderr[-2000:])
+            prefix = os.path.join(d, "db", files[0][:-3])
+            sz = np.fromfile(prefix + ".sz", dtype=np.uint8)
+            nz = np.flatnonzero(sz)
+            sha = {e: hashlib.sha256(open(prefix + "." + e, "rb").read()).hexdigest() for e in ("sz", "ky", "lb")}
+            np.savez_compressed(os.path.join(out, mode + ".npz"), name=os.path.basename(prefix), htsize=sz.size,
+                                nz_bucket=nz.astype(np.uint32), nz_size=sz[nz],
+                                ky=np.fromfile(prefix + ".ky", dtype=np.uint8), lb=np.fromfile(prefix + ".lb", dtype=np.uint16),
+                                sha_sz=sha["sz"], sha_ky=sha["ky"], sha_lb=sha["lb"])
+            print(mode, os.path.basename(prefix), "k-mers:", int(sz.sum()), sha)
+
+
+def make_gpu(out):
+    os.makedirs(out, exist_ok=True)
+    log = open(os.path.join(out, "log.txt"), "w")
+    for mode, binary, k in (("light", "cuCLARK-l", 27), ("full", "cuCLARK", 31)):
+        d = tempfile.mkdtemp()
+        tp = write_targets(d)
+        os.makedirs(os.path.join(d, "db"))
+        base = ["-k", str(k), "-T", tp, "-D", os.path.join(d, "db") + "/"]
+        runs = [("fa", ["-O", os.path.join(WORLD, "reads.fa")]),
+                ("ml", ["-O", os.path.join(WORLD, "reads_ml.fa")]),
+                ("fq", ["-O", os.path.join(WORLD, "reads.fq")]),
+                ("pe", ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")]),
+                ("fa_ext", ["-O", os.path.join(WORLD, "reads.fa"), "--extended"]),
+                ("pe_ext", ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq"), "--extended"]),
+                ("fa_b4n4", ["-O", os.path.join(WORLD, "reads.fa"), "-n", "4", "-b", "4"])]
+        for name, extra in runs:
+            res = os.path.join(d, name)
+            r = run_ref(binary, base + extra + ["-R", res], d)
+            log.write(f"== {mode} {name} rc={r.returncode}\n{r.stdout[-1500:]}\n{r.stderr[-1500:]}\n")
+            if os.path.exists(res + ".csv"):
+                shutil.copy(res + ".csv", os.path.join(out, f"{mode}_{name}.csv"))
+        shutil.rmtree(d, ignore_errors=True)
+    log.close()
+
+
+if __name__ == "__main__":
+    cmd = sys.argv[1]
+    if cmd == "world":
+        make_world()
+    elif cmd == "db":
+        make_db()
+    elif cmd == "gpu":
+        make_gpu(sys.argv[2])

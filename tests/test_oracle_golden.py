@@ -1,0 +1,55 @@
+"""Pins the oracle's database half (A8/A9) to databases written by the UNMODIFIED reference binary
+(tests/golden/ref_db/*.npz, made by tests/golden/make_golden.py db) -- byte for byte."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+WORLD = os.path.join(HERE, "golden", "world")
+
+
+def _targets(tmp_path):
+    labels = open(os.path.join(WORLD, "labels.txt")).read().split()
+    tp = str(tmp_path / "targets.txt")
+    with open(tp, "w") as f:
+        for i, lab in enumerate(labels):
+            f.write(f"{os.path.join(WORLD, 'genomes', f'g{i}.fa')}\t{lab}\n")
+    return tp, labels
+
+
+@pytest.mark.parametrize("mode", ["light", "full"])
+def test_db_identical_to_reference(oracle, tmp_path, mode):
+    g = np.load(os.path.join(HERE, "golden", "ref_db", mode + ".npz"))
+    light = mode == "light"
+    k = 27 if light else 31
+    ht = int(g["htsize"])
+    assert ht == (oracle.HTSIZE_LIGHT if light else oracle.HTSIZE_FULL)
+    tp, labels = _targets(tmp_path)
+    db = oracle.OracleDb.build(tp, k, ht, light=light)
+    assert os.path.basename(oracle.db_name("x", k, len(set(labels)), ht, 0, light, 4)) == str(g["name"])
+    sz = np.ctypeslib.as_array(db.db.sz, shape=(ht,))
+    nz = np.flatnonzero(sz)
+    assert np.array_equal(nz.astype(np.uint32), g["nz_bucket"]) and np.array_equal(sz[nz], g["nz_size"])
+    assert hashlib.sha256(sz.tobytes()).hexdigest() == str(g["sha_sz"])
+    keys = np.ctypeslib.as_array(db.db.keys, shape=(db.n,)).astype(np.uint32)
+    assert hashlib.sha256(keys.tobytes()).hexdigest() == str(g["sha_ky"])
+    lb = np.ctypeslib.as_array(db.db.labels, shape=(db.n,))
+    assert np.array_equal(lb, g["lb"]) and hashlib.sha256(lb.tobytes()).hexdigest() == str(g["sha_lb"])
+
+
+def test_db_file_roundtrip_and_find(oracle, tmp_path):
+    tp, _ = _targets(tmp_path)
+    db = oracle.OracleDb.build(tp, 27, oracle.HTSIZE_LIGHT, light=True)
+    db.write(str(tmp_path / "x"))
+    g = np.load(os.path.join(HERE, "golden", "ref_db", "light.npz"))
+    for e in ("sz", "ky", "lb"):
+        assert hashlib.sha256(open(str(tmp_path / "x") + "." + e, "rb").read()).hexdigest() == str(g["sha_" + e])
+    db2 = oracle.OracleDb.read(str(tmp_path / "x"), oracle.HTSIZE_LIGHT, 27)
+    c, l = db2.pairs()
+    assert c.size == db.n
+    for i in range(0, c.size, 37):
+        assert db2.find(int(c[i])) == int(l[i])
+        assert db2.find(oracle.revcomp(int(c[i]), 27)) == int(l[i])      # either strand
+    assert db2.find(12345) is None

@@ -1,0 +1,168 @@
+"""GPU parity: CUDA path (through the C ABI) vs the CPU oracle, bit-exact u16[5] and rows."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HT_SMALL = 1000003
+
+
+def _reads(world, name, oracle):
+    return oracle.IndexedReads(open(os.path.join(world["dir"], name), "rb").read())
+
+
+@pytest.fixture(scope="module")
+def full_db(small_world, oracle):
+    return oracle.OracleDb.build(small_world["targets"], 31, HT_SMALL)
+
+
+@pytest.fixture(scope="module")
+def gpu_db(full_db):
+    from jn_cuclark_b200 import CuClarkDB
+    db = CuClarkDB(1, 31, 2, len(full_db.labels))
+    c, l = full_db.pairs()
+    db.load_pairs(c, l)
+    yield db
+    db.close()
+
+
+@pytest.mark.parametrize("fname", ["reads.fa", "reads_ml.fa", "reads.fq"])
+def test_u16x5_bit_exact(small_world, oracle, full_db, gpu_db, fname):
+    from jn_cuclark_b200 import CCB_STATS
+    ir = _reads(small_world, fname, oracle)
+    off, cont = ir.pack(31)
+    want, _, nl = full_db.query_packed(31, off, cont)
+    before = gpu_db.stats().lookups
+    got, _ = gpu_db.classify_packed(off, cont, flags=CCB_STATS)
+    assert np.array_equal(got, want)
+    assert gpu_db.stats().lookups - before == nl
+    assert (want[:, 1] > 0).sum() > 1000          # the test is not vacuous
+
+
+def test_extended_rows(small_world, oracle, full_db, gpu_db):
+    ir = _reads(small_world, "reads.fa", oracle)
+    off, cont = ir.pack(31)
+    want, wrows, _ = full_db.query_packed(31, off, cont, row_stride=gpu_db.row_stride)
+    got, rows = gpu_db.classify_packed(off, cont, extended=True)
+    assert np.array_equal(got, want)
+    n = wrows[:, 0].astype(int)
+    for i in range(len(n)):
+        assert rows[i, 0] == n[i]
+        assert np.array_equal(rows[i, 1:1 + 2 * n[i]], wrows[i, 1:1 + 2 * n[i]])
+
+
+def test_dense_path_equals_fast_path(small_world, oracle, full_db, gpu_db):
+    from jn_cuclark_b200 import CCB_FORCE_DENSE
+    ir = _reads(small_world, "reads.fa", oracle)
+    off, cont = ir.pack(31)
+    want, _, _ = full_db.query_packed(31, off, cont)
+    got, _ = gpu_db.classify_packed(off, cont, flags=CCB_FORCE_DENSE)
+    assert np.array_equal(got, want)
+
+
+def test_paired(small_world, oracle, full_db, gpu_db, tmp_path):
+    m = str(tmp_path / "merged.fa")
+    assert oracle.merge_paired(os.path.join(small_world["dir"], "p1.fq"), os.path.join(small_world["dir"], "p2.fq"), m) == 0
+    ir = oracle.IndexedReads(open(m, "rb").read())
+    off, cont = ir.pack(31)
+    want, _, _ = full_db.query_packed(31, off, cont)
+    got, _ = gpu_db.classify_packed(off, cont)
+    assert np.array_equal(got, want)
+
+
+def test_ref_files_loader(small_world, oracle, full_db, tmp_path):
+    """CuClarkDB::read equivalent: load .sz/.ky/.lb written in the reference format, incl. -s sampling."""
+    from jn_cuclark_b200 import CuClarkDB
+    prefix = str(tmp_path / "db")
+    full_db.write(prefix)
+    ir = _reads(small_world, "reads.fa", oracle)
+    off, cont = ir.pack(31)
+    for s in (1, 3):
+        odb = oracle.OracleDb.read(prefix, HT_SMALL, 31, s)
+        want, _, _ = odb.query_packed(31, off, cont)
+        db = CuClarkDB(1, 31, 1, len(full_db.labels))
+        n = db.read(prefix, HT_SMALL, oracle.lib().ccbo_key_bytes(31, HT_SMALL), s)
+        assert n == odb.n
+        got, _ = db.classify_packed(off, cont)
+        db.close()
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("k", [12, 21, 27, 32])
+def test_other_k(small_world, oracle, k):
+    from jn_cuclark_b200 import CuClarkDB
+    odb = oracle.OracleDb.build(small_world["targets"], k, HT_SMALL)
+    ir = _reads(small_world, "reads.fa", oracle)
+    off, cont = ir.pack(k)
+    want, _, _ = odb.query_packed(k, off, cont)
+    db = CuClarkDB(1, k, 1, len(odb.labels))
+    c, l = odb.pairs()
+    db.load_pairs(c, l)
+    got, _ = db.classify_packed(off, cont)
+    db.close()
+    assert np.array_equal(got, want)
+
+
+def test_long_reads_and_many_targets(oracle, tmp_path):
+    """10 kbp reads with 5 % errors (tile loop) and a read touching > 32 targets (dense path)."""
+    import synth
+    from jn_cuclark_b200 import CuClarkDB
+    tp, genomes, _ = synth.make_genomes(str(tmp_path / "g"), 48, 12000, seed=5, shared=False, quirks=False, same_label_pair=False)
+    odb = oracle.OracleDb.build(tp, 31, HT_SMALL)
+    rng = np.random.default_rng(9)
+    reads = []
+    for i in range(40):
+        g = genomes[i % 48]
+        s = g[500:10500].copy()
+        m = rng.random(s.size) < 0.05
+        s[m] = synth.BASES[rng.integers(0, 4, size=int(m.sum()))]
+        if i % 5 == 0:
+            s[rng.integers(0, s.size, size=7)] = ord("N")
+        reads.append((f"long{i}", s))
+    reads.append(("mosaic48", np.concatenate([g[100:180] for g in genomes])))     # 48 targets
+    reads.append(("mosaic33", np.concatenate([g[300:360] for g in genomes[:33]])))
+    synth.write_reads_fasta(str(tmp_path / "r.fa"), reads)
+    ir = oracle.IndexedReads(open(str(tmp_path / "r.fa"), "rb").read())
+    off, cont = ir.pack(31)
+    want, _, _ = odb.query_packed(31, off, cont)
+    db = CuClarkDB(1, 31, 1, len(odb.labels))
+    c, l = odb.pairs()
+    db.load_pairs(c, l)
+    got, _ = db.classify_packed(off, cont)
+    st = db.stats()
+    db.close()
+    assert np.array_equal(got, want)
+    assert st.dense_reads == 2
+
+
+def test_discriminative_rule_on_device(oracle):
+    """k-mers inserted under two labels become misses (HashTableStorage_hh.hh:244)."""
+    from jn_cuclark_b200 import CuClarkDB
+    rng = np.random.default_rng(3)
+    k = 31
+    x = rng.integers(0, 1 << 62, size=20000, dtype=np.uint64)
+    canon = np.array([oracle.canonical(int(v), k) for v in x], dtype=np.uint64)
+    labels = rng.integers(0, 7, size=canon.size).astype(np.uint16)
+    canon = np.concatenate([canon, canon[:5000], canon[5000:8000]])
+    labels = np.concatenate([labels, (labels[:5000] + 1) % 7, labels[5000:8000]]).astype(np.uint16)
+    odb = oracle.OracleDb.from_pairs(canon, labels, k, HT_SMALL)
+    assert odb.n == 15000
+    db = CuClarkDB(1, k, 1, 7)
+    db.load_pairs(canon, labels)
+    info = db.db_info()
+    assert info.tombstones >= 1 and info.entries == 20000
+    # one read per k-mer: [len=31][4 containers]
+    n = 20000
+    off = (np.arange(n + 1, dtype=np.uint32) * 5)
+    cont = np.zeros(n * 5, np.uint16)
+    cont[0::5] = 31
+    v = x[:n] << np.uint64(2)
+    for j in range(4):
+        cont[1 + j::5] = ((v >> np.uint64(48 - 16 * j)) & np.uint64(0xFFFF)).astype(np.uint16)
+    want, _, _ = odb.query_packed(k, off, cont)
+    got, _ = db.classify_packed(off, cont)
+    db.close()
+    assert np.array_equal(got, want)
+    assert (want[:5000, 0] == 0).all() and (want[5000:, 0] == 1).all()
