@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- reads/s and k-mer lookups/s of the cuCLARK classification hot path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+  python bench.py --impl reference [...]                         # reference CPU lookup (oracle/_ref)
+
+A step = one pass of the hot path over one batch of synthetic reads
+(include/ccb_synth.h).  Default workload (N=1) = BASELINE.json configs[1]:
+cuCLARK full mode, k=31, 1,000 x 4 Mbp genomes (~4e9 31-mers), 10 M x 150 bp reads.
+`value`  : whole-job k-mer lookups/s, batch resident in HBM, CUDA events on the launch stream.
+`e2e`    : the same through the C ABI with HOST (pinned) buffers: H2D + query + D2H per step.
+`roofline`: algorithmic bytes = 32 B (one table sector) per lookup vs the measured HBM peak.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+DB_SEED, READS_SEED = 0xC1A2C000 + 2000, 0x5EED0002
+HTSIZE_FULL = 1610612741
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--genomes", type=int, default=1000)
+    ap.add_argument("--genome-len", type=int, default=4_000_000)
+    ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU per step")
+    ap.add_argument("--read-len", type=int, default=150)
+    ap.add_argument("-k", type=int, default=31)
+    ap.add_argument("--load-factor", type=float, default=0.5)
+    ap.add_argument("--slots", type=int, default=4, help="pinned batch slots of the e2e pipeline")
+    ap.add_argument("--sample-genomes", type=int, default=4, help="cpu baseline: genomes in the sample DB")
+    ap.add_argument("--sample-reads", type=int, default=200_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gather", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        sm = sorted(float(r[1]) for r in self.rows if len(r) > 2 and r[1].replace(".", "").isdigit())
+        mx = max([float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()] or [0])
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_sample_oracle(args, threads):
+    """Oracle ('port') on a bounded sample: DB of the first sample-genomes genomes, reads drawn from them."""
+    import oracle_py
+    t0 = time.time()
+    odb = oracle_py.OracleDb.synth(DB_SEED, args.sample_genomes, args.genome_len, args.sample_genomes, args.k, HTSIZE_FULL)
+    t_build = time.time() - t0
+    return odb, t_build
+
+
+def run_reference(args):
+    """Reference arm: the reference's own CPU lookup (hTable::find through oracle/_ref/ref_harness),
+    all host threads, on a bounded sample of the same workload; rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import oracle_py
+    cores = os.cpu_count() or 1
+    import tempfile
+    d = tempfile.mkdtemp(prefix="ccb_ref_")
+    G, LG, NR, L, k = args.sample_genomes, args.genome_len, args.sample_reads, args.read_len, args.k
+    sample = f"DB = first {G} of {args.genomes} genomes x {LG} bp ({G * (LG - k + 1)} {k}-mers, HTSIZE {HTSIZE_FULL}); {NR} x {L} bp reads drawn from them per step"
+    harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+    odb = oracle_py.OracleDb.synth(DB_SEED, G, LG, G, k, HTSIZE_FULL)
+    reads = os.path.join(d, "reads.fa")
+    oracle_py.lib().ccbo_synth_reads_fasta(reads.encode(), READS_SEED, DB_SEED, 0, NR, L, G, LG)
+    times, lookups, kind = [], 0, "port"
+    if os.path.exists(harness) and k == 31:
+        kind = "reference"
+        tp = os.path.join(d, "targets.txt")
+        with open(tp, "w") as f:
+            for g in range(G):
+                f.write(f"{d}/g{g}.fa\tT{g}\n")
+        prefix = oracle_py.db_name(d + "/", k, G, HTSIZE_FULL)
+        odb.write(prefix)
+        del odb
+        r = subprocess.run([harness, "-k", str(k), "-T", tp, "-D", d, "-O", reads, "-n", str(cores),
+                            "--reps", str(args.steps + args.warmup)], capture_output=True, text=True)
+        for line in r.stdout.splitlines():
+            if line.startswith("REFTIME"):
+                kv = dict(x.split("=") for x in line.split()[1:])
+                times.append(float(kv["seconds"])); lookups = int(kv["lookups"])
+        if len(times) < args.steps + args.warmup:
+            print(json.dumps({"impl": "reference", "unavailable": "ref_harness failed: " + r.stderr[-200:].replace("\n", " ")}))
+            return
+    else:
+        ir = oracle_py.IndexedReads(open(reads, "rb").read())
+        off, cont = ir.pack(k)
+        for _ in range(args.steps + args.warmup):
+            t0 = time.time()
+            _, _, lookups = odb.query_packed(k, off, cont, threads=cores)
+            times.append(time.time() - t0)
+    import shutil
+    shutil.rmtree(d, ignore_errors=True)
+    t = sum(times[args.warmup:])
+    v = lookups * args.steps / t
+    print(json.dumps({
+        "impl": "reference", "metric": "kmer_lookups_per_s", "value": v, "unit": "lookups/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "reads_per_s": NR * args.steps / t,
+        "config": {"workload": f"cuCLARK full k={k}, synthetic {args.genomes} x {LG} bp DB, {L} bp SE reads", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "lookups/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from jn_cuclark_b200 import CuClarkDB, CCB_STATS
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cudart = C.CDLL("libcudart.so")
+    k, G, LG, NR, L = args.k, args.genomes, args.genome_len, args.reads, args.read_len
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def d2d(dst, src, nbytes):
+        cudart.cudaMemcpy(C.c_void_p(dst), C.c_void_p(src), C.c_size_t(nbytes), 3)
+
+    # ---- CPU baseline + bit-exact check on a bounded sample (rank 0, N=1 only) --------------
+    cpu_baseline, parity = None, None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        import oracle_py
+        cores = os.cpu_count() or 1
+        SG, SR = args.sample_genomes, args.sample_reads
+        t0 = time.time()
+        odb = oracle_py.OracleDb.synth(DB_SEED, SG, LG, SG, k, HTSIZE_FULL)
+        t_build = time.time() - t0
+        sdb = CuClarkDB(1, k, 1, SG, device=local, load_factor=args.load_factor)
+        sdb.synth_db(DB_SEED, SG, LG, SG)
+        so, sc, snc = sdb.synth_reads_packed(READS_SEED, DB_SEED, 0, SR, L, SG, LG)
+        off = torch.empty(SR + 1, dtype=torch.int32, device="cuda"); cont = torch.empty(snc, dtype=torch.int16, device="cuda")
+        d2d(off.data_ptr(), so, (SR + 1) * 4); d2d(cont.data_ptr(), sc, snc * 2)
+        out = torch.zeros(SR * 5, dtype=torch.int16, device="cuda")
+        sdb.query_device(so, sc, SR, out.data_ptr(), stream=stream)
+        torch.cuda.synchronize()
+        got = out.cpu().numpy().view(np.uint16).reshape(-1, 5)
+        off_h = off.cpu().numpy().view(np.uint32); cont_h = cont.cpu().numpy().view(np.uint16)
+        odb.query_packed(k, off_h[:2001], cont_h, threads=cores)               # warm-up (builds bucket pointers)
+        t0 = time.time()
+        want, _, nl = odb.query_packed(k, off_h, cont_h, threads=cores)
+        t_q = time.time() - t0
+        parity = "bit-exact" if np.array_equal(got, want) else "MISMATCH"
+        sample = (f"DB = first {SG} of {G} genomes x {LG} bp ({odb.n} {k}-mers, HTSIZE {HTSIZE_FULL}, built in {t_build:.1f} s on 1 core); "
+                  f"{SR} x {L} bp reads drawn from them; lookup+vote loop only")
+        cpu_baseline = {"value": nl / t_q, "unit": "lookups/s", "cores": cores, "kind": "port", "sample": sample,
+                        "reads_per_s": SR / t_q, "db_build_kmers_per_s": odb.n / t_build}
+        sdb.device_free(so); sdb.device_free(sc); sdb.close(); del odb, out, off, cont
+        torch.cuda.empty_cache()
+
+    # ---- the workload: replicated table per GPU, reads partitioned by rank -------------------
+    db = CuClarkDB(1, k, args.slots, min(G, 65534), device=local, load_factor=args.load_factor)
+    t0 = time.time()
+    n_kmers = db.synth_db(DB_SEED, G, LG, min(G, 65534))
+    t_db = time.time() - t0
+    info = db.db_info()
+    d_off, d_cont, n_cont = db.synth_reads_packed(READS_SEED, DB_SEED, rank * NR, NR, L, G, LG)
+    out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
+    stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+    db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS, stream)
+    torch.cuda.synchronize()
+    lookups, sectors = int(stats[0]), int(stats[1])
+    classified = int((out.view(-1, 5)[:, 1] != 0).sum())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    # ---- kernel-only: batch resident in HBM ----------------------------------------------------
+    for _ in range(args.warmup):
+        db.query_device(d_off, d_cont, NR, out.data_ptr(), stream=stream)
+    barrier()
+    sampler = ClockSampler(local); sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        db.query_device(d_off, d_cont, NR, out.data_ptr(), stream=stream)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    sampler.stop_flag = True; sampler.join()
+    clocks = sampler.summary()
+    total_lookups = lookups * world
+    if world > 1:
+        t = torch.tensor([lookups], dtype=torch.int64, device="cuda"); dist.all_reduce(t); total_lookups = int(t[0])
+    value = total_lookups * args.steps / (ms * 1e-3)
+
+    # ---- random 32-B gather probe over the same table (practical random-access roofline) -------
+    gather = None
+    if not args.no_gather and rank == 0:
+        npr = 1 << 30
+        res = {}
+        for nbytes in (32, 64):
+            db.bench_gather(npr, nbytes, stream); torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record(); db.bench_gather(npr, nbytes, stream); g1.record(); torch.cuda.synchronize()
+            res[nbytes] = npr * nbytes / (g0.elapsed_time(g1) * 1e-3) / 1e9
+        gather = res
+
+    # ---- end to end through the C ABI with host buffers ------------------------------------------
+    S = args.slots
+    per = (NR + S - 1) // S
+    off_all = torch.empty(NR + 1, dtype=torch.int32, device="cuda"); d2d(off_all.data_ptr(), d_off, (NR + 1) * 4)
+    cont_all = torch.empty(n_cont, dtype=torch.int16, device="cuda"); d2d(cont_all.data_ptr(), d_cont, n_cont * 2)
+    off_h = off_all.cpu().numpy().view(np.uint32); cont_h = cont_all.cpu().numpy().view(np.uint16)
+    del off_all, cont_all
+    bounds = [(s * per, min(NR, (s + 1) * per)) for s in range(S)]
+    max_c = max(int(off_h[b]) - int(off_h[a]) for a, b in bounds)
+    db.malloc(per, max_c, False)
+    sizes = []
+    for s, (a, b) in enumerate(bounds):
+        o, c, f, _ = db.buffers(s)
+        o[: b - a + 1] = off_h[a:b + 1] - off_h[a]
+        nc = int(off_h[b]) - int(off_h[a])
+        c[:nc] = cont_h[int(off_h[a]):int(off_h[b])]
+        sizes.append((b - a, nc))
+    h2d = sum((n + 1) * 4 + nc * 2 for n, nc in sizes); d2h = sum(n * 10 for n, _ in sizes)
+
+    def e2e_step():
+        for s, (n, nc) in enumerate(sizes):
+            db.readyBatch(s, n, nc); db.queryBatch(s)
+        for s in range(S):
+            db.waitForBatch(s)
+
+    for _ in range(args.warmup):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = total_lookups * args.steps / t_e2e
+    # results of the e2e path equal the resident path
+    fin = np.concatenate([db.buffers(s)[2][:n] for s, (n, _) in enumerate(sizes)])
+    same = bool(np.array_equal(fin, out.cpu().numpy().view(np.uint16).reshape(-1, 5)))
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        achieved = (lookups * 32 / (ms * 1e-3 / args.steps)) / 1e9          # this rank's kernel
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("k_query_dram_bytes_per_launch")
+            except Exception:
+                pass
+        line = {
+            "metric": "kmer_lookups_per_s", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "reads_per_s": NR * world * args.steps / (ms * 1e-3),
+            "config": {"workload": f"cuCLARK full k={k}, synthetic {G} x {LG} bp DB ({n_kmers} {k}-mers), {NR} x {L} bp SE reads per GPU",
+                       "parallelism": f"replicated table, reads partitioned x{world}",
+                       "l2": "inputs larger than L2 (table %.1f GB, random access)" % (info.bytes / 1e9),
+                       "table_gb": info.bytes / 1e9, "load_factor": args.load_factor, "db_build_s": t_db,
+                       "max_displacement": info.max_displacement, "lookups_per_step_per_gpu": lookups,
+                       "sectors_per_lookup": sectors / max(lookups, 1), "reads_classified_frac": classified / NR},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "lookups/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "reads_per_s": NR * world * args.steps / t_e2e, "ms_per_step": 1e3 * t_e2e / args.steps,
+                    "slots": S, "results_equal_resident_path": same},
+            "gpu_launches": 2 * args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "bytes_per_lookup": 32,
+                         "kernel": "ccb::k_query", "gather32_gbs": gather and gather[32], "gather64_gbs": gather and gather[64],
+                         "frac_of_gather32": (achieved / gather[32]) if gather else None},
+        }
+        if cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline
+            line["parity_sample"] = parity
+        print(json.dumps(line))
+    db.device_free(d_off); db.device_free(d_cont)
+    db.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -106,6 +106,23 @@ int  ccb_query_device(ccb_handle* h, const void* d_offsets, const void* d_contai
 
 int  ccb_get_stats(const ccb_handle* h, ccb_stats* out);
 
+/* ---- synthetic workload + roofline probe (bench.py and GPU tests; include/ccb_synth.h) ----
+ * ccb_synth_db: build the table from n_genomes counter-generated genomes (label = genome % n_labels).
+ * ccb_synth_reads_packed: reads [first_read, first_read+n_reads) in the packed batch layout, in
+ *   device memory allocated by the library (release with ccb_device_free).
+ * ccb_synth_reads_text: the same reads as text, read_len+1 bytes each ('\n' terminated), to host.
+ * ccb_bench_gather: n_probes independent random aligned loads of 32/64/128 B over the table. */
+int  ccb_synth_db(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len,
+                  uint32_t n_labels, uint64_t* n_kmers);
+int  ccb_synth_reads_packed(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed, uint64_t first_read,
+                            uint32_t n_reads, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len,
+                            void** d_offsets, void** d_containers, uint64_t* n_containers);
+int  ccb_synth_reads_text(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed, uint64_t first_read,
+                          uint32_t n_reads, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len,
+                          char* host_out);
+int  ccb_device_free(ccb_handle* h, void* d_ptr);
+int  ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream);
+
 /* library / build identification, e.g. "cuclark_b200 0.1 sm_100a" */
 const char* ccb_version(void);
 

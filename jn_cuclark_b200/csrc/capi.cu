@@ -1,7 +1,6 @@
 // capi.cu -- C ABI (include/cuclark_b200.h) over the table + query kernels.
 #include "../../include/cuclark_b200.h"
-#include "query.cuh"
-#include "table.cuh"
+#include "capi_internal.cuh"
 
 #include <stdarg.h>
 #include <stdio.h>
@@ -11,49 +10,9 @@
 
 using namespace ccb;
 
-namespace {
+namespace { thread_local std::string g_create_error; }
 
-struct Slot {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t  done = nullptr;
-    // pinned host
-    uint32_t* h_offsets = nullptr; uint16_t* h_cont = nullptr;
-    uint16_t* h_final5 = nullptr;  uint16_t* h_rows = nullptr;
-    // device
-    uint32_t* d_offsets = nullptr; uint16_t* d_cont = nullptr;
-    uint16_t* d_final5 = nullptr;  uint16_t* d_rows = nullptr;
-    uint32_t* d_ovf_list = nullptr; uint32_t* d_ovf_count = nullptr;
-    uint32_t* d_dense_scratch = nullptr;
-    unsigned long long* d_stats = nullptr;     // lookups, sectors
-    uint32_t* h_ovf_count = nullptr;           // pinned
-    unsigned long long* h_stats = nullptr;     // pinned
-    bool      in_flight = false;
-    uint32_t  n_reads = 0;
-    int       flags = 0;
-};
-
-constexpr uint32_t kDenseBlocks = 64;
-thread_local std::string g_create_error;
-
-}  // namespace
-
-struct ccb_handle {
-    ccb_config cfg{};
-    Table      table;
-    bool       db_ready = false, db_building = false;
-    cudaStream_t db_stream = nullptr;
-    std::vector<Slot> slots;
-    uint32_t   max_reads = 0; uint64_t max_cont = 0; bool batch_extended = false;
-    int        row_stride = 0;
-    ccb_stats  stats{};
-    uint64_t   tombstones = 0; uint32_t max_disp = 0;
-    std::string err;
-    // scratch for ccb_query_device
-    uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
-    uint32_t  q_ovf_cap = 0;
-};
-
-static int fail(ccb_handle* h, int code, const char* fmt, ...)
+int ccb_fail(ccb_handle* h, int code, const char* fmt, ...)
 {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
@@ -61,7 +20,7 @@ static int fail(ccb_handle* h, int code, const char* fmt, ...)
     return code ? code : -1;
 }
 #define CU(h, x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) \
-    return fail(h, (int)e_, "%s failed: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+    return ccb_fail(h, (int)e_, "%s failed: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 #define USE_DEV(h) CU(h, cudaSetDevice((h)->cfg.device))
 
 extern "C" const char* ccb_version(void) { return "cuclark_b200 0.1 sm_100a"; }
@@ -73,15 +32,15 @@ extern "C" const char* ccb_last_error(const ccb_handle* h)
 
 extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
 {
-    if (!cfg || !out) return fail(nullptr, -1, "ccb_create: null argument");
-    if (cfg->k < 2 || cfg->k > 32) return fail(nullptr, -2, "The k-mer length should be in [2,32].");
-    if (cfg->n_targets < 1 || cfg->n_targets > 65534) return fail(nullptr, -3, "n_targets must be in [1,65534]");
+    if (!cfg || !out) return ccb_fail(nullptr, -1, "ccb_create: null argument");
+    if (cfg->k < 2 || cfg->k > 32) return ccb_fail(nullptr, -2, "The k-mer length should be in [2,32].");
+    if (cfg->n_targets < 1 || cfg->n_targets > 65534) return ccb_fail(nullptr, -3, "n_targets must be in [1,65534]");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev <= 0)
-        return fail(nullptr, -4, "No CUDA devices found. Abort. (%s)", cudaGetErrorString(e));   // src/CuClarkDB.cu:128
+        return ccb_fail(nullptr, -4, "No CUDA devices found. Abort. (%s)", cudaGetErrorString(e));   // src/CuClarkDB.cu:128
     if (cfg->device < 0 || cfg->device >= ndev)
-        return fail(nullptr, -5, "%d CUDA devices requested. Insufficient devices found. Abort.", cfg->device + 1);
+        return ccb_fail(nullptr, -5, "%d CUDA devices requested. Insufficient devices found. Abort.", cfg->device + 1);
     ccb_handle* h = new ccb_handle();
     h->cfg = *cfg;
     if (h->cfg.n_slots < 1) h->cfg.n_slots = 1;
@@ -89,7 +48,7 @@ extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
     if (h->cfg.load_factor <= 0) h->cfg.load_factor = 0.5;
     h->row_stride = 2 * h->cfg.max_hits + 2;
     if (cudaSetDevice(cfg->device) != cudaSuccess || cudaStreamCreateWithFlags(&h->db_stream, cudaStreamNonBlocking) != cudaSuccess) {
-        fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));
+        ccb_fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));
         delete h; return -6;
     }
     *out = h;
@@ -135,8 +94,8 @@ extern "C" int ccb_db_begin(ccb_handle* h, uint64_t expected_entries)
     if (rc) {
         table_destroy(h->table);
         if (rc == (int)cudaErrorMemoryAllocation)
-            return fail(h, rc, "ERROR: Out of GPU memory for the k-mer table (%llu entries).", (unsigned long long)expected_entries);
-        return fail(h, rc, "table_create failed (%d)", rc);
+            return ccb_fail(h, rc, "ERROR: Out of GPU memory for the k-mer table (%llu entries).", (unsigned long long)expected_entries);
+        return ccb_fail(h, rc, "table_create failed (%d)", rc);
     }
     h->db_building = true;
     return 0;
@@ -144,16 +103,16 @@ extern "C" int ccb_db_begin(ccb_handle* h, uint64_t expected_entries)
 
 extern "C" int ccb_db_add_pairs_device(ccb_handle* h, const void* d_canon, const void* d_labels, uint64_t n)
 {
-    if (!h || !h->db_building) return fail(h, -1, "ccb_db_add_pairs_device: call ccb_db_begin first");
+    if (!h || !h->db_building) return ccb_fail(h, -1, "ccb_db_add_pairs_device: call ccb_db_begin first");
     USE_DEV(h);
     int rc = table_insert_device(h->table, (const uint64_t*)d_canon, (const uint16_t*)d_labels, n, h->db_stream);
-    if (rc) return fail(h, rc, "table insert failed (%d)", rc);
+    if (rc) return ccb_fail(h, rc, "table insert failed (%d)", rc);
     return 0;
 }
 
 extern "C" int ccb_db_add_pairs(ccb_handle* h, const uint64_t* canon, const uint16_t* labels, uint64_t n)
 {
-    if (!h || !h->db_building) return fail(h, -1, "ccb_db_add_pairs: call ccb_db_begin first");
+    if (!h || !h->db_building) return ccb_fail(h, -1, "ccb_db_add_pairs: call ccb_db_begin first");
     USE_DEV(h);
     const uint64_t chunk = 1ull << 24;
     uint64_t* dc = nullptr; uint16_t* dl = nullptr;
@@ -169,14 +128,14 @@ extern "C" int ccb_db_add_pairs(ccb_handle* h, const uint64_t* canon, const uint
         cudaStreamSynchronize(h->db_stream);
     }
     cudaFree(dc); cudaFree(dl);
-    if (rc) return fail(h, rc, "table insert failed (%d)", rc);
+    if (rc) return ccb_fail(h, rc, "table insert failed (%d)", rc);
     CU(h, cudaGetLastError());
     return 0;
 }
 
 extern "C" int ccb_db_end(ccb_handle* h)
 {
-    if (!h || !h->db_building) return fail(h, -1, "ccb_db_end: no table under construction");
+    if (!h || !h->db_building) return ccb_fail(h, -1, "ccb_db_end: no table under construction");
     USE_DEV(h);
     uint32_t st[2] = {0, 0}; unsigned long long cnt[3] = {0, 0, 0};
     cudaMemcpyAsync(st, h->table.d_status, sizeof st, cudaMemcpyDeviceToHost, h->db_stream);
@@ -184,8 +143,8 @@ extern "C" int ccb_db_end(ccb_handle* h)
     int rc = table_finalize(h->table, h->db_stream);
     h->db_building = false;
     h->max_disp = st[1]; h->tombstones = cnt[2];
-    if (rc == -13) { table_destroy(h->table); return fail(h, rc, "k-mer table too full: an entry moved more than %d buckets; lower load_factor", kMaxDisp); }
-    if (rc) { table_destroy(h->table); return fail(h, rc, "table finalize failed (%d): %s", rc, rc > 0 ? cudaGetErrorString((cudaError_t)rc) : ""); }
+    if (rc == -13) { table_destroy(h->table); return ccb_fail(h, rc, "k-mer table too full: an entry moved more than %d buckets; lower load_factor", kMaxDisp); }
+    if (rc) { table_destroy(h->table); return ccb_fail(h, rc, "table finalize failed (%d): %s", rc, rc > 0 ? cudaGetErrorString((cudaError_t)rc) : ""); }
     h->db_ready = true;
     return 0;
 }
@@ -206,17 +165,17 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
 {
     if (!h || !prefix) return -1;
     USE_DEV(h);
-    if (key_bytes != 2 && key_bytes != 4 && key_bytes != 8) return fail(h, -2, "key_bytes must be 2, 4 or 8");
+    if (key_bytes != 2 && key_bytes != 4 && key_bytes != 8) return ccb_fail(h, -2, "key_bytes must be 2, 4 or 8");
     std::string p = prefix;
     FILE* fs = fopen((p + ".sz").c_str(), "rb");
-    if (!fs) return fail(h, -20, "Failed to open %s.sz", prefix);          // src/CuClarkDB.cu:483-488
+    if (!fs) return ccb_fail(h, -20, "Failed to open %s.sz", prefix);          // src/CuClarkDB.cu:483-488
     FILE* fk = fopen((p + ".ky").c_str(), "rb");
-    if (!fk) { fclose(fs); return fail(h, -20, "Failed to open %s.ky", prefix); }
+    if (!fk) { fclose(fs); return ccb_fail(h, -20, "Failed to open %s.ky", prefix); }
     FILE* fl = fopen((p + ".lb").c_str(), "rb");
-    if (!fl) { fclose(fs); fclose(fk); return fail(h, -20, "Failed to open %s.lb", prefix); }
+    if (!fl) { fclose(fs); fclose(fk); return ccb_fail(h, -20, "Failed to open %s.lb", prefix); }
 
     std::vector<uint8_t> sz(htsize);
-    if (fread(sz.data(), 1, htsize, fs) != htsize) { fclose(fs); fclose(fk); fclose(fl); return fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
+    if (fread(sz.data(), 1, htsize, fs) != htsize) { fclose(fs); fclose(fk); fclose(fl); return ccb_fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
     fclose(fs);
     // choose buckets (src/CuClarkDB.cu:503-513): keep every sampling-th non-empty bucket
     const bool all = sampling <= 1;
@@ -262,8 +221,8 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
     fclose(fk); fclose(fl);
     cudaFree(d_sz); cudaFree(d_off); cudaFree(d_keys); cudaFree(d_lab);
     cudaFreeHost(h_off); cudaFreeHost(h_keys); cudaFreeHost(h_lab);
-    if (rc == -22) { table_destroy(h->table); h->db_building = false; return fail(h, rc, "%s.ky/.lb are shorter than the bucket sizes in .sz announce", prefix); }
-    if (rc) { table_destroy(h->table); h->db_building = false; return fail(h, rc, "table insert failed (%d)", rc); }
+    if (rc == -22) { table_destroy(h->table); h->db_building = false; return ccb_fail(h, rc, "%s.ky/.lb are shorter than the bucket sizes in .sz announce", prefix); }
+    if (rc) { table_destroy(h->table); h->db_building = false; return ccb_fail(h, rc, "table insert failed (%d)", rc); }
     rc = ccb_db_end(h);
     if (rc) return rc;
     if (n_loaded) *n_loaded = n_keep;
@@ -289,7 +248,7 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
     if (!h) return -1;
     USE_DEV(h);
     if (max_containers > 0xFFFFFFFFull)
-        return fail(h, -30, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>).");  // CuCLARK_hh.hh:1709-1713
+        return ccb_fail(h, -30, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>).");  // CuCLARK_hh.hh:1709-1713
     free_slots(h);
     h->max_reads = max_reads; h->max_cont = max_containers; h->batch_extended = extended != 0;
     h->slots.resize((size_t)h->cfg.n_slots);
@@ -310,8 +269,8 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
         if (e != cudaSuccess) {
             free_slots(h);
             if (e == cudaErrorMemoryAllocation)   // src/CuClarkDB.cu:65-73
-                return fail(h, (int)e, "ERROR: Out of GPU memory.\nPlease increase the number of batches (-b <numberofbatches>).");
-            return fail(h, (int)e, "batch allocation failed: %s", cudaGetErrorString(e));
+                return ccb_fail(h, (int)e, "ERROR: Out of GPU memory.\nPlease increase the number of batches (-b <numberofbatches>).");
+            return ccb_fail(h, (int)e, "batch allocation failed: %s", cudaGetErrorString(e));
         }
         *s.h_ovf_count = 0; s.h_stats[0] = s.h_stats[1] = 0;
     }
@@ -321,7 +280,7 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
 extern "C" int ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers,
                                  uint16_t** final5, uint16_t** rows)
 {
-    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     Slot& s = h->slots[(size_t)slot];
     if (offsets) *offsets = s.h_offsets;
     if (containers) *containers = s.h_cont;
@@ -352,10 +311,10 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
 
 extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint64_t n_containers, int flags)
 {
-    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
-    if (!h->db_ready) return fail(h, -32, "Failed to find the database.");
-    if (n_reads > h->max_reads || n_containers > h->max_cont) return fail(h, -33, "batch larger than allocated (%u reads, %llu containers)", n_reads, (unsigned long long)n_containers);
-    if ((flags & CCB_EXTENDED) && !h->batch_extended) return fail(h, -34, "extended results requested but ccb_batch_alloc(extended=0)");
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
+    if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    if (n_reads > h->max_reads || n_containers > h->max_cont) return ccb_fail(h, -33, "batch larger than allocated (%u reads, %llu containers)", n_reads, (unsigned long long)n_containers);
+    if ((flags & CCB_EXTENDED) && !h->batch_extended) return ccb_fail(h, -34, "extended results requested but ccb_batch_alloc(extended=0)");
     USE_DEV(h);
     Slot& s = h->slots[(size_t)slot];
     if (s.in_flight) { CU(h, cudaEventSynchronize(s.done)); s.in_flight = false; }
@@ -369,7 +328,7 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
     a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr;
     if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 16, s.stream));
     int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, s.d_dense_scratch, flags, s.stream);
-    if (rc) return fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     CU(h, cudaMemcpyAsync(s.h_final5, s.d_final5, (size_t)n_reads * 10, cudaMemcpyDeviceToHost, s.stream));
     if (flags & CCB_EXTENDED) CU(h, cudaMemcpyAsync(s.h_rows, s.d_rows, (size_t)n_reads * h->row_stride * 2, cudaMemcpyDeviceToHost, s.stream));
     CU(h, cudaMemcpyAsync(s.h_ovf_count, s.d_ovf_count, 4, cudaMemcpyDeviceToHost, s.stream));
@@ -389,7 +348,7 @@ static void harvest(ccb_handle* h, Slot& s)
 
 extern "C" int ccb_batch_wait(ccb_handle* h, int slot)
 {
-    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     Slot& s = h->slots[(size_t)slot];
     if (!s.in_flight) return 0;
     USE_DEV(h);
@@ -400,12 +359,12 @@ extern "C" int ccb_batch_wait(ccb_handle* h, int slot)
 
 extern "C" int ccb_batch_poll(ccb_handle* h, int slot)
 {
-    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(h, -31, "bad slot %d", slot);
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     Slot& s = h->slots[(size_t)slot];
     if (!s.in_flight) return 0;
     cudaError_t e = cudaEventQuery(s.done);
     if (e == cudaErrorNotReady) return 1;
-    if (e != cudaSuccess) return fail(h, (int)e, "cudaEventQuery: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) return ccb_fail(h, (int)e, "cudaEventQuery: %s", cudaGetErrorString(e));
     harvest(h, s);
     return 0;
 }
@@ -423,7 +382,7 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
                                 int flags, void* stream)
 {
     if (!h) return -1;
-    if (!h->db_ready) return fail(h, -32, "Failed to find the database.");
+    if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
     USE_DEV(h);
     if (h->q_ovf_cap < n_reads || !h->q_ovf_list) {
         cudaFree(h->q_ovf_list); h->q_ovf_list = nullptr;
@@ -437,7 +396,7 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
     a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr;
     int rc = run_query(h, a, h->q_ovf_list, h->q_ovf_count, h->q_dense, flags, (cudaStream_t)stream);
-    if (rc) return fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     return 0;
 }
 

@@ -1,0 +1,52 @@
+// capi_internal.cuh -- state behind the opaque ccb_handle (shared by capi.cu and synth.cu).
+#pragma once
+#include "../../include/cuclark_b200.h"
+#include "query.cuh"
+#include "table.cuh"
+#include <string>
+#include <vector>
+
+namespace ccb {
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  done = nullptr;
+    // pinned host
+    uint32_t* h_offsets = nullptr; uint16_t* h_cont = nullptr;
+    uint16_t* h_final5 = nullptr;  uint16_t* h_rows = nullptr;
+    // device
+    uint32_t* d_offsets = nullptr; uint16_t* d_cont = nullptr;
+    uint16_t* d_final5 = nullptr;  uint16_t* d_rows = nullptr;
+    uint32_t* d_ovf_list = nullptr; uint32_t* d_ovf_count = nullptr;
+    uint32_t* d_dense_scratch = nullptr;
+    unsigned long long* d_stats = nullptr;     // lookups, sectors
+    uint32_t* h_ovf_count = nullptr;           // pinned
+    unsigned long long* h_stats = nullptr;     // pinned
+    bool      in_flight = false;
+    uint32_t  n_reads = 0;
+    int       flags = 0;
+};
+
+constexpr uint32_t kDenseBlocks = 64;
+
+}  // namespace ccb
+
+struct ccb_handle {
+    ccb_config cfg{};
+    ccb::Table table;
+    bool       db_ready = false, db_building = false;
+    cudaStream_t db_stream = nullptr;
+    std::vector<ccb::Slot> slots;
+    uint32_t   max_reads = 0; uint64_t max_cont = 0; bool batch_extended = false;
+    int        row_stride = 0;
+    ccb_stats  stats{};
+    uint64_t   tombstones = 0; uint32_t max_disp = 0;
+    std::string err;
+    // scratch for ccb_query_device
+    uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
+    uint32_t  q_ovf_cap = 0;
+};
+
+
+// records the message on the handle (or thread-locally when h == NULL), returns code (never 0)
+int ccb_fail(ccb_handle* h, int code, const char* fmt, ...);

@@ -1,0 +1,226 @@
+// synth.cu -- synthetic benchmark workload generated on the device
+// (definition: include/ccb_synth.h).  Used by bench.py
+// and the GPU tests to build configs whose inputs would take hours to produce
+// through files (C2: 1,000 x 4 Mbp genomes = 4e9 31-mers).
+#include "../../include/cuclark_b200.h"
+#include "../../include/ccb_synth.h"
+#include "capi_internal.cuh"
+#include <cub/device/device_scan.cuh>
+
+using namespace ccb;
+
+namespace {
+
+constexpr int kSeg = 256;   // k-mer start positions per thread
+
+// Every k-mer of every genome -> table (label = genome index % n_labels).
+__global__ void k_synth_db(uint64_t* buckets, uint32_t* flags, uint32_t* status, unsigned long long* counts,
+                           HashParams hp, uint64_t seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels)
+{
+    const int k = hp.k;
+    const uint64_t per_genome = genome_len - k + 1;
+    const uint64_t segs_per_genome = (per_genome + kSeg - 1) / kSeg;
+    const uint64_t total = segs_per_genome * n_genomes;
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    for (uint64_t s = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; s < total; s += stride) {
+        const uint32_t g = (uint32_t)(s / segs_per_genome);
+        const uint64_t p0 = (s % segs_per_genome) * kSeg;
+        const uint64_t p1 = min(p0 + (uint64_t)kSeg, per_genome);
+        const uint64_t gs = ccb_genome_seed(seed, g);
+        uint64_t x = 0, rc = 0;
+        for (int j = 0; j < k - 1; j++) x = (x << 2) | ccb_genome_code(gs, p0 + j);
+        rc = revcomp(x, k);
+        for (uint64_t p = p0; p < p1; p++) {
+            uint64_t code = ccb_genome_code(gs, p + k - 1);
+            x = ((x << 2) | code) & hp.mask;
+            rc = (rc >> 2) | ((3ull - code) << (2 * (k - 1)));
+            insert_one(buckets, flags, status, counts, hp, x < rc ? x : rc, g % n_labels);
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t slots_of_part(uint32_t len) { return 1u + ((len + 7u) >> 3); }
+
+// parts of read i under the reference's packing rules (src/CuCLARK_hh.hh:1629-1707):
+// maximal ACGT runs, runs shorter than k dropped, reads shorter than k empty.
+__device__ __forceinline__ void read_parts(const ccb_read_plan& p, uint32_t L, int k, uint32_t (&beg)[2], uint32_t (&len)[2], int& n)
+{
+    n = 0;
+    if (L < (uint32_t)k) return;
+    if (p.kind == 2u) {
+        if (p.n_pos >= (uint32_t)k) { beg[n] = 0; len[n] = p.n_pos; n++; }
+        uint32_t r = L - 1 - p.n_pos;
+        if (r >= (uint32_t)k) { beg[n] = p.n_pos + 1; len[n] = r; n++; }
+    } else { beg[0] = 0; len[0] = L; n = 1; }
+}
+
+__global__ void k_synth_count(uint64_t rseed, uint64_t first, uint32_t n_reads, uint32_t L, int k,
+                              uint32_t n_genomes, uint64_t genome_len, uint32_t* slots)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    ccb_read_plan p = ccb_plan_read(rseed, first + i, n_genomes, genome_len, L);
+    uint32_t b[2], l[2]; int n;
+    read_parts(p, L, k, b, l, n);
+    uint32_t s = 0;
+    for (int j = 0; j < n; j++) s += slots_of_part(l[j]);
+    slots[i] = s;
+}
+
+__global__ void k_synth_fill(uint64_t rseed, uint64_t dseed, uint64_t first, uint32_t n_reads, uint32_t L, int k,
+                             uint32_t n_genomes, uint64_t genome_len, const uint32_t* offsets, uint16_t* cont)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    ccb_read_plan p = ccb_plan_read(rseed, first + i, n_genomes, genome_len, L);
+    uint32_t b[2], l[2]; int n;
+    read_parts(p, L, k, b, l, n);
+    uint16_t* o = cont + offsets[i];
+    for (int j = 0; j < n; j++) {
+        *o++ = (uint16_t)l[j];
+        uint32_t acc = 0, cnt = 0;
+        for (uint32_t q = 0; q < l[j]; q++) {
+            acc = (acc << 2) | ccb_read_code(&p, dseed, b[j] + q, L);
+            if (++cnt == 8) { *o++ = (uint16_t)acc; acc = 0; cnt = 0; }
+        }
+        if (cnt) *o++ = (uint16_t)(acc << (2 * (8 - cnt)));
+    }
+}
+
+// ASCII text of the same reads (one line per read, '\n' terminated) for file-level tests
+__global__ void k_synth_text(uint64_t rseed, uint64_t dseed, uint64_t first, uint32_t n_reads, uint32_t L,
+                             uint32_t n_genomes, uint64_t genome_len, char* out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    ccb_read_plan p = ccb_plan_read(rseed, first + i, n_genomes, genome_len, L);
+    char* o = out + (size_t)i * (L + 1);
+    for (uint32_t q = 0; q < L; q++) o[q] = ccb_code_char(ccb_read_code(&p, dseed, q, L));
+    o[L] = '\n';
+}
+
+}  // namespace
+
+extern "C" int ccb_synth_db(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len,
+                            uint32_t n_labels, uint64_t* n_kmers)
+{
+    if (!h || n_genomes == 0 || genome_len < (uint64_t)h->cfg.k || n_labels == 0) return ccb_fail(h, -40, "ccb_synth_db: bad arguments");
+    uint64_t total = (uint64_t)n_genomes * (genome_len - h->cfg.k + 1);
+    int rc = ccb_db_begin(h, total);
+    if (rc) return rc;
+    Table& t = h->table;
+    k_synth_db<<<148 * 16, 256, 0, h->db_stream>>>((uint64_t*)t.d_buckets, t.d_flags, t.d_status, t.d_counts, t.hp,
+                                                    db_seed, n_genomes, genome_len, n_labels);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_synth_db launch: %s", cudaGetErrorString(e));
+    rc = ccb_db_end(h);
+    if (rc) return rc;
+    if (n_kmers) *n_kmers = total;
+    return 0;
+}
+
+extern "C" int ccb_synth_reads_packed(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed, uint64_t first_read,
+                                      uint32_t n_reads, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len,
+                                      void** d_offsets, void** d_containers, uint64_t* n_containers)
+{
+    if (!h || !d_offsets || !d_containers || n_reads == 0 || genome_len < read_len) return ccb_fail(h, -41, "ccb_synth_reads_packed: bad arguments");
+    cudaSetDevice(h->cfg.device);
+    uint32_t *slots = nullptr, *off = nullptr; uint16_t* cont = nullptr; void* tmp = nullptr; size_t tmp_bytes = 0;
+    cudaStream_t s = h->db_stream;
+    cudaError_t e;
+    if ((e = cudaMalloc(&slots, ((size_t)n_reads + 1) * 4)) != cudaSuccess || (e = cudaMalloc(&off, ((size_t)n_reads + 1) * 4)) != cudaSuccess)
+        return ccb_fail(h, (int)e, "cudaMalloc: %s", cudaGetErrorString(e));
+    cudaMemsetAsync(slots + n_reads, 0, 4, s);
+    uint32_t g = (n_reads + 255) / 256;
+    k_synth_count<<<g, 256, 0, s>>>(reads_seed, first_read, n_reads, read_len, h->cfg.k, n_genomes, genome_len, slots);
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, slots, off, n_reads + 1, s);
+    cudaMalloc(&tmp, tmp_bytes);
+    cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, slots, off, n_reads + 1, s);
+    uint32_t total = 0;
+    cudaMemcpyAsync(&total, off + n_reads, 4, cudaMemcpyDeviceToHost, s);
+    cudaStreamSynchronize(s);
+    cudaFree(tmp); cudaFree(slots);
+    if ((e = cudaMalloc(&cont, ((size_t)total + 8) * 2)) != cudaSuccess) { cudaFree(off); return ccb_fail(h, (int)e, "cudaMalloc: %s", cudaGetErrorString(e)); }
+    k_synth_fill<<<g, 256, 0, s>>>(reads_seed, db_seed, first_read, n_reads, read_len, h->cfg.k, n_genomes, genome_len, off, cont);
+    e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { cudaFree(off); cudaFree(cont); return ccb_fail(h, (int)e, "synth reads: %s", cudaGetErrorString(e)); }
+    *d_offsets = off; *d_containers = cont;
+    if (n_containers) *n_containers = total;
+    return 0;
+}
+
+extern "C" int ccb_synth_reads_text(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed, uint64_t first_read,
+                                    uint32_t n_reads, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len,
+                                    char* host_out)
+{
+    if (!h || !host_out || n_reads == 0) return ccb_fail(h, -42, "ccb_synth_reads_text: bad arguments");
+    cudaSetDevice(h->cfg.device);
+    char* d = nullptr; size_t bytes = (size_t)n_reads * (read_len + 1);
+    cudaError_t e = cudaMalloc(&d, bytes);
+    if (e != cudaSuccess) return ccb_fail(h, (int)e, "cudaMalloc: %s", cudaGetErrorString(e));
+    k_synth_text<<<(n_reads + 255) / 256, 256, 0, h->db_stream>>>(reads_seed, db_seed, first_read, n_reads, read_len, n_genomes, genome_len, d);
+    e = cudaMemcpyAsync(host_out, d, bytes, cudaMemcpyDeviceToHost, h->db_stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->db_stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return ccb_fail(h, (int)e, "synth text: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+extern "C" int ccb_device_free(ccb_handle* h, void* d_ptr)
+{
+    if (h) cudaSetDevice(h->cfg.device);
+    cudaFree(d_ptr);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Random-access roofline probe: n_probes independent aligned loads of `bytes`
+// (32, 64 or 128) at hashed positions of the resident table, 8 in flight per
+// thread, nothing else.  The query kernel cannot beat this number.
+// ---------------------------------------------------------------------------
+namespace {
+template <int BYTES>
+__global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t n_units, uint64_t n_probes,
+                                                 uint64_t salt, unsigned long long* sink)
+{
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    unsigned long long acc = 0;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_probes; i += 8 * stride) {
+        uint64_t e[8][4];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            uint64_t idx = i + u * stride;
+            uint64_t h = ccb_sm64(idx ^ salt);
+            uint64_t unit = __umul64hi(h, n_units);                 // unit of BYTES bytes
+            const ulonglong4* p = tbl + unit * (BYTES / 32);
+            if (idx < n_probes) {
+                load_bucket(p, e[u]);
+                if (BYTES >= 64) { uint64_t f[4]; load_bucket(p + 1, f); e[u][0] ^= f[0]; }
+                if (BYTES >= 128) { uint64_t f[4]; load_bucket(p + 2, f); e[u][1] ^= f[1]; load_bucket(p + 3, f); e[u][2] ^= f[2]; }
+            } else { e[u][0] = e[u][1] = e[u][2] = e[u][3] = 0; }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) acc += e[u][0] ^ e[u][1] ^ e[u][2] ^ e[u][3];
+    }
+    if (acc == 0x123456789abcdefull) *sink = acc;                   // keep the loads alive
+}
+}  // namespace
+
+extern "C" int ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream)
+{
+    if (!h || !h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    cudaSetDevice(h->cfg.device);
+    static unsigned long long* sink = nullptr;
+    if (!sink) cudaMalloc(&sink, 8);
+    const ulonglong4* tbl = (const ulonglong4*)h->table.d_buckets;
+    uint64_t n32 = h->table.nb;
+    int grid = 148 * 8;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (bytes == 32)       k_gather<32><<<grid, 256, 0, s>>>(tbl, n32, n_probes, 0x5bd1e995u, sink);
+    else if (bytes == 64)  k_gather<64><<<grid, 256, 0, s>>>(tbl, n32 / 2, n_probes, 0x5bd1e995u, sink);
+    else if (bytes == 128) k_gather<128><<<grid, 256, 0, s>>>(tbl, n32 / 4, n_probes, 0x5bd1e995u, sink);
+    else return ccb_fail(h, -43, "ccb_bench_gather: bytes must be 32, 64 or 128");
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_gather launch: %s", cudaGetErrorString(e));
+    return 0;
+}

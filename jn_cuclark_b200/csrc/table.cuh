@@ -79,6 +79,60 @@ __device__ __forceinline__ uint32_t lookup(const TableView& t, uint64_t canon)
     return lab >= kLabelTomb ? kLabelNone : lab;
 }
 
+// ---- insertion (used by table.cu and by the synthetic-workload builder) -------
+__device__ __forceinline__ uint64_t ld_volatile(const uint64_t* p)
+{
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+
+// Insert (canonical, label).  Slots of a bucket fill front to back and never
+// change key afterwards, so every inserter of the same key meets either the
+// key itself or the same first empty slot: no duplicates under concurrency.
+static __device__ __noinline__ void insert_one(uint64_t* buckets, uint32_t* flags, uint32_t* status,
+                           unsigned long long* counts, const HashParams hp,
+                           uint64_t canon, uint32_t label)
+{
+    const uint64_t h = mix2k(canon, hp.k, hp.mask);
+    const uint64_t home = home_of(h, hp);
+    const uint64_t q = key48_of(h) << 16;
+    const uint64_t mine = q | label;
+    for (int d = 0; d <= kMaxDisp; d++) {
+        uint64_t* b = buckets + (home + d) * kSlots;
+#pragma unroll 1
+        for (int s = 0; s < kSlots; s++) {
+            uint64_t e = ld_volatile(b + s);
+            if (e == kEmpty) {
+                e = atomicCAS((unsigned long long*)(b + s), (unsigned long long)kEmpty, (unsigned long long)mine);
+                if (e == kEmpty) {
+                    if (d) atomicMax(status + 1, (uint32_t)d);
+                    atomicAdd(counts + 0, 1ull);
+                    return;
+                }
+            }
+            if ((e ^ q) < 0x10000ull) {                    // same k-mer already present
+                uint32_t have = (uint32_t)(e & 0xFFFF);
+                if (have == label || have == kLabelTomb) { atomicAdd(counts + 1, 1ull); return; }
+                // seen under two labels: not discriminative (reference
+                // HashTableStorage_hh.hh:244, Multiplicity != 1)
+                uint64_t tomb = q | kLabelTomb;
+                for (;;) {
+                    uint64_t old = atomicCAS((unsigned long long*)(b + s), (unsigned long long)e, (unsigned long long)tomb);
+                    if (old == e || (old & 0xFFFF) == kLabelTomb) break;
+                    e = old;
+                }
+                atomicAdd(counts + 2, 1ull);
+                return;
+            }
+        }
+        // bucket full and key absent: leave a breadcrumb for the finalize pass
+        uint64_t bi = home + d;
+        atomicOr(flags + (bi >> 4), (d == 0 ? 1u : 2u) << (2 * (bi & 15)));
+    }
+    atomicExch(status + 0, 1u);                            // displacement limit exceeded
+}
+
 // ---- host-side owner --------------------------------------------------------
 struct Table {
     Bucket*   d_buckets = nullptr;

@@ -70,6 +70,13 @@ SYMBOLS = {
     "ccb_query_device": (C.c_int, [_H, _VP, _VP, C.c_uint32, _VP, _VP, _VP, C.c_int, _VP]),
     "ccb_get_stats": (C.c_int, [_H, C.POINTER(Stats)]),
     "ccb_version": (C.c_char_p, []),
+    "ccb_synth_db": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
+    "ccb_synth_reads_packed": (C.c_int, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
+                                         C.c_uint64, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(C.c_uint64)]),
+    "ccb_synth_reads_text": (C.c_int, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
+                                       C.c_uint64, _VP]),
+    "ccb_device_free": (C.c_int, [_H, _VP]),
+    "ccb_bench_gather": (C.c_int, [_H, C.c_uint64, C.c_int, _VP]),
 }
 
 
@@ -217,6 +224,33 @@ class CuClarkDB:
         s = Stats()
         self._ck(self._lib.ccb_get_stats(self._h, C.byref(s)))
         return s
+
+    # -- synthetic workload (include/ccb_synth.h) ------------------------------
+    def synth_db(self, db_seed: int, n_genomes: int, genome_len: int, n_labels: int) -> int:
+        n = C.c_uint64(0)
+        self._ck(self._lib.ccb_synth_db(self._h, db_seed, n_genomes, genome_len, n_labels, C.byref(n)))
+        return n.value
+
+    def synth_reads_packed(self, reads_seed: int, db_seed: int, first: int, n_reads: int, read_len: int,
+                           n_genomes: int, genome_len: int):
+        """-> (d_offsets, d_containers, n_containers): raw device pointers owned by the caller (device_free)."""
+        o, c, n = _VP(), _VP(), C.c_uint64(0)
+        self._ck(self._lib.ccb_synth_reads_packed(self._h, reads_seed, db_seed, first, n_reads, read_len, n_genomes,
+                                                  genome_len, C.byref(o), C.byref(c), C.byref(n)))
+        return o.value, c.value, n.value
+
+    def synth_reads_text(self, reads_seed: int, db_seed: int, first: int, n_reads: int, read_len: int,
+                         n_genomes: int, genome_len: int) -> np.ndarray:
+        out = np.empty((n_reads, read_len + 1), dtype=np.uint8)
+        self._ck(self._lib.ccb_synth_reads_text(self._h, reads_seed, db_seed, first, n_reads, read_len, n_genomes,
+                                                genome_len, out.ctypes.data))
+        return out
+
+    def device_free(self, ptr: int):
+        self._lib.ccb_device_free(self._h, ptr)
+
+    def bench_gather(self, n_probes: int, nbytes: int = 32, stream: int = 0):
+        self._ck(self._lib.ccb_bench_gather(self._h, n_probes, nbytes, stream or None))
 
     # -- convenience used by tests/bench: one whole batch, synchronously ------
     def classify_packed(self, offsets: np.ndarray, containers: np.ndarray, extended: bool = False,

@@ -708,3 +708,45 @@ int ccbo_merge_paired(const char *f1, const char *f2, const char *outp)
     fclose(a); fclose(b); fclose(o); free(l1); free(l2);
     return rc;
 }
+
+/* ===================================================================== */
+/* synthetic benchmark workload (include/ccb_synth.h) on the CPU          */
+/* ===================================================================== */
+#include "../include/ccb_synth.h"
+
+/* Database of the first n_genomes synthetic genomes, built with the same rules
+ * as any FASTA target (ccbo_extract_fasta + ccbo_db_from_occ). */
+int ccbo_synth_db(uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels,
+                  int k, uint64_t htsize, ccbo_db *db)
+{
+    ccbo_occ_vec occ = {0};
+    unsigned char *txt = malloc(genome_len + 8);
+    if (!txt) return -1;
+    txt[0] = '>'; txt[1] = 'g'; txt[2] = '\n';
+    for (uint32_t g = 0; g < n_genomes; g++) {
+        uint64_t gs = ccb_genome_seed(db_seed, g);
+        for (uint64_t p = 0; p < genome_len; p++) txt[3 + p] = (unsigned char)ccb_code_char(ccb_genome_code(gs, p));
+        int rc = ccbo_extract_fasta(txt, 3 + genome_len, k, 0, 0, (uint16_t)(g % n_labels), &occ);
+        if (rc) { free(txt); free(occ.v); return rc; }
+    }
+    free(txt);
+    return ccbo_db_from_occ(&occ, k, htsize, 0, db);
+}
+
+/* FASTA text of synthetic reads [first, first+n): ">r<i>\n<seq>\n" */
+int ccbo_synth_reads_fasta(const char *path, uint64_t reads_seed, uint64_t db_seed, uint64_t first,
+                           uint32_t n, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len)
+{
+    FILE *f = fopen(path, "wb");
+    if (!f) return -1;
+    char *line = malloc(read_len + 2);
+    for (uint32_t i = 0; i < n; i++) {
+        ccb_read_plan p = ccb_plan_read(reads_seed, first + i, n_genomes, genome_len, read_len);
+        for (uint32_t j = 0; j < read_len; j++) line[j] = ccb_code_char(ccb_read_code(&p, db_seed, j, read_len));
+        line[read_len] = '\n';
+        fprintf(f, ">r%lu\n", (unsigned long)(first + i));
+        fwrite(line, 1, read_len + 1, f);
+    }
+    free(line); fclose(f);
+    return 0;
+}

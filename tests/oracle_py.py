@@ -71,6 +71,8 @@ def lib() -> C.CDLL:
         L.ccbo_merge_paired.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
         L.ccbo_extract_fasta.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_uint16, C.POINTER(OccVec)]
         L.ccbo_db_from_occ.argtypes = [C.POINTER(OccVec), C.c_int, C.c_uint64, C.c_uint, C.POINTER(Db)]
+        L.ccbo_synth_db.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_int, C.c_uint64, C.POINTER(Db)]
+        L.ccbo_synth_reads_fasta.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
         _lib = L
     return _lib
 
@@ -108,6 +110,13 @@ class OracleDb:
         C.memmove(p, occ.ctypes.data, occ.nbytes)
         v = OccVec(p, n, n)
         rc = lib().ccbo_db_from_occ(C.byref(v), k, htsize, min_t, C.byref(self.db))
+        assert rc == 0, rc
+        return self
+
+    @classmethod
+    def synth(cls, db_seed: int, n_genomes: int, genome_len: int, n_labels: int, k: int, htsize: int):
+        self = cls()
+        rc = lib().ccbo_synth_db(db_seed, n_genomes, genome_len, n_labels, k, htsize, C.byref(self.db))
         assert rc == 0, rc
         return self
 

@@ -55,7 +55,7 @@ def make_genomes(out_dir: str, n_genomes: int = 6, length: int = 20000, seed: in
     if quirks:
         genomes[0][300:310] = ord("N")              # N run
         genomes[1][40:45] |= 0x20                   # lower case acgt
-        genomes[min(3, n_genomes - 1)][9000] = ord("R")   # IUPAC code
+        genomes[min(3, n_genomes - 1)][min(9000, length - 1)] = ord("R")   # IUPAC code
     labels = []
     lines = []
     for i, g in enumerate(genomes):

@@ -166,3 +166,40 @@ def test_discriminative_rule_on_device(oracle):
     db.close()
     assert np.array_equal(got, want)
     assert (want[:5000, 0] == 0).all() and (want[5000:, 0] == 1).all()
+
+
+def test_synthetic_workload_matches_oracle(oracle):
+    """bench.py's device-generated DB + packed reads (include/ccb_synth.h) against the CPU oracle."""
+    import ctypes as C
+    import torch
+    from jn_cuclark_b200 import CuClarkDB, CCB_STATS
+    G, LG, NR, L, k = 5, 60000, 6000, 150, 31
+    db = CuClarkDB(1, k, 1, G)
+    n = db.synth_db(0xC1A2C000, G, LG, G)
+    odb = oracle.OracleDb.synth(0xC1A2C000, G, LG, G, k, HT_SMALL)
+    assert db.db_info().entries == odb.n and n == G * (LG - k + 1)
+    d_off, d_cont, nc = db.synth_reads_packed(0x5EED0001, 0xC1A2C000, 0, NR, L, G, LG)
+    off = torch.empty(NR + 1, dtype=torch.int32, device="cuda")
+    cont = torch.empty(nc, dtype=torch.int16, device="cuda")
+    C.cdll.LoadLibrary("libcudart.so").cudaMemcpy(C.c_void_p(off.data_ptr()), C.c_void_p(d_off), C.c_size_t((NR + 1) * 4), 3)
+    C.cdll.LoadLibrary("libcudart.so").cudaMemcpy(C.c_void_p(cont.data_ptr()), C.c_void_p(d_cont), C.c_size_t(nc * 2), 3)
+    off_h = off.cpu().numpy().view(np.uint32)
+    cont_h = cont.cpu().numpy().view(np.uint16)
+    # the packed batch equals packing the text of the same reads with the reference's rules
+    txt = db.synth_reads_text(0x5EED0001, 0xC1A2C000, 0, NR, L, G, LG)
+    fa = b"".join(b">r%d\n" % i + txt[i].tobytes() for i in range(NR))
+    ir = oracle.IndexedReads(fa)
+    off_o, cont_o = ir.pack(k)
+    assert np.array_equal(off_h, off_o) and np.array_equal(cont_h, cont_o)
+    want, _, nl = odb.query_packed(k, off_o, cont_o)
+    out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
+    stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+    db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy().view(np.uint16).reshape(-1, 5)
+    assert np.array_equal(got, want)
+    assert int(stats[0]) == nl
+    frac_hit = (want[:, 1] > 0).mean()
+    assert 0.85 < frac_hit < 0.95                      # 90 % of reads come from a genome
+    db.device_free(d_off); db.device_free(d_cont)
+    db.close()
