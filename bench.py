@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--sample-reads", type=int, default=200_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--kernel-only", action="store_true", help="profiling runs: resident-batch loop only (prints no bench line)")
     return ap.parse_args()
 
 
@@ -173,7 +174,7 @@ def run_b200(args):
 
     # ---- CPU baseline + bit-exact check on a bounded sample (rank 0, N=1 only) --------------
     cpu_baseline, parity = None, None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.kernel_only:
         import oracle_py
         cores = os.cpu_count() or 1
         SG, SR = args.sample_genomes, args.sample_reads
@@ -246,6 +247,14 @@ def run_b200(args):
     if world > 1:
         t = torch.tensor([lookups], dtype=torch.int64, device="cuda"); dist.all_reduce(t); total_lookups = int(t[0])
     value = total_lookups * args.steps / (ms * 1e-3)
+
+    if args.kernel_only:
+        if rank == 0:
+            print(json.dumps({"kernel_only": True, "ms_per_step": ms / args.steps, "lookups_per_s": value}))
+        db.device_free(d_off); db.device_free(d_cont); db.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- random 32-B gather probe over the same table (practical random-access roofline) -------
     gather = None

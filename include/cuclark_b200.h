@@ -122,6 +122,9 @@ int  ccb_synth_reads_text(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed, 
                           char* host_out);
 int  ccb_device_free(ccb_handle* h, void* d_ptr);
 int  ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream);
+/* mode 0 uniform / 1 one 2 MiB page per warp load / 2 lane pairs share a 64-B block / 3 lane quads
+ * share a 128-B line; footprint = bytes of the table the probes are drawn from (0 = whole table) */
+int  ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, int mode, uint64_t footprint, void* stream);
 
 /* library / build identification, e.g. "cuclark_b200 0.1 sm_100a" */
 const char* ccb_version(void);

@@ -174,25 +174,42 @@ extern "C" int ccb_device_free(ccb_handle* h, void* d_ptr)
 }
 
 // ---------------------------------------------------------------------------
-// Random-access roofline probe: n_probes independent aligned loads of `bytes`
-// (32, 64 or 128) at hashed positions of the resident table, 8 in flight per
-// thread, nothing else.  The query kernel cannot beat this number.
+// Random-access roofline probe: n_probes independent aligned 32-byte loads at
+// hashed positions of the resident table, 8 in flight per thread, nothing
+// else.  The query kernel cannot beat the mode-0 number at the same footprint.
+//   bytes   : 32 | 64 | 128 -- consecutive sectors fetched per probe by ONE thread
+//   mode 0  : uniform over the first `footprint` bytes of the table (0 = all)
+//   mode 1  : page-local -- the 32 lanes of a warp draw their sectors from one
+//             random 2 MiB page per load instruction (isolates translation cost)
+//   mode 2  : lane pairs read the two halves of a random 64-byte block
+//   mode 3  : lane quads read the four sectors of a random 128-byte line
 // ---------------------------------------------------------------------------
 namespace {
-template <int BYTES>
-__global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t n_units, uint64_t n_probes,
+template <int BYTES, int MODE>
+__global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t n_sectors, uint64_t n_probes,
                                                  uint64_t salt, unsigned long long* sink)
 {
     const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    const uint64_t n_units = n_sectors / (BYTES / 32);
     unsigned long long acc = 0;
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_probes; i += 8 * stride) {
         uint64_t e[8][4];
 #pragma unroll
         for (int u = 0; u < 8; u++) {
             uint64_t idx = i + u * stride;
-            uint64_t h = ccb_sm64(idx ^ salt);
-            uint64_t unit = __umul64hi(h, n_units);                 // unit of BYTES bytes
-            const ulonglong4* p = tbl + unit * (BYTES / 32);
+            uint64_t sector;
+            if (MODE == 0) {
+                sector = __umul64hi(ccb_sm64(idx ^ salt), n_units) * (BYTES / 32);
+            } else if (MODE == 1) {
+                const uint64_t pages = n_sectors >> 16;                         // 2 MiB = 65536 sectors
+                uint64_t pg = __umul64hi(ccb_sm64((idx >> 5) ^ salt), pages);   // same for the whole warp
+                sector = (pg << 16) | (ccb_sm64(idx ^ salt ^ 0x77ull) & 0xFFFFull);
+            } else if (MODE == 2) {
+                sector = __umul64hi(ccb_sm64((idx >> 1) ^ salt), n_sectors >> 1) * 2 + (idx & 1);
+            } else {
+                sector = __umul64hi(ccb_sm64((idx >> 2) ^ salt), n_sectors >> 2) * 4 + (idx & 3);
+            }
+            const ulonglong4* p = tbl + sector;
             if (idx < n_probes) {
                 load_bucket(p, e[u]);
                 if (BYTES >= 64) { uint64_t f[4]; load_bucket(p + 1, f); e[u][0] ^= f[0]; }
@@ -206,7 +223,7 @@ __global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t 
 }
 }  // namespace
 
-extern "C" int ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream)
+extern "C" int ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, int mode, uint64_t footprint, void* stream)
 {
     if (!h || !h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
     cudaSetDevice(h->cfg.device);
@@ -214,13 +231,24 @@ extern "C" int ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, voi
     if (!sink) cudaMalloc(&sink, 8);
     const ulonglong4* tbl = (const ulonglong4*)h->table.d_buckets;
     uint64_t n32 = h->table.nb;
-    int grid = 148 * 8;
+    if (footprint && footprint / 32 < n32) n32 = footprint / 32;
+    if (n32 < (1u << 16)) return ccb_fail(h, -43, "ccb_bench_gather: footprint below 2 MiB");
+    const int grid = 148 * 8;
+    const uint64_t salt = 0x5bd1e995u;
     cudaStream_t s = (cudaStream_t)stream;
-    if (bytes == 32)       k_gather<32><<<grid, 256, 0, s>>>(tbl, n32, n_probes, 0x5bd1e995u, sink);
-    else if (bytes == 64)  k_gather<64><<<grid, 256, 0, s>>>(tbl, n32 / 2, n_probes, 0x5bd1e995u, sink);
-    else if (bytes == 128) k_gather<128><<<grid, 256, 0, s>>>(tbl, n32 / 4, n_probes, 0x5bd1e995u, sink);
-    else return ccb_fail(h, -43, "ccb_bench_gather: bytes must be 32, 64 or 128");
+    if (mode == 0 && bytes == 32)       k_gather<32, 0><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 0 && bytes == 64)  k_gather<64, 0><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 0 && bytes == 128) k_gather<128, 0><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 1 && bytes == 32)  k_gather<32, 1><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 2 && bytes == 32)  k_gather<32, 2><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 3 && bytes == 32)  k_gather<32, 3><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else return ccb_fail(h, -43, "ccb_bench_gather: unsupported bytes/mode (%d/%d)", bytes, mode);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_gather launch: %s", cudaGetErrorString(e));
     return 0;
+}
+
+extern "C" int ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream)
+{
+    return ccb_bench_gather_ex(h, n_probes, bytes, 0, 0, stream);
 }

@@ -77,6 +77,7 @@ SYMBOLS = {
                                        C.c_uint64, _VP]),
     "ccb_device_free": (C.c_int, [_H, _VP]),
     "ccb_bench_gather": (C.c_int, [_H, C.c_uint64, C.c_int, _VP]),
+    "ccb_bench_gather_ex": (C.c_int, [_H, C.c_uint64, C.c_int, C.c_int, C.c_uint64, _VP]),
 }
 
 
@@ -249,8 +250,8 @@ class CuClarkDB:
     def device_free(self, ptr: int):
         self._lib.ccb_device_free(self._h, ptr)
 
-    def bench_gather(self, n_probes: int, nbytes: int = 32, stream: int = 0):
-        self._ck(self._lib.ccb_bench_gather(self._h, n_probes, nbytes, stream or None))
+    def bench_gather(self, n_probes: int, nbytes: int = 32, stream: int = 0, mode: int = 0, footprint: int = 0):
+        self._ck(self._lib.ccb_bench_gather_ex(self._h, n_probes, nbytes, mode, footprint, stream or None))
 
     # -- convenience used by tests/bench: one whole batch, synchronously ------
     def classify_packed(self, offsets: np.ndarray, containers: np.ndarray, extended: bool = False,
