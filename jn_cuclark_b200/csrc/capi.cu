@@ -4,6 +4,7 @@
 
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -51,9 +52,23 @@ extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
         ccb_fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));
         delete h; return -6;
     }
+    // A probe touches ONE 32-byte sector of a random line; by default the L2 fills the whole
+    // 128-byte line from HBM on a miss (ncu r01: 4.0 DRAM sectors per requested sector), which
+    // makes DRAM bytes, not lookups, the bound.  Ask for sector-granular fills.
+    {
+        size_t want = 32;
+        if (const char* e = getenv("CCB_L2_FETCH")) want = (size_t)atoi(e);
+        if (want) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, want);
+        size_t got = 0; cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+        h->l2_fetch = (int)got;
+        if (h->cfg.verbose) fprintf(stderr, "L2 fetch granularity: %zu B\n", got);
+        cudaGetLastError();
+    }
     *out = h;
     return 0;
 }
+
+extern "C" int ccb_l2_fetch_granularity(const ccb_handle* h) { return h ? h->l2_fetch : -1; }
 
 static void free_slots(ccb_handle* h)
 {

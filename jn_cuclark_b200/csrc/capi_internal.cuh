@@ -42,6 +42,7 @@ struct ccb_handle {
     ccb_stats  stats{};
     uint64_t   tombstones = 0; uint32_t max_disp = 0;
     std::string err;
+    int        l2_fetch = 0;          // cudaLimitMaxL2FetchGranularity in effect
     // scratch for ccb_query_device
     uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
     uint32_t  q_ovf_cap = 0;

@@ -183,6 +183,7 @@ extern "C" int ccb_device_free(ccb_handle* h, void* d_ptr)
 //             random 2 MiB page per load instruction (isolates translation cost)
 //   mode 2  : lane pairs read the two halves of a random 64-byte block
 //   mode 3  : lane quads read the four sectors of a random 128-byte line
+//   mode 4-7: mode 0 with other load flavours (plain / .cs / 2 x 16 B / L2 evict-first hint)
 // ---------------------------------------------------------------------------
 namespace {
 template <int BYTES, int MODE>
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t 
         for (int u = 0; u < 8; u++) {
             uint64_t idx = i + u * stride;
             uint64_t sector;
-            if (MODE == 0) {
+            if (MODE == 0 || MODE >= 4) {
                 sector = __umul64hi(ccb_sm64(idx ^ salt), n_units) * (BYTES / 32);
             } else if (MODE == 1) {
                 const uint64_t pages = n_sectors >> 16;                         // 2 MiB = 65536 sectors
@@ -210,7 +211,22 @@ __global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t 
                 sector = __umul64hi(ccb_sm64((idx >> 2) ^ salt), n_sectors >> 2) * 4 + (idx & 3);
             }
             const ulonglong4* p = tbl + sector;
-            if (idx < n_probes) {
+            if (idx < n_probes && MODE == 4) {          // plain ld.global (L1-allocating, coherent path)
+                asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];"
+                             : "=l"(e[u][0]), "=l"(e[u][1]), "=l"(e[u][2]), "=l"(e[u][3]) : "l"(p));
+            } else if (idx < n_probes && MODE == 5) {   // streaming (evict-first) load
+                asm volatile("ld.global.cs.v4.u64 {%0,%1,%2,%3}, [%4];"
+                             : "=l"(e[u][0]), "=l"(e[u][1]), "=l"(e[u][2]), "=l"(e[u][3]) : "l"(p));
+            } else if (idx < n_probes && MODE == 6) {   // two 16-byte loads of the sector
+                const ulonglong2* p2 = reinterpret_cast<const ulonglong2*>(p);
+                asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(e[u][0]), "=l"(e[u][1]) : "l"(p2));
+                asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(e[u][2]), "=l"(e[u][3]) : "l"(p2 + 1));
+            } else if (idx < n_probes && MODE == 7) {   // L2 evict-first policy, no L1 allocation
+                uint64_t pol;
+                asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+                asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u64 {%0,%1,%2,%3}, [%4], %5;"
+                             : "=l"(e[u][0]), "=l"(e[u][1]), "=l"(e[u][2]), "=l"(e[u][3]) : "l"(p), "l"(pol));
+            } else if (idx < n_probes) {
                 load_bucket(p, e[u]);
                 if (BYTES >= 64) { uint64_t f[4]; load_bucket(p + 1, f); e[u][0] ^= f[0]; }
                 if (BYTES >= 128) { uint64_t f[4]; load_bucket(p + 2, f); e[u][1] ^= f[1]; load_bucket(p + 3, f); e[u][2] ^= f[2]; }
@@ -242,6 +258,10 @@ extern "C" int ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, 
     else if (mode == 1 && bytes == 32)  k_gather<32, 1><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
     else if (mode == 2 && bytes == 32)  k_gather<32, 2><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
     else if (mode == 3 && bytes == 32)  k_gather<32, 3><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 4 && bytes == 32)  k_gather<32, 4><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 5 && bytes == 32)  k_gather<32, 5><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 6 && bytes == 32)  k_gather<32, 6><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 7 && bytes == 32)  k_gather<32, 7><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
     else return ccb_fail(h, -43, "ccb_bench_gather: unsupported bytes/mode (%d/%d)", bytes, mode);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_gather launch: %s", cudaGetErrorString(e));

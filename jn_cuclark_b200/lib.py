@@ -70,6 +70,7 @@ SYMBOLS = {
     "ccb_query_device": (C.c_int, [_H, _VP, _VP, C.c_uint32, _VP, _VP, _VP, C.c_int, _VP]),
     "ccb_get_stats": (C.c_int, [_H, C.POINTER(Stats)]),
     "ccb_version": (C.c_char_p, []),
+    "ccb_l2_fetch_granularity": (C.c_int, [_H]),
     "ccb_synth_db": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
     "ccb_synth_reads_packed": (C.c_int, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
                                          C.c_uint64, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(C.c_uint64)]),
@@ -220,6 +221,9 @@ class CuClarkDB:
                      d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
         self._ck(self._lib.ccb_query_device(self._h, d_offsets, d_containers, n_reads, d_final5,
                                             d_rows or None, d_stats or None, flags, stream or None))
+
+    def l2_fetch_granularity(self) -> int:
+        return self._lib.ccb_l2_fetch_granularity(self._h)
 
     def stats(self) -> Stats:
         s = Stats()

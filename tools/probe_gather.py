@@ -16,7 +16,7 @@ db.synth_db(0xC1A2C000 + 2000, G, 4_000_000, min(G, 65534))
 info = db.db_info()
 stream = torch.cuda.current_stream().cuda_stream
 NP = 1 << 30
-res = {"table_gb": info.bytes / 1e9, "n_probes": NP, "rows": []}
+res = {"l2_fetch": db.l2_fetch_granularity(), "table_gb": info.bytes / 1e9, "n_probes": NP, "rows": []}
 
 
 def run(nbytes, mode, fp):
@@ -32,7 +32,9 @@ def run(nbytes, mode, fp):
     print(row, flush=True)
 
 
-for fp in (32 << 20, 64 << 20, 128 << 20, 256 << 20, 512 << 20, 1 << 30, 4 << 30, 16 << 30, 0):
+QUICK = len(sys.argv) > 2
+print("l2 fetch granularity", res["l2_fetch"], flush=True)
+for fp in ((0,) if QUICK else (32 << 20, 64 << 20, 128 << 20, 256 << 20, 512 << 20, 1 << 30, 4 << 30, 16 << 30, 0)):
     if fp and fp > info.bytes:
         continue
     run(32, 0, fp)
@@ -40,5 +42,5 @@ for mode in (1, 2, 3):
     run(32, mode, 0)
 run(64, 0, 0)
 run(128, 0, 0)
-json.dump(res, open(os.path.join(ROOT, "gpurun_out", "gather_probe.json"), "w"), indent=1)
+json.dump(res, open(os.path.join(ROOT, "gpurun_out", "gather_probe_l2f%d.json" % res["l2_fetch"]), "w"), indent=1)
 db.close()
