@@ -126,6 +126,10 @@ int  ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream)
  * share a 128-B line; footprint = bytes of the table the probes are drawn from (0 = whole table) */
 int  ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, int mode, uint64_t footprint, void* stream);
 
+/* number of CUDA devices visible (0 when there is none or no driver); slots of a handle */
+int  ccb_device_count(void);
+int  ccb_batch_slots(const ccb_handle* h);
+
 /* cudaLimitMaxL2FetchGranularity in effect on the handle's device (ccb_create asks for 32 B so
  * that a probe costs one DRAM sector, not a 128-byte line; env CCB_L2_FETCH=0|32|64|128 overrides) */
 int  ccb_l2_fetch_granularity(const ccb_handle* h);

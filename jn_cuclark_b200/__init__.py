@@ -7,6 +7,7 @@ tests and ``bench.py``; it has NO CPU fallback: importing :mod:`.lib` raises if
 the CUDA library has not been built (``python -c 'import __graft_entry__ as g;
 g.build()'`` or ``make -C jn_cuclark_b200``).
 """
+from . import host  # noqa: F401
 from .lib import (  # noqa: F401
     CCB_EXTENDED, CCB_FORCE_DENSE, CCB_STATS, CcbError, CuClarkDB, lib_path, load_library,
 )

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -17,7 +18,7 @@ int ccb_fail(ccb_handle* h, int code, const char* fmt, ...)
 {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
-    if (h) h->err = buf; else g_create_error = buf;
+    if (h) { std::lock_guard<std::mutex> g(h->mu); h->err = buf; } else g_create_error = buf;
     return code ? code : -1;
 }
 #define CU(h, x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) \
@@ -67,6 +68,15 @@ extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
     *out = h;
     return 0;
 }
+
+extern "C" int ccb_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int ccb_batch_slots(const ccb_handle* h) { return h ? h->cfg.n_slots : 0; }
 
 extern "C" int ccb_l2_fetch_granularity(const ccb_handle* h) { return h ? h->l2_fetch : -1; }
 
@@ -273,7 +283,7 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
         cudaError_t e = cudaSuccess;
         auto ok = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
         ok(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-        ok(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        ok(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming | cudaEventBlockingSync));
         ok(cudaMallocHost(&s.h_offsets, so)); ok(cudaMallocHost(&s.h_cont, sc)); ok(cudaMallocHost(&s.h_final5, sf));
         ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 16));
         ok(cudaMalloc(&s.d_offsets, so)); ok(cudaMalloc(&s.d_cont, sc)); ok(cudaMalloc(&s.d_final5, sf));
@@ -355,6 +365,7 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
 
 static void harvest(ccb_handle* h, Slot& s)
 {
+    std::lock_guard<std::mutex> g(h->mu);          // slots may be waited on from several host threads
     h->stats.reads += s.n_reads;
     h->stats.dense_reads += (s.flags & CCB_FORCE_DENSE) ? s.n_reads : *s.h_ovf_count;
     if (s.flags & CCB_STATS) { h->stats.lookups += s.h_stats[0]; h->stats.sectors += s.h_stats[1]; }

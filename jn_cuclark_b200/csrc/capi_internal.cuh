@@ -3,6 +3,7 @@
 #include "../../include/cuclark_b200.h"
 #include "query.cuh"
 #include "table.cuh"
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -42,6 +43,7 @@ struct ccb_handle {
     ccb_stats  stats{};
     uint64_t   tombstones = 0; uint32_t max_disp = 0;
     std::string err;
+    std::mutex  mu;                  // guards err and stats
     int        l2_fetch = 0;          // cudaLimitMaxL2FetchGranularity in effect
     // scratch for ccb_query_device
     uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;

@@ -1,0 +1,385 @@
+// cli_main.cpp -- bin/cuCLARK and bin/cuCLARK-l (compiled with -DCCB_LIGHT).
+//
+// Drop-in for the reference classifier binaries at the process boundary
+// (SURVEY.md section 8, B1): the flag set, defaults, messages and exit codes of
+// reference src/main.cc:71-290, the file handling of CuCLARK::run / runSimple
+// (src/CuCLARK_hh.hh:384-574) and the result file <R>.csv.  scripts/
+// classify_metagenome.sh and `kent -c` call it unchanged.  `-m <n>` is accepted
+// and ignored (north-star text; the reference has no such flag).
+#include "../../include/cuclark_b200.h"
+#include "hostpipe.hpp"
+
+#include <fcntl.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <sys/time.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <iostream>
+#include <string>
+#include <thread>
+#include <vector>
+
+using std::cerr;
+using std::cout;
+using std::endl;
+using std::string;
+using std::vector;
+
+// src/parameters.hh:37-48 / src/parameters_light_hh:37-49
+#ifdef CCB_LIGHT
+static const uint64_t HTSIZE = 57777779ull;
+static const int MAXHITS = 23;
+static const bool kLight = true;
+#else
+static const uint64_t HTSIZE = 1610612741ull;
+static const int MAXHITS = 15;
+static const bool kLight = false;
+#endif
+static const int MAXK = 32;
+static const unsigned SFACTORMAX = 30;
+#define CCB_CLI_VERSION "1.1.3-b200"
+
+static void printUsage()
+{   // option list of src/main.cc:38-68
+    cout << "\n";
+    cout << (kLight ? "cuCLARK-l" : "cuCLARK") << " -- B200 build: classification of metagenomic reads on CUDA sm_100a\n\n";
+    cout << "./" << (kLight ? "cuCLARK-l" : "cuCLARK") << " -k <kmerSize> -T <fileTargets> -D <directoryDB/> -O <fileObjects> -R <fileResults> -n <numberofthreads> ...\n\n";
+    cout << "Definitions of parameters (cf. README file, for details):\n\n";
+    cout << "-k <kmerSize>,       \t k-mer length:\tinteger, >= 2 and <= 32 (in version 1.*).\n";
+    cout << "-t <minFreqTarget>,  \t minimum of k-mer frequency/occurence for the discriminative k-mers:  integer, >=0.\n";
+    cout << "-T <fileTargets>,    \t filename of the targets definition: text.\n";
+    cout << "-D <directoryDB/>,   \t directory of the database : text.\n";
+    cout << "-O <fileObjects>,    \t file containing objects: text.\n";
+    cout << "-P <file1> <file2>,  \t Paired-end fastq files: texts.\n";
+    cout << "-R <fileResults>,    \t file to store results:  text. Results are stored in CSV format in the file <fileResults>.csv (the extension \".csv\" is automatically added to the filename).\n";
+    cout << "-n <numberofthreads>,\t number of threads:\tinteger >= 1.\n";
+    cout << "-b <numberofbatches>,\t number of batches:\tinteger >= number of threads.\n";
+    cout << "-d <numberofdevices>,\t number of CUDA devices to use:\tinteger >= 1.\n";
+    cout << "--tsk,               \t to request a detailed creation of the database (target specific k-mers files).\n";
+    cout << "-g <iteration>,      \t gap or number of non-overlapping k-mers to pass for the database creation (for CuCLARK-l only). The default value is 4.\n";
+    cout << "-s <factor>,         \t sampling factor value (for CuCLARK only).\n";
+    cout << "--extended,          \t extended output (one column of hit counts per target).\n";
+    cout << "--verbose,           \t progress messages.\n";
+    cout << "\n";
+    cout << "--help,              \t to print help/options.\n";
+    cout << "--version,           \t to print the version info.\n";
+    cout << endl;
+}
+
+static bool validFile(const char* f)
+{   // src/file.cc:275-283
+    FILE* fd = fopen(f, "r");
+    if (!fd) return false;
+    fclose(fd);
+    return true;
+}
+
+static bool read_line(FILE* f, string& out)
+{   // getLineFromFile (src/file.cc:121-139): one trailing '\n' removed
+    char* line = NULL; size_t cap = 0;
+    ssize_t n = getline(&line, &cap, f);
+    if (n < 0) { free(line); out.clear(); return false; }
+    out.assign(line, (size_t)n);
+    free(line);
+    if (!out.empty() && out.back() == '\n') out.pop_back();
+    return true;
+}
+
+static void split(const string& s, const char* seps, size_t max_el, vector<string>& out)
+{
+    out.clear();
+    size_t i = 0;
+    while (i < s.size() && out.size() < max_el) {
+        while (i < s.size() && strchr(seps, s[i]) && s[i]) i++;
+        size_t j = i;
+        while (j < s.size() && !(strchr(seps, s[j]) && s[j])) j++;
+        if (j > i) out.push_back(s.substr(i, j - i));
+        i = j;
+    }
+}
+
+struct Targets {
+    vector<string> names;          // [0] = "NA", then labels in order of first appearance (src/CuCLARK_hh.hh:1874-1878)
+    size_t n_labels = 0;
+};
+
+// getTargetsData (src/CuCLARK_hh.hh:1790-1901): "<file> <label> [<label_c>]" per line
+static void read_targets(const char* path, Targets& t)
+{
+    FILE* f = fopen(path, "r");
+    if (!f) { cerr << "Failed to open targets data in file: " << path << endl; exit(-1); }
+    string line; vector<string> el;
+    while (read_line(f, line)) {            // every listed file must exist (:1800-1811)
+        split(line, " \t\n\r", 1, el);
+        if (el.empty()) continue;
+        if (!validFile(el[0].c_str())) { cerr << "Failed to open file: " << el[0] << " defined in " << path << endl; exit(-1); }
+    }
+    rewind(f);
+    vector<string> labels, labels_c;
+    while (read_line(f, line)) {
+        split(line, " ,\n\t\r", 3, el);
+        if (el.empty()) continue;
+        if (el.size() < 2) { cerr << " Missing label for " << el[0] << endl; exit(-1); }
+        if (std::find(labels.begin(), labels.end(), el[1]) == labels.end()) labels.push_back(el[1]);
+        if (el.size() > 2 && std::find(labels_c.begin(), labels_c.end(), el[2]) == labels_c.end()) labels_c.push_back(el[2]);
+    }
+    fclose(f);
+    t.names.clear();
+    t.names.push_back("NA");
+    for (auto& l : labels) t.names.push_back(l);
+    for (auto& l : labels_c) t.names.push_back(l);
+    t.n_labels = labels.size() + labels_c.size();
+}
+
+struct Cli {
+    size_t k = 31, cpu = 1, iterKmers = 0, batches = 1, devices = 0;
+    unsigned minT = 0, sfactor = 1;
+    bool tsk = false, ext = false, verbose = false;
+    const char *targets = NULL, *folder = NULL, *objects = NULL, *objects2 = NULL, *results = NULL;
+};
+
+struct Engine {
+    Cli cli;
+    Targets tg;
+    vector<ccb_handle*> devs;
+    int key_bytes = 4;
+    string dbname;
+
+    void open_devices()
+    {
+        int ndev = ccb_device_count();
+        if (ndev <= 0) { cerr << "No CUDA devices found. Abort.\n"; exit(1); }                       // src/CuClarkDB.cu:126-129
+        if ((size_t)ndev < cli.devices) { cerr << cli.devices << " CUDA devices requested. Insufficient devices found. Abort.\n"; exit(1); }
+        if (cli.devices > 0) { cerr << "Using " << cli.devices << " CUDA devices as requested.\n"; ndev = (int)cli.devices; }
+        const int workers = (int)std::max<size_t>(cli.cpu, (size_t)ndev);
+        for (int d = 0; d < ndev; d++) {
+            ccb_config c;
+            memset(&c, 0, sizeof c);
+            c.device = d; c.k = (int)cli.k; c.n_targets = (int)std::max<size_t>(tg.n_labels, 1); c.max_hits = MAXHITS;
+            c.n_slots = (workers + ndev - 1) / ndev + 1; c.load_factor = 0; c.verbose = cli.verbose;
+            ccb_handle* h = NULL;
+            if (ccb_create(&c, &h)) { cerr << ccb_last_error(NULL) << endl; exit(1); }
+            devs.push_back(h);
+        }
+    }
+
+    void load_db()
+    {   // getdbName (src/CuCLARK_hh.hh:581-592) + loadSpecificTargetSets (:599-632)
+        char name[4096];
+        if (kLight) snprintf(name, sizeof name, "%s/db_central_k%lu_t%lu_s%lu_m%lu_light_%lu.tsk", cli.folder, cli.k, tg.n_labels, (size_t)HTSIZE, (size_t)cli.minT, cli.iterKmers);
+        else        snprintf(name, sizeof name, "%s/db_central_k%lu_t%lu_s%lu_m%lu.tsk", cli.folder, cli.k, tg.n_labels, (size_t)HTSIZE, (size_t)cli.minT);
+        dbname = name;
+        for (const char* e : {".sz", ".ky", ".lb"})
+            if (!validFile((dbname + e).c_str())) {
+                cerr << "Failed to find the database." << endl;
+                cerr << "(" << dbname << e << " is missing; this build loads databases written by the reference's CPU builder and does not create them)" << endl;
+                exit(-1);
+            }
+        if (cli.verbose) cerr << "Loading database [" << dbname << ".*] (s=" << cli.sfactor << ")..." << endl;
+        vector<std::thread> th; vector<int> rc(devs.size(), 0);
+        for (size_t d = 0; d < devs.size(); d++)
+            th.emplace_back([&, d] { uint64_t n = 0; rc[d] = ccb_db_load_files(devs[d], dbname.c_str(), HTSIZE, key_bytes, cli.sfactor, &n); });
+        for (auto& t : th) t.join();
+        for (size_t d = 0; d < devs.size(); d++)
+            if (rc[d]) { cerr << ccb_last_error(devs[d]) << endl; exit(1); }
+    }
+
+    // runSimple (src/CuCLARK_hh.hh:513-574) on a text already in memory or mapped
+    void classify(const char* shown_name, const uint8_t* map, size_t nb, const char* result_prefix, bool paired)
+    {
+        string res = string(result_prefix) + ".csv";
+        ccbh::ClassifyOptions o;
+        o.k = (int)cli.k; o.threads = (int)cli.cpu; o.paired = paired; o.extended = cli.ext; o.verbose = cli.verbose;
+        o.row_stride = 2 * MAXHITS + 2; o.dump_final5 = getenv("CCB_DUMP_FINAL5");
+        ccbh::ClassifyStats st; string err;
+        struct timeval a, b;
+        gettimeofday(&a, NULL);
+        cerr << (cli.ext ? "Writing extended results... " : "Writing results... ") << endl;
+        int rc = ccbh::classify_text(devs, map, nb, res.c_str(), tg.names, o, st, err);
+        if (rc) { cerr << err << endl; exit(rc == 255 ? -1 : 1); }
+        cerr << "Done." << endl;
+        gettimeofday(&b, NULL);
+        double diff = (b.tv_sec - a.tv_sec) + (b.tv_usec - a.tv_usec) / 1000000.0;
+        char buf[256];                                                                   // printSpeedStats (:1931-1939)
+        snprintf(buf, sizeof buf, "Done in %.1fs (%zu reads/min, %zu reads)\n", diff, (size_t)(((double)st.reads) / diff * 60.0), (size_t)st.reads);
+        cerr << buf << "Results: " << res << "\n";
+        (void)shown_name;
+    }
+
+    void run_file(const char* file, const char* result_prefix)
+    {
+        cerr << "Classifying: " << file << "\n";
+        int fd = open(file, O_RDONLY);
+        struct stat sb;
+        if (fd == -1 || fstat(fd, &sb) != 0 || sb.st_size == 0) { cerr << "Failed to open " << file << endl; if (fd != -1) close(fd); return; }
+        void* map = mmap(0, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (map == MAP_FAILED) { close(fd); cerr << "Failed to mmapping the file." << endl; return; }
+        madvise(map, (size_t)sb.st_size, MADV_SEQUENTIAL);
+        classify(file, (const uint8_t*)map, (size_t)sb.st_size, result_prefix, false);
+        munmap(map, (size_t)sb.st_size);
+        close(fd);
+    }
+
+    void run_pair(const char* f1, const char* f2, const char* result_prefix)
+    {   // the reference writes <f1>_ConcatenatedByCLARK.fa, classifies it as FASTA and deletes it
+        // (src/CuCLARK_hh.hh:442-452); the same text is built in memory here.
+        vector<char> text; string err;
+        if (ccbh::join_pairs(f1, f2, text, err)) { cerr << err << endl; exit(1); }
+        cerr << "Classifying: " << f1 << "_ConcatenatedByCLARK.fa" << "\n";
+        if (text.empty()) { cerr << "Failed to open " << f1 << "_ConcatenatedByCLARK.fa" << endl; return; }
+        classify(f1, (const uint8_t*)text.data(), text.size(), result_prefix, true);
+    }
+
+    static bool is_reads_file(const char* path)
+    {   // src/CuCLARK_hh.hh:398-416: first line starts with '>' or '@', or has exactly two tokens
+        FILE* f = fopen(path, "r");
+        string line;
+        if (!f) return true;
+        read_line(f, line);
+        fclose(f);
+        vector<string> el;
+        split(line, " \t,", (size_t)-1, el);
+        return (!line.empty() && (line[0] == '>' || line[0] == '@')) || el.size() == 2;
+    }
+
+    void run()
+    {
+        const bool results_exists = validFile(cli.results);
+        if (!cli.objects2) {
+            if (!results_exists || is_reads_file(cli.objects)) { run_file(cli.objects, cli.results); return; }
+            FILE* rf = fopen(cli.results, "r"); FILE* of = fopen(cli.objects, "r");       // lists of files (:419-428)
+            string o, r;
+            while (read_line(of, o) && read_line(rf, r)) run_file(o.c_str(), r.c_str());
+            fclose(rf); fclose(of);
+            return;
+        }
+        if (!results_exists || is_reads_file(cli.objects)) { run_pair(cli.objects, cli.objects2, cli.results); return; }
+        FILE* rf = fopen(cli.results, "r"); FILE* f1 = fopen(cli.objects, "r"); FILE* f2 = fopen(cli.objects2, "r");
+        string a, b, r;
+        while (read_line(f1, a) && read_line(f2, b) && read_line(rf, r)) run_pair(a.c_str(), b.c_str(), r.c_str());
+        fclose(rf); fclose(f1); fclose(f2);
+    }
+};
+
+int main(int argc, char** argv)
+{
+    if (argc == 2) {
+        string val(argv[1]);
+        if (val == "--help" || val == "--HELP") { printUsage(); return 0; }
+        if (val == "--version" || val == "--VERSION") {
+            cout << "Version: " << CCB_CLI_VERSION << " (" << ccb_version() << "; command line of cuCLARK 1.1, R. Kobus / CLARK 1.1.3, R. Ounit)" << endl;
+            return 0;
+        }
+    }
+    if (argc < 6) {
+        cerr << "To run " << argv[0] << ", at least four  parameters are necessary:\n";
+        cerr << "filename of the targets definition, directory of database, filename for objects, filename for results." << endl;
+        printUsage();
+        return -1;
+    }
+    Cli c;
+    auto need = [&](int& i, const char* msg) { if (++i >= argc) { cerr << msg << endl; exit(1); } return argv[i]; };
+    for (int i = 1; i < argc; i++) {
+        string val(argv[i]);
+        if (val == "-k") {
+            c.k = (size_t)atoi(need(i, "Please specify the k-mer length!"));
+            if (c.k <= 1 || c.k > (size_t)MAXK) { cerr << "The k-mer length should be in [2," << MAXK << "]." << endl; exit(1); }
+            continue;
+        }
+        if (val == "-t") {
+            c.minT = (unsigned)atoi(need(i, "Please specify the minimum frequency (targets)!"));
+            if (c.minT >= 65536) { cerr << "The min k-mer frequency should be in [0,65535]." << endl; exit(1); }
+            continue;
+        }
+        if (val == "-n") {
+            c.cpu = (size_t)atoi(need(i, "Please specify the number of threads!"));
+            if (c.batches < c.cpu) c.batches = c.cpu;
+            if (c.cpu < 1) { cerr << "The number of threads should be higher than 0." << endl; exit(1); }
+            continue;
+        }
+        if (val == "--tsk") { c.tsk = true; continue; }
+        if (val == "--extended") { c.ext = true; continue; }
+        if (val == "-T") {
+            c.targets = need(i, "Please specify the targets!");
+            if (!validFile(c.targets)) { cerr << "Failed to find/read the file of the targets definition: " << c.targets << endl; exit(1); }
+            continue;
+        }
+        if (val == "-O") {
+            c.objects = need(i, "Please specify the objects!");
+            if (!validFile(c.objects)) { cerr << "Failed to find/read the filename of objects: " << c.objects << endl; exit(1); }
+            continue;
+        }
+        if (val == "-P") {
+            if (i + 2 >= argc) { cerr << "Please specify the paired-end reads!" << endl; exit(1); }
+            c.objects = argv[++i]; c.objects2 = argv[++i];
+            if (!validFile(c.objects)) { cerr << "Failed to find/read " << c.objects << endl; exit(1); }
+            if (!validFile(c.objects2)) { cerr << "Failed to find/read " << c.objects2 << endl; exit(1); }
+            continue;
+        }
+        if (val == "-D") {
+            c.folder = need(i, "Please specify the database directory!");
+            if (!validFile(c.folder)) { cerr << "Failed to find/read the directory:  " << c.folder << endl; exit(1); }
+            continue;
+        }
+        if (val == "-R") { c.results = need(i, "Please specify where to store results!"); continue; }
+        if (val == "-g") {
+            c.iterKmers = (size_t)atoi(need(i, "Please specify a gap value!"));
+            if (c.iterKmers < 4) { cerr << "The gap value should be >= 4." << endl; exit(1); }
+            continue;
+        }
+        if (val == "-s") {
+            c.sfactor = (unsigned)atoi(need(i, "Please specify a sampling factor value!"));
+            if (c.sfactor < 2 || c.sfactor > SFACTORMAX) { cerr << "The sampling factor value should be in the interval [2," << SFACTORMAX << "]." << endl; exit(1); }
+            continue;
+        }
+        if (val == "-b") {
+            c.batches = (size_t)atoi(need(i, "Please specify the number of batches!"));
+            if (c.batches < c.cpu) { cerr << "The number of batches should be higher than the number of threads." << endl; exit(1); }
+            continue;
+        }
+        if (val == "-d") {
+            c.devices = (size_t)atoi(need(i, "Please specify the number of devices to use!"));
+            if (c.devices < 1) { cerr << "The number of devices should be higher than 0." << endl; exit(1); }
+            continue;
+        }
+        if (val == "--verbose") { c.verbose = true; continue; }
+        if (val == "-m") { need(i, "Please specify the mode!"); continue; }      // tolerated, ignored
+        cerr << "Failed to recognize option: " << val << endl;
+        exit(1);
+    }
+    if (kLight) { if (c.iterKmers == 0) c.iterKmers = 4; c.k = 27; c.sfactor = 1; }     // src/main.cc:214-222
+    else c.iterKmers = 0;
+    if (!c.targets || !c.folder || !c.objects || !c.results) {
+        cerr << "Failed to run " << argv[0] << ": at least four  parameters are necessary";
+        cerr << ": file of targets, directory of database, file of objects, file for results." << endl;
+        printUsage();
+        exit(1);
+    }
+    string folder(c.folder);
+    if (folder[folder.size() - 1] != '/') folder.push_back('/');
+    c.folder = folder.c_str();
+
+    // key width by k (src/main.cc:251-286)
+    const size_t t_b = (size_t)(log((double)HTSIZE) / log(4.0));
+    Engine e;
+    e.cli = c;
+    e.key_bytes = c.k <= t_b + 8 ? 2 : (c.k <= t_b + 16 ? 4 : 8);
+    read_targets(c.targets, e.tg);
+    if (c.verbose) {                                                                       // CuCLARK::print (:1906-1926)
+        if (c.minT > 0) cerr << "Minimum k-mers occurences in Targets is set to " << c.minT << endl;
+        if (c.tsk) cerr << "Creation of targets specific k-mers files requested " << endl;
+        if (kLight) cerr << "Using light database in RAM (" << c.iterKmers << ")" << endl;
+        if (c.sfactor > 2) cerr << "Sampling factor is " << c.sfactor << endl;
+    }
+    e.open_devices();
+    e.load_db();
+    e.run();
+    for (ccb_handle* h : e.devs) ccb_destroy(h);
+    return 0;
+}

@@ -1,0 +1,532 @@
+// hostpipe.cpp -- see hostpipe.hpp
+#include "hostpipe.hpp"
+#include "../../include/cuclark_b200.h"
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <map>
+#include <mutex>
+#include <stdio.h>
+#include <string.h>
+#include <thread>
+#include <chrono>
+#include <memory>
+#include <stdlib.h>
+
+namespace ccbh {
+
+// ---------------------------------------------------------------------------
+// A1: indexing
+// ---------------------------------------------------------------------------
+namespace {
+
+inline bool is_sep(uint8_t c) { return c == ' ' || c == '\t' || c == '\n'; }   // src/CuCLARK_hh.hh:302
+
+struct Rec { uint64_t ns, ne, ss, se, len; };
+
+// The reference scans a name with a pre-increment (src/CuCLARK_hh.hh:1370, 1499): the first
+// byte after the marker is never tested, and one byte past the end may be read (it sees the
+// zero padding of the mapping, which is not a separator).
+inline size_t name_end(const uint8_t* m, size_t nb, size_t i)
+{
+    while (i < nb) {
+        ++i;
+        if (i < nb && is_sep(m[i])) break;
+    }
+    return i;
+}
+
+inline size_t past_newline(const uint8_t* m, size_t nb, size_t i)
+{   // while (i < nb && m[i++] != '\n') {}
+    if (i >= nb) return i;
+    const void* p = memchr(m + i, '\n', nb - i);
+    return p ? (size_t)((const uint8_t*)p - m) + 1 : nb;
+}
+
+inline size_t to_newline(const uint8_t* m, size_t nb, size_t i)
+{   // while (i < nb && m[i] != '\n') i++;
+    if (i >= nb) return i;
+    const void* p = memchr(m + i, '\n', nb - i);
+    return p ? (size_t)((const uint8_t*)p - m) : nb;
+}
+
+// FASTA record whose '>' is at p.  Returns the position of the next record's '>' (or >= nb).
+inline size_t fasta_record(const uint8_t* m, size_t nb, size_t p, Rec& r)
+{
+    size_t i = p + 1;
+    r.ns = i;
+    i = name_end(m, nb, i);
+    r.ne = i;
+    i = past_newline(m, nb, i);
+    r.ss = r.se = i;
+    uint64_t lines = 0;
+    while (i < nb && m[i] != '>') {            // a '>' only ends the record at the start of a line
+        i = to_newline(m, nb, i);
+        lines++;
+        r.se = i++;
+    }
+    r.len = (r.se - r.ss + 1) - lines;         // bytes minus newlines (:1388-1389); 1 for an empty record
+    return i;
+}
+
+// FASTQ record starting at p (four lines, no validation, :1496-1524).  Returns the next record's start.
+inline size_t fastq_record(const uint8_t* m, size_t nb, size_t p, Rec& r)
+{
+    size_t i = p + 1;
+    r.ns = i;
+    i = name_end(m, nb, i);
+    r.ne = i;
+    i = past_newline(m, nb, i);
+    r.ss = i;
+    i = to_newline(m, nb, i);
+    r.se = i++;
+    r.len = r.se - r.ss;
+    i = past_newline(m, nb, i);
+    i = past_newline(m, nb, i);
+    return i;
+}
+
+inline void push(ReadSet& o, const Rec& r)
+{
+    o.name_s.push_back(r.ns); o.name_e.push_back(r.ne);
+    o.seq_s.push_back(r.ss); o.seq_e.push_back(r.se); o.len.push_back(r.len);
+}
+
+void index_sequential(const uint8_t* m, size_t nb, bool fasta, ReadSet& o)
+{
+    Rec r;
+    size_t p = 0;
+    if (fasta) {
+        for (;;) {
+            p = fasta_record(m, nb, p, r);
+            push(o, r);
+            if (p >= nb) break;
+        }
+    } else {
+        for (;;) {
+            p = fastq_record(m, nb, p, r);
+            push(o, r);
+            if (p + 1 >= nb) break;                // (++i) >= nb, :1521
+        }
+    }
+}
+
+void append(ReadSet& o, const ReadSet& a)
+{
+    o.name_s.insert(o.name_s.end(), a.name_s.begin(), a.name_s.end());
+    o.name_e.insert(o.name_e.end(), a.name_e.begin(), a.name_e.end());
+    o.seq_s.insert(o.seq_s.end(), a.seq_s.begin(), a.seq_s.end());
+    o.seq_e.insert(o.seq_e.end(), a.seq_e.begin(), a.seq_e.end());
+    o.len.insert(o.len.end(), a.len.begin(), a.len.end());
+}
+
+}  // namespace
+
+int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
+{
+    out.clear();
+    out.map = m; out.nb = nb;
+    if (nb == 0 || (m[0] != '>' && m[0] != '@')) return -1;
+    out.fasta = m[0] == '>';
+    const bool fasta = out.fasta;
+    int T = threads < 1 ? 1 : threads;
+    if (nb < (size_t)(1 << 20)) T = 1;
+    if (T == 1) { index_sequential(m, nb, fasta, out); return 0; }
+
+    // Parallel over byte ranges.  Record starts are found locally ('>' at the start of a line;
+    // every fourth line for FASTQ), each record is then parsed by the same code as the
+    // sequential path.  The only input for which local detection and the sequential scan can
+    // disagree is a record whose marker is directly followed by a newline (the name scan then
+    // runs into the next line, see name_end): such files are re-indexed sequentially.
+    std::vector<size_t> cut((size_t)T + 1);
+    for (int t = 0; t <= T; t++) cut[(size_t)t] = nb / (size_t)T * (size_t)t;
+    cut[(size_t)T] = nb;
+    std::vector<uint64_t> newlines((size_t)T, 0);
+    std::vector<ReadSet> part((size_t)T);
+    std::atomic<bool> odd(false);
+    if (!fasta) {
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; t++) th.emplace_back([&, t] {
+            uint64_t c = 0;
+            const uint8_t* p = m + cut[(size_t)t]; const uint8_t* e = m + cut[(size_t)t + 1];
+            while (p < e) { const void* q = memchr(p, '\n', (size_t)(e - p)); if (!q) break; c++; p = (const uint8_t*)q + 1; }
+            newlines[(size_t)t] = c;
+        });
+        for (auto& x : th) x.join();
+    }
+    std::vector<uint64_t> line0((size_t)T, 0);      // index of the line that contains byte cut[t]
+    for (int t = 1; t < T; t++) line0[(size_t)t] = line0[(size_t)t - 1] + newlines[(size_t)t - 1];
+    {
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; t++) th.emplace_back([&, t] {
+            ReadSet& o = part[(size_t)t];
+            const size_t b = cut[(size_t)t], e = cut[(size_t)t + 1];
+            Rec r;
+            if (fasta) {
+                size_t p = b;
+                while (p < e) {                     // next '>' that starts a line, inside [b, e)
+                    const void* q = memchr(m + p, '>', e - p);
+                    if (!q) break;
+                    p = (size_t)((const uint8_t*)q - m);
+                    if (p == 0 || m[p - 1] == '\n') {
+                        if (p + 1 >= nb || m[p + 1] == '\n') { odd = true; return; }
+                        size_t nx = fasta_record(m, nb, p, r);
+                        push(o, r);
+                        p = nx;                     // may lie beyond e: the next thread owns it
+                    } else p++;
+                }
+            } else {
+                uint64_t line = line0[(size_t)t];
+                size_t p = b;
+                if (t == 0) {                       // line 0 starts at byte 0
+                    if (nb > 1 && m[1] == '\n') { odd = true; return; }
+                    fastq_record(m, nb, 0, r); push(o, r);
+                }
+                while (p < e) {
+                    const void* q = memchr(m + p, '\n', e - p);
+                    if (!q) break;
+                    p = (size_t)((const uint8_t*)q - m) + 1;     // start of line `line + 1`
+                    line++;
+                    if ((line & 3) == 0 && p + 1 < nb) {
+                        if (m[p + 1] == '\n') { odd = true; return; }
+                        fastq_record(m, nb, p, r); push(o, r);
+                    }
+                }
+            }
+        });
+        for (auto& x : th) x.join();
+    }
+    if (odd) { out.clear(); index_sequential(m, nb, fasta, out); return 0; }
+    size_t total = 0;
+    for (auto& p : part) total += p.n();
+    out.name_s.reserve(total); out.name_e.reserve(total); out.seq_s.reserve(total); out.seq_e.reserve(total); out.len.reserve(total);
+    for (auto& p : part) append(out, p);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// A2: 2-bit packing
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr uint32_t kMaxPart = 65528;     // multiple of 8 below 2^16: longer ACGT runs are split
+
+struct CodeTable {
+    uint8_t t[256];
+    CodeTable()
+    {   // 0..3: code (A=3 C=2 G=1 T/U=0, src/CuCLARK_hh.hh:294-297); 4: newline (skipped, :1673); 5: ends a part
+        for (int i = 0; i < 256; i++) t[i] = 5;
+        t[(int)'\n'] = 4;
+        t[(int)'A'] = t[(int)'a'] = 3; t[(int)'C'] = t[(int)'c'] = 2; t[(int)'G'] = t[(int)'g'] = 1;
+        t[(int)'T'] = t[(int)'t'] = t[(int)'U'] = t[(int)'u'] = 0;
+    }
+};
+const CodeTable kCodes;
+
+struct PartWriter {
+    uint16_t* c; size_t cc, cap; int k;
+    size_t hdr = 0; uint32_t plen = 0; uint32_t acc = 0, cnt = 0; bool open = false; uint64_t hist = 0;
+    bool overflow = false;
+
+    inline void put(uint32_t code)
+    {
+        acc = (acc << 2) | code; hist = (hist << 2) | code; plen++;
+        if (++cnt == 8) { if (cc < cap) c[cc++] = (uint16_t)acc; else overflow = true; acc = 0; cnt = 0; }
+    }
+    inline void begin() { hdr = cc; if (cc < cap) cc++; else overflow = true; plen = 0; acc = 0; cnt = 0; open = true; }
+    inline void end()
+    {   // keep the part iff it holds at least one k-mer (:1646-1650, :1700-1703)
+        if (!open) return;
+        if (cnt) { if (cc < cap) c[cc++] = (uint16_t)(acc << (2 * (8 - cnt))); else overflow = true; }
+        if (plen < (uint32_t)k) cc = hdr; else if (hdr < cap) c[hdr] = (uint16_t)plen;
+        open = false; acc = 0; cnt = 0;
+    }
+    inline void base(uint32_t code)
+    {
+        if (!open) begin();
+        else if (plen == kMaxPart) {               // split: next part restarts k-1 bases back
+            const uint64_t h = hist;
+            end(); begin();
+            for (int j = k - 2; j >= 0; j--) put((uint32_t)(h >> (2 * j)) & 3u);
+        }
+        put(code);
+    }
+};
+
+}  // namespace
+
+size_t pack_bound(const ReadSet& r, size_t first, size_t count, int k)
+{
+    size_t tot = 0;
+    for (size_t i = first; i < first + count; i++) {
+        if (r.len[i] < (uint64_t)k) continue;
+        size_t b = (size_t)(r.seq_e[i] - r.seq_s[i]);
+        tot += b / 8 + b / (size_t)k + 4 + (b / kMaxPart) * 8;
+    }
+    return tot + 8;
+}
+
+int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
+                   uint32_t* offsets, uint16_t* cont, size_t cap)
+{
+    PartWriter w{cont, 0, cap, k};
+    const uint8_t* m = r.map;
+    for (size_t j = 0; j < count; j++) {
+        const size_t i = first + j;
+        offsets[j] = (uint32_t)w.cc;
+        if (r.len[i] < (uint64_t)k) continue;       // :1632, reads without a k-mer store nothing
+        const uint8_t* p = m + r.seq_s[i]; const uint8_t* e = m + r.seq_e[i];
+        for (; p < e; p++) {
+            const uint32_t code = kCodes.t[*p];
+            if (code < 4) w.base(code);
+            else if (code == 5) w.end();
+        }
+        w.end();
+        if (w.overflow) return -1;
+        if (w.cc > 0xFFFFFFFFull) return -2;        // :1709
+    }
+    offsets[count] = (uint32_t)w.cc;
+    return (int64_t)w.cc;
+}
+
+// ---------------------------------------------------------------------------
+// A10: paired-end join (src/file.cc:205-268), in memory
+// ---------------------------------------------------------------------------
+namespace {
+
+struct LineReader {
+    FILE* f; char* buf = nullptr; size_t cap = 0; ssize_t n = 0;
+    explicit LineReader(FILE* f_) : f(f_) {}
+    ~LineReader() { free(buf); if (f) fclose(f); }
+    bool next()
+    {   // getLineFromFile: strips one trailing '\n' only
+        n = getline(&buf, &cap, f);
+        if (n < 0) { n = 0; return false; }
+        if (n > 0 && buf[n - 1] == '\n') buf[--n] = 0;
+        return true;
+    }
+};
+
+// first token of a header line split at ' ', '/', '\t' and the '@' marker itself
+inline void pair_id(const char* s, size_t n, const char*& b, size_t& len)
+{
+    size_t i = 0;
+    auto sep = [](char c) { return c == ' ' || c == '/' || c == '\t' || c == '@'; };
+    while (i < n && sep(s[i])) i++;
+    b = s + i;
+    size_t j = i;
+    while (j < n && !sep(s[j])) j++;
+    len = j - i;
+}
+
+}  // namespace
+
+int join_pairs(const char* file1, const char* file2, std::vector<char>& out, std::string& err)
+{
+    LineReader a(fopen(file1, "r")), b(fopen(file2, "r"));
+    if (!a.f || !b.f) { err = std::string("Failed to find/read ") + (!a.f ? file1 : file2); return 1; }
+    if (!a.next() || !b.next() || a.buf[0] != b.buf[0]) { err = "Error: the files have different format!"; return 1; }
+    if (a.buf[0] != '@') { err = "Error: paired-end reads must be FASTQ files!"; return 1; }
+    rewind(a.f); rewind(b.f);
+    out.clear();
+    while (a.next() && b.next()) {
+        if (!(a.n && b.n && a.buf[0] == '@' && b.buf[0] == '@')) continue;
+        const char *ia, *ib; size_t la, lb;
+        pair_id(a.buf, (size_t)a.n, ia, la); pair_id(b.buf, (size_t)b.n, ib, lb);
+        if (la != lb || memcmp(ia, ib, la) != 0) { err = "Error: read id does not match between files!"; return 1; }
+        out.push_back('>'); out.insert(out.end(), ia, ia + la); out.push_back('\n');
+        if (!(a.next() && b.next())) { err = "Error: Found read without sequence"; return 1; }
+        out.insert(out.end(), a.buf, a.buf + a.n); out.push_back('N');
+        out.insert(out.end(), b.buf, b.buf + b.n); out.push_back('\n');
+        if (a.next() && b.next()) { if (a.next() && b.next()) continue; }     // '+' and quality lines
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// A7: CSV
+// ---------------------------------------------------------------------------
+void csv_header(std::string& out, bool extended, const std::vector<std::string>& names)
+{
+    out += "Object_ID";
+    if (extended) for (size_t t = 1; t < names.size(); t++) { out += ','; out += names[t]; }
+    out += ",Gamma,Assignment,Score,Confidence\n";
+}
+
+void csv_rows(std::string& out, const ReadSet& r, size_t first, size_t count, int k, bool paired, bool extended,
+              const std::vector<std::string>& names, const uint16_t* final5, const uint16_t* rows, int row_stride)
+{
+    char num[96];
+    const size_t n_targets = names.size() - 1;
+    for (size_t j = 0; j < count; j++) {
+        const size_t i = first + j;
+        const uint16_t* f = final5 + 5 * j;
+        const unsigned total = f[0], ib = f[1], best = f[2], second = f[4];
+        // name: at most OBJECTNAMEMAX-1 = 39 bytes, ended early by a NUL (strncpy, :2102-2105)
+        size_t nl = (size_t)(r.name_e[i] - r.name_s[i]);
+        if (nl >= 40) nl = 39;
+        const char* nm = (const char*)r.map + r.name_s[i];
+        const void* z = memchr(nm, 0, nl);
+        if (z) nl = (size_t)((const char*)z - nm);
+        out.append(nm, nl);
+        if (extended) {
+            const uint16_t* row = rows + (size_t)row_stride * j;
+            unsigned w = 0;
+            for (unsigned h = 0; h < row[0]; h++) {
+                const unsigned ti = row[1 + 2 * h], sc = row[2 + 2 * h];
+                for (; w < ti; w++) out += ",0";
+                int m = snprintf(num, sizeof num, ",%d", (int)sc);
+                out.append(num, (size_t)m); w++;
+            }
+            for (; w < n_targets; w++) out += ",0";
+        }
+        const uint32_t norm = paired ? (uint32_t)r.len[i] - 1u : (uint32_t)r.len[i];     // ITYPE is u32; NBN = 1 (:2107)
+        const double gamma = (double)total / (((double)norm - (double)k) + 1.0);         // :2110
+        double delta = (double)(best + second);
+        delta = (delta < 0.001) ? 0 : ((double)best) / delta;                              // :2111-2112
+        int m = snprintf(num, sizeof num, ",%g,", gamma);
+        out.append(num, (size_t)m);
+        out += names[ib < names.size() ? ib : 0];
+        m = snprintf(num, sizeof num, ",%u,%g\n", best, delta);
+        out.append(num, (size_t)m);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// pipeline: workers pack -> submit -> wait -> format; text is appended in batch order
+// ---------------------------------------------------------------------------
+namespace {
+
+struct DevSlots {
+    ccb_handle* h;
+    std::mutex mu; std::condition_variable cv;
+    std::vector<int> free_slots;
+    std::mutex submit_mu;                          // queryBatch is serialised per device (omp critical(cudaQuery))
+};
+
+struct OrderedSink {
+    FILE* f = nullptr; FILE* dump = nullptr;
+    std::mutex mu;
+    size_t next = 0;
+    std::map<size_t, std::pair<std::string, std::vector<uint16_t>>> ready;
+    bool io_error = false;
+    void put(size_t b, std::string&& text, std::vector<uint16_t>&& raw)
+    {
+        std::lock_guard<std::mutex> g(mu);
+        ready.emplace(b, std::make_pair(std::move(text), std::move(raw)));
+        for (auto it = ready.find(next); it != ready.end(); it = ready.find(next)) {
+            const std::string& s = it->second.first;
+            if (!s.empty() && fwrite(s.data(), 1, s.size(), f) != s.size()) io_error = true;
+            if (dump && !it->second.second.empty()) fwrite(it->second.second.data(), 2, it->second.second.size(), dump);
+            ready.erase(it);
+            next++;
+        }
+    }
+};
+
+}  // namespace
+
+int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size_t nb, const char* result_csv,
+                  const std::vector<std::string>& names, const ClassifyOptions& opt, ClassifyStats& stats, std::string& err)
+{
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    ReadSet rs;
+    if (index_reads(map, nb, opt.threads, rs) != 0) { err = "Failed to recognize the format of the file."; return 255; }
+    stats.seconds_index = now() - t0;
+    const size_t n = rs.n();
+    stats.reads = n;
+
+    // batches: bounded by sequence bytes and read count so that pinned slots stay modest and
+    // there are enough of them in flight to hide packing behind the GPU and vice versa
+    const size_t kMaxBatchReads = 1u << 20, kMaxBatchBytes = 64u << 20;
+    std::vector<size_t> bstart{0};
+    {
+        size_t bytes = 0, cnt = 0;
+        for (size_t i = 0; i < n; i++) {
+            size_t b = (size_t)(rs.seq_e[i] - rs.seq_s[i]);
+            if (cnt && (cnt >= kMaxBatchReads || bytes + b > kMaxBatchBytes)) { bstart.push_back(i); bytes = 0; cnt = 0; }
+            bytes += b; cnt++;
+        }
+        bstart.push_back(n);
+    }
+    const size_t nbatches = bstart.size() - 1;
+    stats.batches = nbatches;
+    size_t max_reads = 1, max_cont = 1;
+    for (size_t b = 0; b < nbatches; b++) {
+        max_reads = std::max(max_reads, bstart[b + 1] - bstart[b]);
+        max_cont = std::max(max_cont, pack_bound(rs, bstart[b], bstart[b + 1] - bstart[b], opt.k));
+    }
+
+    const int workers = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(opt.threads, 1), nbatches));
+    std::vector<std::unique_ptr<DevSlots>> ds;
+    for (ccb_handle* h : devs) {
+        if (int rc = ccb_batch_alloc(h, (uint32_t)max_reads, max_cont, opt.extended)) { err = ccb_last_error(h); return rc; }
+        ds.emplace_back(new DevSlots());
+        ds.back()->h = h;
+        for (int s = 0; s < ccb_batch_slots(h); s++) ds.back()->free_slots.push_back(s);
+    }
+
+    OrderedSink sink;
+    sink.f = fopen(result_csv, "w");
+    if (!sink.f) { err = std::string("Failed to create/open file result: ") + result_csv; return 1; }
+    if (opt.dump_final5) sink.dump = fopen(opt.dump_final5, "wb");
+    {
+        std::string hdr; csv_header(hdr, opt.extended, names);
+        fwrite(hdr.data(), 1, hdr.size(), sink.f);
+    }
+
+    std::atomic<size_t> next_batch(0);
+    std::atomic<int> failed(0);
+    std::mutex err_mu;
+    auto fail = [&](int rc, const std::string& m) { std::lock_guard<std::mutex> g(err_mu); if (!failed) { failed = rc ? rc : 1; err = m; } };
+
+    auto work = [&](int wid) {
+        for (;;) {
+            // take a slot first, then a batch number: the oldest unwritten batch always owns a slot
+            DevSlots& d = *ds[(size_t)wid % ds.size()];
+            int slot;
+            {
+                std::unique_lock<std::mutex> g(d.mu);
+                d.cv.wait(g, [&] { return !d.free_slots.empty(); });
+                slot = d.free_slots.back(); d.free_slots.pop_back();
+            }
+            const size_t b = next_batch.fetch_add(1);
+            auto release = [&] { { std::lock_guard<std::mutex> g(d.mu); d.free_slots.push_back(slot); } d.cv.notify_one(); };
+            if (b >= nbatches || failed) { release(); return; }
+            const size_t first = bstart[b], cnt = bstart[b + 1] - first;
+            uint32_t* off; uint16_t *cont, *fin, *rows;
+            ccb_batch_buffers(d.h, slot, &off, &cont, &fin, &rows);
+            const int64_t nc = pack_reads(rs, first, cnt, opt.k, off, cont, max_cont);
+            if (nc == -2) { fail(255, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>)."); release(); sink.put(b, "", {}); continue; }
+            if (nc < 0) { fail(255, "Bad container estimation. Abort."); release(); sink.put(b, "", {}); continue; }
+            int rc;
+            {
+                std::lock_guard<std::mutex> g(d.submit_mu);
+                rc = ccb_batch_submit(d.h, slot, (uint32_t)cnt, (uint64_t)nc, opt.extended ? CCB_EXTENDED : 0);
+            }
+            if (!rc) rc = ccb_batch_wait(d.h, slot);
+            if (rc) { fail(rc, ccb_last_error(d.h)); release(); sink.put(b, "", {}); continue; }
+            std::string text;
+            text.reserve(cnt * 48);
+            csv_rows(text, rs, first, cnt, opt.k, opt.paired, opt.extended, names, fin, rows, opt.row_stride);
+            std::vector<uint16_t> raw;
+            if (sink.dump) raw.assign(fin, fin + cnt * 5);
+            release();
+            sink.put(b, std::move(text), std::move(raw));
+        }
+    };
+    std::vector<std::thread> th;
+    for (int w = 0; w < workers; w++) th.emplace_back(work, w);
+    for (auto& t : th) t.join();
+    const bool io_err = sink.io_error || fclose(sink.f) != 0;
+    if (sink.dump) fclose(sink.dump);
+    for (auto& d : ds) ccb_batch_free(d->h);
+    stats.seconds_total = now() - t0;
+    if (failed) return failed;
+    if (io_err) { err = std::string("Failed to write ") + result_csv; return 1; }
+    return 0;
+}
+
+}  // namespace ccbh

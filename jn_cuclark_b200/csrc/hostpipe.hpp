@@ -1,0 +1,75 @@
+// hostpipe.hpp -- host side of the classification path: read indexing, 2-bit
+// packing, in-memory paired-end join, CSV formatting and the batch pipeline
+// that feeds the C ABI (include/cuclark_b200.h).
+//
+// Replaces the host engine pieces of the reference that sit on the hot path
+// (src/CuCLARK_hh.hh:1335-1783 index/pack/enqueue, :1945-2122 print,
+// src/file.cc:205-268 pair join).  Rules that decide results are the
+// reference's; the organisation is not: indexing is parallel over byte ranges,
+// batches are packed by a pool of workers into library-owned pinned slots, the
+// CSV text of a batch is formatted by the worker that packed it and appended in
+// input order, paired files are joined in memory instead of through a
+// temporary FASTA file.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+struct ccb_handle;
+
+namespace ccbh {
+
+// One entry per read, byte offsets into the mapped text (A1, src/CuCLARK_hh.hh:1364-1394, 1496-1524)
+struct ReadSet {
+    const uint8_t* map = nullptr;
+    size_t nb = 0;
+    bool fasta = true;
+    std::vector<uint64_t> name_s, name_e;   // name bytes [name_s, name_e)
+    std::vector<uint64_t> seq_s, seq_e;     // sequence bytes [seq_s, seq_e) (may contain newlines)
+    std::vector<uint64_t> len;              // length used for gamma
+    size_t n() const { return len.size(); }
+    void clear() { name_s.clear(); name_e.clear(); seq_s.clear(); seq_e.clear(); len.clear(); }
+};
+
+// 0 = ok, -1 = neither '>' nor '@' first ("Failed to recognize the format of the file.")
+int index_reads(const uint8_t* map, size_t nb, int threads, ReadSet& out);
+
+// upper bound on u16 containers reads [first, first+count) can occupy
+size_t pack_bound(const ReadSet& r, size_t first, size_t count, int k);
+// A2 (src/CuCLARK_hh.hh:1615-1715): returns the number of containers written, -1 if cap is too small.
+// Parts longer than 65528 bases are split with k-1 bases of overlap (the reference's u16 part
+// length wraps there); everything else follows the reference's rules.
+int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
+                   uint32_t* offsets, uint16_t* containers, size_t cap);
+
+// A10 (src/file.cc:205-268): ">id\n<mate1>N<mate2>\n" per pair, in memory.  0 = ok, otherwise err is set.
+int join_pairs(const char* file1, const char* file2, std::vector<char>& out, std::string& err);
+
+// A7 (src/CuCLARK_hh.hh:1952-1967, 2096-2118)
+void csv_header(std::string& out, bool extended, const std::vector<std::string>& target_names);
+void csv_rows(std::string& out, const ReadSet& r, size_t first, size_t count, int k, bool paired, bool extended,
+              const std::vector<std::string>& target_names, const uint16_t* final5, const uint16_t* rows, int row_stride);
+
+struct ClassifyOptions {
+    int  k = 31;
+    int  threads = 1;
+    bool paired = false;
+    bool extended = false;
+    bool verbose = false;
+    int  row_stride = 32;
+    const char* dump_final5 = nullptr;     // optional: raw u16[5] per read (second best is not in the CSV)
+};
+
+struct ClassifyStats {
+    uint64_t reads = 0, batches = 0;
+    double   seconds_index = 0, seconds_total = 0;
+};
+
+// Classify the reads of one mapped text with the given device handles (one per GPU, replicated
+// table; batches are dealt round-robin) and write <result_csv>.  0 = ok; err set otherwise.
+int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size_t nb, const char* result_csv,
+                  const std::vector<std::string>& target_names, const ClassifyOptions& opt,
+                  ClassifyStats& stats, std::string& err);
+
+}  // namespace ccbh

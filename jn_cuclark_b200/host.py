@@ -1,0 +1,105 @@
+"""ctypes binding of the host-side C ABI (include/ccb_host.h): read indexing, packing, paired-end
+join and CSV formatting exactly as bin/cuCLARK[-l] use them.  Compiled C++ inside
+libcuclark_b200.so; nothing here computes in Python."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .lib import load_library
+
+_VP = C.c_void_p
+HOST_SYMBOLS = {
+    "ccb_host_index": (_VP, [_VP, C.c_size_t, C.c_int]),
+    "ccb_host_reads_free": (None, [_VP]),
+    "ccb_host_reads_count": (C.c_size_t, [_VP]),
+    "ccb_host_reads_is_fasta": (C.c_int, [_VP]),
+    "ccb_host_reads_field": (C.POINTER(C.c_uint64), [_VP, C.c_int]),
+    "ccb_host_pack_bound": (C.c_size_t, [_VP, C.c_size_t, C.c_size_t, C.c_int]),
+    "ccb_host_pack": (C.c_int64, [_VP, C.c_size_t, C.c_size_t, C.c_int, _VP, _VP, C.c_size_t]),
+    "ccb_host_join_pairs": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(_VP), C.POINTER(C.c_size_t), C.c_char_p, C.c_size_t]),
+    "ccb_host_csv": (C.c_int, [_VP, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int,
+                               _VP, _VP, C.c_int, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
+    "ccb_host_free": (None, [_VP]),
+}
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = load_library()
+    if not _bound:
+        for name, (res, args) in HOST_SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _bound = True
+    return L
+
+
+FIELDS = ("name_s", "name_e", "seq_s", "seq_e", "len")
+
+
+class HostReads:
+    """Index of one FASTA/FASTQ text (reference src/CuCLARK_hh.hh:1340-1534)."""
+
+    def __init__(self, data: bytes, threads: int = 1):
+        self.data = np.frombuffer(data, dtype=np.uint8)
+        self._L = _lib()
+        self._r = self._L.ccb_host_index(self.data.ctypes.data, self.data.size, threads)
+        if not self._r:
+            raise ValueError("Failed to recognize the format of the file.")
+        self.n = self._L.ccb_host_reads_count(self._r)
+        self.is_fasta = bool(self._L.ccb_host_reads_is_fasta(self._r))
+
+    def arr(self, name: str) -> np.ndarray:
+        p = self._L.ccb_host_reads_field(self._r, FIELDS.index(name))
+        return np.ctypeslib.as_array(p, shape=(self.n,)).copy() if self.n else np.zeros(0, np.uint64)
+
+    def pack(self, k: int, first: int = 0, count: int | None = None):
+        count = self.n - first if count is None else count
+        cap = self._L.ccb_host_pack_bound(self._r, first, count, k)
+        off = np.zeros(count + 1, np.uint32)
+        cont = np.zeros(cap, np.uint16)
+        nc = self._L.ccb_host_pack(self._r, first, count, k, off.ctypes.data, cont.ctypes.data, cap)
+        if nc < 0:
+            raise RuntimeError(f"ccb_host_pack failed ({nc})")
+        return off, cont[:nc].copy()
+
+    def csv(self, k: int, paired: bool, names: list[str], out5: np.ndarray, rows: np.ndarray | None = None,
+            header: bool = True) -> bytes:
+        arr = (C.c_char_p * len(names))(*[s.encode() for s in names])
+        out5 = np.ascontiguousarray(out5, np.uint16)
+        ext = rows is not None
+        if ext:
+            rows = np.ascontiguousarray(rows, np.uint16)
+        out, n = _VP(), C.c_size_t(0)
+        rc = self._L.ccb_host_csv(self._r, 0, self.n, k, int(paired), int(ext), int(header), arr, len(names),
+                                  out5.ctypes.data, rows.ctypes.data if ext else None, rows.shape[1] if ext else 0,
+                                  C.byref(out), C.byref(n))
+        if rc:
+            raise RuntimeError(f"ccb_host_csv failed ({rc})")
+        s = C.string_at(out.value, n.value)
+        self._L.ccb_host_free(out)
+        return s
+
+    def __del__(self):
+        try:
+            if self._r:
+                self._L.ccb_host_reads_free(self._r)
+                self._r = None
+        except Exception:
+            pass
+
+
+def join_pairs(f1: str, f2: str) -> bytes:
+    """src/file.cc:205-268 in memory: b'>id\\nR1NR2\\n' per pair."""
+    L = _lib()
+    out, n = _VP(), C.c_size_t(0)
+    err = C.create_string_buffer(512)
+    rc = L.ccb_host_join_pairs(f1.encode(), f2.encode(), C.byref(out), C.byref(n), err, 512)
+    if rc:
+        raise RuntimeError(err.value.decode())
+    s = C.string_at(out.value, n.value)
+    L.ccb_host_free(out)
+    return s

@@ -71,6 +71,8 @@ SYMBOLS = {
     "ccb_get_stats": (C.c_int, [_H, C.POINTER(Stats)]),
     "ccb_version": (C.c_char_p, []),
     "ccb_l2_fetch_granularity": (C.c_int, [_H]),
+    "ccb_device_count": (C.c_int, []),
+    "ccb_batch_slots": (C.c_int, [_H]),
     "ccb_synth_db": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
     "ccb_synth_reads_packed": (C.c_int, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
                                          C.c_uint64, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(C.c_uint64)]),

@@ -5,10 +5,33 @@ import re
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared():
-    h = open(os.path.join(ROOT, "include", "cuclark_b200.h")).read()
+def _declared(header="cuclark_b200.h"):
+    h = open(os.path.join(ROOT, "include", header)).read()
     h = re.sub(r"/\*.*?\*/", "", h, flags=re.S)
     return sorted(set(re.findall(r"\b(ccb_[a-z0-9_]+)\s*\(", h)))
+
+
+def test_host_header_symbols_exported_and_bound():
+    from jn_cuclark_b200 import host, lib
+    L = lib.load_library()
+    names = _declared("ccb_host.h")
+    assert len(names) >= 10
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/ccb_host.h but not exported"
+        assert n in host.HOST_SYMBOLS, f"{n} has no ctypes prototype"
+
+
+def test_cli_binaries_built():
+    import subprocess
+    for b in ("cuCLARK", "cuCLARK-l"):
+        p = os.path.join(ROOT, "bin", b)
+        assert os.path.exists(p), p + " missing: run make -C jn_cuclark_b200"
+        r = subprocess.run([p, "--version"], capture_output=True, text=True)
+        assert r.returncode == 0 and "sm_100a" in r.stdout
+        r = subprocess.run([p, "-k", "31", "-T", "/nonexistent", "-D", "/tmp", "-O", "x", "-R", "y"], capture_output=True, text=True)
+        assert r.returncode == 1 and "Failed to find/read the file of the targets definition" in r.stderr
+        r = subprocess.run([p, "-k", "31", "-Q", "zz", "-D", "/tmp", "-O", "x"], capture_output=True, text=True)
+        assert r.returncode == 1 and "Failed to recognize option: -Q" in r.stderr
 
 
 def test_header_symbols_exported_and_bound():

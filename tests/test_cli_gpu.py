@@ -1,0 +1,131 @@
+"""Process boundary: bin/cuCLARK and bin/cuCLARK-l on reference-format
+databases, CSV compared byte for byte with the oracle's CSV (and with the reference GPU binary's
+CSVs under tests/golden/ref_gpu/ when present); u16[5] dump compared bit-exactly."""
+import glob
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+WORLD = os.path.join(HERE, "golden", "world")
+REFGPU = os.path.join(HERE, "golden", "ref_gpu")
+
+
+def _write_ref_db(npz, folder):
+    """Re-create the .sz/.ky/.lb files the unmodified reference wrote (tests/golden/make_golden.py db)."""
+    g = np.load(npz)
+    prefix = os.path.join(folder, str(g["name"]))
+    sz = np.zeros(int(g["htsize"]), np.uint8)
+    sz[g["nz_bucket"]] = g["nz_size"]
+    sz.tofile(prefix + ".sz")
+    g["ky"].tofile(prefix + ".ky")
+    g["lb"].tofile(prefix + ".lb")
+    return prefix
+
+
+@pytest.fixture(scope="module", params=["light", "full"])
+def setup(request, tmp_path_factory, oracle):
+    mode = request.param
+    d = str(tmp_path_factory.mktemp("cli_" + mode))
+    labels = open(os.path.join(WORLD, "labels.txt")).read().split()
+    tp = os.path.join(d, "targets.txt")
+    with open(tp, "w") as f:
+        for i, lab in enumerate(labels):
+            f.write(f"{os.path.join(WORLD, 'genomes', f'g{i}.fa')}\t{lab}\n")
+    os.makedirs(os.path.join(d, "db"))
+    prefix = _write_ref_db(os.path.join(HERE, "golden", "ref_db", mode + ".npz"), os.path.join(d, "db"))
+    light = mode == "light"
+    k = 27 if light else 31
+    ht = oracle.HTSIZE_LIGHT if light else oracle.HTSIZE_FULL
+    odb = oracle.OracleDb.read(prefix, ht, k)
+    names, seen = ["NA"], set()
+    for lab in labels:
+        if lab not in seen:
+            seen.add(lab); names.append(lab)
+    return {"mode": mode, "dir": d, "targets": tp, "k": k, "odb": odb, "names": names,
+            "bin": os.path.join(ROOT, "bin", "cuCLARK-l" if light else "cuCLARK"),
+            "row_stride": 2 * (23 if light else 15) + 2}
+
+
+def _run(s, extra, res, env=None):
+    cmd = [s["bin"], "-k", "31", "-T", s["targets"], "-D", os.path.join(s["dir"], "db"), "-R", res] + extra
+    e = dict(os.environ)
+    if env:
+        e.update(env)
+    r = subprocess.run(cmd, capture_output=True, text=True, env=e, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    return r
+
+
+def _oracle_csv(s, oracle, data, path, paired=False, extended=False):
+    ir = oracle.IndexedReads(data)
+    off, cont = ir.pack(s["k"])
+    out5, rows, _ = s["odb"].query_packed(s["k"], off, cont, row_stride=s["row_stride"] if extended else 0)
+    ir.write_csv(path, s["k"], paired, s["names"], out5, rows if extended else None)
+    return out5
+
+
+CASES = [("fa", ["-O", "reads.fa"], {}), ("ml", ["-O", "reads_ml.fa"], {}), ("fq", ["-O", "reads.fq"], {}),
+         ("fa_ext", ["-O", "reads.fa", "--extended"], {"extended": True}),
+         ("fa_b4n4", ["-O", "reads.fa", "-n", "4", "-b", "4"], {}),
+         ("fq_m", ["-O", "reads.fq", "-m", "0", "--verbose"], {})]
+
+
+@pytest.mark.parametrize("name,args,kw", CASES, ids=[c[0] for c in CASES])
+def test_single_end(setup, oracle, tmp_path, name, args, kw):
+    s = setup
+    args = [os.path.join(WORLD, a) if a.startswith("reads") else a for a in args]
+    res = str(tmp_path / "out")
+    dump = str(tmp_path / "final5.bin")
+    r = _run(s, args, res, {"CCB_DUMP_FINAL5": dump})
+    assert "Classifying: " in r.stderr and "reads/min" in r.stderr and "Results: " + res + ".csv" in r.stderr
+    data = open(args[1], "rb").read()
+    want5 = _oracle_csv(s, oracle, data, str(tmp_path / "want.csv"), extended=kw.get("extended", False))
+    assert open(res + ".csv", "rb").read() == open(str(tmp_path / "want.csv"), "rb").read()
+    got5 = np.fromfile(dump, np.uint16).reshape(-1, 5)
+    assert np.array_equal(got5, want5)                   # includes second best, which the CSV does not print
+    ref = os.path.join(REFGPU, f"{s['mode']}_{name}.csv")
+    if os.path.exists(ref):
+        assert open(res + ".csv", "rb").read() == open(ref, "rb").read(), "differs from the reference GPU binary's CSV"
+
+
+@pytest.mark.parametrize("ext", [False, True])
+def test_paired(setup, oracle, tmp_path, ext):
+    s = setup
+    p1, p2 = os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")
+    res = str(tmp_path / "out")
+    _run(s, ["-P", p1, p2] + (["--extended"] if ext else []), res)
+    m = str(tmp_path / "m.fa")
+    assert oracle.merge_paired(p1, p2, m) == 0
+    _oracle_csv(s, oracle, open(m, "rb").read(), str(tmp_path / "want.csv"), paired=True, extended=ext)
+    assert open(res + ".csv", "rb").read() == open(str(tmp_path / "want.csv"), "rb").read()
+    assert not glob.glob(p1 + "_Concatenated*")          # no temp file is left (none is written)
+    ref = os.path.join(REFGPU, f"{s['mode']}_{'pe_ext' if ext else 'pe'}.csv")
+    if os.path.exists(ref):
+        assert open(res + ".csv", "rb").read() == open(ref, "rb").read()
+
+
+def test_list_of_files_mode(setup, oracle, tmp_path):
+    """-O and -R name lists of files when -R exists and -O is not a reads file (CuCLARK_hh.hh:386-428)."""
+    s = setup
+    if s["mode"] != "light":
+        pytest.skip("one variant is enough")
+    objs, ress = tmp_path / "objs.txt", tmp_path / "ress.txt"
+    objs.write_text(os.path.join(WORLD, "reads.fa") + "\n" + os.path.join(WORLD, "reads.fq") + "\n")
+    ress.write_text(str(tmp_path / "a") + "\n" + str(tmp_path / "b") + "\n")
+    _run(s, ["-O", str(objs)], str(ress))
+    for out, src in (("a", "reads.fa"), ("b", "reads.fq")):
+        _oracle_csv(s, oracle, open(os.path.join(WORLD, src), "rb").read(), str(tmp_path / "w.csv"))
+        assert open(str(tmp_path / out) + ".csv", "rb").read() == open(str(tmp_path / "w.csv"), "rb").read()
+
+
+def test_missing_db_fails_like_reference(setup, tmp_path):
+    s = setup
+    r = subprocess.run([s["bin"], "-T", s["targets"], "-D", str(tmp_path), "-O", os.path.join(WORLD, "reads.fa"), "-R", str(tmp_path / "o")],
+                       capture_output=True, text=True)
+    assert r.returncode == 255 and "Failed to find the database." in r.stderr

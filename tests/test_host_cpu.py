@@ -1,0 +1,150 @@
+"""Host logic (C++ in libcuclark_b200.so, include/ccb_host.h) against the CPU oracle: read indexing
+(A1), 2-bit packing (A2), paired-end join (A10) and CSV text (A7).  No GPU needed."""
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+WORLD = os.path.join(HERE, "golden", "world")
+
+EDGE_FASTA = [
+    b">r1\nACGT\n",
+    b">r1\nACGT",                                    # no trailing newline
+    b">r1 desc here\nACGTACGTACGTACGTACGTACGTACGTACGTACGT\n>r2\tx\nACGTNACGTACGTACGTACGTACGTACGTACGTACGTACGTACGTA\n",
+    b">empty\n>next\nACGTACGTACGTACGTACGTACGTACGTACGTAAA\n",
+    b">multi\nACGTACGTAC\nGTACGTACGTACGTACG\nTACGTACGTACG\n>x\nacgtnnacgu\n",
+    b">a_name_that_is_much_longer_than_thirty_nine_characters_for_sure and more\nACGTACGTACGTACGTACGTACGTACGTACGTACGTACGT\n",
+    b">q\nACGT>ACGT\n>ACGT\nAC\n",                   # '>' inside a line; '>' line directly after a header
+    b">\nACGT\nTTTT\n>z\nAC\n",                      # empty name swallows the next line
+    b"> lead\nACGTACGTACGTACGTACGTACGTACGTACGTA\n\n\n>t\n\nACGT\n",
+]
+EDGE_FASTQ = [
+    b"@r1\nACGT\n+\nIIII\n",
+    b"@r1\nACGT\n+\nIIII",
+    b"@r1 d\nACGTNNACGTACGTACGTACGTACGTACGTACGTACGTACGTAC\n+r1\nIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIIII\n@r2/1\nAC\n+\n@I\n",
+    b"@r1\nACGT\n+\nIIII\n\n",
+    b"@r1\nACGT\n+\nIIII\n\n\n",
+    b"@\nACGT\n+\nIIII\n@r2\nACGT\n+\nIIII\n",     # empty name
+    b"@r1\nACGT\n+\nIIII\n@r2\nACGT\n",              # truncated record
+]
+
+
+def _same_index(oracle, host, data, threads=1):
+    a = oracle.IndexedReads(data)
+    b = host.HostReads(data, threads)
+    assert a.n == b.n
+    for f in ("name_s", "name_e", "seq_s", "seq_e", "len"):
+        assert np.array_equal(a.arr(f), b.arr(f)), f
+    return a, b
+
+
+@pytest.mark.parametrize("data", EDGE_FASTA + EDGE_FASTQ)
+def test_index_pack_csv_edge_cases(oracle, data):
+    from jn_cuclark_b200 import host
+    a, b = _same_index(oracle, host, data)
+    for k in (4, 12, 31):
+        oa, ca = a.pack(k)
+        ob, cb = b.pack(k)
+        assert np.array_equal(oa, ob) and np.array_equal(ca, cb)
+    rng = np.random.default_rng(1)
+    out5 = rng.integers(0, 40, size=(a.n, 5)).astype(np.uint16)
+    out5[:, 1] = rng.integers(0, 4, size=a.n)
+    out5[0, :] = 0                                   # gamma 0 / confidence 0
+    names = ["NA", "T0", "T1", "T2"]
+    for paired in (False, True):
+        p = "/tmp/ccb_csv_%d.csv" % os.getpid()
+        a.write_csv(p, 31, paired, names, out5)
+        assert open(p, "rb").read() == b.csv(31, paired, names, out5)
+        os.remove(p)
+
+
+@pytest.mark.parametrize("fname", ["reads.fa", "reads_ml.fa", "reads.fq"])
+def test_world_files(oracle, fname):
+    from jn_cuclark_b200 import host
+    data = open(os.path.join(WORLD, fname), "rb").read()
+    a, b = _same_index(oracle, host, data)
+    for k in (27, 31):
+        oa, ca = a.pack(k)
+        ob, cb = b.pack(k)
+        assert np.array_equal(oa, ob) and np.array_equal(ca, cb)
+    # sub-range packing = slices of the whole
+    ob2, cb2 = b.pack(31, 100, 50)
+    ob, cb = b.pack(31)
+    assert np.array_equal(ob2, ob[100:151] - ob[100]) and np.array_equal(cb2, cb[ob[100]:ob[150]])
+
+
+def _big(kind, n, rng, odd=False):
+    parts = []
+    for i in range(n):
+        L = int(rng.integers(20, 300))
+        s = bytes(rng.choice(np.frombuffer(b"ACGTN", np.uint8), size=L, p=[.245, .245, .245, .245, .02]))
+        if kind == "fa":
+            if i % 7 == 0:
+                s = b"\n".join(s[j:j + 60] for j in range(0, L, 60))
+            parts.append(b">r%d some text\n%s\n" % (i, s))
+        else:
+            q = b"@" * L if i % 5 == 0 else b"I" * L       # quality lines that start with '@'
+            parts.append(b"@r%d/1\n%s\n+\n%s\n" % (i, s, q))
+    if odd:
+        parts.insert(n // 2, b">\nACGT\n" if kind == "fa" else b"@\nACGT\n+\nIIII\n")
+    return b"".join(parts)
+
+
+@pytest.mark.parametrize("kind", ["fa", "fq"])
+@pytest.mark.parametrize("odd", [False, True])
+def test_parallel_index_equals_sequential(oracle, kind, odd):
+    from jn_cuclark_b200 import host
+    data = _big(kind, 12000, np.random.default_rng(5), odd)
+    assert len(data) > (1 << 20)
+    for threads in (3, 8):
+        _same_index(oracle, host, data, threads)
+
+
+def test_join_pairs(oracle, tmp_path):
+    from jn_cuclark_b200 import host
+    m = str(tmp_path / "m.fa")
+    f1, f2 = os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")
+    assert oracle.merge_paired(f1, f2, m) == 0
+    assert open(m, "rb").read() == host.join_pairs(f1, f2)
+    with pytest.raises(RuntimeError, match="FASTQ"):
+        host.join_pairs(os.path.join(WORLD, "reads.fa"), os.path.join(WORLD, "reads.fa"))
+    bad = tmp_path / "bad.fq"
+    bad.write_bytes(b"@other/2\nACGT\n+\nIIII\n")
+    with pytest.raises(RuntimeError, match="does not match"):
+        host.join_pairs(f1, str(bad))
+
+
+def test_extended_csv(oracle):
+    from jn_cuclark_b200 import host
+    data = open(os.path.join(WORLD, "reads.fa"), "rb").read()
+    a, b = _same_index(oracle, host, data)
+    rng = np.random.default_rng(2)
+    names = ["NA"] + ["T%d" % i for i in range(6)]
+    out5 = rng.integers(0, 100, size=(a.n, 5)).astype(np.uint16)
+    out5[:, 1] = rng.integers(0, 7, size=a.n)
+    rows = np.zeros((a.n, 32), np.uint16)
+    for i in range(a.n):
+        t = np.sort(rng.choice(6, size=int(rng.integers(0, 5)), replace=False))
+        rows[i, 0] = t.size
+        rows[i, 1:1 + 2 * t.size:2] = t
+        rows[i, 2:2 + 2 * t.size:2] = rng.integers(1, 99, size=t.size)
+    p = "/tmp/ccb_csvx_%d.csv" % os.getpid()
+    a.write_csv(p, 31, False, names, out5, rows)
+    assert open(p, "rb").read() == b.csv(31, False, names, out5, rows)
+    os.remove(p)
+
+
+def test_long_part_is_split_not_wrapped():
+    """Parts longer than 65528 bases are split with k-1 overlap (the reference's u16 length wraps)."""
+    from jn_cuclark_b200 import host
+    rng = np.random.default_rng(3)
+    L, k = 150000, 31
+    s = bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=L))
+    b = host.HostReads(b">long\n" + s + b"\n")
+    off, cont = b.pack(k)
+    lens, p, total_kmers = [], 0, 0
+    while p < off[1]:
+        n = int(cont[p]); lens.append(n); total_kmers += n - k + 1; p += 1 + (n + 7) // 8
+    assert lens == [65528, 65528, L - 2 * (65528 - (k - 1))]
+    assert total_kmers == L - k + 1
