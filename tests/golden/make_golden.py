@@ -6,6 +6,9 @@
   python tests/golden/make_golden.py db        # reference CPU database build (runs anywhere; the
                                                # binary stops at its CUDA probe after writing the DB)
                                                # -> tests/golden/ref_db/{light,full}.npz
+  python tests/golden/make_golden.py csv       # reference host engine (unmodified: parse, pack, merge, CSV)
+                                               # + reference hash-table lookup + CPU stand-in for the
+                                               # device kernels (oracle/ref_cpu_device.cc) -> tests/golden/ref_csv/
   python tests/golden/make_golden.py gpu OUT   # on a GPU box: reference classification CSVs -> OUT/
                                                # (copied to tests/golden/ref_gpu/ afterwards)
 """
@@ -85,10 +88,10 @@ def make_db():
             print(mode, os.path.basename(prefix), "k-mers:", int(sz.sum()), sha)
 
 
-def make_gpu(out):
+def make_gpu(out, suffix=""):
     os.makedirs(out, exist_ok=True)
     log = open(os.path.join(out, "log.txt"), "w")
-    for mode, binary, k in (("light", "cuCLARK-l", 27), ("full", "cuCLARK", 31)):
+    for mode, binary, k in (("light", "cuCLARK-l" + suffix, 27), ("full", "cuCLARK" + suffix, 31)):
         d = tempfile.mkdtemp()
         tp = write_targets(d)
         os.makedirs(os.path.join(d, "db"))
@@ -99,7 +102,10 @@ def make_gpu(out):
                 ("pe", ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")]),
                 ("fa_ext", ["-O", os.path.join(WORLD, "reads.fa"), "--extended"]),
                 ("pe_ext", ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq"), "--extended"]),
-                ("fa_b4n4", ["-O", os.path.join(WORLD, "reads.fa"), "-n", "4", "-b", "4"])]
+                # -n 4 -b 4 crashes inside the reference's own engine on the CPU stand-in (its printer thread
+                # races with the packers); the batch split is exercised single-threaded there
+                ("fa_b4n4", ["-O", os.path.join(WORLD, "reads.fa"), "-n", "4", "-b", "4"]) if not suffix else
+                ("fa_b4", ["-O", os.path.join(WORLD, "reads.fa"), "-b", "4"])]
         if mode == "full":                           # each full-mode run reloads a 1.6 GB .sz: keep to three
             runs = [r for r in runs if r[0] in ("fq", "fa_ext", "pe_ext")]
         for name, extra in runs:
@@ -123,3 +129,6 @@ if __name__ == "__main__":
         make_db()
     elif cmd == "gpu":
         make_gpu(sys.argv[2])
+    elif cmd == "csv":
+        # reference host engine + CPU stand-in for its device layer (oracle/ref_cpu_device.cc): runs anywhere
+        make_gpu(os.path.join(HERE, "ref_csv"), "_cpu")

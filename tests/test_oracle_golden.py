@@ -53,3 +53,43 @@ def test_db_file_roundtrip_and_find(oracle, tmp_path):
         assert db2.find(int(c[i])) == int(l[i])
         assert db2.find(oracle.revcomp(int(c[i]), 27)) == int(l[i])      # either strand
     assert db2.find(12345) is None
+
+
+# ---- CSVs written by the reference's own host engine (tests/golden/ref_csv/, make_golden.py csv) ----
+REF_CSV = os.path.join(HERE, "golden", "ref_csv")
+CSV_CASES = {"fa": ("reads.fa", False, False), "ml": ("reads_ml.fa", False, False), "fq": ("reads.fq", False, False),
+             "fa_ext": ("reads.fa", False, True), "fa_b4": ("reads.fa", False, False),
+             "pe": (None, True, False), "pe_ext": (None, True, True)}
+
+
+@pytest.fixture(scope="module")
+def golden_dbs(oracle, tmp_path_factory):
+    d = tmp_path_factory.mktemp("gdb")
+    tp, labels = _targets(d)
+    names, seen = ["NA"], set()
+    for lab in labels:
+        if lab not in seen:
+            seen.add(lab); names.append(lab)
+    return {"light": (oracle.OracleDb.build(tp, 27, oracle.HTSIZE_LIGHT, light=True), 27, 48),
+            "full": (oracle.OracleDb.build(tp, 31, oracle.HTSIZE_FULL), 31, 32), "names": names}
+
+
+@pytest.mark.parametrize("path", sorted(os.path.basename(p) for p in __import__("glob").glob(os.path.join(REF_CSV, "*.csv"))))
+def test_oracle_csv_equals_reference_host_engine(oracle, golden_dbs, tmp_path, path):
+    """Parse, part split, pack, pair merge, gamma/confidence formatting: the oracle's CSV is byte-identical
+    to the one the reference's unmodified host engine wrote for the same input."""
+    mode, case = path[:-4].split("_", 1)
+    src, paired, ext = CSV_CASES[case]
+    db, k, stride = golden_dbs[mode]
+    if paired:
+        m = str(tmp_path / "m.fa")
+        assert oracle.merge_paired(os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq"), m) == 0
+        data = open(m, "rb").read()
+    else:
+        data = open(os.path.join(WORLD, src), "rb").read()
+    ir = oracle.IndexedReads(data)
+    off, cont = ir.pack(k)
+    out5, rows, _ = db.query_packed(k, off, cont, row_stride=stride if ext else 0)
+    out = str(tmp_path / "o.csv")
+    ir.write_csv(out, k, paired, golden_dbs["names"], out5, rows if ext else None)
+    assert open(out, "rb").read() == open(os.path.join(REF_CSV, path), "rb").read()
