@@ -239,6 +239,130 @@ __global__ void __launch_bounds__(256) k_gather(const ulonglong4* tbl, uint64_t 
 }
 }  // namespace
 
+// ---------------------------------------------------------------------------
+// Line-reuse probes (what a minimizer-bucketed table would do): all four sectors of a random
+// 128-byte line are wanted by ONE thread.
+//   mode 8 : sector 0 first, sectors 1-3 only after it has arrived (dependent address)
+//   mode 9 : prefetch.global.L2 of the lines of step j+1, then the 4 sectors of the lines of step j
+//   mode 10: like 9 without the prefetch (all four sectors at once = bytes=128 mode 0, control)
+// n_probes counts LINES.  LPT lines per thread per step.
+// ---------------------------------------------------------------------------
+namespace {
+template <int MODE>
+__global__ void __launch_bounds__(256) k_line_reuse(const ulonglong4* tbl, uint64_t n_lines, uint64_t n_probes,
+                                                     uint64_t salt, unsigned long long* sink)
+{
+    constexpr int LPT = 4;
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    const uint64_t steps = n_probes / (stride * LPT);
+    unsigned long long acc = 0;
+    auto line_of = [&](uint64_t step, int u) { return __umul64hi(ccb_sm64(((step * LPT + u) * stride + tid) ^ salt), n_lines) * 4; };
+    if (MODE == 9) {
+#pragma unroll
+        for (int u = 0; u < LPT; u++) asm volatile("prefetch.global.L2 [%0];" :: "l"(tbl + line_of(0, u)));
+    }
+    for (uint64_t st = 0; st < steps; st++) {
+        if (MODE == 9 && st + 1 < steps) {
+#pragma unroll
+            for (int u = 0; u < LPT; u++) asm volatile("prefetch.global.L2 [%0];" :: "l"(tbl + line_of(st + 1, u)));
+        }
+        uint64_t e[LPT][4];
+        if (MODE == 8) {
+#pragma unroll
+            for (int u = 0; u < LPT; u++) load_bucket(tbl + line_of(st, u), e[u]);
+#pragma unroll
+            for (int u = 0; u < LPT; u++) {
+                const ulonglong4* p = tbl + line_of(st, u) + (e[u][0] == 0x1234567ull ? 1 : 0);   // depends on sector 0
+                uint64_t f[4];
+                load_bucket(p + 1, f); acc += f[0];
+                load_bucket(p + 2, f); acc += f[1];
+                load_bucket(p + 3, f); acc += f[2];
+                acc += e[u][3];
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+#pragma unroll
+                for (int u = 0; u < LPT; u++) load_bucket(tbl + line_of(st, u) + q, e[u]);
+#pragma unroll
+                for (int u = 0; u < LPT; u++) acc += e[u][q];
+            }
+        }
+    }
+    if (acc == 0x123456789abcdefull) *sink = acc;
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// mode 11: every lane fetches whole random 128-byte lines with ONE bulk async copy each
+// (cp.async.bulk global -> shared, completion on a per-warp mbarrier), LPT lines per lane per step.
+// mode 12: the same lines with cooperative cp.async (8 lanes x 16 B per line, request list in smem).
+// ---------------------------------------------------------------------------
+namespace {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+template <int MODE>
+__global__ void __launch_bounds__(128) k_line_bulk(const ulonglong4* tbl, uint64_t n_lines, uint64_t n_probes,
+                                                    uint64_t salt, unsigned long long* sink)
+{
+    constexpr int LPT = 2, WARPS = 4;
+    __shared__ alignas(128) unsigned char buf[WARPS][32 * LPT][128];
+    __shared__ alignas(8) unsigned long long bar[WARPS];
+    __shared__ uint32_t req[WARPS][32 * LPT];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    const uint64_t steps = n_probes / (stride * LPT);
+    const uint32_t bar_a = smem_u32(&bar[w]);
+    if (MODE == 11) {
+        if (lane == 0) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar_a));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+    }
+    unsigned long long acc = 0;
+    uint32_t parity = 0;
+    for (uint64_t st = 0; st < steps; st++) {
+        uint64_t line[LPT];
+#pragma unroll
+        for (int u = 0; u < LPT; u++) line[u] = __umul64hi(ccb_sm64(((st * LPT + u) * stride + tid) ^ salt), n_lines);
+        if (MODE == 11) {
+            if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_a), "r"(32 * LPT * 128) : "memory");
+            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < LPT; u++)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 128, [%2];"
+                             :: "r"(smem_u32(&buf[w][lane * LPT + u][0])), "l"(tbl + line[u] * 4), "r"(bar_a) : "memory");
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(bar_a), "r"(parity) : "memory");
+            parity ^= 1;
+        } else {
+#pragma unroll
+            for (int u = 0; u < LPT; u++) req[w][lane * LPT + u] = (uint32_t)line[u];
+            __syncwarp();
+#pragma unroll 4
+            for (int j = 0; j < 32 * LPT; j += 4) {
+                const int li = j + (lane >> 3);
+                const unsigned char* src = (const unsigned char*)(tbl + (uint64_t)req[w][li] * 4) + (lane & 7) * 16;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(&buf[w][li][(lane & 7) * 16])), "l"(src) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+        }
+#pragma unroll
+        for (int u = 0; u < LPT; u++) {
+            const ulonglong2* q = (const ulonglong2*)&buf[w][lane * LPT + u][0];
+            acc += q[0].x ^ q[3].y ^ q[5].x ^ q[7].y;
+        }
+        __syncwarp();
+    }
+    if (acc == 0x123456789abcdefull) *sink = acc;
+}
+}  // namespace
+
 extern "C" int ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, int mode, uint64_t footprint, void* stream)
 {
     if (!h || !h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
@@ -262,6 +386,11 @@ extern "C" int ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, 
     else if (mode == 5 && bytes == 32)  k_gather<32, 5><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
     else if (mode == 6 && bytes == 32)  k_gather<32, 6><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
     else if (mode == 7 && bytes == 32)  k_gather<32, 7><<<grid, 256, 0, s>>>(tbl, n32, n_probes, salt, sink);
+    else if (mode == 8)  k_line_reuse<8><<<grid, 256, 0, s>>>(tbl, n32 / 4, n_probes, salt, sink);
+    else if (mode == 9)  k_line_reuse<9><<<grid, 256, 0, s>>>(tbl, n32 / 4, n_probes, salt, sink);
+    else if (mode == 10) k_line_reuse<10><<<grid, 256, 0, s>>>(tbl, n32 / 4, n_probes, salt, sink);
+    else if (mode == 11) k_line_bulk<11><<<148 * 3, 128, 0, s>>>(tbl, n32 / 4, n_probes, salt, sink);
+    else if (mode == 12) k_line_bulk<12><<<148 * 3, 128, 0, s>>>(tbl, n32 / 4, n_probes, salt, sink);
     else return ccb_fail(h, -43, "ccb_bench_gather: unsupported bytes/mode (%d/%d)", bytes, mode);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_gather launch: %s", cudaGetErrorString(e));
