@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU per step")
     ap.add_argument("--read-len", type=int, default=150)
     ap.add_argument("-k", type=int, default=31)
-    ap.add_argument("--load-factor", type=float, default=0.5)
+    ap.add_argument("--load-factor", type=float, default=0.4)
     ap.add_argument("--slots", type=int, default=4, help="pinned batch slots of the e2e pipeline")
     ap.add_argument("--sample-genomes", type=int, default=4, help="cpu baseline: genomes in the sample DB")
     ap.add_argument("--sample-reads", type=int, default=200_000)

@@ -39,7 +39,7 @@ typedef struct ccb_config {
     int    n_targets;     /* number of targets = labels 0..n_targets-1 (<= 65534)           */
     int    max_hits;      /* MAXHITS of the variant: 15 full / 23 light (parameters.hh:44)  */
     int    n_slots;       /* batch slots (reference: -b batches); >= 1, 2+ overlaps copies  */
-    double load_factor;   /* table fill (entries / slots), 0 = default 0.5                  */
+    double load_factor;   /* table fill (entries / slots), 0 = default 0.4                  */
     int    verbose;
 } ccb_config;
 

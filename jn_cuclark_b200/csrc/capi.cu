@@ -47,7 +47,7 @@ extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
     h->cfg = *cfg;
     if (h->cfg.n_slots < 1) h->cfg.n_slots = 1;
     if (h->cfg.max_hits < 1) h->cfg.max_hits = 15;
-    if (h->cfg.load_factor <= 0) h->cfg.load_factor = 0.5;
+    if (h->cfg.load_factor <= 0) h->cfg.load_factor = 0.4;
     h->row_stride = 2 * h->cfg.max_hits + 2;
     if (cudaSetDevice(cfg->device) != cudaSuccess || cudaStreamCreateWithFlags(&h->db_stream, cudaStreamNonBlocking) != cudaSuccess) {
         ccb_fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));

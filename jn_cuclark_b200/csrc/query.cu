@@ -17,9 +17,10 @@
 //    cp.async.bulk (TMA path) into the warp's shared-memory staging area,
 //    completion on a per-warp mbarrier; adjacent lanes that continue the same
 //    run share the line;
-//  * probes then read one 32-byte sector from shared memory; only overflow
-//    chains and tiles with more than kLinesMax distinct lines touch global
-//    memory directly;
+//  * probes then compare the 12 keys of the staged line in shared memory; a k-mer whose home
+//    line says "look further" (overflow) is queued and rides along with the
+//    NEXT tile's fetch, asking for the next line of its probe sequence, so a
+//    tile pays one memory round trip however long the chains are;
 //  * votes: a lane run-length-merges its labels, then adds (label,count) to an
 //    8-slot accumulator of its read in shared memory; best / second best are
 //    taken on the key (count desc, target asc) == the reference's ascending
@@ -29,16 +30,25 @@
 
 namespace ccb {
 
-constexpr int kWarps      = 4;
+constexpr int kWarps      = 1;             // warps per CTA (shared memory, not the CTA shape, bounds residency)
+constexpr int kCtasPerSm  = 8;
 constexpr int kSeg        = 16;            // k-mer start positions per lane
-constexpr int kLinesMax   = 96;            // lines staged per warp tile
+constexpr int kLinesMax   = 128;           // lines staged per warp tile
 constexpr int kLineStride = 144;           // bytes between staged lines (128 + 16: conflict-free sector reads)
 constexpr int kAccSlots   = 8;
+constexpr int kQueue      = 160;           // k-mers that wait for the next line of their probe sequence
+constexpr int kItemRows   = kQueue / 32;
 constexpr uint32_t kAccEmpty = 0xFFFFFFFFu;
 constexpr uint32_t kNoLine   = 0xFFFFFFFFu;
 
+// a k-mer that was not settled by its home line: it asks for line `hop` of its probe sequence in the NEXT
+// tile's fetch, so a tile never waits for more than one memory round trip
+struct alignas(16) Item { uint64_t c; uint32_t home; uint16_t hop; uint8_t rid; uint8_t s0; };
+
 struct alignas(128) WarpSmem {
     unsigned char lines[kLinesMax * kLineStride];
+    Item     items[2][kQueue];
+    uint32_t nq[2];
     uint32_t acc_lab[32][kAccSlots];
     uint32_t acc_cnt[32][kAccSlots];
     uint32_t acc_ovf[32];
@@ -140,8 +150,29 @@ __device__ __forceinline__ uint32_t valid_mask(const uint16_t* c, int nsl, int P
     return vm;
 }
 
+// Search a staged line (shared memory, byte address `base`) for c: all 12 keys, straight-line code.
+// Returns 0 = resolved (lab = raw label or kLabelNone), 1 = the key may have left for the next
+// line of its probe sequence (its bit in the line's filter of leavers is set).
+__device__ __forceinline__ int probe_staged(uint32_t base, uint64_t c, uint32_t& lab)
+{
+    const uint32_t lb = leave_bit(c);
+    uint32_t meta = 0;
+    lab = kLabelNone;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint64_t e[4];
+        asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(e[0]), "=l"(e[1]) : "r"(base + q * 32));
+        asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(e[2]), "=l"(e[3]) : "r"(base + q * 32 + 16));
+        if (e[0] == c) lab = (uint32_t)e[3] & 0xFFFFu;
+        if (e[1] == c) lab = (uint32_t)(e[3] >> 16) & 0xFFFFu;
+        if (e[2] == c) lab = (uint32_t)(e[3] >> 32) & 0xFFFFu;
+        if ((lb >> 4) == (uint32_t)q) meta = (uint32_t)(e[3] >> 48);
+    }
+    return (lab == kLabelNone && ((meta >> (lb & 15u)) & 1u)) ? 1 : 0;
+}
+
 template <int W, bool STATS>
-__global__ void __launch_bounds__(kWarps * 32, 3)
+__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm)
 k_query(const TableView t, const QueryArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -176,36 +207,44 @@ k_query(const TableView t, const QueryArgs a)
 #pragma unroll
         for (int s = 0; s < kAccSlots; s++) { ws.acc_lab[lane][s] = kAccEmpty; ws.acc_cnt[lane][s] = 0; }
         ws.acc_ovf[lane] = 0;
+        if (lane < 2) ws.nq[lane] = 0;
         __syncwarp();
 
-        int done = 0, long_tile = 0;
-        while (done < cnt) {
+        int done = 0, long_tile = 0, qsel = 0;
+        for (;;) {
+            const int n_it = (int)*(volatile uint32_t*)&ws.nq[qsel];       // items carried over from the previous tile
+            if (done >= cnt && n_it == 0) break;
+            const Item* qin = ws.items[qsel];
+            Item* qout = ws.items[qsel ^ 1];
+
             // ---- tile: which (read, segment) does each lane work on ---------------------------
-            const int nseg_first = __shfl_sync(FULL, nseg_mine, done);
-            int src, seg, n_fin;                     // holder lane of my read, my segment, reads finished by this tile
-            bool active;
-            if (nseg_first > 32) {                   // long read: the whole warp, several tiles
-                src = done; seg = long_tile * 32 + lane; active = seg < nseg_first;
-                long_tile++;
-                n_fin = long_tile * 32 >= nseg_first ? 1 : 0;
-                if (n_fin) long_tile = 0;
-            } else {                                 // pack as many consecutive reads as fit in 32 lanes
-                const bool cand = lane >= done && lane < cnt;
-                int incl = cand ? nseg_mine : 0;
+            int src = 0, seg = 0, n_fin = 0;        // holder lane of my read, my segment, reads whose positions end here
+            bool active = false;
+            if (done < cnt) {
+                const int nseg_first = __shfl_sync(FULL, nseg_mine, done);
+                if (nseg_first > 32) {               // long read: the whole warp, several tiles
+                    src = done; seg = long_tile * 32 + lane; active = seg < nseg_first;
+                    long_tile++;
+                    n_fin = long_tile * 32 >= nseg_first ? 1 : 0;
+                    if (n_fin) long_tile = 0;
+                } else {                             // pack as many consecutive reads as fit in 32 lanes
+                    const bool cand = lane >= done && lane < cnt;
+                    int incl = cand ? nseg_mine : 0;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
-                const bool fits = cand && incl <= 32;
-                n_fin = __popc(__ballot_sync(FULL, fits));
-                const int used = __shfl_sync(FULL, incl, done + n_fin - 1);
-                const bool owner = fits && nseg_mine > 0;
-                const uint32_t startmask = __reduce_or_sync(FULL, owner ? (1u << (incl - nseg_mine)) : 0u);
-                const uint32_t nz = __ballot_sync(FULL, owner);
-                active = lane < used;
-                const int idx = __popc(startmask & (lt_mask | (1u << lane)));          // reads starting at or before my lane
-                src = active ? __fns(nz, 0, idx) : done;
-                if (src < 0 || src > 31) src = done;
-                const int a0 = __shfl_sync(FULL, incl - nseg_mine, src);
-                seg = lane - a0;
+                    for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+                    const bool fits = cand && incl <= 32;
+                    n_fin = __popc(__ballot_sync(FULL, fits));
+                    const int used = __shfl_sync(FULL, incl, done + n_fin - 1);
+                    const bool owner = fits && nseg_mine > 0;
+                    const uint32_t startmask = __reduce_or_sync(FULL, owner ? (1u << (incl - nseg_mine)) : 0u);
+                    const uint32_t nz = __ballot_sync(FULL, owner);
+                    active = lane < used;
+                    const int idx = __popc(startmask & (lt_mask | (1u << lane)));      // reads starting at or before my lane
+                    src = active ? __fns(nz, 0, idx) : done;
+                    if (src < 0 || src > 31) src = done;
+                    const int a0 = __shfl_sync(FULL, incl - nseg_mine, src);
+                    seg = lane - a0;
+                }
             }
             const uint32_t rbeg = __shfl_sync(FULL, beg_mine, src);
             const int rnsl = __shfl_sync(FULL, nsl_mine, src);
@@ -248,8 +287,28 @@ k_query(const TableView t, const QueryArgs a)
             int off = my_lines;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL, off, d); if (lane >= d) off += v; }
-            const int total_lines = __shfl_sync(FULL, off, 31);
+            const int pos_lines = __shfl_sync(FULL, off, 31);
             off -= my_lines;                          // exclusive
+
+            // ---- carried items: the next line of their probe sequence --------------------------
+            // item j is handled by lane j & 31 in row j >> 5; items of one run are adjacent in the queue
+            uint32_t it_line[kItemRows]; int it_slot[kItemRows]; uint32_t it_start = 0;
+            int item_lines = 0;
+#pragma unroll
+            for (int r = 0; r < kItemRows; r++) {
+                const int j = r * 32 + lane;
+                bool st = false;
+                it_line[r] = kNoLine;
+                if (j < n_it) {
+                    it_line[r] = hop_line(qin[j].home, qin[j].hop, n_lines);
+                    st = j == 0 || hop_line(qin[j - 1].home, qin[j - 1].hop, n_lines) != it_line[r];
+                }
+                const uint32_t b = __ballot_sync(FULL, st);
+                it_slot[r] = pos_lines + item_lines + __popc(b & (lt_mask | (1u << lane))) - 1;
+                if (st) it_start |= 1u << r;
+                item_lines += __popc(b);
+            }
+            const int total_lines = pos_lines + item_lines;
             const int n_stage = min(total_lines, kLinesMax);
 
             // ---- phase B: one 128-byte bulk copy per run into the staging area ---------------
@@ -265,41 +324,34 @@ k_query(const TableView t, const QueryArgs a)
                                          :: "r"(lines_a + slot * kLineStride), "l"(t.sectors + 4ull * line[i]), "r"(bar_a) : "memory");
                     }
                 }
+#pragma unroll
+                for (int r = 0; r < kItemRows; r++) {
+                    if (((it_start >> r) & 1u) && it_slot[r] < kLinesMax)
+                        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 128, [%2];"
+                                     :: "r"(lines_a + it_slot[r] * kLineStride), "l"(t.sectors + 4ull * it_line[r]), "r"(bar_a) : "memory");
+                }
                 uint32_t ok = 0;
                 while (!ok)
                     asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
                                  : "=r"(ok) : "r"(bar_a), "r"(parity) : "memory");
                 parity ^= 1u;
             }
-            if (STATS) st_lines += my_lines;
+            if (STATS) st_lines += my_lines + __popc(it_start);
 
             // ---- phase C: probes from shared memory, votes ------------------------------------
-            uint32_t cur_lab = kLabelNone, cur_cnt = 0;
+            uint32_t cur_lab = kLabelNone, cur_cnt = 0, pend = 0;
 #pragma unroll
             for (int i = 0; i < kSeg; i++) {
                 if ((vm >> i) & 1u) {
                     const int slot = off + __popc(starts & ((2u << i) - 1u)) - 1;
-                    const uint32_t sec = sector_of(cn[i]);
-                    uint32_t lab = kLabelNone, extra = 0;
+                    uint32_t lab = kLabelNone, nsec = 4;
                     if (slot < kLinesMax) {
-                        const uint32_t base = lines_a + slot * kLineStride;
-                        const uint64_t pb = pass_bit(cn[i]);
-                        int q = 0;
-                        for (;;) {                   // the four sectors of the home line, cyclically, in shared memory
-                            const uint32_t p = base + ((sec + q) & 3u) * 32;
-                            uint64_t e[4];
-                            asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(e[0]), "=l"(e[1]) : "r"(p));
-                            asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(e[2]), "=l"(e[3]) : "r"(p + 16));
-                            lab = match_sector(e, cn[i]);
-                            if (lab != kLabelNone || !(e[3] & pb)) break;
-                            if (++q == 4) { lab = probe_chain(t, line[i], sec, cn[i], 4, STATS ? &extra : nullptr); break; }
-                        }
-                        if (STATS) extra += q < 4 ? q : 3;
+                        if (probe_staged(lines_a + slot * kLineStride, cn[i], lab)) pend |= 1u << i;
                     } else {
-                        lab = probe_chain(t, line[i], sec, cn[i], 0, STATS ? &extra : nullptr);
-                        if (STATS) extra--;
+                        nsec = 0;
+                        lab = probe_chain(t, line[i], cn[i], 0, STATS ? &nsec : nullptr);
                     }
-                    if (STATS) { st_lookups++; st_sectors += 1 + extra; }
+                    if (STATS) { st_lookups++; st_sectors += nsec; }
                     if (lab < kLabelTomb) {
                         if (lab == cur_lab) cur_cnt++;
                         else { if (cur_cnt) acc_add(ws, src, cur_lab, cur_cnt); cur_lab = lab; cur_cnt = 1; }
@@ -307,51 +359,118 @@ k_query(const TableView t, const QueryArgs a)
                 }
             }
             if (cur_cnt) acc_add(ws, src, cur_lab, cur_cnt);
-            __syncwarp();
 
-            // ---- results of the reads this tile completed (src/CuClarkDB.cu:1370-1405) ---------
-            if (lane >= done && lane < done + n_fin) {
-                uint32_t sum = 0, k1 = 0, k2 = 0; int nnz = 0;
-                for (int s = 0; s < kAccSlots; s++) {
-                    const uint32_t lab = ws.acc_lab[lane][s];
-                    if (lab == kAccEmpty) break;
-                    const uint32_t c16 = ws.acc_cnt[lane][s] & 0xFFFFu;      // reference counters are u16
-                    if (!c16) continue;
-                    nnz++; sum += c16;
-                    const uint32_t key = (c16 << 16) | (0xFFFFu - lab);
-                    if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
-                }
-                uint16_t* o5 = a.out5 + (size_t)r_mine * 5;
-                o5[0] = (uint16_t)sum;
-                o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
-                o5[2] = (uint16_t)(k1 >> 16);
-                o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
-                o5[4] = (uint16_t)(k2 >> 16);
-                if (a.rows) {
-                    uint16_t* row = a.rows + (size_t)r_mine * a.row_stride;
-                    const int fit = (a.row_stride - 1) / 2;
-                    row[0] = (uint16_t)min(nnz, fit);
-                    for (int s = 0; s < kAccSlots; s++) {
-                        const uint32_t lab = ws.acc_lab[lane][s];
-                        if (lab == kAccEmpty) break;
-                        const uint32_t c16 = ws.acc_cnt[lane][s] & 0xFFFFu;
-                        if (!c16) continue;
-                        int rank = 0;
-                        for (int u = 0; u < kAccSlots; u++) {
-                            const uint32_t l2 = ws.acc_lab[lane][u];
-                            if (l2 != kAccEmpty && (ws.acc_cnt[lane][u] & 0xFFFFu) && l2 < lab) rank++;
+            // carried items against the line they asked for
+            uint32_t requeue = 0;
+#pragma unroll
+            for (int r = 0; r < kItemRows; r++) {
+                const int j = r * 32 + lane;
+                if (j < n_it) {
+                    const Item it = qin[j];
+                    uint32_t lab = kLabelNone, nsec = 4;
+                    if (it_slot[r] < kLinesMax) {
+                        if (probe_staged(lines_a + it_slot[r] * kLineStride, it.c, lab)) {
+                            if (it.hop + 1 < kMaxHops) requeue |= 1u << r;
                         }
-                        if (rank < fit) { row[1 + 2 * rank] = (uint16_t)lab; row[2 + 2 * rank] = (uint16_t)c16; }
+                    } else {
+                        nsec = 0;
+                        lab = probe_chain(t, it.home, it.c, it.hop, STATS ? &nsec : nullptr);
                     }
-                }
-                if (ws.acc_ovf[lane] && a.ovf_list) {
-                    const uint32_t slot = atomicAdd(a.ovf_count, 1u);
-                    a.ovf_list[slot] = r_mine;
+                    if (STATS) st_sectors += nsec;
+                    if (lab < kLabelTomb) acc_add(ws, it.rid, lab, 1);
                 }
             }
+
+            // ---- queue for the next tile: my unresolved positions (lane-major, so the k-mers of one
+            //      run stay adjacent), then the items that have to hop again ----------------------
+            const int my_pend = __popc(pend);
+            int poff = my_pend;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL, poff, d); if (lane >= d) poff += v; }
+            const int pos_items = __shfl_sync(FULL, poff, 31);
+            poff -= my_pend;
+#pragma unroll
+            for (int i = 0; i < kSeg; i++) {
+                if ((pend >> i) & 1u) {
+                    const int idx = poff + __popc(pend & ((1u << i) - 1u));
+                    if (idx < kQueue) {
+                        Item it; it.c = cn[i]; it.home = line[i]; it.hop = 1; it.rid = (uint8_t)src; it.s0 = 0;
+                        qout[idx] = it;
+                    } else {                         // queue full: finish this one in global memory now
+                        uint32_t nsec = 0;
+                        const uint32_t lab = probe_chain(t, line[i], cn[i], 1, STATS ? &nsec : nullptr);
+                        if (STATS) st_sectors += nsec;
+                        if (lab < kLabelTomb) acc_add(ws, src, lab, 1);
+                    }
+                }
+            }
+            int n_out = pos_items;
+#pragma unroll
+            for (int r = 0; r < kItemRows; r++) {
+                const bool rq = (requeue >> r) & 1u;
+                const uint32_t b = __ballot_sync(FULL, rq);
+                if (rq) {
+                    Item it = qin[r * 32 + lane];
+                    it.hop++;
+                    const int idx = n_out + __popc(b & lt_mask);
+                    if (idx < kQueue) qout[idx] = it;
+                    else {
+                        uint32_t nsec = 0;
+                        const uint32_t lab = probe_chain(t, it.home, it.c, it.hop, STATS ? &nsec : nullptr);
+                        if (STATS) st_sectors += nsec;
+                        if (lab < kLabelTomb) acc_add(ws, it.rid, lab, 1);
+                    }
+                }
+                n_out += __popc(b);
+            }
+            __syncwarp();
+            if (lane == 0) { ws.nq[qsel] = 0; ws.nq[qsel ^ 1] = (uint32_t)min(n_out, kQueue); }
+            qsel ^= 1;
             done += n_fin;
             __syncwarp();
         }
+
+        // ---- results of the chunk's reads (src/CuClarkDB.cu:1370-1405) --------------------------
+        if (lane < cnt) {
+            uint32_t sum = 0, k1 = 0, k2 = 0; int nnz = 0;
+            for (int s = 0; s < kAccSlots; s++) {
+                const uint32_t lab = ws.acc_lab[lane][s];
+                if (lab == kAccEmpty) break;
+                const uint32_t c16 = ws.acc_cnt[lane][s] & 0xFFFFu;      // reference counters are u16
+                if (!c16) continue;
+                nnz++; sum += c16;
+                const uint32_t key = (c16 << 16) | (0xFFFFu - lab);
+                if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
+            }
+            uint16_t* o5 = a.out5 + (size_t)r_mine * 5;
+            o5[0] = (uint16_t)sum;
+            o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
+            o5[2] = (uint16_t)(k1 >> 16);
+            o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
+            o5[4] = (uint16_t)(k2 >> 16);
+            if (a.rows) {
+                uint16_t* row = a.rows + (size_t)r_mine * a.row_stride;
+                const int fit = (a.row_stride - 1) / 2;
+                row[0] = (uint16_t)min(nnz, fit);
+                for (int s = 0; s < kAccSlots; s++) {
+                    const uint32_t lab = ws.acc_lab[lane][s];
+                    if (lab == kAccEmpty) break;
+                    const uint32_t c16 = ws.acc_cnt[lane][s] & 0xFFFFu;
+                    if (!c16) continue;
+                    int rank = 0;
+                    for (int u = 0; u < kAccSlots; u++) {
+                        const uint32_t l2 = ws.acc_lab[lane][u];
+                        if (l2 != kAccEmpty && (ws.acc_cnt[lane][u] & 0xFFFFu) && l2 < lab) rank++;
+                    }
+                    if (rank < fit) { row[1 + 2 * rank] = (uint16_t)lab; row[2 + 2 * rank] = (uint16_t)c16; }
+                }
+            }
+            if (ws.acc_ovf[lane] && a.ovf_list) {
+                const uint32_t slot = atomicAdd(a.ovf_count, 1u);
+                a.ovf_list[slot] = r_mine;
+            }
+        }
+        __syncwarp();
     }
     if (STATS) {
 #pragma unroll
@@ -376,7 +495,7 @@ static int launch_one(const TableView& t, const QueryArgs& a, cudaStream_t s)
     }
     const uint32_t n_chunks = (a.n_reads + 31u) / 32u;
     uint32_t ctas = (n_chunks + kWarps - 1) / kWarps;
-    const uint32_t cap = 148u * 3u;                 // 3 resident CTAs per SM, warps stride over chunks of 32 reads
+    const uint32_t cap = 148u * kCtasPerSm;         // resident CTAs, warps stride over chunks of 32 reads
     if (ctas > cap) ctas = cap;
     k_query<W, STATS><<<ctas, kWarps * 32, smem, s>>>(t, a);
     return (int)cudaGetLastError();

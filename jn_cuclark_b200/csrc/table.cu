@@ -53,7 +53,7 @@ static int grid_for(uint64_t n, int block)
 int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s)
 {
     if (k < 2 || k > 32) return -10;
-    if (!(load_factor > 0.0 && load_factor <= 0.9)) load_factor = 0.5;
+    if (!(load_factor > 0.0 && load_factor <= 0.9)) load_factor = 0.4;
     uint64_t n_lines = (uint64_t)((double)expected_entries / (4.0 * kSectorKeys * load_factor)) + 1;
     if (n_lines < 16) n_lines = 16;
     if (n_lines > 0xFFFFFF00ull) return -14;                // line index is 32 bits (> 500 GB of table)

@@ -15,13 +15,13 @@
 //             + 3 labels (u16; 0xFFFF unset, 0xFFFE = seen under two labels) + u16 meta
 //   home    = 4 * line_of(min over the k-mer's m-mers of phi64(canonical m-mer)) + sector_of(c)
 //
-// Keys are stored whole, so membership is exact.  Probe sequence of a k-mer: the
-// four sectors of its home line, cyclically from sector_of(c); then the four
-// sectors of hop_line(home, 1), hop_line(home, 2), ... (all k-mers of a line hop
-// together, so a run still needs one line per hop).  The 16 meta bits of a sector
-// are a Bloom filter of the keys that had to pass it when it was full
-// (bit pass_bit(c)): a lookup goes on to the next sector only if its bit is set,
-// so a miss usually stops at the first sector.
+// Keys are stored whole, so membership is exact.  A k-mer lives in any of the 12
+// slots of its home line (insertion starts at sector_of(c) to spread contention);
+// when the line is full it goes to hop_line(home, 1), hop_line(home, 2), ... (all
+// k-mers of a line hop together, so a run still needs one line per hop).  The
+// 4 x 16 meta bits of a line are a Bloom filter of the keys that had to leave it
+// (bit leave_bit(c)): a lookup that does not find its key in a line goes on only
+// if its bit is set, so a miss usually costs one line.
 #pragma once
 #include <cuda_runtime.h>
 #include "kmer.cuh"
@@ -35,8 +35,8 @@ struct TableView {
 
 struct alignas(32) Sector { uint64_t key[3]; uint64_t lm; };   // lm = lab0 | lab1<<16 | lab2<<32 | meta<<48
 constexpr uint64_t kLmInit = 0x0000FFFFFFFFFFFFull;
-// meta bit of key c in the filter of passers
-__device__ __forceinline__ uint64_t pass_bit(uint64_t c) { return 1ull << (48 + (uint32_t)((c * 0xD6E8FEB86659FD93ull) >> 60)); }
+// bit (0..63) of key c in the line's filter of leavers: sector bit>>4, meta bit bit&15
+__device__ __forceinline__ uint32_t leave_bit(uint64_t c) { return (uint32_t)((c * 0xD6E8FEB86659FD93ull) >> 58); }
 
 __device__ __forceinline__ void load_bucket(const ulonglong4* p, uint64_t (&e)[4])
 {
@@ -55,25 +55,31 @@ __device__ __forceinline__ uint32_t match_sector(const uint64_t (&e)[4], uint64_
     return lab;
 }
 
-// sector index of step j of the probe sequence (home line, first sector s0)
-__device__ __forceinline__ uint64_t probe_sector(const HashParams& hp, uint32_t home, uint32_t s0, int j)
+__device__ __forceinline__ uint32_t probe_line(const HashParams& hp, uint32_t home, int h)
 {
-    const int h = j >> 2;
-    const uint32_t line = h == 0 ? home : hop_line(home, h, hp.n_lines);
-    return 4ull * line + ((s0 + (uint32_t)j) & 3u);
+    return h == 0 ? home : hop_line(home, h, hp.n_lines);
 }
 
-// Walk the probe sequence of c in global memory from step j0.  Returns the raw label
+// Walk the probe sequence of c in global memory from hop h0.  Returns the raw label
 // (target, kLabelTomb) or kLabelNone.  probes (optional) counts sectors read.
-static __device__ __noinline__ uint32_t probe_chain(const TableView& t, uint32_t home, uint32_t s0, uint64_t c, int j0, uint32_t* probes)
+static __device__ __noinline__ uint32_t probe_chain(const TableView& t, uint32_t home, uint64_t c, int h0, uint32_t* probes)
 {
-    for (int j = j0; j < 4 * kMaxHops; j++) {
-        uint64_t e[4];
-        load_bucket(t.sectors + probe_sector(t.hp, home, s0, j), e);
-        if (probes) (*probes)++;
-        uint32_t lab = match_sector(e, c);
+    const uint32_t lb = leave_bit(c);
+    for (int h = h0; h < kMaxHops; h++) {
+        const ulonglong4* L = t.sectors + 4ull * probe_line(t.hp, home, h);
+        uint64_t e[4][4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) load_bucket(L + q, e[q]);
+        if (probes) (*probes) += 4;
+        uint32_t lab = kLabelNone; uint64_t meta = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint32_t l = match_sector(e[q], c);
+            if (l != kLabelNone) lab = l;
+            if ((lb >> 4) == (uint32_t)q) meta = e[q][3] >> 48;
+        }
         if (lab != kLabelNone) return lab;
-        if (!(e[3] & pass_bit(c))) return kLabelNone;
+        if (!((meta >> (lb & 15u)) & 1ull)) return kLabelNone;
     }
     return kLabelNone;
 }
@@ -86,7 +92,7 @@ __device__ __forceinline__ uint32_t home_line(const HashParams& hp, uint64_t can
 // generic lookup (dense path, tests): target label or kLabelNone
 __device__ __forceinline__ uint32_t lookup(const TableView& t, uint64_t canon)
 {
-    uint32_t lab = probe_chain(t, home_line(t.hp, canon), sector_of(canon), canon, 0, nullptr);
+    uint32_t lab = probe_chain(t, home_line(t.hp, canon), canon, 0, nullptr);
     return lab >= kLabelTomb ? kLabelNone : lab;
 }
 
@@ -122,26 +128,29 @@ __device__ __forceinline__ void merge_label(uint64_t* lm, int j, uint32_t label,
 static __device__ __noinline__ void insert_one(uint64_t* sectors, uint32_t* status, unsigned long long* counts,
                                                const HashParams hp, uint64_t canon, uint32_t label)
 {
-    const uint32_t home = home_line(hp, canon), s0 = sector_of(canon);
-    for (int d = 0; d < 4 * kMaxHops; d++) {
-        uint64_t* sec = sectors + probe_sector(hp, home, s0, d) * 4;
+    const uint32_t home = home_line(hp, canon), s0 = sector_of(canon), lb = leave_bit(canon);
+    for (int h = 0; h < kMaxHops; h++) {
+        uint64_t* line = sectors + 16ull * probe_line(hp, home, h);
+        for (int q = 0; q < 4; q++) {
+            uint64_t* sec = line + 4 * ((s0 + q) & 3u);
 #pragma unroll 1
-        for (int j = 0; j < kSectorKeys; j++) {
-            uint64_t e = ld_volatile(sec + j);
-            if (e == kEmpty) {
-                e = atomicCAS((unsigned long long*)(sec + j), (unsigned long long)kEmpty, (unsigned long long)canon);
+            for (int j = 0; j < kSectorKeys; j++) {
+                uint64_t e = ld_volatile(sec + j);
                 if (e == kEmpty) {
-                    if (d) atomicMax(status + 1, (uint32_t)d);
-                    if (d >= 4) atomicAdd(counts + 3, 1ull);                 // lives outside its home line
-                    atomicAdd(counts + 0, 1ull);
-                    e = canon;
+                    e = atomicCAS((unsigned long long*)(sec + j), (unsigned long long)kEmpty, (unsigned long long)canon);
+                    if (e == kEmpty) {
+                        if (h) { atomicMax(status + 1, (uint32_t)h); atomicAdd(counts + 3, 1ull); }   // lives outside its home line
+                        atomicAdd(counts + 0, 1ull);
+                        e = canon;
+                    }
                 }
+                if (e == canon) { merge_label(sec + 3, j, label, counts); return; }
             }
-            if (e == canon) { merge_label(sec + 3, j, label, counts); return; }
         }
-        // sector full and key absent: later lookups have to go on from here
-        const uint64_t pb = pass_bit(canon);
-        if (!(ld_volatile(sec + 3) & pb)) atomicOr((unsigned long long*)(sec + 3), (unsigned long long)pb);
+        // line full and key absent: later lookups of this key have to go on from here
+        uint64_t* lm = line + 4 * (lb >> 4) + 3;
+        const uint64_t bit = 1ull << (48 + (lb & 15u));
+        if (!(ld_volatile(lm) & bit)) atomicOr((unsigned long long*)lm, (unsigned long long)bit);
     }
     atomicExch(status + 0, 1u);                            // probe sequence exhausted
 }
