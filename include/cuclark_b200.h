@@ -39,25 +39,23 @@ typedef struct ccb_config {
     int    n_targets;     /* number of targets = labels 0..n_targets-1 (<= 65534)           */
     int    max_hits;      /* MAXHITS of the variant: 15 full / 23 light (parameters.hh:44)  */
     int    n_slots;       /* batch slots (reference: -b batches); >= 1, 2+ overlaps copies  */
-    double load_factor;   /* table fill (entries / slots), 0 = default 0.4                  */
+    double load_factor;   /* table fill, 0 = default 0.5                                    */
     int    verbose;
 } ccb_config;
 
 typedef struct ccb_db_info {
     uint64_t entries;       /* occupied slots (incl. tombstones)        */
-    uint64_t buckets;       /* home sectors (32 B, 3 entries each)      */
+    uint64_t buckets;       /* home buckets                             */
     uint64_t bytes;         /* device bytes of the table                */
     uint64_t tombstones;    /* k-mers seen under more than one label    */
-    uint32_t max_displacement; /* longest probe sequence, in sectors        */
-    uint64_t hopped;        /* entries stored outside their home line   */
+    uint32_t max_displacement;
 } ccb_db_info;
 
 typedef struct ccb_stats {
     uint64_t reads;         /* reads submitted                          */
     uint64_t lookups;       /* k-mers probed   (only with CCB_STATS)    */
-    uint64_t sectors;       /* 32-byte table sectors examined (CCB_STATS) */
+    uint64_t sectors;       /* 32-byte table sectors read (CCB_STATS)   */
     uint64_t dense_reads;   /* reads re-done by the dense exact path    */
-    uint64_t lines;         /* 128-byte table lines fetched (CCB_STATS) */
 } ccb_stats;
 
 enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4 };
@@ -101,7 +99,7 @@ int  ccb_sync(ccb_handle* h);
 /* Device-resident variant of queryBatch for callers that already hold the batch
  * in HBM (multi-GPU pipelines, kernel-only timing): all pointers are device
  * pointers, stream is a cudaStream_t (NULL = default stream).  d_rows may be NULL.
- * d_stats (optional) = 4 x u64 device counters {lookups, sectors, lines, spare}, accumulated. */
+ * d_stats (optional) = 2 x u64 device counters {lookups, sectors}, accumulated. */
 int  ccb_query_device(ccb_handle* h, const void* d_offsets, const void* d_containers,
                       uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
                       int flags, void* stream);

@@ -47,7 +47,7 @@ extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
     h->cfg = *cfg;
     if (h->cfg.n_slots < 1) h->cfg.n_slots = 1;
     if (h->cfg.max_hits < 1) h->cfg.max_hits = 15;
-    if (h->cfg.load_factor <= 0) h->cfg.load_factor = 0.4;
+    if (h->cfg.load_factor <= 0) h->cfg.load_factor = 0.5;
     h->row_stride = 2 * h->cfg.max_hits + 2;
     if (cudaSetDevice(cfg->device) != cudaSuccess || cudaStreamCreateWithFlags(&h->db_stream, cudaStreamNonBlocking) != cudaSuccess) {
         ccb_fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));
@@ -162,13 +162,13 @@ extern "C" int ccb_db_end(ccb_handle* h)
 {
     if (!h || !h->db_building) return ccb_fail(h, -1, "ccb_db_end: no table under construction");
     USE_DEV(h);
-    uint32_t st[2] = {0, 0}; unsigned long long cnt[4] = {0, 0, 0, 0};
+    uint32_t st[2] = {0, 0}; unsigned long long cnt[3] = {0, 0, 0};
     cudaMemcpyAsync(st, h->table.d_status, sizeof st, cudaMemcpyDeviceToHost, h->db_stream);
     cudaMemcpyAsync(cnt, h->table.d_counts, sizeof cnt, cudaMemcpyDeviceToHost, h->db_stream);
     int rc = table_finalize(h->table, h->db_stream);
     h->db_building = false;
     h->max_disp = st[1]; h->tombstones = cnt[2];
-    if (rc == -13) { table_destroy(h->table); return ccb_fail(h, rc, "k-mer table too full: a probe sequence exceeded %d lines; lower load_factor", kMaxHops); }
+    if (rc == -13) { table_destroy(h->table); return ccb_fail(h, rc, "k-mer table too full: an entry moved more than %d buckets; lower load_factor", kMaxDisp); }
     if (rc) { table_destroy(h->table); return ccb_fail(h, rc, "table finalize failed (%d): %s", rc, rc > 0 ? cudaGetErrorString((cudaError_t)rc) : ""); }
     h->db_ready = true;
     return 0;
@@ -177,8 +177,8 @@ extern "C" int ccb_db_end(ccb_handle* h)
 extern "C" int ccb_db_get_info(const ccb_handle* h, ccb_db_info* info)
 {
     if (!h || !info || !h->db_ready) return -1;
-    info->entries = h->table.n_inserted; info->buckets = h->table.n_home; info->bytes = h->table.bytes();
-    info->tombstones = h->tombstones; info->max_displacement = h->max_disp; info->hopped = h->table.n_hopped;
+    info->entries = h->table.n_inserted; info->buckets = h->table.nb; info->bytes = h->table.bytes();
+    info->tombstones = h->tombstones; info->max_displacement = h->max_disp;
     return 0;
 }
 
@@ -285,11 +285,11 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
         ok(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         ok(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming | cudaEventBlockingSync));
         ok(cudaMallocHost(&s.h_offsets, so)); ok(cudaMallocHost(&s.h_cont, sc)); ok(cudaMallocHost(&s.h_final5, sf));
-        ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 32));
+        ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 16));
         ok(cudaMalloc(&s.d_offsets, so)); ok(cudaMalloc(&s.d_cont, sc)); ok(cudaMalloc(&s.d_final5, sf));
         ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 4)); ok(cudaMalloc(&s.d_ovf_count, 4));
         ok(cudaMalloc(&s.d_dense_scratch, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
-        ok(cudaMalloc(&s.d_stats, 32));
+        ok(cudaMalloc(&s.d_stats, 16));
         if (extended) { ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
         if (e != cudaSuccess) {
             free_slots(h);
@@ -297,7 +297,7 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
                 return ccb_fail(h, (int)e, "ERROR: Out of GPU memory.\nPlease increase the number of batches (-b <numberofbatches>).");
             return ccb_fail(h, (int)e, "batch allocation failed: %s", cudaGetErrorString(e));
         }
-        *s.h_ovf_count = 0; s.h_stats[0] = s.h_stats[1] = s.h_stats[2] = s.h_stats[3] = 0;
+        *s.h_ovf_count = 0; s.h_stats[0] = s.h_stats[1] = 0;
     }
     return 0;
 }
@@ -351,13 +351,13 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
     a.offsets = s.d_offsets; a.containers = s.d_cont; a.n_reads = n_reads;
     a.out5 = s.d_final5; a.rows = (flags & CCB_EXTENDED) ? s.d_rows : nullptr; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr;
-    if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 32, s.stream));
+    if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 16, s.stream));
     int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, s.d_dense_scratch, flags, s.stream);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     CU(h, cudaMemcpyAsync(s.h_final5, s.d_final5, (size_t)n_reads * 10, cudaMemcpyDeviceToHost, s.stream));
     if (flags & CCB_EXTENDED) CU(h, cudaMemcpyAsync(s.h_rows, s.d_rows, (size_t)n_reads * h->row_stride * 2, cudaMemcpyDeviceToHost, s.stream));
     CU(h, cudaMemcpyAsync(s.h_ovf_count, s.d_ovf_count, 4, cudaMemcpyDeviceToHost, s.stream));
-    if (flags & CCB_STATS) CU(h, cudaMemcpyAsync(s.h_stats, s.d_stats, 32, cudaMemcpyDeviceToHost, s.stream));
+    if (flags & CCB_STATS) CU(h, cudaMemcpyAsync(s.h_stats, s.d_stats, 16, cudaMemcpyDeviceToHost, s.stream));
     CU(h, cudaEventRecord(s.done, s.stream));
     s.in_flight = true;
     return 0;
@@ -368,7 +368,7 @@ static void harvest(ccb_handle* h, Slot& s)
     std::lock_guard<std::mutex> g(h->mu);          // slots may be waited on from several host threads
     h->stats.reads += s.n_reads;
     h->stats.dense_reads += (s.flags & CCB_FORCE_DENSE) ? s.n_reads : *s.h_ovf_count;
-    if (s.flags & CCB_STATS) { h->stats.lookups += s.h_stats[0]; h->stats.sectors += s.h_stats[1]; h->stats.lines += s.h_stats[2]; }
+    if (s.flags & CCB_STATS) { h->stats.lookups += s.h_stats[0]; h->stats.sectors += s.h_stats[1]; }
     s.in_flight = false;
 }
 

@@ -19,13 +19,13 @@
 
 namespace ccb {
 
-// Labels 0..0xFFFD are targets.
-constexpr uint64_t kEmpty      = ~0ull;     // never a canonical k-mer (poly-A is not canonical; k<32 values are < 2^2k)
-constexpr uint32_t kLabelTomb  = 0xFFFEu;   // k-mer seen under >1 label (not discriminative)
-constexpr uint32_t kLabelNone  = 0xFFFFu;
-constexpr int      kSectorKeys = 3;         // 3 x (8 B key + 2 B label) + 2 B meta = one 32-byte sector
-constexpr int      kMaxHops    = 24;        // lines a probe sequence may visit (4 sectors each)
-constexpr int      kWin        = 12;        // minimizer window (m-mers per k-mer) when k >= kWin + 11
+// 64-bit entry = key48 << 16 | label.  Labels 0..0xFFFD are targets.
+constexpr uint64_t kEmpty     = ~0ull;     // never a valid entry: label 0xFFFF is reserved
+constexpr uint32_t kLabelTomb = 0xFFFEu;   // k-mer seen under >1 label (not discriminative)
+constexpr uint32_t kLabelNone = 0xFFFFu;
+constexpr int      kSlots     = 4;         // 4 x 8 B = one 32-byte DRAM sector
+constexpr int      kMaxDisp   = 62;        // max buckets an entry may sit past its home
+constexpr int      kPadBuckets = 64;       // physical buckets after the last home bucket (no wrap)
 
 CCB_HD int code_of(unsigned char c)
 {   // >=0: x-encoding code; -1: anything else
@@ -57,54 +57,48 @@ CCB_HD uint64_t canonical(uint64_t x, int k)
     return x < r ? x : r;
 }
 
-// ---- minimizer addressing (DESIGN.md "Table v2") ---------------------------------
-// m-mer length: k >= 23 -> m = k - 11 (window of 12 m-mers); shorter k-mers are their own minimizer.
-CCB_HD int mmer_len(int k) { return k >= kWin + 11 ? k - (kWin - 1) : k; }
-
-// order/identity hash of a canonical m-mer: odd multiply mod 2^64 (injective), compared as u64
-CCB_HD uint64_t phi64(uint64_t cm) { return cm * 0x9E3779B97F4A7C15ull; }
-
-// min over the m-mers of a k-mer of phi64(canonical m-mer); identical for a k-mer and its reverse complement
-CCB_HD uint64_t minimizer_phi(uint64_t x, int k, int m)
+// Bijection on [0, 2^(2k)): xorshift and odd multiplies, all reduced mod 2^(2k).
+// Being invertible is what lets the table drop the bits implied by the bucket.
+CCB_HD uint64_t mix2k(uint64_t c, int k, uint64_t mask)
 {
-    const uint64_t mm = kmask(m);
-    uint64_t best = ~0ull;
-    for (int j = 0; j + m <= k; j++) {
-        uint64_t f = (x >> (2 * (k - m - j))) & mm;
-        uint64_t r = revcomp(f, m);
-        uint64_t p = phi64(f < r ? f : r);
-        best = p < best ? p : best;
-    }
-    return best;
-}
-
-CCB_HD uint32_t mulhi32(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }
-
-// 128-byte line of the table that is home to every k-mer whose minimizer hashes to `phi`
-CCB_HD uint32_t line_of(uint64_t phi, uint32_t n_lines)
-{
-    uint64_t z = (phi ^ (phi >> 29)) * 0xBF58476D1CE4E5B9ull;     // the minimum is concentrated near 0: remix
-    return mulhi32((uint32_t)(z >> 32), n_lines);
-}
-
-// h-th line (h >= 1) of the probe sequence of the k-mers whose home line is `home`
-CCB_HD uint32_t hop_line(uint32_t home, int h, uint32_t n_lines)
-{
-    uint64_t z = (((uint64_t)home << 8) | (uint32_t)h) * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 32)) * 0xBF58476D1CE4E5B9ull;
-    return mulhi32((uint32_t)(z >> 32), n_lines);
-}
-
-// sector (0..3) of the home line where the probe sequence of canonical k-mer c starts
-CCB_HD uint32_t sector_of(uint64_t c)
-{
-    return ((uint32_t)c * 0x9E3779B1u + (uint32_t)(c >> 32) * 0x85EBCA77u) >> 30;
+    uint64_t h = c;
+    h ^= h >> k;
+    h = (h * 0xff51afd7ed558ccdull) & mask;
+    h ^= h >> k;
+    h = (h * 0xc4ceb9fe1a85ec53ull) & mask;
+    h ^= h >> k;
+    return h;
 }
 
 struct HashParams {
-    uint32_t n_lines;  // home lines (4 sectors each)
-    int      k, m;     // k-mer and minimizer length
-    uint64_t kmsk;     // 2^(2k)-1
+    uint64_t nb;      // number of home buckets
+    uint64_t mask;    // 2^(2k)-1
+    int      k;
+    int      shift;   // 64 - 2k
 };
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ uint64_t mulhi64(uint64_t a, uint64_t b) { return __umul64hi(a, b); }
+#endif
+inline uint64_t mulhi64_host(uint64_t a, uint64_t b) { return (uint64_t)(((unsigned __int128)a * b) >> 64); }
+
+// home bucket = floor(h * nb / 2^(2k)); stored key = low 48 bits of h.
+// (home, key48) determines h as long as nb >= 64 * 2^max(0,2k-48) and no entry
+// sits more than kMaxDisp buckets past its home (DESIGN.md "Table").
+CCB_HD uint64_t home_of(uint64_t h, const HashParams& p)
+{
+#if defined(__CUDA_ARCH__)
+    return mulhi64(h << p.shift, p.nb);
+#else
+    return mulhi64_host(h << p.shift, p.nb);
+#endif
+}
+CCB_HD uint64_t key48_of(uint64_t h) { return h & 0xFFFFFFFFFFFFull; }
+
+inline uint64_t min_buckets_for_k(int k)
+{
+    int extra = 2 * k - 48;
+    return extra > 0 ? (64ull << extra) : 64ull;
+}
 
 }  // namespace ccb

@@ -15,14 +15,14 @@ struct QueryArgs {
     uint16_t*       out5;
     uint16_t*       rows;
     int             row_stride;      // u16 per row
-    // reads that hit more than 8 distinct targets are re-done by the dense kernel
+    // reads that hit more than 32 distinct targets are re-done by the dense kernel
     uint32_t*       ovf_list;
     uint32_t*       ovf_count;
-    // optional accounting [0]=k-mers probed [1]=32-byte table sectors examined [2]=128-byte lines fetched [3] spare
+    // optional accounting [0]=k-mers probed [1]=32-byte sectors read
     unsigned long long* stats;
 };
 
-// fast path (query.cu): minimizer-addressed line staging, several short reads per warp
+// fast path: one warp per read, votes kept in registers
 int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s);
 // exact path for any number of distinct targets: one CTA per listed read, dense
 // per-CTA counters in global scratch (n_scratch_blocks * n_targets u32)

@@ -14,7 +14,7 @@ namespace {
 constexpr int kSeg = 256;   // k-mer start positions per thread
 
 // Every k-mer of every genome -> table (label = genome index % n_labels).
-__global__ void k_synth_db(uint64_t* sectors, uint32_t* status, unsigned long long* counts,
+__global__ void k_synth_db(uint64_t* buckets, uint32_t* flags, uint32_t* status, unsigned long long* counts,
                            HashParams hp, uint64_t seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels)
 {
     const int k = hp.k;
@@ -32,9 +32,9 @@ __global__ void k_synth_db(uint64_t* sectors, uint32_t* status, unsigned long lo
         rc = revcomp(x, k);
         for (uint64_t p = p0; p < p1; p++) {
             uint64_t code = ccb_genome_code(gs, p + k - 1);
-            x = ((x << 2) | code) & hp.kmsk;
+            x = ((x << 2) | code) & hp.mask;
             rc = (rc >> 2) | ((3ull - code) << (2 * (k - 1)));
-            insert_one(sectors, status, counts, hp, x < rc ? x : rc, g % n_labels);
+            insert_one(buckets, flags, status, counts, hp, x < rc ? x : rc, g % n_labels);
         }
     }
 }
@@ -109,7 +109,7 @@ extern "C" int ccb_synth_db(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes,
     int rc = ccb_db_begin(h, total);
     if (rc) return rc;
     Table& t = h->table;
-    k_synth_db<<<148 * 16, 256, 0, h->db_stream>>>((uint64_t*)t.d_sectors, t.d_status, t.d_counts, t.hp,
+    k_synth_db<<<148 * 16, 256, 0, h->db_stream>>>((uint64_t*)t.d_buckets, t.d_flags, t.d_status, t.d_counts, t.hp,
                                                     db_seed, n_genomes, genome_len, n_labels);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_synth_db launch: %s", cudaGetErrorString(e));
@@ -369,8 +369,8 @@ extern "C" int ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, 
     cudaSetDevice(h->cfg.device);
     static unsigned long long* sink = nullptr;
     if (!sink) cudaMalloc(&sink, 8);
-    const ulonglong4* tbl = (const ulonglong4*)h->table.d_sectors;
-    uint64_t n32 = h->table.n_home;
+    const ulonglong4* tbl = (const ulonglong4*)h->table.d_buckets;
+    uint64_t n32 = h->table.nb;
     if (footprint && footprint / 32 < n32) n32 = footprint / 32;
     if (n32 < (1u << 16)) return ccb_fail(h, -43, "ccb_bench_gather: footprint below 2 MiB");
     const int grid = 148 * 8;

@@ -10,21 +10,23 @@ __global__ void k_fill_empty(ulonglong4* b, uint64_t n)
 {
     uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
-    const ulonglong4 v = make_ulonglong4(kEmpty, kEmpty, kEmpty, kLmInit);
+    const ulonglong4 v = make_ulonglong4(kEmpty, kEmpty, kEmpty, kEmpty);
     for (; i < n; i += stride) b[i] = v;
 }
 
-__global__ void k_insert_pairs(uint64_t* sectors, uint32_t* status, unsigned long long* counts, HashParams hp,
+__global__ void k_insert_pairs(uint64_t* buckets, uint32_t* flags, uint32_t* status,
+                               unsigned long long* counts, HashParams hp,
                                const uint64_t* canon, const uint16_t* labels, uint64_t n)
 {
     uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
-    for (; i < n; i += stride) insert_one(sectors, status, counts, hp, canon[i], labels[i]);
+    for (; i < n; i += stride) insert_one(buckets, flags, status, counts, hp, canon[i], labels[i]);
 }
 
 // Reference layout (A9): canonical = key * HTSIZE + bucket (src/hashTable_hh.hh:469).
 template <typename KEY>
-__global__ void k_insert_ref_chunk(uint64_t* sectors, uint32_t* status, unsigned long long* counts, HashParams hp,
+__global__ void k_insert_ref_chunk(uint64_t* buckets, uint32_t* flags, uint32_t* status,
+                                   unsigned long long* counts, HashParams hp,
                                    uint64_t htsize, uint64_t r0, uint32_t nbk,
                                    const uint8_t* sz, const uint32_t* off,
                                    const KEY* keys, const uint16_t* labels)
@@ -36,8 +38,24 @@ __global__ void k_insert_ref_chunk(uint64_t* sectors, uint32_t* status, unsigned
         uint32_t o = off[i];
         for (uint32_t j = 0; j < n; j++) {
             uint64_t c = (uint64_t)keys[o + j] * htsize + (r0 + i);
-            insert_one(sectors, status, counts, hp, c, labels[o + j]);
+            insert_one(buckets, flags, status, counts, hp, c, labels[o + j]);
         }
+    }
+}
+
+// Order the entries of every full bucket so that (e0 > e1) == A, (e2 > e3) == B.
+__global__ void k_finalize(ulonglong4* b, const uint32_t* flags, uint64_t n)
+{
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    for (; i < n; i += stride) {
+        ulonglong4 v = b[i];
+        if (v.w == kEmpty) continue;                         // not full: flags are never set
+        uint32_t f = (flags[i >> 4] >> (2 * (i & 15))) & 3u;
+        bool A = f & 1u, B = f & 2u;
+        if ((v.x > v.y) != A) { unsigned long long t = v.x; v.x = v.y; v.y = t; }
+        if ((v.z > v.w) != B) { unsigned long long t = v.z; v.z = v.w; v.w = t; }
+        b[i] = v;
     }
 }
 
@@ -53,29 +71,33 @@ static int grid_for(uint64_t n, int block)
 int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s)
 {
     if (k < 2 || k > 32) return -10;
-    if (!(load_factor > 0.0 && load_factor <= 0.9)) load_factor = 0.4;
-    uint64_t n_lines = (uint64_t)((double)expected_entries / (4.0 * kSectorKeys * load_factor)) + 1;
-    if (n_lines < 16) n_lines = 16;
-    if (n_lines > 0xFFFFFF00ull) return -14;                // line index is 32 bits (> 500 GB of table)
-    t.n_home = 4 * n_lines;
-    t.n_phys = t.n_home;
-    t.hp.n_lines = (uint32_t)n_lines; t.hp.k = k; t.hp.m = mmer_len(k); t.hp.kmsk = kmask(k);
+    if (!(load_factor > 0.0 && load_factor <= 0.95)) load_factor = 0.5;
+    uint64_t nb = (uint64_t)((double)expected_entries / (kSlots * load_factor)) + 1;
+    uint64_t mn = min_buckets_for_k(k);
+    if (nb < mn) nb = mn;
+    t.nb = nb;
+    t.n_phys = nb + kPadBuckets;
+    t.hp.nb = nb; t.hp.k = k; t.hp.shift = 64 - 2 * k; t.hp.mask = kmask(k);
     t.finalized = false; t.n_inserted = 0;
-    CK(cudaMalloc(&t.d_sectors, t.n_phys * sizeof(Sector)));
+    CK(cudaMalloc(&t.d_buckets, t.n_phys * sizeof(Bucket)));
+    size_t fw = (t.n_phys + 15) / 16;
+    CK(cudaMalloc(&t.d_flags, fw * sizeof(uint32_t)));
     CK(cudaMalloc(&t.d_status, 2 * sizeof(uint32_t)));
-    CK(cudaMalloc(&t.d_counts, 4 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&t.d_counts, 3 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(t.d_flags, 0, fw * sizeof(uint32_t), s));
     CK(cudaMemsetAsync(t.d_status, 0, 2 * sizeof(uint32_t), s));
-    CK(cudaMemsetAsync(t.d_counts, 0, 4 * sizeof(unsigned long long), s));
-    k_fill_empty<<<grid_for(t.n_phys, 256), 256, 0, s>>>((ulonglong4*)t.d_sectors, t.n_phys);
+    CK(cudaMemsetAsync(t.d_counts, 0, 3 * sizeof(unsigned long long), s));
+    k_fill_empty<<<grid_for(t.n_phys, 256), 256, 0, s>>>((ulonglong4*)t.d_buckets, t.n_phys);
     CK(cudaGetLastError());
     return 0;
 }
 
 int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_labels, uint64_t n, cudaStream_t s)
 {
-    if (t.finalized || !t.d_sectors) return -11;
+    if (t.finalized || !t.d_buckets) return -11;
     if (n == 0) return 0;
-    k_insert_pairs<<<grid_for(n, 256), 256, 0, s>>>((uint64_t*)t.d_sectors, t.d_status, t.d_counts, t.hp, d_canon, d_labels, n);
+    k_insert_pairs<<<grid_for(n, 256), 256, 0, s>>>((uint64_t*)t.d_buckets, t.d_flags, t.d_status, t.d_counts,
+                                                    t.hp, d_canon, d_labels, n);
     CK(cudaGetLastError());
     return 0;
 }
@@ -84,16 +106,16 @@ int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
                            const uint8_t* d_sz, const uint32_t* d_off,
                            const void* d_keys, int key_bytes, const uint16_t* d_labels, cudaStream_t s)
 {
-    if (t.finalized || !t.d_sectors) return -11;
+    if (t.finalized || !t.d_buckets) return -11;
     if (nbk == 0) return 0;
     int g = grid_for(nbk, 256);
-    uint64_t* b = (uint64_t*)t.d_sectors;
+    uint64_t* b = (uint64_t*)t.d_buckets;
     if (key_bytes == 2)
-        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint16_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint16_t*)d_keys, d_labels);
     else if (key_bytes == 4)
-        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint32_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint32_t*)d_keys, d_labels);
     else if (key_bytes == 8)
-        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint64_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint64_t*)d_keys, d_labels);
     else return -12;
     CK(cudaGetLastError());
     return 0;
@@ -101,20 +123,24 @@ int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
 
 int table_finalize(Table& t, cudaStream_t s)
 {
-    if (t.finalized || !t.d_sectors) return -11;
-    uint32_t st[2]; unsigned long long cnt[4];
+    if (t.finalized || !t.d_buckets) return -11;
+    k_finalize<<<grid_for(t.n_phys, 256), 256, 0, s>>>((ulonglong4*)t.d_buckets, t.d_flags, t.n_phys);
+    CK(cudaGetLastError());
+    uint32_t st[2]; unsigned long long cnt[3];
     CK(cudaMemcpyAsync(st, t.d_status, sizeof st, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(cnt, t.d_counts, sizeof cnt, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
-    t.n_inserted = cnt[0]; t.n_hopped = cnt[3];
+    CK(cudaFree(t.d_flags)); t.d_flags = nullptr;
+    t.n_inserted = cnt[0];
     t.finalized = true;
-    if (st[0]) return -13;                                  // table too full: a probe sequence ran out
+    if (st[0]) return -13;                                  // table too full: displacement > kMaxDisp
     return 0;
 }
 
 void table_destroy(Table& t)
 {
-    if (t.d_sectors) cudaFree(t.d_sectors);
+    if (t.d_buckets) cudaFree(t.d_buckets);
+    if (t.d_flags) cudaFree(t.d_flags);
     if (t.d_status) cudaFree(t.d_status);
     if (t.d_counts) cudaFree(t.d_counts);
     t = Table{};

@@ -38,12 +38,12 @@ class _Config(C.Structure):
 
 class DbInfo(C.Structure):
     _fields_ = [("entries", C.c_uint64), ("buckets", C.c_uint64), ("bytes", C.c_uint64),
-                ("tombstones", C.c_uint64), ("max_displacement", C.c_uint32), ("hopped", C.c_uint64)]
+                ("tombstones", C.c_uint64), ("max_displacement", C.c_uint32)]
 
 
 class Stats(C.Structure):
     _fields_ = [("reads", C.c_uint64), ("lookups", C.c_uint64), ("sectors", C.c_uint64),
-                ("dense_reads", C.c_uint64), ("lines", C.c_uint64)]
+                ("dense_reads", C.c_uint64)]
 
 
 _lib = None

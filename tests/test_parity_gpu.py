@@ -193,7 +193,7 @@ def test_synthetic_workload_matches_oracle(oracle):
     assert np.array_equal(off_h, off_o) and np.array_equal(cont_h, cont_o)
     want, _, nl = odb.query_packed(k, off_o, cont_o)
     out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
-    stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+    stats = torch.zeros(2, dtype=torch.int64, device="cuda")
     db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     got = out.cpu().numpy().view(np.uint16).reshape(-1, 5)
