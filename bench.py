@@ -130,7 +130,7 @@ def run_reference(args):
                 kv = dict(x.split("=") for x in line.split()[1:])
                 times.append(float(kv["seconds"])); lookups = int(kv["lookups"])
         if len(times) < args.steps + args.warmup:
-            print(json.dumps({"impl": "reference", "unavailable": "ref_harness failed: " + r.stderr[-200:].replace("\n", " ")}))
+            emit(json.dumps({"impl": "reference", "unavailable": "ref_harness failed: " + r.stderr[-200:].replace("\n", " ")}))
             return
     else:
         ir = oracle_py.IndexedReads(open(reads, "rb").read())
@@ -143,7 +143,7 @@ def run_reference(args):
     shutil.rmtree(d, ignore_errors=True)
     t = sum(times[args.warmup:])
     v = lookups * args.steps / t
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "kmer_lookups_per_s", "value": v, "unit": "lookups/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
@@ -250,7 +250,7 @@ def run_b200(args):
 
     if args.kernel_only:
         if rank == 0:
-            print(json.dumps({"kernel_only": True, "ms_per_step": ms / args.steps, "lookups_per_s": value}))
+            emit(json.dumps({"kernel_only": True, "ms_per_step": ms / args.steps, "lookups_per_s": value}))
         db.device_free(d_off); db.device_free(d_cont); db.close()
         if world > 1:
             dist.destroy_process_group()
@@ -352,14 +352,32 @@ def run_b200(args):
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
             line["parity_sample"] = parity
-        print(json.dumps(line))
+        emit(json.dumps(line))
     db.device_free(d_off); db.device_free(d_cont)
     db.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(text):
+    """The JSON line goes to the real stdout; everything else a library prints (NCCL's version
+    banner, for one) was moved to stderr by quiet_stdout()."""
+    out = _REAL_STDOUT or sys.stdout
+    out.write(text + "\n"); out.flush()
+
+
+def quiet_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
 if __name__ == "__main__":
+    quiet_stdout()
     a = parse()
     if a.impl == "reference":
         run_reference(a)
