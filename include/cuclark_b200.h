@@ -79,6 +79,32 @@ int  ccb_db_add_pairs_device(ccb_handle* h, const void* d_canon, const void* d_l
 int  ccb_db_end(ccb_handle* h);
 int  ccb_db_get_info(const ccb_handle* h, ccb_db_info* info);
 
+/* Database construction from target FASTA files -- replaces the reference's
+ * single-threaded makeSpecificTargetSets (src/CuCLARK_hh.hh:691-1329: scan loops
+ * :1129-1198 full, :711-767 light), EHashtable::addElement / RemoveCommon
+ * (src/HashTableStorage_hh.hh:422-461, 230-280) and hTable::write
+ * (src/hashTable_hh.hh:474-546).  Full mode: every overlapping k-mer of every
+ * ACGTU run; light mode: non-overlapping k-mers, every gap-th of them per file.
+ * A canonical k-mer is stored iff all its occurrences carry one label and its
+ * occurrence count (saturating at 254) exceeds min_count.  ccb_build_end writes
+ * <prefix>.sz/.ky/.lb byte-for-byte as the reference does (prefix may be NULL)
+ * and, when load_table != 0, leaves the k-mer table ready for queries.
+ * k comes from ccb_config.  max_bases bounds the bases all add_fasta calls
+ * together may carry (the sum of the file sizes will do).  ccb_build_add_fasta
+ * may be called from several host threads. */
+typedef struct ccb_build_info {
+    uint64_t bases;          /* ACGTU bases scanned */
+    uint64_t occurrences;    /* k-mers emitted before de-duplication */
+    uint64_t distinct;       /* distinct canonical k-mers */
+    uint64_t stored;         /* discriminative k-mers written / loaded */
+    uint32_t max_bucket;     /* largest reference bucket (must be <= 255) */
+    uint32_t reserved;
+} ccb_build_info;
+int  ccb_build_begin(ccb_handle* h, uint64_t htsize, int key_bytes, int light, unsigned gap,
+                     unsigned min_count, uint64_t max_bases);
+int  ccb_build_add_fasta(ccb_handle* h, const unsigned char* text, uint64_t len, uint16_t label);
+int  ccb_build_end(ccb_handle* h, const char* prefix, int load_table, ccb_build_info* info);
+
 /* CuClarkDB::malloc (src/CuClarkDB.cu:322-421): pinned host + device buffers for
  * every slot, owned by the library; the caller fills offsets/containers in
  * place and reads final5/rows in place after ccb_batch_wait. */

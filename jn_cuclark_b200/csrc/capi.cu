@@ -1,6 +1,7 @@
 // capi.cu -- C ABI (include/cuclark_b200.h) over the table + query kernels.
 #include "../../include/cuclark_b200.h"
 #include "capi_internal.cuh"
+#include "dbbuild.cuh"
 
 #include <stdarg.h>
 #include <stdio.h>
@@ -101,6 +102,7 @@ extern "C" void ccb_destroy(ccb_handle* h)
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     free_slots(h);
+    build_free(h);
     table_destroy(h->table);
     cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense);
     if (h->db_stream) cudaStreamDestroy(h->db_stream);

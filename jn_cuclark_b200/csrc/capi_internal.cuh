@@ -29,6 +29,7 @@ struct Slot {
 };
 
 constexpr uint32_t kDenseBlocks = 64;
+struct BuildState;                   // dbbuild.cu
 
 }  // namespace ccb
 
@@ -48,6 +49,9 @@ struct ccb_handle {
     // scratch for ccb_query_device
     uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
     uint32_t  q_ovf_cap = 0;
+    // database construction in progress (ccb_build_*)
+    ccb::BuildState* build = nullptr;
+    std::mutex  build_mu;
 };
 
 

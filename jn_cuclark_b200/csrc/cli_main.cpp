@@ -20,6 +20,8 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 #include <iostream>
 #include <string>
 #include <thread>
@@ -107,6 +109,7 @@ static void split(const string& s, const char* seps, size_t max_el, vector<strin
 struct Targets {
     vector<string> names;          // [0] = "NA", then labels in order of first appearance (src/CuCLARK_hh.hh:1874-1878)
     size_t n_labels = 0;
+    vector<std::pair<string, uint16_t>> files;   // target file -> 0-based label index (m_targetsID, :1830-1840)
 };
 
 // getTargetsData (src/CuCLARK_hh.hh:1790-1901): "<file> <label> [<label_c>]" per line
@@ -127,9 +130,11 @@ static void read_targets(const char* path, Targets& t)
         if (el.empty()) continue;
         if (el.size() < 2) { cerr << " Missing label for " << el[0] << endl; exit(-1); }
         if (std::find(labels.begin(), labels.end(), el[1]) == labels.end()) labels.push_back(el[1]);
+        t.files.emplace_back(el[0], (uint16_t)(std::find(labels.begin(), labels.end(), el[1]) - labels.begin()));
         if (el.size() > 2 && std::find(labels_c.begin(), labels_c.end(), el[2]) == labels_c.end()) labels_c.push_back(el[2]);
     }
     fclose(f);
+    if (!labels_c.empty()) t.files.clear();       // a third column (label_c) is outside the rebuilt path: never build from it
     t.names.clear();
     t.names.push_back("NA");
     for (auto& l : labels) t.names.push_back(l);
@@ -175,12 +180,9 @@ struct Engine {
         if (kLight) snprintf(name, sizeof name, "%s/db_central_k%lu_t%lu_s%lu_m%lu_light_%lu.tsk", cli.folder, cli.k, tg.n_labels, (size_t)HTSIZE, (size_t)cli.minT, cli.iterKmers);
         else        snprintf(name, sizeof name, "%s/db_central_k%lu_t%lu_s%lu_m%lu.tsk", cli.folder, cli.k, tg.n_labels, (size_t)HTSIZE, (size_t)cli.minT);
         dbname = name;
-        for (const char* e : {".sz", ".ky", ".lb"})
-            if (!validFile((dbname + e).c_str())) {
-                cerr << "Failed to find the database." << endl;
-                cerr << "(" << dbname << e << " is missing; this build loads databases written by the reference's CPU builder and does not create them)" << endl;
-                exit(-1);
-            }
+        bool present = true;
+        for (const char* e : {".sz", ".ky", ".lb"}) present = present && validFile((dbname + e).c_str());
+        if (!present && build_db()) return;          // built on the device and already resident
         if (cli.verbose) cerr << "Loading database [" << dbname << ".*] (s=" << cli.sfactor << ")..." << endl;
         vector<std::thread> th; vector<int> rc(devs.size(), 0);
         for (size_t d = 0; d < devs.size(); d++)
@@ -188,6 +190,51 @@ struct Engine {
         for (auto& t : th) t.join();
         for (size_t d = 0; d < devs.size(); d++)
             if (rc[d]) { cerr << ccb_last_error(devs[d]) << endl; exit(1); }
+    }
+
+    // makeSpecificTargetSets (src/CuCLARK_hh.hh:691-1329): the database is absent, build it from the
+    // target FASTA files on device 0, write <dbname>.sz/.ky/.lb, then load it everywhere.
+    // returns true when the table is already resident (one device, no -s sampling).
+    bool build_db()
+    {
+        if (tg.files.empty()) { cerr << "Failed to find the database." << endl; exit(-1); }
+        cerr << "Starting the creation of the database of targets specific " << cli.k << "-mers from input files..." << endl;
+        uint64_t total = 0;
+        for (auto& f : tg.files) { struct stat sb; if (stat(f.first.c_str(), &sb) == 0) total += (uint64_t)sb.st_size; }
+        ccb_handle* h = devs[0];
+        if (ccb_build_begin(h, HTSIZE, key_bytes, kLight ? 1 : 0, (unsigned)cli.iterKmers, cli.minT, total)) { cerr << ccb_last_error(h) << endl; exit(1); }
+        std::atomic<size_t> next{0}, done{0};
+        std::mutex io;
+        bool failed = false;
+        auto work = [&] {
+            for (size_t t = next++; t < tg.files.size(); t = next++) {
+                const string& fn = tg.files[t].first;
+                int fd = open(fn.c_str(), O_RDONLY);
+                struct stat sb;
+                if (fd == -1 || fstat(fd, &sb) == -1) { std::lock_guard<std::mutex> g(io); cerr << "Failed to open " << fn << endl; if (fd != -1) close(fd); continue; }
+                if (sb.st_size == 0) { close(fd); continue; }
+                void* map = mmap(0, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+                if (map == MAP_FAILED) { close(fd); std::lock_guard<std::mutex> g(io); cerr << "Failed to open " << fn << endl; continue; }
+                int rc = ccb_build_add_fasta(h, (const unsigned char*)map, (uint64_t)sb.st_size, tg.files[t].second);
+                munmap(map, (size_t)sb.st_size); close(fd);
+                std::lock_guard<std::mutex> g(io);
+                if (rc) { cerr << fn << ": " << ccb_last_error(h) << endl; failed = true; }
+                cerr << "\r Progress report: (" << ++done << "/" << tg.files.size() << ")              ";
+            }
+        };
+        vector<std::thread> th;
+        for (size_t i = 0; i < std::max<size_t>(1, std::min<size_t>(cli.cpu, tg.files.size())); i++) th.emplace_back(work);
+        for (auto& t : th) t.join();
+        if (failed) exit(1);
+        const bool resident = devs.size() == 1 && cli.sfactor <= 1;
+        ccb_build_info bi;
+        memset(&bi, 0, sizeof bi);
+        cerr << endl << "Creating database in disk..." << endl;
+        if (ccb_build_end(h, dbname.c_str(), resident ? 1 : 0, &bi)) { cerr << ccb_last_error(h) << endl; exit(1); }
+        cerr << bi.bases << " nt read in total." << endl;
+        cerr << "Mother Hashtable successfully built. " << bi.distinct << " " << cli.k << "-mers stored." << endl;
+        cerr << bi.stored << " " << cli.k << "-mers successfully stored in database." << endl;
+        return resident;
     }
 
     // runSimple (src/CuCLARK_hh.hh:513-574) on a text already in memory or mapped

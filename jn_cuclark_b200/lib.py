@@ -41,6 +41,11 @@ class DbInfo(C.Structure):
                 ("tombstones", C.c_uint64), ("max_displacement", C.c_uint32)]
 
 
+class BuildInfo(C.Structure):
+    _fields_ = [("bases", C.c_uint64), ("occurrences", C.c_uint64), ("distinct", C.c_uint64),
+                ("stored", C.c_uint64), ("max_bucket", C.c_uint32), ("reserved", C.c_uint32)]
+
+
 class Stats(C.Structure):
     _fields_ = [("reads", C.c_uint64), ("lookups", C.c_uint64), ("sectors", C.c_uint64),
                 ("dense_reads", C.c_uint64)]
@@ -60,6 +65,9 @@ SYMBOLS = {
     "ccb_db_add_pairs_device": (C.c_int, [_H, _VP, _VP, C.c_uint64]),
     "ccb_db_end": (C.c_int, [_H]),
     "ccb_db_get_info": (C.c_int, [_H, C.POINTER(DbInfo)]),
+    "ccb_build_begin": (C.c_int, [_H, C.c_uint64, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint64]),
+    "ccb_build_add_fasta": (C.c_int, [_H, C.c_char_p, C.c_uint64, C.c_uint16]),
+    "ccb_build_end": (C.c_int, [_H, C.c_char_p, C.c_int, C.POINTER(BuildInfo)]),
     "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
     "ccb_batch_buffers": (C.c_int, [_H, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
     "ccb_batch_submit": (C.c_int, [_H, C.c_int, C.c_uint32, C.c_uint64, C.c_int]),
@@ -174,6 +182,19 @@ class CuClarkDB:
     def db_info(self) -> DbInfo:
         info = DbInfo()
         self._ck(self._lib.ccb_db_get_info(self._h, C.byref(info)))
+        return info
+
+    def build(self, targets, htsize: int, key_bytes: int = 4, light: bool = False, gap: int = 4,
+              min_count: int = 0, prefix: str | None = None, load_table: bool = True) -> BuildInfo:
+        """makeSpecificTargetSets + hTable::write (src/CuCLARK_hh.hh:691-1329, src/hashTable_hh.hh:474-546)
+        on the device.  targets: iterable of (fasta bytes, 0-based label index)."""
+        targets = list(targets)
+        total = sum(len(t) for t, _ in targets)
+        self._ck(self._lib.ccb_build_begin(self._h, htsize, key_bytes, int(light), gap, min_count, total))
+        for text, label in targets:
+            self._ck(self._lib.ccb_build_add_fasta(self._h, text, len(text), label))
+        info = BuildInfo()
+        self._ck(self._lib.ccb_build_end(self._h, prefix.encode() if prefix else None, int(load_table), C.byref(info)))
         return info
 
     # -- batches --------------------------------------------------------------

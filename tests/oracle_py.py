@@ -171,6 +171,11 @@ class OracleDb:
             pass
 
 
+def key_bytes(k: int, htsize: int) -> int:
+    """src/main.cc:251-286: width of the stored keys (T16/T32/T64)."""
+    return int(lib().ccbo_key_bytes(k, htsize))
+
+
 def db_name(folder: str, k: int, n_labels: int, htsize: int, min_t: int = 0, light: bool = False, gap: int = 4) -> str:
     buf = C.create_string_buffer(4400)
     lib().ccbo_db_name(buf, 4400, folder.encode(), k, n_labels, htsize, min_t, int(light), gap)
