@@ -22,6 +22,8 @@
 #include "dbbuild.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <algorithm>
+#include <chrono>
+#include <memory>
 #include <stdio.h>
 #include <string.h>
 
@@ -288,24 +290,48 @@ constexpr uint64_t kStageBytes = 256ull << 20;
 // FASTA text -> code stream (full mode).  Rules of src/CuCLARK_hh.hh:1129-1198: '\n' is skipped
 // (:1170), any other byte outside ACGTU/acgtu resets the window (:1173), '>' resets and the rest
 // of that line is skipped (:1176-1188).  A reset closes the file.
-void compact_fasta(const unsigned char* t, uint64_t len, std::vector<uint8_t>& out, uint64_t& bases)
+struct CodeBuf {                       // uninitialised byte buffer (a std::vector would zero-fill it first)
+    std::unique_ptr<uint8_t[]> p; size_t n = 0;
+    const uint8_t* data() const { return p.get(); }
+    size_t size() const { return n; }
+};
+
+void compact_fasta(const unsigned char* t, uint64_t len, CodeBuf& out, uint64_t& bases)
 {
-    out.clear(); out.reserve(len + 2);
-    uint64_t i = 0, nb = 0;
+    out.p.reset(new uint8_t[len + 2]);
+    uint8_t* o = out.p.get();
+    uint64_t i = 0, resets = 0;
     bool last_reset = true;
     while (i < len) {
-        const unsigned char ch = t[i];
-        const int c = code_of(ch);
-        if (c >= 0) { out.push_back((uint8_t)c); nb++; last_reset = false; i++; continue; }
-        if (ch == '\n') { i++; continue; }
-        if (!last_reset) { out.push_back(4); last_reset = true; }
-        if (ch == '>') {
+        if (t[i] == '>') {                                     // header: reset, skip the line
+            if (!last_reset) { *o++ = 4; resets++; last_reset = true; }
             const void* e = memchr(t + i, '\n', len - i);
             i = e ? (uint64_t)((const unsigned char*)e - t) + 1 : len;
-        } else i++;
+            continue;
+        }
+        const void* e = memchr(t + i, '\n', len - i);
+        const uint64_t end = e ? (uint64_t)((const unsigned char*)e - t) : len;
+        // fast path: a line of nothing but ACGTU/acgtu, translated without branches
+        const uint64_t m = end - i;
+        unsigned bad = 0;
+        for (uint64_t j = 0; j < m; j++) {
+            const unsigned ch = t[i + j], up = ch & 0xDFu, v = (ch >> 1) & 3u;
+            bad |= (unsigned)!(up == 'A' || up == 'C' || up == 'G' || up == 'T' || up == 'U');
+            o[j] = (uint8_t)(3u - (v ^ (v >> 1)));             // A=3 C=2 G=1 T/U=0
+        }
+        if (!bad) { if (m) last_reset = false; o += m; i = end + 1; continue; }
+        // slow path: byte by byte up to the end of this line (a '>' inside skips the rest of it)
+        for (; i < end; i++) {
+            const int c = code_of(t[i]);
+            if (c >= 0) { *o++ = (uint8_t)c; last_reset = false; continue; }
+            if (!last_reset) { *o++ = 4; resets++; last_reset = true; }
+            if (t[i] == '>') { i = end; break; }
+        }
+        i = end + 1;
     }
-    if (!last_reset) out.push_back(4);
-    bases += nb;
+    if (!last_reset) { *o++ = 4; resets++; }
+    out.n = (size_t)(o - out.p.get());
+    bases += out.n - resets;
 }
 
 // light mode (src/CuCLARK_hh.hh:711-767): non-overlapping windows, the window is cleared after each
@@ -415,7 +441,7 @@ extern "C" int ccb_build_add_fasta(ccb_handle* h, const unsigned char* text, uin
         b->bases += nb;
         return 0;
     }
-    std::vector<uint8_t> codes; uint64_t nb = 0;
+    CodeBuf codes; uint64_t nb = 0;
     compact_fasta(text, len, codes, nb);
     std::lock_guard<std::mutex> g(h->build_mu);
     USE_DEV(h);
@@ -440,6 +466,12 @@ int build_end_t(ccb_handle* h, BuildState* b, const char* prefix, int load_table
 {
     cudaStream_t s = h->db_stream;
     const uint64_t htsize = b->htsize;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {          // --verbose: wall time of each phase (every phase ends synchronised)
+        auto now = std::chrono::steady_clock::now();
+        if (h->cfg.verbose) fprintf(stderr, "  build: %-28s %8.3f s\n", what, std::chrono::duration<double>(now - t_last).count());
+        t_last = now;
+    };
     // ---- remaining input -------------------------------------------------------------------
     if (b->light) {
         const uint64_t n = b->l_c.size();
@@ -468,6 +500,7 @@ int build_end_t(ccb_handle* h, BuildState* b, const char* prefix, int load_table
     cudaFree(b->d_codes); b->d_codes = nullptr;
     if (b->h_codes) { cudaFreeHost(b->h_codes); b->h_codes = nullptr; }
     const uint64_t n = b->n_occ;
+    lap("last flush");
 
     // ---- sort by (bucket, key) -------------------------------------------------------------
     const size_t vbytes = WIDE ? 8 : 2;
@@ -505,6 +538,7 @@ int build_end_t(ccb_handle* h, BuildState* b, const char* prefix, int load_table
         cudaFree(tmp);
     }
 
+    lap("sort by (bucket, key)");
     // ---- keep the discriminative ones, in order ------------------------------------------------
     uint64_t n_keep = 0, n_distinct = 0;
     if (n) {
@@ -523,6 +557,7 @@ int build_end_t(ccb_handle* h, BuildState* b, const char* prefix, int load_table
         n_distinct = hc[0]; n_keep = hc[1];
         cudaFree(flag); cudaFree(tile_kept); cudaFree(tile_base); cudaFree(counters);
     }
+    lap("filter + compaction");
     // the sorted occurrences are no longer needed
     cudaFree(b->d_key[cur_key]); b->d_key[cur_key] = nullptr;
     cudaFree(b->d_val[cur_val]); b->d_val[cur_val] = nullptr;
@@ -542,6 +577,7 @@ int build_end_t(ccb_handle* h, BuildState* b, const char* prefix, int load_table
         return ccb_fail(h, -54, "database build: a bucket holds %u k-mers, the .sz format allows 255", max_bucket);
     }
 
+    lap("bucket sizes");
     // ---- files ---------------------------------------------------------------------------------
     int rc = 0;
     if (prefix) {
@@ -572,12 +608,14 @@ int build_end_t(ccb_handle* h, BuildState* b, const char* prefix, int load_table
     }
     cudaFree(d_sz);
     if (rc) return rc;
+    if (prefix) lap("write .sz/.ky/.lb");
 
     // ---- table for queries -----------------------------------------------------------------------
     if (load_table) {
         rc = ccb_db_begin(h, n_keep);
         if (!rc && n_keep) rc = ccb_db_add_pairs_device(h, out_c, out_lab, n_keep);
         if (!rc) rc = ccb_db_end(h);
+        lap("k-mer table");
     }
     return rc;
 }
