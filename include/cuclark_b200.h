@@ -105,6 +105,30 @@ int  ccb_build_begin(ccb_handle* h, uint64_t htsize, int key_bytes, int light, u
 int  ccb_build_add_fasta(ccb_handle* h, const unsigned char* text, uint64_t len, uint16_t label);
 int  ccb_build_end(ccb_handle* h, const char* prefix, int load_table, ccb_build_info* info);
 
+/* Sharded table -- a database larger than one device's memory.  The reference cuts the bucket
+ * range into parts and swaps them through one GPU (CuClarkDB::read / swapDbParts,
+ * src/CuClarkDB.cu:552-559, 776-815, queryKernel's range filter :1211-1214, mergeKernel :1261-1355).
+ * Here shard g of n_shards (<= 8) lives on GPU g and a batch takes one exchange each way:
+ *   ccb_shard_config  before the database is loaded/built/synthesised: keep only this shard's k-mers
+ *   ccb_shard_count   d_pos = u32[n_shards*n_reads+1]: exclusive scan, laid out [owner][read], of the
+ *                     number of k-mers each read sends to each owner ([n_shards*n_reads] = total)
+ *   ccb_shard_route   read r's mixed k-mers (u64) for owner g go to dst[g][d_pos[g*n_reads+r]-seg_base[g] ...);
+ *                     dst[g] is a device pointer this process may store to (a local send segment or a
+ *                     peer GPU's inbox); seg_base and dst are HOST arrays of n_shards entries
+ *   ccb_shard_probe   owner side: d_labels[i] (u16) = label of mixed k-mer d_hashes[i], 0xFFFF = none;
+ *                     d_stats (optional) = 2 x u64 {lookups, sectors}, accumulated
+ *   ccb_shard_vote    requester side: labels of (owner g, read r) are read at
+ *                     src[g][d_pos[g*n_reads+r]-seg_base[g] ...); writes u16[5] per read (+ rows)
+ * Results are identical to ccb_query_device on the unsharded table. */
+int  ccb_shard_config(ccb_handle* h, int n_shards, int shard);
+int  ccb_shard_count(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
+                     int n_shards, void* d_pos, void* stream);
+int  ccb_shard_route(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
+                     int n_shards, const void* d_pos, const uint64_t* seg_base, void* const* dst, void* stream);
+int  ccb_shard_probe(ccb_handle* h, const void* d_hashes, uint64_t n, void* d_labels, void* d_stats, void* stream);
+int  ccb_shard_vote(ccb_handle* h, uint32_t n_reads, int n_shards, const void* d_pos, const uint64_t* seg_base,
+                    const void* const* src, void* d_final5, void* d_rows, void* stream);
+
 /* CuClarkDB::malloc (src/CuClarkDB.cu:322-421): pinned host + device buffers for
  * every slot, owned by the library; the caller fills offsets/containers in
  * place and reads final5/rows in place after ccb_batch_wait. */

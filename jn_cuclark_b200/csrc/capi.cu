@@ -104,7 +104,7 @@ extern "C" void ccb_destroy(ccb_handle* h)
     free_slots(h);
     build_free(h);
     table_destroy(h->table);
-    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense);
+    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense); cudaFree(h->shard_scan_tmp);
     if (h->db_stream) cudaStreamDestroy(h->db_stream);
     delete h;
 }
@@ -117,7 +117,7 @@ extern "C" int ccb_db_begin(ccb_handle* h, uint64_t expected_entries)
     if (!h) return -1;
     USE_DEV(h);
     if (h->db_building || h->db_ready) { table_destroy(h->table); h->db_ready = h->db_building = false; }
-    int rc = table_create(h->table, h->cfg.k, expected_entries, h->cfg.load_factor, h->db_stream);
+    int rc = table_create(h->table, h->cfg.k, expected_entries, h->cfg.load_factor, h->db_stream, h->n_shards, h->shard);
     if (rc) {
         table_destroy(h->table);
         if (rc == (int)cudaErrorMemoryAllocation)
@@ -340,6 +340,7 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
 {
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    if (h->n_shards > 1) return ccb_fail(h, -63, "this handle holds one shard of the table: use the ccb_shard_* calls");
     if (n_reads > h->max_reads || n_containers > h->max_cont) return ccb_fail(h, -33, "batch larger than allocated (%u reads, %llu containers)", n_reads, (unsigned long long)n_containers);
     if ((flags & CCB_EXTENDED) && !h->batch_extended) return ccb_fail(h, -34, "extended results requested but ccb_batch_alloc(extended=0)");
     USE_DEV(h);
@@ -411,6 +412,7 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
 {
     if (!h) return -1;
     if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    if (h->n_shards > 1) return ccb_fail(h, -63, "this handle holds one shard of the table: use the ccb_shard_* calls");
     USE_DEV(h);
     if (h->q_ovf_cap < n_reads || !h->q_ovf_list) {
         cudaFree(h->q_ovf_list); h->q_ovf_list = nullptr;

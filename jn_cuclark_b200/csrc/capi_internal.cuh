@@ -49,6 +49,9 @@ struct ccb_handle {
     // scratch for ccb_query_device
     uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
     uint32_t  q_ovf_cap = 0;
+    // sharded table (ccb_shard_*): this handle holds shard `shard` of `n_shards`
+    uint32_t   n_shards = 1, shard = 0;
+    void*      shard_scan_tmp = nullptr; size_t shard_scan_bytes = 0;
     // database construction in progress (ccb_build_*)
     ccb::BuildState* build = nullptr;
     std::mutex  build_mu;

@@ -71,10 +71,14 @@ CCB_HD uint64_t mix2k(uint64_t c, int k, uint64_t mask)
 }
 
 struct HashParams {
-    uint64_t nb;      // number of home buckets
+    uint64_t nb;      // number of home buckets (of the WHOLE table, all shards)
     uint64_t mask;    // 2^(2k)-1
     int      k;
     int      shift;   // 64 - 2k
+    // sharded table (DESIGN.md "Sharded mode"): the hash space is cut into n_shards equal ranges,
+    // nb is a multiple of n_shards, so shard g holds the home buckets [g*nb/n_shards, (g+1)*nb/n_shards)
+    uint32_t n_shards;   // 0 or 1: not sharded
+    uint32_t shard;
 };
 
 #if defined(__CUDACC__)
@@ -91,6 +95,15 @@ CCB_HD uint64_t home_of(uint64_t h, const HashParams& p)
     return mulhi64(h << p.shift, p.nb);
 #else
     return mulhi64_host(h << p.shift, p.nb);
+#endif
+}
+// owner shard of a mixed k-mer: floor(h * n_shards / 2^(2k)) == home / (nb / n_shards)
+CCB_HD uint32_t owner_of(uint64_t h, int shift, uint32_t n_shards)
+{
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)mulhi64(h << shift, (uint64_t)n_shards);
+#else
+    return (uint32_t)mulhi64_host(h << shift, (uint64_t)n_shards);
 #endif
 }
 CCB_HD uint64_t key48_of(uint64_t h) { return h & 0xFFFFFFFFFFFFull; }

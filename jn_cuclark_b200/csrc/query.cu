@@ -67,9 +67,52 @@ __device__ __forceinline__ void vote4(const uint32_t (&lab)[4], uint32_t& acc_la
     }
 }
 
-template <bool STATS>
+// Writes a read's result {sumN, idxBest, best, idxSecond, second} (src/CuClarkDB.cu:1370-1405), its
+// sparse row when asked for, and lists it for the dense pass when it overflowed the accumulators.
+__device__ __forceinline__ void finish_read(const QueryArgs& a, uint32_t r, uint32_t acc_lab, uint32_t acc_cnt,
+                                            int nacc, bool overflow, int lane)
+{
+    const uint32_t cnt16 = lane < nacc ? (acc_cnt & 0xFFFFu) : 0u;   // reference counters are u16
+    const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, cnt16);
+    const uint32_t key = cnt16 ? ((cnt16 << 16) | (0xFFFFu - acc_lab)) : 0u;
+    const uint32_t k1 = __reduce_max_sync(0xFFFFFFFFu, key);
+    const uint32_t k2 = __reduce_max_sync(0xFFFFFFFFu, key == k1 ? 0u : key);
+    if (lane < 5) {
+        uint32_t v;
+        if (lane == 0) v = sum;
+        else if (lane == 1) v = k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u;
+        else if (lane == 2) v = k1 >> 16;
+        else if (lane == 3) v = k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u;
+        else v = k2 >> 16;
+        a.out5[(size_t)r * 5 + lane] = (uint16_t)v;
+    }
+    if (a.rows) {
+        uint16_t* row = a.rows + (size_t)r * a.row_stride;
+        int rank = 0;
+        for (int j = 0; j < nacc; j++) {
+            uint32_t l = __shfl_sync(0xFFFFFFFFu, acc_lab, j);
+            rank += (l < acc_lab) ? 1 : 0;
+        }
+        if (lane == 0) row[0] = (uint16_t)min(nacc, (a.row_stride - 1) / 2);
+        if (lane < nacc && 2 * rank + 2 < a.row_stride) {
+            row[1 + 2 * rank] = (uint16_t)acc_lab;
+            row[2 + 2 * rank] = (uint16_t)acc_cnt;
+        }
+    }
+    if (overflow && lane == 0 && a.ovf_list) {
+        uint32_t i = atomicAdd(a.ovf_count, 1u);
+        a.ovf_list[i] = r;
+    }
+}
+
+// MODE 0: classify against a table held whole (the product path).
+// MODE 1/2: sharded table -- count, then write, each read's mixed k-mers per owner shard
+//           (same walk, so both passes see the k-mers in the same order).
+enum { kModeQuery = 0, kModeCount = 1, kModeRoute = 2 };
+
+template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 2)
-k_query(const TableView t, const QueryArgs a)
+k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
 {
     __shared__ WarpSmem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31;
@@ -121,6 +164,14 @@ k_query(const TableView t, const QueryArgs a)
         uint32_t acc_lab = kLabelNone, acc_cnt = 0;
         int nacc = 0; bool overflow = false;
         unsigned long long st_lookups = 0; uint32_t st_sectors = 0;
+        uint32_t sent[kMaxShards];                 // MODE 1/2: k-mers of this read per owner so far
+        uint64_t* out_g[kMaxShards];               // MODE 2: where this read's k-mers for owner g start
+#pragma unroll
+        for (int g = 0; g < kMaxShards; g++) {
+            sent[g] = 0; out_g[g] = nullptr;
+            if (MODE == kModeRoute && g < (int)ra.n_shards)
+                out_g[g] = ra.dst[g] + (__ldg(ra.pos + (size_t)g * a.n_reads + r) - ra.seg_base[g]);
+        }
 
         const int total_pos = 8 * (nslots - 1) - (k - 1);
         if (total_pos > 0) {
@@ -193,55 +244,52 @@ k_query(const TableView t, const QueryArgs a)
                         ok[j] = (p0 + i < npos) && (((vm >> i) & validk) == validk);
                         uint64_t cn = x < rc ? x : rc;
                         uint64_t h = mix2k(cn, k, kmsk);
-                        home[j] = home_of(h, t.hp);
-                        q[j] = key48_of(h) << 16;
-                        if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
-                    }
-                    uint32_t lab[4];
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        lab[j] = kLabelNone;
-                        if (ok[j]) {
-                            uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &st_sectors : nullptr);
-                            lab[j] = l >= kLabelTomb ? kLabelNone : l;
-                            if (STATS) { st_lookups++; st_sectors++; }
+                        if (MODE == kModeQuery) {
+                            home[j] = home_of(h, t.hp);
+                            q[j] = key48_of(h) << 16;
+                            if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
+                        } else {
+                            q[j] = h;
+                            home[j] = ok[j] ? owner_of(h, t.hp.shift, ra.n_shards) : 0xFFFFFFFFull;
                         }
                     }
-                    vote4(lab, acc_lab, acc_cnt, nacc, overflow, lane);
+                    if (MODE == kModeQuery) {
+                        uint32_t lab[4];
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            lab[j] = kLabelNone;
+                            if (ok[j]) {
+                                uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &st_sectors : nullptr);
+                                lab[j] = l >= kLabelTomb ? kLabelNone : l;
+                                if (STATS) { st_lookups++; st_sectors++; }
+                            }
+                        }
+                        vote4(lab, acc_lab, acc_cnt, nacc, overflow, lane);
+                    } else {
+                        const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+#pragma unroll
+                            for (int og = 0; og < kMaxShards; og++) {
+                                if (og < (int)ra.n_shards) {
+                                    const bool mine = home[j] == (uint64_t)og;
+                                    const uint32_t b = __ballot_sync(0xFFFFFFFFu, mine);
+                                    if (MODE == kModeRoute && mine) out_g[og][sent[og] + __popc(b & lt)] = q[j];
+                                    sent[og] += __popc(b);
+                                }
+                            }
+                        }
+                    }
                 }
             }
         }
-        // ---- result: {sumN, idxBest, best, idxSecond, second} (src/CuClarkDB.cu:1370-1405) ----
-        const uint32_t cnt16 = lane < nacc ? (acc_cnt & 0xFFFFu) : 0u;   // reference counters are u16
-        const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, cnt16);
-        const uint32_t key = cnt16 ? ((cnt16 << 16) | (0xFFFFu - acc_lab)) : 0u;
-        const uint32_t k1 = __reduce_max_sync(0xFFFFFFFFu, key);
-        const uint32_t k2 = __reduce_max_sync(0xFFFFFFFFu, key == k1 ? 0u : key);
-        if (lane < 5) {
-            uint32_t v;
-            if (lane == 0) v = sum;
-            else if (lane == 1) v = k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u;
-            else if (lane == 2) v = k1 >> 16;
-            else if (lane == 3) v = k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u;
-            else v = k2 >> 16;
-            a.out5[(size_t)r * 5 + lane] = (uint16_t)v;
-        }
-        if (a.rows) {
-            uint16_t* row = a.rows + (size_t)r * a.row_stride;
-            int rank = 0;
-            for (int j = 0; j < nacc; j++) {
-                uint32_t l = __shfl_sync(0xFFFFFFFFu, acc_lab, j);
-                rank += (l < acc_lab) ? 1 : 0;
-            }
-            if (lane == 0) row[0] = (uint16_t)min(nacc, (a.row_stride - 1) / 2);
-            if (lane < nacc && 2 * rank + 2 < a.row_stride) {
-                row[1 + 2 * rank] = (uint16_t)acc_lab;
-                row[2 + 2 * rank] = (uint16_t)acc_cnt;
-            }
-        }
-        if (overflow && lane == 0 && a.ovf_list) {
-            uint32_t i = atomicAdd(a.ovf_count, 1u);
-            a.ovf_list[i] = r;
+        if (MODE == kModeQuery) {
+            finish_read(a, r, acc_lab, acc_cnt, nacc, overflow, lane);
+        } else if (MODE == kModeCount) {
+            uint32_t mine = 0;
+#pragma unroll
+            for (int g = 0; g < kMaxShards; g++) if (lane == g) mine = sent[g];
+            if (lane < (int)ra.n_shards) ra.counts[(size_t)lane * a.n_reads + r] = mine;
         }
         if (STATS) {
             unsigned long long l = st_lookups, s = st_sectors;
@@ -264,8 +312,21 @@ int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s)
     // per 10 M reads -- a static split leaves the slower SMs as the tail).
     uint32_t cap = 148u * 128u;
     if (ctas > cap) ctas = cap;
-    if (a.stats) k_query<true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a);
-    else         k_query<false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a);
+    const RouteArgs none{};
+    if (a.stats) k_query<kModeQuery, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none);
+    else         k_query<kModeQuery, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none);
+    return (int)cudaGetLastError();
+}
+
+int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s)
+{
+    if (a.n_reads == 0) return 0;
+    if (ra.n_shards < 1 || ra.n_shards > (uint32_t)kMaxShards) return -60;
+    uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
+    uint32_t cap = 148u * 128u;
+    if (ctas > cap) ctas = cap;
+    if (write) k_query<kModeRoute, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra);
+    else       k_query<kModeCount, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra);
     return (int)cudaGetLastError();
 }
 
@@ -282,6 +343,49 @@ __device__ __forceinline__ uint64_t kmer_at(const uint16_t* data, int j, int k, 
         x = (x << 2) | ((data[p >> 3] >> (2 * (7 - (p & 7)))) & 3u);
     }
     return x & mask;
+}
+
+// top-2 under (count desc, target asc) + sum over a CTA's dense counters, then the result row
+__device__ __forceinline__ void dense_result(const QueryArgs& a, uint32_t r, const uint32_t* cnt, uint32_t n_targets,
+                                             uint32_t (&s_key)[2][256], uint32_t (&s_sum)[256])
+{
+    uint32_t k1 = 0, k2 = 0, sum = 0;
+    for (uint32_t i = threadIdx.x; i < n_targets; i += blockDim.x) {
+        uint32_t c16 = cnt[i] & 0xFFFFu;
+        if (!c16) continue;
+        sum += c16;
+        uint32_t key = (c16 << 16) | (0xFFFFu - i);
+        if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
+    }
+    s_key[0][threadIdx.x] = k1; s_key[1][threadIdx.x] = k2; s_sum[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            uint32_t a1 = s_key[0][threadIdx.x], a2 = s_key[1][threadIdx.x];
+            uint32_t b1 = s_key[0][threadIdx.x + o], b2 = s_key[1][threadIdx.x + o];
+            uint32_t m1 = max(a1, b1);
+            uint32_t m2 = max(min(a1, b1), max(a2, b2));
+            s_key[0][threadIdx.x] = m1; s_key[1][threadIdx.x] = m2;
+            s_sum[threadIdx.x] += s_sum[threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        k1 = s_key[0][0]; k2 = s_key[1][0];
+        uint16_t* o5 = a.out5 + (size_t)r * 5;
+        o5[0] = (uint16_t)s_sum[0];
+        o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
+        o5[2] = (uint16_t)(k1 >> 16);
+        o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
+        o5[4] = (uint16_t)(k2 >> 16);
+        if (a.rows) {
+            uint16_t* row = a.rows + (size_t)r * a.row_stride;
+            int n = 0, fit = (a.row_stride - 1) / 2;
+            for (uint32_t i = 0; i < n_targets && n < fit; i++)
+                if (cnt[i] & 0xFFFFu) { row[1 + 2 * n] = (uint16_t)i; row[2 + 2 * n] = (uint16_t)cnt[i]; n++; }
+            row[0] = (uint16_t)n;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -310,44 +414,7 @@ k_query_dense(const TableView t, const QueryArgs a, const uint32_t* read_list, c
             }
         }
         __syncthreads();
-        // top-2 under (count desc, target asc) + sum
-        uint32_t k1 = 0, k2 = 0, sum = 0;
-        for (uint32_t i = threadIdx.x; i < n_targets; i += blockDim.x) {
-            uint32_t c16 = cnt[i] & 0xFFFFu;
-            if (!c16) continue;
-            sum += c16;
-            uint32_t key = (c16 << 16) | (0xFFFFu - i);
-            if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
-        }
-        s_key[0][threadIdx.x] = k1; s_key[1][threadIdx.x] = k2; s_sum[threadIdx.x] = sum;
-        __syncthreads();
-        for (int o = 128; o; o >>= 1) {
-            if ((int)threadIdx.x < o) {
-                uint32_t a1 = s_key[0][threadIdx.x], a2 = s_key[1][threadIdx.x];
-                uint32_t b1 = s_key[0][threadIdx.x + o], b2 = s_key[1][threadIdx.x + o];
-                uint32_t m1 = max(a1, b1);
-                uint32_t m2 = max(min(a1, b1), max(a2, b2));
-                s_key[0][threadIdx.x] = m1; s_key[1][threadIdx.x] = m2;
-                s_sum[threadIdx.x] += s_sum[threadIdx.x + o];
-            }
-            __syncthreads();
-        }
-        if (threadIdx.x == 0) {
-            k1 = s_key[0][0]; k2 = s_key[1][0];
-            uint16_t* o5 = a.out5 + (size_t)r * 5;
-            o5[0] = (uint16_t)s_sum[0];
-            o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
-            o5[2] = (uint16_t)(k1 >> 16);
-            o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
-            o5[4] = (uint16_t)(k2 >> 16);
-            if (a.rows) {
-                uint16_t* row = a.rows + (size_t)r * a.row_stride;
-                int n = 0, fit = (a.row_stride - 1) / 2;
-                for (uint32_t i = 0; i < n_targets && n < fit; i++)
-                    if (cnt[i] & 0xFFFFu) { row[1 + 2 * n] = (uint16_t)i; row[2 + 2 * n] = (uint16_t)cnt[i]; n++; }
-                row[0] = (uint16_t)n;
-            }
-        }
+        dense_result(a, r, cnt, n_targets, s_key, s_sum);
         __syncthreads();
     }
 }
@@ -359,6 +426,127 @@ int launch_query_dense(const TableView& t, const QueryArgs& a, const uint32_t* r
     if (max_list == 0 || n_scratch_blocks == 0) return 0;
     uint32_t g = max_list < n_scratch_blocks ? max_list : n_scratch_blocks;
     k_query_dense<<<g, 256, 0, s>>>(t, a, read_list, d_n_list, max_list, n_targets, scratch);
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// sharded table: owner-side probe of a k-mer list, requester-side vote from label lists
+// ---------------------------------------------------------------------------
+// 4 independent probes in flight per thread, as in k_query.
+template <bool STATS>
+__global__ void __launch_bounds__(256) k_probe_list(const TableView t, const uint64_t* __restrict__ hashes, uint64_t n,
+                                                    uint16_t* __restrict__ labels, unsigned long long* stats)
+{
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    uint32_t sectors = 0; unsigned long long lookups = 0;
+    for (uint64_t i0 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+        uint64_t e[4][4], home[4], q[4]; bool ok[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint64_t i = i0 + j * stride;
+            ok[j] = i < n;
+            const uint64_t h = ok[j] ? __ldg(hashes + i) : 0;
+            home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
+            if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (ok[j]) {
+                const uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &sectors : nullptr);
+                labels[i0 + j * stride] = (uint16_t)(l >= kLabelTomb ? kLabelNone : l);
+                if (STATS) { lookups++; sectors++; }
+            }
+        }
+    }
+    if (STATS) {
+        unsigned long long l = lookups, sc = sectors;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) { l += __shfl_xor_sync(0xFFFFFFFFu, l, o); sc += __shfl_xor_sync(0xFFFFFFFFu, sc, o); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(stats + 0, l); atomicAdd(stats + 1, sc); }
+    }
+}
+
+int launch_probe_list(const TableView& t, const uint64_t* hashes, uint64_t n, uint16_t* labels,
+                      unsigned long long* stats, cudaStream_t s)
+{
+    if (n == 0) return 0;
+    uint64_t g = (n + 1023) / 1024;
+    if (g > 148ull * 64) g = 148ull * 64;
+    if (stats) k_probe_list<true><<<(uint32_t)g, 256, 0, s>>>(t, hashes, n, labels, stats);
+    else       k_probe_list<false><<<(uint32_t)g, 256, 0, s>>>(t, hashes, n, labels, stats);
+    return (int)cudaGetLastError();
+}
+
+// one warp per read: the read's labels are n_shards contiguous runs
+__global__ void __launch_bounds__(kWarpsPerCta * 32) k_vote_lists(const QueryArgs a, const VoteArgs va)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t total_warps = gridDim.x * kWarpsPerCta;
+    for (uint32_t r = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); r < a.n_reads; r += total_warps) {
+        uint32_t acc_lab = kLabelNone, acc_cnt = 0;
+        int nacc = 0; bool overflow = false;
+        for (uint32_t g = 0; g < va.n_shards; g++) {
+            const size_t pi = (size_t)g * a.n_reads + r;
+            const uint32_t b = __ldg(va.pos + pi), e = __ldg(va.pos + pi + 1);
+            const uint16_t* src = va.src[g] + ((uint64_t)b - va.seg_base[g]);
+            for (uint32_t o = 0; o < e - b; o += 128) {
+                uint32_t lab[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t i = o + 32 * j + lane;
+                    lab[j] = i < e - b ? (uint32_t)__ldg(src + i) : kLabelNone;
+                    if (lab[j] >= kLabelTomb) lab[j] = kLabelNone;
+                }
+                vote4(lab, acc_lab, acc_cnt, nacc, overflow, lane);
+            }
+        }
+        finish_read(a, r, acc_lab, acc_cnt, nacc, overflow, lane);
+    }
+}
+
+int launch_vote_lists(const QueryArgs& a, const VoteArgs& va, cudaStream_t s)
+{
+    if (a.n_reads == 0) return 0;
+    uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
+    if (ctas > 148u * 64u) ctas = 148u * 64u;
+    k_vote_lists<<<ctas, kWarpsPerCta * 32, 0, s>>>(a, va);
+    return (int)cudaGetLastError();
+}
+
+// exact path for reads that hit more than 32 distinct targets: dense counters in global scratch
+__global__ void __launch_bounds__(256)
+k_vote_lists_dense(const QueryArgs a, const VoteArgs va, const uint32_t* read_list, const uint32_t* d_n_list,
+                   uint32_t max_list, uint32_t n_targets, uint32_t* scratch)
+{
+    __shared__ uint32_t s_key[2][256];
+    __shared__ uint32_t s_sum[256];
+    uint32_t n_list = d_n_list ? min(*d_n_list, max_list) : max_list;
+    uint32_t* cnt = scratch + (size_t)blockIdx.x * n_targets;
+    for (uint32_t li = blockIdx.x; li < n_list; li += gridDim.x) {
+        const uint32_t r = read_list ? read_list[li] : li;
+        for (uint32_t i = threadIdx.x; i < n_targets; i += blockDim.x) cnt[i] = 0;
+        __syncthreads();
+        for (uint32_t g = 0; g < va.n_shards; g++) {
+            const size_t pi = (size_t)g * a.n_reads + r;
+            const uint32_t b = va.pos[pi], e = va.pos[pi + 1];
+            const uint16_t* src = va.src[g] + ((uint64_t)b - va.seg_base[g]);
+            for (uint32_t i = threadIdx.x; i < e - b; i += blockDim.x) {
+                const uint32_t lab = src[i];
+                if (lab < kLabelTomb && lab < n_targets) atomicAdd(cnt + lab, 1u);
+            }
+        }
+        __syncthreads();
+        dense_result(a, r, cnt, n_targets, s_key, s_sum);
+        __syncthreads();
+    }
+}
+
+int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
+                            uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s)
+{
+    if (max_list == 0 || n_scratch_blocks == 0) return 0;
+    uint32_t g = max_list < n_scratch_blocks ? max_list : n_scratch_blocks;
+    k_vote_lists_dense<<<g, 256, 0, s>>>(a, va, read_list, d_n_list, max_list, n_targets, scratch);
     return (int)cudaGetLastError();
 }
 

@@ -22,6 +22,33 @@ struct QueryArgs {
     unsigned long long* stats;
 };
 
+// Sharded table: each read's mixed k-mers h = mix2k(canonical) are sent
+// to the shard that owns them.  Per read r and owner g the k-mers occupy
+//   dst[g][pos[g * n_reads + r] - seg_base[g] ...)      (pos = exclusive scan of counts, [owner][read])
+// and the labels come back at the same indices of src[g].
+constexpr int kMaxShards = 8;
+struct RouteArgs {
+    uint32_t        n_shards;
+    uint32_t*       counts;                 // count pass: u32[n_shards * n_reads]
+    const uint32_t* pos;                    // u32[n_shards * n_reads + 1]
+    uint64_t        seg_base[kMaxShards];   // pos of owner g's first k-mer (= pos[g * n_reads])
+    uint64_t*       dst[kMaxShards];        // route pass: owner g's segment (local send buffer or peer inbox)
+};
+int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s);
+// owner side: labels[i] = label of mixed k-mer hashes[i] (0xFFFF: absent or not discriminative)
+int launch_probe_list(const TableView& t, const uint64_t* hashes, uint64_t n, uint16_t* labels,
+                      unsigned long long* stats, cudaStream_t s);
+// requester side: vote from the returned label lists; overflowing reads go to ovf_list as in launch_query
+struct VoteArgs {
+    uint32_t        n_shards;
+    const uint32_t* pos;
+    uint64_t        seg_base[kMaxShards];
+    const uint16_t* src[kMaxShards];
+};
+int launch_vote_lists(const QueryArgs& a, const VoteArgs& va, cudaStream_t s);
+int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
+                            uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s);
+
 // fast path: one warp per read, votes kept in registers
 int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s);
 // exact path for any number of distinct targets: one CTA per listed read, dense

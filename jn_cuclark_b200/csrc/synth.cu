@@ -109,7 +109,7 @@ extern "C" int ccb_synth_db(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes,
     int rc = ccb_db_begin(h, total);
     if (rc) return rc;
     Table& t = h->table;
-    k_synth_db<<<148 * 16, 256, 0, h->db_stream>>>((uint64_t*)t.d_buckets, t.d_flags, t.d_status, t.d_counts, t.hp,
+    k_synth_db<<<148 * 16, 256, 0, h->db_stream>>>((uint64_t*)t.d_buckets - t.lo * kSlots, t.d_flags - t.lo / 16, t.d_status, t.d_counts, t.hp,
                                                     db_seed, n_genomes, genome_len, n_labels);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_synth_db launch: %s", cudaGetErrorString(e));

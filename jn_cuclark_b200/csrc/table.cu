@@ -68,16 +68,23 @@ static int grid_for(uint64_t n, int block)
     return (int)g;
 }
 
-int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s)
+int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s,
+                 uint32_t n_shards, uint32_t shard)
 {
+    if (n_shards == 0) n_shards = 1;
+    if (shard >= n_shards) return -10;
     if (k < 2 || k > 32) return -10;
     if (!(load_factor > 0.0 && load_factor <= 0.95)) load_factor = 0.5;
     uint64_t nb = (uint64_t)((double)expected_entries / (kSlots * load_factor)) + 1;
     uint64_t mn = min_buckets_for_k(k);
     if (nb < mn) nb = mn;
-    t.nb = nb;
-    t.n_phys = nb + kPadBuckets;
+    const uint64_t unit = 16ull * n_shards;               // shard boundaries on multiples of 16 buckets (flag words)
+    nb = (nb + unit - 1) / unit * unit;
+    const uint64_t per = nb / n_shards;
+    t.nb = nb; t.lo = per * shard;
+    t.n_phys = per + kPadBuckets;
     t.hp.nb = nb; t.hp.k = k; t.hp.shift = 64 - 2 * k; t.hp.mask = kmask(k);
+    t.hp.n_shards = n_shards; t.hp.shard = shard;
     t.finalized = false; t.n_inserted = 0;
     CK(cudaMalloc(&t.d_buckets, t.n_phys * sizeof(Bucket)));
     size_t fw = (t.n_phys + 15) / 16;
@@ -96,7 +103,7 @@ int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_lab
 {
     if (t.finalized || !t.d_buckets) return -11;
     if (n == 0) return 0;
-    k_insert_pairs<<<grid_for(n, 256), 256, 0, s>>>((uint64_t*)t.d_buckets, t.d_flags, t.d_status, t.d_counts,
+    k_insert_pairs<<<grid_for(n, 256), 256, 0, s>>>((uint64_t*)t.d_buckets - t.lo * kSlots, t.d_flags - t.lo / 16, t.d_status, t.d_counts,
                                                     t.hp, d_canon, d_labels, n);
     CK(cudaGetLastError());
     return 0;
@@ -109,13 +116,14 @@ int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
     if (t.finalized || !t.d_buckets) return -11;
     if (nbk == 0) return 0;
     int g = grid_for(nbk, 256);
-    uint64_t* b = (uint64_t*)t.d_buckets;
+    uint64_t* b = (uint64_t*)t.d_buckets - t.lo * kSlots;   // indexed by global bucket
+    uint32_t* fl = t.d_flags - t.lo / 16;
     if (key_bytes == 2)
-        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint16_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint16_t*)d_keys, d_labels);
     else if (key_bytes == 4)
-        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint32_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint32_t*)d_keys, d_labels);
     else if (key_bytes == 8)
-        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, t.d_flags, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint64_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint64_t*)d_keys, d_labels);
     else return -12;
     CK(cudaGetLastError());
     return 0;

@@ -25,7 +25,8 @@
 namespace ccb {
 
 struct TableView {
-    const ulonglong4* buckets;   // nb + kPadBuckets
+    const ulonglong4* buckets;   // indexed by GLOBAL home bucket: nb + kPadBuckets of them, or, for a
+                                 // shard, a pointer moved back by the shard's first bucket
     HashParams        hp;
 };
 
@@ -95,6 +96,7 @@ static __device__ __noinline__ void insert_one(uint64_t* buckets, uint32_t* flag
                            uint64_t canon, uint32_t label)
 {
     const uint64_t h = mix2k(canon, hp.k, hp.mask);
+    if (hp.n_shards > 1 && owner_of(h, hp.shift, hp.n_shards) != hp.shard) return;   // another shard's k-mer
     const uint64_t home = home_of(h, hp);
     const uint64_t q = key48_of(h) << 16;
     const uint64_t mine = q | label;
@@ -139,18 +141,21 @@ struct Table {
     uint32_t* d_flags   = nullptr;   // 2 bits per bucket while building
     uint32_t* d_status  = nullptr;   // [0] error (displacement overflow) [1] max displacement seen
     unsigned long long* d_counts = nullptr; // [0] inserted new [1] duplicates same label [2] tombstoned
-    uint64_t  nb = 0;                // home buckets
-    uint64_t  n_phys = 0;            // nb + kPadBuckets
+    uint64_t  nb = 0;                // home buckets of the whole table
+    uint64_t  lo = 0;                // first home bucket held here (0 unless sharded)
+    uint64_t  n_phys = 0;            // buckets held: nb (or nb / n_shards) + kPadBuckets
     HashParams hp{};
     bool      finalized = false;
     uint64_t  n_inserted = 0;        // entries occupying a slot (incl. tombstones)
 
-    TableView view() const { return TableView{reinterpret_cast<const ulonglong4*>(d_buckets), hp}; }
+    TableView view() const { return TableView{reinterpret_cast<const ulonglong4*>(d_buckets) - lo, hp}; }
     size_t bytes() const { return n_phys * sizeof(Bucket); }
 };
 
 // All return cudaError_t-compatible ints (0 = ok) or negative library codes.
-int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s);
+// expected_entries counts the WHOLE table; shard g of n_shards allocates 1/n_shards of the buckets
+int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s,
+                 uint32_t n_shards = 1, uint32_t shard = 0);
 int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_labels, uint64_t n, cudaStream_t s);
 // reference on-disk layout chunk (A9): buckets [r0, r0+nbk) with per-bucket
 // size (0 when skipped by -s sampling) and key offset relative to d_keys.

@@ -68,6 +68,11 @@ SYMBOLS = {
     "ccb_build_begin": (C.c_int, [_H, C.c_uint64, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint64]),
     "ccb_build_add_fasta": (C.c_int, [_H, C.c_char_p, C.c_uint64, C.c_uint16]),
     "ccb_build_end": (C.c_int, [_H, C.c_char_p, C.c_int, C.POINTER(BuildInfo)]),
+    "ccb_shard_config": (C.c_int, [_H, C.c_int, C.c_int]),
+    "ccb_shard_count": (C.c_int, [_H, _VP, _VP, C.c_uint32, C.c_int, _VP, _VP]),
+    "ccb_shard_route": (C.c_int, [_H, _VP, _VP, C.c_uint32, C.c_int, _VP, C.POINTER(C.c_uint64), C.POINTER(_VP), _VP]),
+    "ccb_shard_probe": (C.c_int, [_H, _VP, C.c_uint64, _VP, _VP, _VP]),
+    "ccb_shard_vote": (C.c_int, [_H, C.c_uint32, C.c_int, _VP, C.POINTER(C.c_uint64), C.POINTER(_VP), _VP, _VP, _VP]),
     "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
     "ccb_batch_buffers": (C.c_int, [_H, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
     "ccb_batch_submit": (C.c_int, [_H, C.c_int, C.c_uint32, C.c_uint64, C.c_int]),
@@ -244,6 +249,27 @@ class CuClarkDB:
                      d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
         self._ck(self._lib.ccb_query_device(self._h, d_offsets, d_containers, n_reads, d_final5,
                                             d_rows or None, d_stats or None, flags, stream or None))
+
+    # -- sharded table (row E2): raw device pointers, the caller owns buffers and the exchange ----
+    def shard_config(self, n_shards: int, shard: int):
+        self._ck(self._lib.ccb_shard_config(self._h, n_shards, shard))
+
+    def shard_count(self, d_offsets: int, d_containers: int, n_reads: int, n_shards: int, d_pos: int, stream: int = 0):
+        self._ck(self._lib.ccb_shard_count(self._h, d_offsets, d_containers, n_reads, n_shards, d_pos, stream or None))
+
+    def shard_route(self, d_offsets: int, d_containers: int, n_reads: int, n_shards: int, d_pos: int,
+                    seg_base, dst, stream: int = 0):
+        sb = (C.c_uint64 * n_shards)(*[int(x) for x in seg_base])
+        dp = (_VP * n_shards)(*[int(x) for x in dst])
+        self._ck(self._lib.ccb_shard_route(self._h, d_offsets, d_containers, n_reads, n_shards, d_pos, sb, dp, stream or None))
+
+    def shard_probe(self, d_hashes: int, n: int, d_labels: int, d_stats: int = 0, stream: int = 0):
+        self._ck(self._lib.ccb_shard_probe(self._h, d_hashes or None, n, d_labels or None, d_stats or None, stream or None))
+
+    def shard_vote(self, n_reads: int, n_shards: int, d_pos: int, seg_base, src, d_final5: int, d_rows: int = 0, stream: int = 0):
+        sb = (C.c_uint64 * n_shards)(*[int(x) for x in seg_base])
+        sp = (_VP * n_shards)(*[int(x) for x in src])
+        self._ck(self._lib.ccb_shard_vote(self._h, n_reads, n_shards, d_pos, sb, sp, d_final5, d_rows or None, stream or None))
 
     def l2_fetch_granularity(self) -> int:
         return self._lib.ccb_l2_fetch_granularity(self._h)

@@ -124,8 +124,23 @@ def test_list_of_files_mode(setup, oracle, tmp_path):
         assert open(str(tmp_path / out) + ".csv", "rb").read() == open(str(tmp_path / "w.csv"), "rb").read()
 
 
-def test_missing_db_fails_like_reference(setup, tmp_path):
+def test_missing_db_is_built_like_reference(setup, tmp_path):
+    """CuCLARK ctor (src/CuCLARK_hh.hh:306-311): no .sz/.ky/.lb for these targets -> build them, then classify.
+    Byte-level checks of the built files live in test_build_gpu.py."""
     s = setup
     r = subprocess.run([s["bin"], "-T", s["targets"], "-D", str(tmp_path), "-O", os.path.join(WORLD, "reads.fa"), "-R", str(tmp_path / "o")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-1500:]
+    assert "Starting the creation of the database of targets specific" in r.stderr and "successfully stored in database." in r.stderr
+    assert sorted(os.path.splitext(f)[1] for f in os.listdir(tmp_path) if f.startswith("db_central")) == [".ky", ".lb", ".sz"]
+
+
+def test_missing_db_and_unbuildable_targets_fail_like_reference(setup, tmp_path):
+    """A three-column targets file (label_c) is outside the rebuilt path: nothing to build from ->
+    the reference's 'Failed to find the database.' exit (src/CuCLARK_hh.hh:635-639)."""
+    s = setup
+    tp = tmp_path / "targets3.txt"
+    tp.write_text("".join(line.rstrip("\n") + "\tC0\n" for line in open(s["targets"])))
+    r = subprocess.run([s["bin"], "-T", str(tp), "-D", str(tmp_path), "-O", os.path.join(WORLD, "reads.fa"), "-R", str(tmp_path / "o")],
                        capture_output=True, text=True)
     assert r.returncode == 255 and "Failed to find the database." in r.stderr

@@ -1,0 +1,166 @@
+"""Sharded-table mode (row E2): count -> route -> probe -> vote gives the oracle's u16[5] / rows bit for bit,
+for 1, 2, 3 and 8 shards.  With one GPU all shards live on the same device and the exchange is a pointer
+hand-over; with two or more GPUs the same kernels run one process per GPU with NCCL all-to-all in between
+(jn_cuclark_b200/sharded.py)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HT_SMALL = 1000003
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _classify_sharded_one_gpu(shards, off, cont, extended=False):
+    """All shards on this device: shard g's handle probes segment g of the send buffer."""
+    import torch
+    G = len(shards)
+    n = off.size - 1
+    dev = torch.device("cuda", 0)
+    d_off = torch.from_numpy(np.ascontiguousarray(off, dtype=np.uint32).view(np.int32)).to(dev)
+    d_cont = torch.from_numpy(np.ascontiguousarray(cont, dtype=np.uint16).view(np.int16)).to(dev)
+    pos = torch.empty(G * n + 1, dtype=torch.int32, device=dev)
+    rq = shards[0]
+    rq.shard_count(d_off.data_ptr(), d_cont.data_ptr(), n, G, pos.data_ptr())
+    bounds = [int(pos[g * n].item()) & 0xFFFFFFFF for g in range(G + 1)]
+    total = bounds[G]
+    send = torch.full((max(total, 1),), -1, dtype=torch.int64, device=dev)
+    rq.shard_route(d_off.data_ptr(), d_cont.data_ptr(), n, G, pos.data_ptr(), bounds[:G],
+                   [send.data_ptr() + 8 * bounds[g] for g in range(G)])
+    labels = torch.full((max(total, 1),), 0x7777, dtype=torch.int16, device=dev)
+    stats = torch.zeros(2, dtype=torch.int64, device=dev)
+    for g in range(G):
+        shards[g].shard_probe(send.data_ptr() + 8 * bounds[g], bounds[g + 1] - bounds[g], labels.data_ptr() + 2 * bounds[g], stats.data_ptr())
+    out = torch.zeros(n * 5, dtype=torch.int16, device=dev)
+    rows = torch.zeros(n * rq.row_stride, dtype=torch.int16, device=dev) if extended else None
+    rq.shard_vote(n, G, pos.data_ptr(), bounds[:G], [labels.data_ptr() + 2 * bounds[g] for g in range(G)],
+                  out.data_ptr(), rows.data_ptr() if extended else 0)
+    torch.cuda.synchronize()
+    o = out.cpu().numpy().view(np.uint16).reshape(n, 5)
+    r = rows.cpu().numpy().view(np.uint16).reshape(n, rq.row_stride) if extended else None
+    return o, r, int(stats[0]), bounds
+
+
+def _make_shards(odb, G, k=31, ext=False):
+    from jn_cuclark_b200 import CuClarkDB
+    c, l = odb.pairs()
+    out = []
+    for g in range(G):
+        db = CuClarkDB(1, k, 1, len(odb.labels))
+        db.shard_config(G, g)
+        db.load_pairs(c, l)
+        if ext:
+            db.malloc(1, 1, True)
+        out.append(db)
+    return out
+
+
+@pytest.mark.parametrize("G", [1, 2, 3, 8])
+def test_sharded_equals_oracle(small_world, oracle, G):
+    odb = oracle.OracleDb.build(small_world["targets"], 31, HT_SMALL)
+    ir = oracle.IndexedReads(open(os.path.join(small_world["dir"], "reads.fa"), "rb").read())
+    off, cont = ir.pack(31)
+    want, wrows, nl = odb.query_packed(31, off, cont, row_stride=32)
+    shards = _make_shards(odb, G)
+    try:
+        entries = [s.db_info().entries for s in shards]
+        assert sum(entries) == odb.n                       # every k-mer lives on exactly one shard
+        if G > 1:
+            assert min(entries) > 0.5 * odb.n / G          # and the hash space is cut evenly
+        got, rows, lookups, bounds = _classify_sharded_one_gpu(shards, off, cont, extended=True)
+        assert lookups == nl and bounds[G] == nl
+        assert np.array_equal(got, want)
+        n = wrows[:, 0].astype(int)
+        for i in range(len(n)):
+            assert rows[i, 0] == n[i] and np.array_equal(rows[i, 1:1 + 2 * n[i]], wrows[i, 1:1 + 2 * n[i]])
+        # a whole-table query on a shard must refuse, not read out of bounds
+        if G > 1:
+            from jn_cuclark_b200 import CcbError
+            with pytest.raises(CcbError):
+                shards[0].classify_packed(off, cont)
+    finally:
+        for s in shards:
+            s.close()
+
+
+def test_sharded_long_reads_many_targets_and_empty(oracle, tmp_path):
+    import synth
+    tp, genomes, _ = synth.make_genomes(str(tmp_path / "g"), 48, 12000, seed=5, shared=False, quirks=False, same_label_pair=False)
+    odb = oracle.OracleDb.build(tp, 31, HT_SMALL)
+    rng = np.random.default_rng(9)
+    reads = []
+    for i in range(12):
+        s = genomes[i % 48][500:10500].copy()
+        m = rng.random(s.size) < 0.05
+        s[m] = synth.BASES[rng.integers(0, 4, size=int(m.sum()))]
+        reads.append((f"long{i}", s))
+    reads.append(("mosaic48", np.concatenate([g[100:180] for g in genomes])))      # > 32 targets: dense vote
+    reads.append(("short", genomes[0][:20]))                                       # no k-mer at all
+    reads.append(("allN", np.full(200, ord("N"), np.uint8)))
+    synth.write_reads_fasta(str(tmp_path / "r.fa"), reads)
+    ir = oracle.IndexedReads(open(str(tmp_path / "r.fa"), "rb").read())
+    off, cont = ir.pack(31)
+    want, _, nl = odb.query_packed(31, off, cont)
+    shards = _make_shards(odb, 4)
+    try:
+        got, _, lookups, _ = _classify_sharded_one_gpu(shards, off, cont)
+        assert lookups == nl and np.array_equal(got, want)
+        # empty batch
+        got0, _, l0, _ = _classify_sharded_one_gpu(shards, np.zeros(1, np.uint32), np.zeros(0, np.uint16))
+        assert got0.shape == (0, 5) and l0 == 0
+    finally:
+        for s in shards:
+            s.close()
+
+
+def _nccl_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from jn_cuclark_b200 import CuClarkDB
+    from jn_cuclark_b200.sharded import ShardedClassifier
+    G_, LG, L, NR, k = 6, 50000, 150, 4000 + 500 * rank, 31
+    whole = CuClarkDB(1, k, 1, G_, device=rank)
+    whole.synth_db(11, G_, LG, G_)
+    d_off, d_cont, _ = whole.synth_reads_packed(22, 11, rank * 100000, NR, L, G_, LG)
+    ref = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
+    whole.query_device(d_off, d_cont, NR, ref.data_ptr())
+    torch.cuda.synchronize()
+    part = CuClarkDB(1, k, 1, G_, device=rank)
+    part.shard_config(world, rank)
+    part.synth_db(11, G_, LG, G_)
+    sc = ShardedClassifier(part)
+    out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
+    sc.classify(d_off, d_cont, NR, out)
+    torch.cuda.synchronize()
+    same = bool(torch.equal(out, ref))
+    classified = int((ref.view(-1, 5)[:, 1] != 0).sum())
+    q.put((rank, same, classified, part.db_info().entries, whole.db_info().entries, sc.last["sent"]))
+    dist.barrier()
+    whole.device_free(d_off); whole.device_free(d_cont); whole.close(); part.close()
+    dist.destroy_process_group()
+
+
+def test_sharded_two_processes_nccl():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29700 + os.getpid() % 200
+    ps = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    got = sorted(q.get(timeout=600) for _ in ps)
+    for p in ps:
+        p.join(120)
+        assert p.exitcode == 0
+    assert all(g[1] for g in got), got                      # sharded == replicated, bit for bit
+    assert all(g[2] > 1000 for g in got)
+    assert got[0][3] + got[1][3] == got[0][4]               # shards partition the table
