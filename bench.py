@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--sample-reads", type=int, default=200_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--sharded", action="store_true",
+                    help="row E2: the table sharded over the N GPUs (k-mer all-to-all) instead of replicated")
+    ap.add_argument("--chunks", type=int, default=1, help="--sharded: split each rank's batch into this many exchange rounds")
     ap.add_argument("--kernel-only", action="store_true", help="profiling runs: resident-batch loop only (prints no bench line)")
     return ap.parse_args()
 
@@ -359,6 +362,123 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_sharded(args):
+    """Row E2: table sharded over the N GPUs, each step = count -> route -> all-to-all -> probe -> all-to-all -> vote
+    for every rank's own reads.  Same metric; `value` times device-resident batches, `e2e` adds the H2D/D2H copies."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from jn_cuclark_b200 import CuClarkDB
+    from jn_cuclark_b200.sharded import ShardedClassifier
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cudart = C.CDLL("libcudart.so")
+    k, G, LG, NR, L = args.k, args.genomes, args.genome_len, args.reads, args.read_len
+    db = CuClarkDB(1, k, 1, min(G, 65534), device=local, load_factor=args.load_factor)
+    db.shard_config(world, rank)
+    t0 = time.time(); n_kmers = db.synth_db(DB_SEED, G, LG, min(G, 65534)); t_db = time.time() - t0
+    info = db.db_info()
+    nch = max(1, args.chunks)
+    per = (NR + nch - 1) // nch
+    batches = []
+    for c in range(nch):
+        n = min(per, NR - c * per)
+        o, cc, nc = db.synth_reads_packed(READS_SEED, DB_SEED, rank * NR + c * per, n, L, G, LG)
+        batches.append((o, cc, nc, n, torch.zeros(n * 5, dtype=torch.int16, device="cuda")))
+    sc = ShardedClassifier(db)
+    stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+
+    def step(st=None):
+        for o, cc, nc, n, out in batches:
+            sc.classify(o, cc, n, out, stats=st)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); return float(t[0])
+
+    step(stats); torch.cuda.synchronize()
+    lookups_here = int(stats[0])                                   # probes served by this shard
+    tl = torch.tensor([lookups_here], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tl)
+    total_lookups = int(tl[0])
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local); sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record(); barrier()
+    ms = allmax(e0.elapsed_time(e1))
+    sampler.stop_flag = True; sampler.join()
+    value = total_lookups * args.steps / (ms * 1e-3)
+    # probe kernel alone (the HBM-bound one) on this rank's inbox of the last exchange
+    inbox, n_in = sc._keep[2], sc.last["received"]
+    lab = sc._keep[3]
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    db.shard_probe(inbox.data_ptr(), n_in, lab.data_ptr()); torch.cuda.synchronize()
+    p0.record(); db.shard_probe(inbox.data_ptr(), n_in, lab.data_ptr()); p1.record(); torch.cuda.synchronize()
+    probe_ms = p0.elapsed_time(p1)
+    # end to end: packed batches start in pinned host memory, results end there
+    host = []
+    for o, cc, nc, n, out in batches:
+        ho = torch.empty(n + 1, dtype=torch.int32).pin_memory(); hc = torch.empty(nc, dtype=torch.int16).pin_memory()
+        cudart.cudaMemcpy(C.c_void_p(ho.data_ptr()), C.c_void_p(o), C.c_size_t((n + 1) * 4), 2)
+        cudart.cudaMemcpy(C.c_void_p(hc.data_ptr()), C.c_void_p(cc), C.c_size_t(nc * 2), 2)
+        host.append((ho, hc, torch.empty(n * 5, dtype=torch.int16).pin_memory(),
+                     torch.empty(n + 1, dtype=torch.int32, device="cuda"), torch.empty(nc, dtype=torch.int16, device="cuda")))
+    h2d = sum(h[0].numel() * 4 + h[1].numel() * 2 for h in host); d2h = sum(h[2].numel() * 2 for h in host)
+
+    def e2e_step():
+        for (o, cc, nc, n, out), (ho, hc, hr, do, dc) in zip(batches, host):
+            do.copy_(ho, non_blocking=True); dc.copy_(hc, non_blocking=True)
+            sc.classify(do.data_ptr(), dc.data_ptr(), n, out)
+            hr.copy_(out, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e_step(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    t_e2e = allmax(time.perf_counter() - t0)
+    barrier()
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        achieved = n_in * 32 / (probe_ms * 1e-3) / 1e9
+        emit(json.dumps({
+            "metric": "kmer_lookups_per_s", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "reads_per_s": NR * world * args.steps / (ms * 1e-3),
+            "config": {"workload": f"cuCLARK full k={k}, synthetic {G} x {LG} bp DB ({n_kmers} {k}-mers), {NR} x {L} bp SE reads per GPU",
+                       "parallelism": f"table sharded x{world} by hash range, k-mer all-to-all (NCCL), {nch} exchange round(s) per step",
+                       "l2": "inputs larger than L2 (shard %.1f GB, random access)" % (info.bytes / 1e9),
+                       "shard_gb": info.bytes / 1e9, "shard_entries": info.entries, "db_build_s": t_db,
+                       "kmers_sent_per_step_rank0": sc.last["sent"] * nch, "probes_per_step_rank0": lookups_here},
+            "clocks": sampler.summary(),
+            "e2e": {"value": total_lookups * args.steps / t_e2e, "unit": "lookups/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e / args.steps},
+            "gpu_launches": 6 * nch * args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak_source": peak_src, "bytes_per_lookup": 32, "kernel": "ccb::k_probe_list", "probe_ms": probe_ms,
+                         "probes": n_in}}))
+    for o, cc, nc, n, out in batches:
+        db.device_free(o); db.device_free(cc)
+    db.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 _REAL_STDOUT = None
 
 
@@ -381,5 +501,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.sharded:
+        run_sharded(a)
     else:
         run_b200(a)

@@ -68,7 +68,9 @@ class ShardedClassifier:
         db.shard_probe(inbox.data_ptr(), n_in, lab_out.data_ptr(), stats.data_ptr() if stats is not None else 0, stream)
         lab_in = torch.empty(max(total, 1), dtype=torch.int16, device=self.dev)
         if G > 1:
-            dist.all_to_all_single(lab_in[:total], lab_out[:n_in], send_counts, recv_counts, group=self.group)
+            # NCCL has no 16-bit integer type: the labels travel as bytes
+            dist.all_to_all_single(lab_in[:total].view(torch.uint8), lab_out[:n_in].view(torch.uint8),
+                                   [2 * c for c in send_counts], [2 * c for c in recv_counts], group=self.group)
         else:
             lab_in[:total].copy_(lab_out[:n_in])
         src_ptr = [lab_in.data_ptr() + 2 * bounds_h[g] for g in range(G)]

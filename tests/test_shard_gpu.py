@@ -116,6 +116,15 @@ def test_sharded_long_reads_many_targets_and_empty(oracle, tmp_path):
 
 
 def _nccl_worker(rank, world, port, q):
+    try:
+        _nccl_worker_body(rank, world, port, q)
+    except BaseException as e:                       # report instead of leaving the parent to time out
+        import traceback
+        q.put((rank, False, -1, 0, 0, traceback.format_exc()[-1500:]))
+        raise
+
+
+def _nccl_worker_body(rank, world, port, q):
     import torch
     import torch.distributed as dist
     sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
@@ -157,7 +166,8 @@ def test_sharded_two_processes_nccl():
     ps = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in ps:
         p.start()
-    got = sorted(q.get(timeout=600) for _ in ps)
+    got = sorted(q.get(timeout=300) for _ in ps)
+    assert all(g[1] for g in got), got
     for p in ps:
         p.join(120)
         assert p.exitcode == 0
