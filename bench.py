@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--sharded", action="store_true",
                     help="row E2: the table sharded over the N GPUs (k-mer all-to-all) instead of replicated")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
+                    help="--sharded: NCCL all-to-all, or kernels storing into peer inboxes (CUDA IPC over NVLink)")
     ap.add_argument("--chunks", type=int, default=1, help="--sharded: split each rank's batch into this many exchange rounds")
     ap.add_argument("--kernel-only", action="store_true", help="profiling runs: resident-batch loop only (prints no bench line)")
     return ap.parse_args()
@@ -369,7 +371,7 @@ def run_sharded(args):
     import torch
     import torch.distributed as dist
     from jn_cuclark_b200 import CuClarkDB
-    from jn_cuclark_b200.sharded import ShardedClassifier
+    from jn_cuclark_b200.sharded import ShardedClassifier, PeerShardedClassifier
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -388,7 +390,13 @@ def run_sharded(args):
         n = min(per, NR - c * per)
         o, cc, nc = db.synth_reads_packed(READS_SEED, DB_SEED, rank * NR + c * per, n, L, G, LG)
         batches.append((o, cc, nc, n, torch.zeros(n * 5, dtype=torch.int16, device="cuda")))
-    sc = ShardedClassifier(db)
+    peer = args.exchange == "peer"
+    if peer:
+        # region size: the batch's k-mers spread evenly over the owners, with 25 % slack (mix2k is uniform)
+        cap = int(per * (L - k + 1) / world * 1.25) + 4096
+        sc = PeerShardedClassifier(db, cap)
+    else:
+        sc = ShardedClassifier(db)
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
 
     def step(st=None):
@@ -424,12 +432,32 @@ def run_sharded(args):
     sampler.stop_flag = True; sampler.join()
     value = total_lookups * args.steps / (ms * 1e-3)
     # probe kernel alone (the HBM-bound one) on this rank's inbox of the last exchange
-    inbox, n_in = sc._keep[2], sc.last["received"]
-    lab = sc._keep[3]
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    db.shard_probe(inbox.data_ptr(), n_in, lab.data_ptr()); torch.cuda.synchronize()
-    p0.record(); db.shard_probe(inbox.data_ptr(), n_in, lab.data_ptr()); p1.record(); torch.cuda.synchronize()
+    if peer:
+        assert not sc.overflowed(), "inbox capacity exceeded"
+        n_in = lookups_here // nch
+        barrier()
+        sc.stage_probe(); torch.cuda.synchronize()
+        p0.record(); sc.stage_probe(); p1.record(); torch.cuda.synchronize()
+        barrier()
+        sent_rank0 = lookups_here
+        # one more batch, phase by phase (count+route / probe / vote), barriers outside the brackets
+        o, cc, nc, n, out = batches[0]
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+        ev[0].record(); pos_ = sc.stage_route(o, cc, n); ev[1].record(); barrier()
+        ev[2].record(); sc.stage_probe(); ev[3].record(); barrier()
+        ev[4].record(); sc.stage_vote(pos_, n, out); ev[5].record(); torch.cuda.synchronize(); barrier()
+        phases = {"count_route_ms": ev[0].elapsed_time(ev[1]), "probe_ms": ev[2].elapsed_time(ev[3]),
+                  "vote_ms": ev[4].elapsed_time(ev[5]), "reads": n}
+    else:
+        inbox, n_in = sc._keep[2], sc.last["received"]
+        lab = sc._keep[3]
+        db.shard_probe(inbox.data_ptr(), n_in, lab.data_ptr()); torch.cuda.synchronize()
+        p0.record(); db.shard_probe(inbox.data_ptr(), n_in, lab.data_ptr()); p1.record(); torch.cuda.synchronize()
+        sent_rank0 = sc.last["sent"] * nch
     probe_ms = p0.elapsed_time(p1)
+    if not peer:
+        phases = None
     # end to end: packed batches start in pinned host memory, results end there
     host = []
     for o, cc, nc, n, out in batches:
@@ -461,10 +489,10 @@ def run_sharded(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic", "reads_per_s": NR * world * args.steps / (ms * 1e-3),
             "config": {"workload": f"cuCLARK full k={k}, synthetic {G} x {LG} bp DB ({n_kmers} {k}-mers), {NR} x {L} bp SE reads per GPU",
-                       "parallelism": f"table sharded x{world} by hash range, k-mer all-to-all (NCCL), {nch} exchange round(s) per step",
+                       "parallelism": f"table sharded x{world} by hash range, k-mer exchange = " + ("kernel stores into peer inboxes (CUDA IPC over NVLink)" if peer else "NCCL all-to-all") + f", {nch} exchange round(s) per step",
                        "l2": "inputs larger than L2 (shard %.1f GB, random access)" % (info.bytes / 1e9),
                        "shard_gb": info.bytes / 1e9, "shard_entries": info.entries, "db_build_s": t_db,
-                       "kmers_sent_per_step_rank0": sc.last["sent"] * nch, "probes_per_step_rank0": lookups_here},
+                       "kmers_sent_per_step_rank0": sent_rank0, "probes_per_step_rank0": lookups_here, "phases_rank0": phases},
             "clocks": sampler.summary(),
             "e2e": {"value": total_lookups * args.steps / t_e2e, "unit": "lookups/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e / args.steps},
@@ -472,6 +500,8 @@ def run_sharded(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src, "bytes_per_lookup": 32, "kernel": "ccb::k_probe_list", "probe_ms": probe_ms,
                          "probes": n_in}}))
+    if peer:
+        sc.close()
     for o, cc, nc, n, out in batches:
         db.device_free(o); db.device_free(cc)
     db.close()

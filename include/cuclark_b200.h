@@ -128,6 +128,27 @@ int  ccb_shard_route(ccb_handle* h, const void* d_offsets, const void* d_contain
 int  ccb_shard_probe(ccb_handle* h, const void* d_hashes, uint64_t n, void* d_labels, void* d_stats, void* stream);
 int  ccb_shard_vote(ccb_handle* h, uint32_t n_reads, int n_shards, const void* d_pos, const uint64_t* seg_base,
                     const void* const* src, void* d_final5, void* d_rows, void* stream);
+/* Peer exchange -- the same phases with NVLink stores instead of a collective and no host round trip:
+ * seg_base == NULL in ccb_shard_route / ccb_shard_vote means "segment g starts at d_pos[g*n_reads]",
+ * read on the device.
+ *   ccb_shard_route_peer   dst[g] = this rank's region (cap k-mers) of owner g's inbox, mapped here;
+ *                          afterwards *count_dst[g] (u64 in owner g's memory) = k-mers sent to g.
+ *                          More than cap k-mers for one owner: the excess is dropped, *d_error (u32) = 1
+ *   ccb_shard_probe_inbox  inbox = n_shards regions of cap k-mers, region s holds d_counts_in[s] (u64) k-mers
+ *                          from rank s; the label of inbox[s][i] is stored at lab_dst[s][i] (rank s's memory)
+ *   ccb_device_alloc / ccb_ipc_export / ccb_ipc_open / ccb_ipc_close
+ *                          buffers another process may map (cudaIpc*; 64-byte handles)
+ * A barrier across the ranks (any stream-ordered one, e.g. an NCCL all-reduce of one word) must separate
+ * route_peer from probe_inbox and probe_inbox from vote. */
+int  ccb_shard_route_peer(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
+                          int n_shards, const void* d_pos, void* const* dst, uint64_t cap,
+                          void* const* count_dst, void* d_error, void* stream);
+int  ccb_shard_probe_inbox(ccb_handle* h, int n_shards, const void* d_inbox, uint64_t cap, const void* d_counts_in,
+                           void* const* lab_dst, void* d_stats, void* stream);
+int  ccb_device_alloc(ccb_handle* h, uint64_t bytes, void** ptr);
+int  ccb_ipc_export(ccb_handle* h, void* ptr, unsigned char out[64]);
+int  ccb_ipc_open(ccb_handle* h, const unsigned char in[64], void** ptr);
+int  ccb_ipc_close(ccb_handle* h, void* ptr);
 
 /* CuClarkDB::malloc (src/CuClarkDB.cu:322-421): pinned host + device buffers for
  * every slot, owned by the library; the caller fills offsets/containers in

@@ -166,11 +166,18 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
         unsigned long long st_lookups = 0; uint32_t st_sectors = 0;
         uint32_t sent[kMaxShards];                 // MODE 1/2: k-mers of this read per owner so far
         uint64_t* out_g[kMaxShards];               // MODE 2: where this read's k-mers for owner g start
+        uint32_t room[kMaxShards];                 // MODE 2: how many of them fit (capacity-bounded peer inbox)
 #pragma unroll
         for (int g = 0; g < kMaxShards; g++) {
-            sent[g] = 0; out_g[g] = nullptr;
-            if (MODE == kModeRoute && g < (int)ra.n_shards)
-                out_g[g] = ra.dst[g] + (__ldg(ra.pos + (size_t)g * a.n_reads + r) - ra.seg_base[g]);
+            sent[g] = 0; out_g[g] = nullptr; room[g] = 0xFFFFFFFFu;
+            if (MODE == kModeRoute && g < (int)ra.n_shards) {
+                const uint64_t base = ra.derive_base ? (uint64_t)__ldg(ra.pos + (size_t)g * a.n_reads) : ra.seg_base[g];
+                out_g[g] = ra.dst[g] + (__ldg(ra.pos + (size_t)g * a.n_reads + r) - base);
+                if (ra.cap) {                            // elements of this read that still fit owner g's segment
+                    const uint64_t first = (uint64_t)(out_g[g] - ra.dst[g]);
+                    room[g] = first < ra.cap ? (uint32_t)min(ra.cap - first, (uint64_t)0xFFFFFFFFu) : 0u;
+                }
+            }
         }
 
         const int total_pos = 8 * (nslots - 1) - (k - 1);
@@ -274,7 +281,10 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
                                 if (og < (int)ra.n_shards) {
                                     const bool mine = home[j] == (uint64_t)og;
                                     const uint32_t b = __ballot_sync(0xFFFFFFFFu, mine);
-                                    if (MODE == kModeRoute && mine) out_g[og][sent[og] + __popc(b & lt)] = q[j];
+                                    if (MODE == kModeRoute && mine) {
+                                        const uint32_t at = sent[og] + __popc(b & lt);
+                                        if (at < room[og]) out_g[og][at] = q[j];
+                                    }
                                     sent[og] += __popc(b);
                                 }
                             }
@@ -301,6 +311,7 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
             if (lane == 0) { atomicAdd(a.stats + 0, l); atomicAdd(a.stats + 1, s); }
         }
     }
+    if (MODE == kModeRoute) __threadfence_system();      // the stores may have gone to a peer GPU
 }
 
 int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s)
@@ -488,7 +499,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_vote_lists(const QueryArg
         for (uint32_t g = 0; g < va.n_shards; g++) {
             const size_t pi = (size_t)g * a.n_reads + r;
             const uint32_t b = __ldg(va.pos + pi), e = __ldg(va.pos + pi + 1);
-            const uint16_t* src = va.src[g] + ((uint64_t)b - va.seg_base[g]);
+            const uint64_t base = va.derive_base ? (uint64_t)__ldg(va.pos + (size_t)g * a.n_reads) : va.seg_base[g];
+            const uint16_t* src = va.src[g] + ((uint64_t)b - base);
             for (uint32_t o = 0; o < e - b; o += 128) {
                 uint32_t lab[4];
 #pragma unroll
@@ -529,7 +541,8 @@ k_vote_lists_dense(const QueryArgs a, const VoteArgs va, const uint32_t* read_li
         for (uint32_t g = 0; g < va.n_shards; g++) {
             const size_t pi = (size_t)g * a.n_reads + r;
             const uint32_t b = va.pos[pi], e = va.pos[pi + 1];
-            const uint16_t* src = va.src[g] + ((uint64_t)b - va.seg_base[g]);
+            const uint64_t base = va.derive_base ? (uint64_t)va.pos[(size_t)g * a.n_reads] : va.seg_base[g];
+            const uint16_t* src = va.src[g] + ((uint64_t)b - base);
             for (uint32_t i = threadIdx.x; i < e - b; i += blockDim.x) {
                 const uint32_t lab = src[i];
                 if (lab < kLabelTomb && lab < n_targets) atomicAdd(cnt + lab, 1u);
@@ -547,6 +560,76 @@ int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32
     if (max_list == 0 || n_scratch_blocks == 0) return 0;
     uint32_t g = max_list < n_scratch_blocks ? max_list : n_scratch_blocks;
     k_vote_lists_dense<<<g, 256, 0, s>>>(a, va, read_list, d_n_list, max_list, n_targets, scratch);
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// peer exchange: counts to the owners, owner-side probe straight out of the inbox
+// ---------------------------------------------------------------------------
+struct CountDst { unsigned long long* p[kMaxShards]; };
+
+__global__ void k_post_counts(const uint32_t* __restrict__ pos, uint32_t n_reads, uint32_t n_shards, uint64_t cap,
+                              CountDst dst, uint32_t* error)
+{
+    const uint32_t g = threadIdx.x;
+    if (g >= n_shards) return;
+    const uint64_t n = (uint64_t)pos[(size_t)(g + 1) * n_reads] - pos[(size_t)g * n_reads];
+    if (cap && n > cap) { if (error) atomicExch(error, 1u); *dst.p[g] = cap; }
+    else *dst.p[g] = n;
+    __threadfence_system();
+}
+
+int launch_post_counts(const uint32_t* pos, uint32_t n_reads, uint32_t n_shards, uint64_t cap,
+                       unsigned long long* const* count_dst, uint32_t* error, cudaStream_t s)
+{
+    CountDst d{};
+    for (uint32_t g = 0; g < n_shards; g++) d.p[g] = count_dst[g];
+    k_post_counts<<<1, 32, 0, s>>>(pos, n_reads, n_shards, cap, d, error);
+    return (int)cudaGetLastError();
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(256) k_probe_inbox(const TableView t, const InboxArgs ia, unsigned long long* stats)
+{
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    uint32_t sectors = 0; unsigned long long lookups = 0;
+    for (uint32_t sidx = 0; sidx < ia.n_shards; sidx++) {
+        const uint64_t n = ia.counts_in[sidx];
+        const uint64_t* __restrict__ hashes = ia.inbox + (size_t)sidx * ia.cap;
+        uint16_t* __restrict__ labels = ia.lab_dst[sidx];
+        for (uint64_t i0 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+            uint64_t e[4][4], home[4], q[4]; bool ok[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint64_t i = i0 + j * stride;
+                ok[j] = i < n;
+                const uint64_t h = ok[j] ? hashes[i] : 0;
+                home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
+                if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if (ok[j]) {
+                    const uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &sectors : nullptr);
+                    labels[i0 + j * stride] = (uint16_t)(l >= kLabelTomb ? kLabelNone : l);
+                    if (STATS) { lookups++; sectors++; }
+                }
+            }
+        }
+    }
+    __threadfence_system();
+    if (STATS) {
+        unsigned long long l = lookups, sc = sectors;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) { l += __shfl_xor_sync(0xFFFFFFFFu, l, o); sc += __shfl_xor_sync(0xFFFFFFFFu, sc, o); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(stats + 0, l); atomicAdd(stats + 1, sc); }
+    }
+}
+
+int launch_probe_inbox(const TableView& t, const InboxArgs& ia, unsigned long long* stats, cudaStream_t s)
+{
+    if (stats) k_probe_inbox<true><<<148 * 32, 256, 0, s>>>(t, ia, stats);
+    else       k_probe_inbox<false><<<148 * 32, 256, 0, s>>>(t, ia, stats);
     return (int)cudaGetLastError();
 }
 

@@ -33,6 +33,8 @@ struct RouteArgs {
     const uint32_t* pos;                    // u32[n_shards * n_reads + 1]
     uint64_t        seg_base[kMaxShards];   // pos of owner g's first k-mer (= pos[g * n_reads])
     uint64_t*       dst[kMaxShards];        // route pass: owner g's segment (local send buffer or peer inbox)
+    uint32_t        derive_base;            // 1: take seg_base[g] from pos[g * n_reads] on the device (no host round trip)
+    uint64_t        cap;                    // elements a segment may hold; stores beyond it are dropped (0 = unlimited)
 };
 int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s);
 // owner side: labels[i] = label of mixed k-mer hashes[i] (0xFFFF: absent or not discriminative)
@@ -44,7 +46,22 @@ struct VoteArgs {
     const uint32_t* pos;
     uint64_t        seg_base[kMaxShards];
     const uint16_t* src[kMaxShards];
+    uint32_t        derive_base;
 };
+// Peer exchange (no NCCL on the data path): after the route pass, tell every owner how many k-mers it
+// got from this rank (count_dst[g] points into owner g's memory); over-capacity sets *error.
+int launch_post_counts(const uint32_t* pos, uint32_t n_reads, uint32_t n_shards, uint64_t cap,
+                       unsigned long long* const* count_dst, uint32_t* error, cudaStream_t s);
+// owner side over an inbox of n_shards regions of `cap` k-mers each, region s filled by rank s with
+// counts_in[s] k-mers; the label of inbox[s][i] is stored to lab_dst[s][i] (rank s's memory)
+struct InboxArgs {
+    uint32_t        n_shards;
+    uint64_t        cap;
+    const uint64_t* inbox;
+    const unsigned long long* counts_in;
+    uint16_t*       lab_dst[kMaxShards];
+};
+int launch_probe_inbox(const TableView& t, const InboxArgs& ia, unsigned long long* stats, cudaStream_t s);
 int launch_vote_lists(const QueryArgs& a, const VoteArgs& va, cudaStream_t s);
 int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
                             uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s);

@@ -16,6 +16,7 @@
 // The caller (jn_cuclark_b200/sharded.py, one process per GPU) owns the buffers and the exchange.
 #include "capi_internal.cuh"
 #include <cub/device/device_scan.cuh>
+#include <string.h>
 
 using namespace ccb;
 
@@ -69,12 +70,13 @@ extern "C" int ccb_shard_count(ccb_handle* h, const void* d_offsets, const void*
 extern "C" int ccb_shard_route(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
                                int n_shards, const void* d_pos, const uint64_t* seg_base, void* const* dst, void* stream)
 {
-    if (!h || !seg_base || !dst) return -1;
+    if (!h || !dst) return -1;
     USE_DEV(h);
     TableView tv; int rc = hp_for_routing(h, n_shards, tv); if (rc) return rc;
     QueryArgs a{}; a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
     RouteArgs ra{}; ra.n_shards = (uint32_t)n_shards; ra.pos = (const uint32_t*)d_pos;
-    for (int g = 0; g < n_shards; g++) { ra.seg_base[g] = seg_base[g]; ra.dst[g] = (uint64_t*)dst[g]; }
+    ra.derive_base = seg_base ? 0u : 1u;
+    for (int g = 0; g < n_shards; g++) { ra.seg_base[g] = seg_base ? seg_base[g] : 0; ra.dst[g] = (uint64_t*)dst[g]; }
     rc = launch_route(tv, a, ra, true, (cudaStream_t)stream);
     if (rc) return ccb_fail(h, rc, "route launch failed");
     return 0;
@@ -93,7 +95,7 @@ extern "C" int ccb_shard_probe(ccb_handle* h, const void* d_hashes, uint64_t n, 
 extern "C" int ccb_shard_vote(ccb_handle* h, uint32_t n_reads, int n_shards, const void* d_pos, const uint64_t* seg_base,
                               const void* const* src, void* d_final5, void* d_rows, void* stream)
 {
-    if (!h || !seg_base || !src) return -1;
+    if (!h || !src) return -1;
     if (n_shards < 1 || n_shards > kMaxShards) return ccb_fail(h, -60, "at most %d shards", kMaxShards);
     USE_DEV(h);
     cudaStream_t s = (cudaStream_t)stream;
@@ -107,10 +109,86 @@ extern "C" int ccb_shard_vote(ccb_handle* h, uint32_t n_reads, int n_shards, con
     QueryArgs a{}; a.n_reads = n_reads; a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
     a.ovf_list = h->q_ovf_list; a.ovf_count = h->q_ovf_count;
     VoteArgs va{}; va.n_shards = (uint32_t)n_shards; va.pos = (const uint32_t*)d_pos;
-    for (int g = 0; g < n_shards; g++) { va.seg_base[g] = seg_base[g]; va.src[g] = (const uint16_t*)src[g]; }
+    va.derive_base = seg_base ? 0u : 1u;
+    for (int g = 0; g < n_shards; g++) { va.seg_base[g] = seg_base ? seg_base[g] : 0; va.src[g] = (const uint16_t*)src[g]; }
     CU(h, cudaMemsetAsync(h->q_ovf_count, 0, 4, s));
     int rc = launch_vote_lists(a, va, s);
     if (!rc) rc = launch_vote_lists_dense(a, va, h->q_ovf_list, h->q_ovf_count, n_reads, (uint32_t)h->cfg.n_targets, h->q_dense, kDenseBlocks, s);
     if (rc) return ccb_fail(h, rc, "vote launch failed");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// peer exchange: the route kernel stores into the owners' inboxes, the probe kernel stores the labels
+// into the requesters' label boxes -- NVLink carries plain stores, no collective on the data path.
+// ---------------------------------------------------------------------------
+extern "C" int ccb_shard_route_peer(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
+                                    int n_shards, const void* d_pos, void* const* dst, uint64_t cap,
+                                    void* const* count_dst, void* d_error, void* stream)
+{
+    if (!h || !dst || !count_dst) return -1;
+    USE_DEV(h);
+    TableView tv; int rc = hp_for_routing(h, n_shards, tv); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    QueryArgs a{}; a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
+    RouteArgs ra{}; ra.n_shards = (uint32_t)n_shards; ra.pos = (const uint32_t*)d_pos; ra.derive_base = 1; ra.cap = cap;
+    for (int g = 0; g < n_shards; g++) ra.dst[g] = (uint64_t*)dst[g];
+    rc = launch_route(tv, a, ra, true, s);
+    if (!rc) rc = launch_post_counts((const uint32_t*)d_pos, n_reads, (uint32_t)n_shards, cap,
+                                     (unsigned long long* const*)count_dst, (uint32_t*)d_error, s);
+    if (rc) return ccb_fail(h, rc, "route launch failed");
+    return 0;
+}
+
+extern "C" int ccb_shard_probe_inbox(ccb_handle* h, int n_shards, const void* d_inbox, uint64_t cap, const void* d_counts_in,
+                                     void* const* lab_dst, void* d_stats, void* stream)
+{
+    if (!h || !lab_dst) return -1;
+    if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    if (n_shards < 1 || n_shards > kMaxShards) return ccb_fail(h, -60, "at most %d shards", kMaxShards);
+    USE_DEV(h);
+    InboxArgs ia{}; ia.n_shards = (uint32_t)n_shards; ia.cap = cap; ia.inbox = (const uint64_t*)d_inbox;
+    ia.counts_in = (const unsigned long long*)d_counts_in;
+    for (int g = 0; g < n_shards; g++) ia.lab_dst[g] = (uint16_t*)lab_dst[g];
+    int rc = launch_probe_inbox(h->table.view(), ia, (unsigned long long*)d_stats, (cudaStream_t)stream);
+    if (rc) return ccb_fail(h, rc, "probe launch failed");
+    return 0;
+}
+
+extern "C" int ccb_device_alloc(ccb_handle* h, uint64_t bytes, void** ptr)
+{
+    if (!h || !ptr) return -1;
+    USE_DEV(h);
+    CU(h, cudaMalloc(ptr, bytes ? bytes : 1));
+    return 0;
+}
+
+// CUDA IPC: 64-byte handle of a ccb_device_alloc'ed buffer, opened by the process that drives a peer GPU
+extern "C" int ccb_ipc_export(ccb_handle* h, void* ptr, unsigned char out[64])
+{
+    if (!h || !ptr || !out) return -1;
+    USE_DEV(h);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t mh;
+    CU(h, cudaIpcGetMemHandle(&mh, ptr));
+    memcpy(out, &mh, 64);
+    return 0;
+}
+
+extern "C" int ccb_ipc_open(ccb_handle* h, const unsigned char in[64], void** ptr)
+{
+    if (!h || !in || !ptr) return -1;
+    USE_DEV(h);
+    cudaIpcMemHandle_t mh;
+    memcpy(&mh, in, 64);
+    CU(h, cudaIpcOpenMemHandle(ptr, mh, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+
+extern "C" int ccb_ipc_close(ccb_handle* h, void* ptr)
+{
+    if (!h || !ptr) return -1;
+    USE_DEV(h);
+    CU(h, cudaIpcCloseMemHandle(ptr));
     return 0;
 }

@@ -73,6 +73,12 @@ SYMBOLS = {
     "ccb_shard_route": (C.c_int, [_H, _VP, _VP, C.c_uint32, C.c_int, _VP, C.POINTER(C.c_uint64), C.POINTER(_VP), _VP]),
     "ccb_shard_probe": (C.c_int, [_H, _VP, C.c_uint64, _VP, _VP, _VP]),
     "ccb_shard_vote": (C.c_int, [_H, C.c_uint32, C.c_int, _VP, C.POINTER(C.c_uint64), C.POINTER(_VP), _VP, _VP, _VP]),
+    "ccb_shard_route_peer": (C.c_int, [_H, _VP, _VP, C.c_uint32, C.c_int, _VP, C.POINTER(_VP), C.c_uint64, C.POINTER(_VP), _VP, _VP]),
+    "ccb_shard_probe_inbox": (C.c_int, [_H, C.c_int, _VP, C.c_uint64, _VP, C.POINTER(_VP), _VP, _VP]),
+    "ccb_device_alloc": (C.c_int, [_H, C.c_uint64, C.POINTER(_VP)]),
+    "ccb_ipc_export": (C.c_int, [_H, _VP, C.c_char_p]),
+    "ccb_ipc_open": (C.c_int, [_H, C.c_char_p, C.POINTER(_VP)]),
+    "ccb_ipc_close": (C.c_int, [_H, _VP]),
     "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
     "ccb_batch_buffers": (C.c_int, [_H, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
     "ccb_batch_submit": (C.c_int, [_H, C.c_int, C.c_uint32, C.c_uint64, C.c_int]),
@@ -259,7 +265,7 @@ class CuClarkDB:
 
     def shard_route(self, d_offsets: int, d_containers: int, n_reads: int, n_shards: int, d_pos: int,
                     seg_base, dst, stream: int = 0):
-        sb = (C.c_uint64 * n_shards)(*[int(x) for x in seg_base])
+        sb = (C.c_uint64 * n_shards)(*[int(x) for x in seg_base]) if seg_base is not None else None
         dp = (_VP * n_shards)(*[int(x) for x in dst])
         self._ck(self._lib.ccb_shard_route(self._h, d_offsets, d_containers, n_reads, n_shards, d_pos, sb, dp, stream or None))
 
@@ -267,9 +273,38 @@ class CuClarkDB:
         self._ck(self._lib.ccb_shard_probe(self._h, d_hashes or None, n, d_labels or None, d_stats or None, stream or None))
 
     def shard_vote(self, n_reads: int, n_shards: int, d_pos: int, seg_base, src, d_final5: int, d_rows: int = 0, stream: int = 0):
-        sb = (C.c_uint64 * n_shards)(*[int(x) for x in seg_base])
+        sb = (C.c_uint64 * n_shards)(*[int(x) for x in seg_base]) if seg_base is not None else None
         sp = (_VP * n_shards)(*[int(x) for x in src])
         self._ck(self._lib.ccb_shard_vote(self._h, n_reads, n_shards, d_pos, sb, sp, d_final5, d_rows or None, stream or None))
+
+    def shard_route_peer(self, d_offsets: int, d_containers: int, n_reads: int, n_shards: int, d_pos: int,
+                         dst, cap: int, count_dst, d_error: int = 0, stream: int = 0):
+        dp = (_VP * n_shards)(*[int(x) for x in dst])
+        cp = (_VP * n_shards)(*[int(x) for x in count_dst])
+        self._ck(self._lib.ccb_shard_route_peer(self._h, d_offsets, d_containers, n_reads, n_shards, d_pos, dp, cap, cp,
+                                                d_error or None, stream or None))
+
+    def shard_probe_inbox(self, n_shards: int, d_inbox: int, cap: int, d_counts_in: int, lab_dst, d_stats: int = 0, stream: int = 0):
+        lp = (_VP * n_shards)(*[int(x) for x in lab_dst])
+        self._ck(self._lib.ccb_shard_probe_inbox(self._h, n_shards, d_inbox, cap, d_counts_in, lp, d_stats or None, stream or None))
+
+    def device_alloc(self, nbytes: int) -> int:
+        p = _VP()
+        self._ck(self._lib.ccb_device_alloc(self._h, nbytes, C.byref(p)))
+        return p.value
+
+    def ipc_export(self, ptr: int) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._ck(self._lib.ccb_ipc_export(self._h, ptr, buf))
+        return buf.raw
+
+    def ipc_open(self, handle: bytes) -> int:
+        p = _VP()
+        self._ck(self._lib.ccb_ipc_open(self._h, handle, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, ptr: int):
+        self._ck(self._lib.ccb_ipc_close(self._h, ptr))
 
     def l2_fetch_granularity(self) -> int:
         return self._lib.ccb_l2_fetch_granularity(self._h)

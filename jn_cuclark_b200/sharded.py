@@ -80,3 +80,107 @@ class ShardedClassifier:
         # keep the temporaries alive until the stream has consumed them
         self._keep = (pos, send, inbox, lab_out, lab_in)
         return out5
+
+
+class PeerShardedClassifier:
+    """Same phases, but the exchange is done BY the kernels: `k_query<route>` stores each k-mer straight into
+    the owner GPU's inbox and `k_probe_inbox` stores each label straight into the requester GPU's label box
+    (peer memory mapped with CUDA IPC, plain stores over NVLink / NVSwitch).  No collective moves data, the
+    host never learns the segment sizes (they travel as device words), and nothing on the host synchronises
+    per batch; two one-word all-reduces per batch act as stream-ordered barriers between the phases.
+
+    cap = k-mers one rank may send to one owner per batch (the inbox region size); a batch that needs
+    more sets `error` and must be re-run in smaller pieces."""
+
+    def __init__(self, db: CuClarkDB, cap: int, group=None, peers=None):
+        self.db, self.cap, self.group = db, int(cap), group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        G = self.world if peers is None else len(peers["inbox"])
+        self.G = G
+        self._opened = []
+        if peers is None:
+            # own buffers (plain cudaMalloc so that they can be exported), zeroed counts
+            self.inbox = db.device_alloc(G * self.cap * 8)
+            self.labbox = db.device_alloc(G * self.cap * 2)
+            self.counts_in = db.device_alloc(G * 8)
+            self._owned = [self.inbox, self.labbox, self.counts_in]
+            mine = (db.ipc_export(self.inbox), db.ipc_export(self.labbox), db.ipc_export(self.counts_in), self.cap)
+            allh = [None] * G
+            if G > 1:
+                dist.all_gather_object(allh, mine, group=group)
+            else:
+                allh[0] = mine
+            if any(hd[3] != self.cap for hd in allh):
+                raise ValueError(f"every rank must use the same inbox region size, got {[hd[3] for hd in allh]}")
+            self.peer_inbox, self.peer_labbox, self.peer_counts = [], [], []
+            for g in range(G):
+                if g == self.rank:
+                    ptrs = (self.inbox, self.labbox, self.counts_in)
+                else:
+                    ptrs = tuple(db.ipc_open(hd) for hd in allh[g][:3])
+                    self._opened.extend(ptrs)
+                self.peer_inbox.append(ptrs[0]); self.peer_labbox.append(ptrs[1]); self.peer_counts.append(ptrs[2])
+        else:
+            # explicit pointer tables (tests: every shard on one device of one process)
+            self._owned = []
+            self.rank = peers["rank"]
+            self.peer_inbox, self.peer_labbox, self.peer_counts = peers["inbox"], peers["labbox"], peers["counts"]
+            self.inbox, self.labbox, self.counts_in = self.peer_inbox[self.rank], self.peer_labbox[self.rank], self.peer_counts[self.rank]
+        self.error = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self._bar = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self._keep = None
+
+    def barrier(self):
+        if self.world > 1 and dist.is_initialized():
+            dist.all_reduce(self._bar, group=self.group)
+
+    # the three stages are separate so that a single-process test can interleave several "ranks"
+    def stage_route(self, d_offsets, d_containers, n_reads):
+        G, r, cap, db = self.G, self.rank, self.cap, self.db
+        stream = torch.cuda.current_stream().cuda_stream
+        pos = torch.empty(G * n_reads + 1, dtype=torch.int32, device=self.dev)
+        db.shard_count(d_offsets, d_containers, n_reads, G, pos.data_ptr(), stream)
+        db.shard_route_peer(d_offsets, d_containers, n_reads, G, pos.data_ptr(),
+                            [self.peer_inbox[g] + r * cap * 8 for g in range(G)], cap,
+                            [self.peer_counts[g] + r * 8 for g in range(G)], self.error.data_ptr(), stream)
+        self._keep = pos
+        return pos
+
+    def stage_probe(self, stats=None):
+        G, r, cap = self.G, self.rank, self.cap
+        stream = torch.cuda.current_stream().cuda_stream
+        self.db.shard_probe_inbox(G, self.inbox, cap, self.counts_in, [self.peer_labbox[s] + r * cap * 2 for s in range(G)],
+                                  stats.data_ptr() if stats is not None else 0, stream)
+
+    def stage_vote(self, pos, n_reads, out5, rows=None):
+        G, cap = self.G, self.cap
+        stream = torch.cuda.current_stream().cuda_stream
+        self.db.shard_vote(n_reads, G, pos.data_ptr(), None, [self.labbox + g * cap * 2 for g in range(G)],
+                           out5.data_ptr(), rows.data_ptr() if rows is not None else 0, stream)
+
+    def classify(self, d_offsets: int, d_containers: int, n_reads: int, out5: torch.Tensor,
+                 rows: torch.Tensor | None = None, stats: torch.Tensor | None = None) -> torch.Tensor:
+        pos = self.stage_route(d_offsets, d_containers, n_reads)
+        self.barrier()                       # every rank's k-mers and counts have landed
+        self.stage_probe(stats)
+        self.barrier()                       # every owner's labels have landed
+        self.stage_vote(pos, n_reads, out5, rows)
+        return out5
+
+    def overflowed(self) -> bool:
+        """True if some batch since the last call sent more than cap k-mers to one owner (host sync)."""
+        v = bool(int(self.error.item()))
+        self.error.zero_()
+        return v
+
+    def close(self):
+        torch.cuda.synchronize()
+        if self.world > 1 and dist.is_initialized():
+            dist.barrier(group=self.group)
+        for p in self._opened:
+            self.db.ipc_close(p)
+        for p in self._owned:
+            self.db.device_free(p)
+        self._opened, self._owned = [], []

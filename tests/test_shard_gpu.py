@@ -115,6 +115,56 @@ def test_sharded_long_reads_many_targets_and_empty(oracle, tmp_path):
             s.close()
 
 
+def test_peer_exchange_kernels_one_gpu(small_world, oracle):
+    """The peer-store exchange with every shard on this one device: route kernels store into the owners'
+    inbox regions, probe kernels store labels into the requesters' label boxes, counts travel as device words."""
+    import torch
+    from jn_cuclark_b200.sharded import PeerShardedClassifier
+    G = 3
+    odb = oracle.OracleDb.build(small_world["targets"], 31, HT_SMALL)
+    ir = oracle.IndexedReads(open(os.path.join(small_world["dir"], "reads.fa"), "rb").read())
+    off, cont = ir.pack(31)
+    n = off.size - 1
+    want, _, nl = odb.query_packed(31, off, cont)
+    shards = _make_shards(odb, G)
+    dev = torch.device("cuda", 0)
+    cap = int(nl)                                           # worst case: everything to one owner
+    inbox = [torch.zeros(G * cap, dtype=torch.int64, device=dev) for _ in range(G)]
+    labbox = [torch.zeros(G * cap, dtype=torch.int16, device=dev) for _ in range(G)]
+    counts = [torch.zeros(G, dtype=torch.int64, device=dev) for _ in range(G)]
+    peers = lambda r: {"rank": r, "inbox": [t.data_ptr() for t in inbox], "labbox": [t.data_ptr() for t in labbox],
+                       "counts": [t.data_ptr() for t in counts]}
+    try:
+        cls = [PeerShardedClassifier(shards[r], cap, peers=peers(r)) for r in range(G)]
+        # "rank" r classifies the r-th third of the reads
+        cut = [0, n // 3, 2 * n // 3, n]
+        parts = []
+        for r in range(G):
+            a, b = cut[r], cut[r + 1]
+            o = (off[a:b + 1] - off[a]).astype(np.uint32)
+            c = cont[int(off[a]):int(off[b])]
+            parts.append((torch.from_numpy(o.view(np.int32)).to(dev), torch.from_numpy(np.ascontiguousarray(c).view(np.int16)).to(dev), b - a))
+        stats = torch.zeros(2, dtype=torch.int64, device=dev)
+        pos = [cls[r].stage_route(parts[r][0].data_ptr(), parts[r][1].data_ptr(), parts[r][2]) for r in range(G)]
+        for r in range(G):
+            cls[r].stage_probe(stats)
+        outs = [torch.zeros(parts[r][2] * 5, dtype=torch.int16, device=dev) for r in range(G)]
+        for r in range(G):
+            cls[r].stage_vote(pos[r], parts[r][2], outs[r])
+        torch.cuda.synchronize()
+        got = np.concatenate([o.cpu().numpy().view(np.uint16).reshape(-1, 5) for o in outs])
+        assert int(stats[0]) == nl and not any(c.overflowed() for c in cls)
+        assert np.array_equal(got, want)
+        assert int(sum(int(c.sum()) for c in counts)) == nl
+        # capacity too small: flagged, never written out of bounds
+        small = [PeerShardedClassifier(shards[r], 1000, peers=peers(r)) for r in range(G)]
+        small[0].stage_route(parts[0][0].data_ptr(), parts[0][1].data_ptr(), parts[0][2])
+        assert small[0].overflowed()
+    finally:
+        for s_ in shards:
+            s_.close()
+
+
 def _nccl_worker(rank, world, port, q):
     try:
         _nccl_worker_body(rank, world, port, q)
@@ -148,6 +198,15 @@ def _nccl_worker_body(rank, world, port, q):
     sc.classify(d_off, d_cont, NR, out)
     torch.cuda.synchronize()
     same = bool(torch.equal(out, ref))
+    # the same through the peer-store exchange (CUDA IPC inboxes, no collective on the data path)
+    from jn_cuclark_b200.sharded import PeerShardedClassifier
+    pc = PeerShardedClassifier(part, cap=(4000 + 500 * world) * (L - k + 1))      # the same on every rank
+    for _ in range(3):                                   # buffers are reused batch after batch
+        out2 = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
+        pc.classify(d_off, d_cont, NR, out2)
+    torch.cuda.synchronize()
+    same = same and bool(torch.equal(out2, ref)) and not pc.overflowed()
+    pc.close()
     classified = int((ref.view(-1, 5)[:, 1] != 0).sum())
     q.put((rank, same, classified, part.db_info().entries, whole.db_info().entries, sc.last["sent"]))
     dist.barrier()
