@@ -2,6 +2,9 @@
 #include "../../include/cuclark_b200.h"
 #include "capi_internal.cuh"
 #include "dbbuild.cuh"
+#include <algorithm>
+#include <memory>
+#include <thread>
 
 #include <stdarg.h>
 #include <stdio.h>
@@ -201,53 +204,80 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
     FILE* fl = fopen((p + ".lb").c_str(), "rb");
     if (!fl) { fclose(fs); fclose(fk); return ccb_fail(h, -20, "Failed to open %s.lb", prefix); }
 
-    std::vector<uint8_t> sz(htsize);
-    if (fread(sz.data(), 1, htsize, fs) != htsize) { fclose(fs); fclose(fk); fclose(fl); return ccb_fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
+    std::unique_ptr<uint8_t[]> sz(new uint8_t[htsize]);
+    if (fread(sz.get(), 1, htsize, fs) != htsize) { fclose(fs); fclose(fk); fclose(fl); return ccb_fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
     fclose(fs);
+    // per block of 64 Ki buckets: keys and non-empty buckets (all host threads), then the blocks are
+    // grouped into chunks the staging buffers can hold
+    const uint64_t BS = 1ull << 16;
+    const uint64_t nblk = (htsize + BS - 1) / BS;
+    std::vector<uint64_t> blk_keys(nblk), blk_nz(nblk), blk_rank(nblk + 1, 0), blk_kept(nblk, 0);
+    const unsigned nthr = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    auto par = [&](auto&& fn) {
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nthr; t++) th.emplace_back([&, t] { for (uint64_t b = t; b < nblk; b += nthr) fn(b); });
+        for (auto& x : th) x.join();
+    };
+    par([&](uint64_t b) {
+        const uint64_t lo = b * BS, hi = std::min(htsize, lo + BS);
+        uint64_t k = 0, z = 0;
+        for (uint64_t i = lo; i < hi; i++) { k += sz[i]; z += sz[i] != 0; }
+        blk_keys[b] = k; blk_nz[b] = z;
+    });
+    for (uint64_t b = 0; b < nblk; b++) blk_rank[b + 1] = blk_rank[b] + blk_nz[b];
     // choose buckets (src/CuClarkDB.cu:503-513): keep every sampling-th non-empty bucket
     const bool all = sampling <= 1;
-    uint64_t n_keep = 0; uint32_t nonzero = 0;
-    std::vector<uint8_t> keep;                 // size used on device (0 = skipped)
-    if (!all) keep.assign(htsize, 0);
-    for (uint64_t b = 0; b < htsize; b++) if (sz[b]) {
-        nonzero++;
-        bool k2 = all || (nonzero % sampling) == 0;
-        if (k2) n_keep += sz[b];
-        if (!all && k2) keep[b] = sz[b];
+    uint64_t n_keep = 0;
+    if (all) { for (uint64_t b = 0; b < nblk; b++) n_keep += blk_keys[b]; }
+    else {
+        par([&](uint64_t b) {
+            const uint64_t lo = b * BS, hi = std::min(htsize, lo + BS);
+            uint64_t rank = blk_rank[b], k = 0;
+            for (uint64_t i = lo; i < hi; i++) if (sz[i]) { rank++; if (rank % sampling == 0) k += sz[i]; }
+            blk_kept[b] = k;
+        });
+        for (uint64_t b = 0; b < nblk; b++) n_keep += blk_kept[b];
     }
-    const uint8_t* ksz = all ? sz.data() : keep.data();
     int rc = ccb_db_begin(h, n_keep);
     if (rc) { fclose(fk); fclose(fl); return rc; }
 
-    const uint32_t CB = 1u << 24;               // buckets per chunk
-    const uint64_t CK = 1ull << 25;             // max keys per chunk
-    uint8_t* d_sz = nullptr; uint32_t* d_off = nullptr; void* d_keys = nullptr; uint16_t* d_lab = nullptr;
-    uint32_t* h_off = nullptr; void* h_keys = nullptr; uint16_t* h_lab = nullptr;
-    CU(h, cudaMalloc(&d_sz, CB)); CU(h, cudaMalloc(&d_off, CB * 4ull));
-    CU(h, cudaMalloc(&d_keys, (CK + 256) * key_bytes)); CU(h, cudaMalloc(&d_lab, (CK + 256) * 2));
-    CU(h, cudaMallocHost(&h_off, CB * 4ull));
-    CU(h, cudaMallocHost(&h_keys, (CK + 256) * key_bytes)); CU(h, cudaMallocHost(&h_lab, (CK + 256) * 2));
-    uint64_t b = 0; rc = 0;
-    while (b < htsize && !rc) {
-        uint32_t nb = 0; uint64_t nk = 0;       // nk counts ALL keys of the chunk (file order)
-        while (b + nb < htsize && nb < CB && nk + sz[b + nb] <= CK + 255) {
-            h_off[nb] = (uint32_t)nk; nk += sz[b + nb]; nb++;
-            if (nk >= CK) break;
-        }
-        if (nk) {
-            if (fread(h_keys, (size_t)key_bytes, nk, fk) != nk || fread(h_lab, 2, nk, fl) != nk) { rc = -22; break; }
-            cudaMemcpyAsync(d_keys, h_keys, nk * key_bytes, cudaMemcpyHostToDevice, h->db_stream);
-            cudaMemcpyAsync(d_lab, h_lab, nk * 2, cudaMemcpyHostToDevice, h->db_stream);
-            cudaMemcpyAsync(d_sz, ksz + b, nb, cudaMemcpyHostToDevice, h->db_stream);
-            cudaMemcpyAsync(d_off, h_off, nb * 4ull, cudaMemcpyHostToDevice, h->db_stream);
-            rc = table_insert_ref_chunk(h->table, htsize, b, nb, d_sz, d_off, d_keys, key_bytes, d_lab, h->db_stream);
-            cudaStreamSynchronize(h->db_stream);
-        }
-        b += nb;
+    const uint32_t CB = 1u << 24;               // max buckets per chunk
+    const uint64_t CK = 1ull << 25;             // max keys per chunk (a block holds at most 255 * 64 Ki < CK)
+    const size_t scratch_bytes = table_ref_chunk_scratch(CB);
+    uint32_t* d_off = nullptr; uint32_t* d_rank = nullptr; void* d_scratch = nullptr;
+    CU(h, cudaMalloc(&d_off, CB * 4ull)); CU(h, cudaMalloc(&d_rank, CB * 4ull)); CU(h, cudaMalloc(&d_scratch, scratch_bytes));
+    struct Stage { uint8_t* d_sz = nullptr; void* d_keys = nullptr; uint16_t* d_lab = nullptr;
+                   uint8_t* h_sz = nullptr; void* h_keys = nullptr; uint16_t* h_lab = nullptr; cudaEvent_t done = nullptr; bool busy = false; } st[2];
+    for (auto& x : st) {
+        CU(h, cudaMalloc(&x.d_sz, CB)); CU(h, cudaMalloc(&x.d_keys, CK * key_bytes)); CU(h, cudaMalloc(&x.d_lab, CK * 2));
+        CU(h, cudaMallocHost(&x.h_sz, CB)); CU(h, cudaMallocHost(&x.h_keys, CK * key_bytes)); CU(h, cudaMallocHost(&x.h_lab, CK * 2));
+        CU(h, cudaEventCreateWithFlags(&x.done, cudaEventDisableTiming));
     }
+    uint64_t blk = 0; rc = 0; int cur = 0;
+    while (blk < nblk && !rc) {
+        uint64_t nk = 0, e = blk;
+        while (e < nblk && (e - blk) * BS < CB && nk + blk_keys[e] <= CK) { nk += blk_keys[e]; e++; }
+        const uint64_t b0 = blk * BS, b1 = std::min(htsize, e * BS);
+        const uint32_t nb = (uint32_t)(b1 - b0);
+        Stage& x = st[cur];
+        if (x.busy) { cudaEventSynchronize(x.done); x.busy = false; }      // the copy engines are done with this stage
+        if (nk) {
+            if (fread(x.h_keys, (size_t)key_bytes, nk, fk) != nk || fread(x.h_lab, 2, nk, fl) != nk) { rc = -22; break; }
+            memcpy(x.h_sz, sz.get() + b0, nb);
+            cudaMemcpyAsync(x.d_keys, x.h_keys, nk * key_bytes, cudaMemcpyHostToDevice, h->db_stream);
+            cudaMemcpyAsync(x.d_lab, x.h_lab, nk * 2, cudaMemcpyHostToDevice, h->db_stream);
+            cudaMemcpyAsync(x.d_sz, x.h_sz, nb, cudaMemcpyHostToDevice, h->db_stream);
+            rc = table_insert_ref_chunk(h->table, htsize, b0, nb, x.d_sz, d_off, d_rank, d_scratch, scratch_bytes,
+                                        blk_rank[blk], all ? 1u : sampling, x.d_keys, key_bytes, x.d_lab, h->db_stream);
+            cudaEventRecord(x.done, h->db_stream); x.busy = true;
+            cur ^= 1;                                                      // read the next chunk while this one is inserted
+        }
+        blk = e;
+    }
+    cudaStreamSynchronize(h->db_stream);
     fclose(fk); fclose(fl);
-    cudaFree(d_sz); cudaFree(d_off); cudaFree(d_keys); cudaFree(d_lab);
-    cudaFreeHost(h_off); cudaFreeHost(h_keys); cudaFreeHost(h_lab);
+    cudaFree(d_off); cudaFree(d_rank); cudaFree(d_scratch);
+    for (auto& x : st) { cudaFree(x.d_sz); cudaFree(x.d_keys); cudaFree(x.d_lab); cudaFreeHost(x.h_sz); cudaFreeHost(x.h_keys); cudaFreeHost(x.h_lab); if (x.done) cudaEventDestroy(x.done); }
     if (rc == -22) { table_destroy(h->table); h->db_building = false; return ccb_fail(h, rc, "%s.ky/.lb are shorter than the bucket sizes in .sz announce", prefix); }
     if (rc) { table_destroy(h->table); h->db_building = false; return ccb_fail(h, rc, "table insert failed (%d)", rc); }
     rc = ccb_db_end(h);

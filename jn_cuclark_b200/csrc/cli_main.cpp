@@ -184,12 +184,15 @@ struct Engine {
         for (const char* e : {".sz", ".ky", ".lb"}) present = present && validFile((dbname + e).c_str());
         if (!present && build_db()) return;          // built on the device and already resident
         if (cli.verbose) cerr << "Loading database [" << dbname << ".*] (s=" << cli.sfactor << ")..." << endl;
+        struct timeval t0, t1;
+        gettimeofday(&t0, NULL);
         vector<std::thread> th; vector<int> rc(devs.size(), 0);
         for (size_t d = 0; d < devs.size(); d++)
             th.emplace_back([&, d] { uint64_t n = 0; rc[d] = ccb_db_load_files(devs[d], dbname.c_str(), HTSIZE, key_bytes, cli.sfactor, &n); });
         for (auto& t : th) t.join();
         for (size_t d = 0; d < devs.size(); d++)
             if (rc[d]) { cerr << ccb_last_error(devs[d]) << endl; exit(1); }
+        if (cli.verbose) { gettimeofday(&t1, NULL); cerr << "Loading time: " << (t1.tv_sec - t0.tv_sec) + (t1.tv_usec - t0.tv_usec) / 1e6 << " s\n"; }
     }
 
     // makeSpecificTargetSets (src/CuCLARK_hh.hh:691-1329): the database is absent, build it from the
@@ -256,6 +259,11 @@ struct Engine {
         char buf[256];                                                                   // printSpeedStats (:1931-1939)
         snprintf(buf, sizeof buf, "Done in %.1fs (%zu reads/min, %zu reads)\n", diff, (size_t)(((double)st.reads) / diff * 60.0), (size_t)st.reads);
         cerr << buf << "Results: " << res << "\n";
+        if (cli.verbose) {
+            snprintf(buf, sizeof buf, "  host pipeline: index %.3f s, slots %.3f s, total %.3f s, %zu batches; worker seconds: pack %.3f, device wait %.3f, rows %.3f, writer %.3f\n",
+                     st.seconds_index, st.seconds_alloc, st.seconds_total, (size_t)st.batches, st.cpu_pack, st.cpu_wait, st.cpu_format, st.cpu_sink);
+            cerr << buf;
+        }
         (void)shown_name;
     }
 

@@ -354,10 +354,32 @@ void csv_header(std::string& out, bool extended, const std::vector<std::string>&
     out += ",Gamma,Assignment,Score,Confidence\n";
 }
 
+namespace {
+// printf("%g") of a ratio of two small integers is by far the most expensive part of a row and takes few
+// distinct values in a batch: a direct-mapped memo keyed by the integers keeps the text exactly printf's.
+struct FmtMemo {
+    struct E { uint64_t key; uint8_t len; char s[39]; };
+    std::vector<E> e;
+    FmtMemo() : e(4096) { for (auto& x : e) x.key = ~0ull; }
+    template <typename F> void put(std::string& out, uint64_t key, F&& make)
+    {
+        E& x = e[(size_t)((key * 0x9E3779B97F4A7C15ull) >> 52)];
+        if (x.key != key) {
+            char buf[96];
+            const int m = make(buf, sizeof buf);
+            if (m < 0 || m >= (int)sizeof x.s) { out.append(buf, (size_t)std::max(m, 0)); return; }
+            x.key = key; x.len = (uint8_t)m; memcpy(x.s, buf, (size_t)m);
+        }
+        out.append(x.s, x.len);
+    }
+};
+}  // namespace
+
 void csv_rows(std::string& out, const ReadSet& r, size_t first, size_t count, int k, bool paired, bool extended,
               const std::vector<std::string>& names, const uint16_t* final5, const uint16_t* rows, int row_stride)
 {
     char num[96];
+    FmtMemo memo_gamma, memo_tail;
     const size_t n_targets = names.size() - 1;
     for (size_t j = 0; j < count; j++) {
         const size_t i = first + j;
@@ -382,14 +404,16 @@ void csv_rows(std::string& out, const ReadSet& r, size_t first, size_t count, in
             for (; w < n_targets; w++) out += ",0";
         }
         const uint32_t norm = paired ? (uint32_t)r.len[i] - 1u : (uint32_t)r.len[i];     // ITYPE is u32; NBN = 1 (:2107)
-        const double gamma = (double)total / (((double)norm - (double)k) + 1.0);         // :2110
-        double delta = (double)(best + second);
-        delta = (delta < 0.001) ? 0 : ((double)best) / delta;                              // :2111-2112
-        int m = snprintf(num, sizeof num, ",%g,", gamma);
-        out.append(num, (size_t)m);
+        memo_gamma.put(out, ((uint64_t)total << 32) | norm, [&](char* b, size_t cap) {
+            const double gamma = (double)total / (((double)norm - (double)k) + 1.0);     // :2110
+            return snprintf(b, cap, ",%g,", gamma);
+        });
         out += names[ib < names.size() ? ib : 0];
-        m = snprintf(num, sizeof num, ",%u,%g\n", best, delta);
-        out.append(num, (size_t)m);
+        memo_tail.put(out, ((uint64_t)best << 16) | second, [&](char* b, size_t cap) {
+            double delta = (double)(best + second);
+            delta = (delta < 0.001) ? 0 : ((double)best) / delta;                          // :2111-2112
+            return snprintf(b, cap, ",%u,%g\n", best, delta);
+        });
     }
 }
 
@@ -440,7 +464,8 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
 
     // batches: bounded by sequence bytes and read count so that pinned slots stay modest and
     // there are enough of them in flight to hide packing behind the GPU and vice versa
-    const size_t kMaxBatchReads = 1u << 20, kMaxBatchBytes = 64u << 20;
+    // (and small enough that every worker gets several: 10 M x 150 bp reads -> 77 batches)
+    const size_t kMaxBatchReads = 1u << 17, kMaxBatchBytes = 32u << 20;
     std::vector<size_t> bstart{0};
     {
         size_t bytes = 0, cnt = 0;
@@ -460,6 +485,7 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     }
 
     const int workers = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(opt.threads, 1), nbatches));
+    const double t_alloc0 = now();
     std::vector<std::unique_ptr<DevSlots>> ds;
     for (ccb_handle* h : devs) {
         if (int rc = ccb_batch_alloc(h, (uint32_t)max_reads, max_cont, opt.extended)) { err = ccb_last_error(h); return rc; }
@@ -467,6 +493,9 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
         ds.back()->h = h;
         for (int s = 0; s < ccb_batch_slots(h); s++) ds.back()->free_slots.push_back(s);
     }
+
+    stats.seconds_alloc = now() - t_alloc0;
+    std::mutex stat_mu;
 
     OrderedSink sink;
     sink.f = fopen(result_csv, "w");
@@ -483,6 +512,10 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     auto fail = [&](int rc, const std::string& m) { std::lock_guard<std::mutex> g(err_mu); if (!failed) { failed = rc ? rc : 1; err = m; } };
 
     auto work = [&](int wid) {
+        double c_pack = 0, c_wait = 0, c_fmt = 0, c_sink = 0;
+        struct Fold { std::mutex& m; ClassifyStats& st; double &a, &b, &c, &d;
+                      ~Fold() { std::lock_guard<std::mutex> g(m); st.cpu_pack += a; st.cpu_wait += b; st.cpu_format += c; st.cpu_sink += d; } }
+            fold{stat_mu, stats, c_pack, c_wait, c_fmt, c_sink};
         for (;;) {
             // take a slot first, then a batch number: the oldest unwritten batch always owns a slot
             DevSlots& d = *ds[(size_t)wid % ds.size()];
@@ -498,7 +531,9 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
             const size_t first = bstart[b], cnt = bstart[b + 1] - first;
             uint32_t* off; uint16_t *cont, *fin, *rows;
             ccb_batch_buffers(d.h, slot, &off, &cont, &fin, &rows);
+            double t1 = now();
             const int64_t nc = pack_reads(rs, first, cnt, opt.k, off, cont, max_cont);
+            c_pack += now() - t1; t1 = now();
             if (nc == -2) { fail(255, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>)."); release(); sink.put(b, "", {}); continue; }
             if (nc < 0) { fail(255, "Bad container estimation. Abort."); release(); sink.put(b, "", {}); continue; }
             int rc;
@@ -508,13 +543,16 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
             }
             if (!rc) rc = ccb_batch_wait(d.h, slot);
             if (rc) { fail(rc, ccb_last_error(d.h)); release(); sink.put(b, "", {}); continue; }
+            c_wait += now() - t1; t1 = now();
             std::string text;
             text.reserve(cnt * 48);
             csv_rows(text, rs, first, cnt, opt.k, opt.paired, opt.extended, names, fin, rows, opt.row_stride);
             std::vector<uint16_t> raw;
             if (sink.dump) raw.assign(fin, fin + cnt * 5);
             release();
+            c_fmt += now() - t1; t1 = now();
             sink.put(b, std::move(text), std::move(raw));
+            c_sink += now() - t1;
         }
     };
     std::vector<std::thread> th;

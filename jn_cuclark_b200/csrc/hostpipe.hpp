@@ -64,6 +64,9 @@ struct ClassifyOptions {
 struct ClassifyStats {
     uint64_t reads = 0, batches = 0;
     double   seconds_index = 0, seconds_total = 0;
+    // where the wall time of one file went: slot allocation, and summed over the workers:
+    // packing, waiting for the device, formatting rows, waiting for the ordered writer
+    double   seconds_alloc = 0, cpu_pack = 0, cpu_wait = 0, cpu_format = 0, cpu_sink = 0;
 };
 
 // Classify the reads of one mapped text with the given device handles (one per GPU, replicated

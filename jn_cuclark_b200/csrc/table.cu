@@ -1,5 +1,7 @@
 // table.cu -- building the bucketed table on the device (see table.cuh).
 #include "table.cuh"
+#include <cub/device/device_scan.cuh>
+#include <thrust/iterator/transform_iterator.h>
 #include <stdio.h>
 
 namespace ccb {
@@ -23,18 +25,23 @@ __global__ void k_insert_pairs(uint64_t* buckets, uint32_t* flags, uint32_t* sta
     for (; i < n; i += stride) insert_one(buckets, flags, status, counts, hp, canon[i], labels[i]);
 }
 
-// Reference layout (A9): canonical = key * HTSIZE + bucket (src/hashTable_hh.hh:469).
+// Reference layout (A9): canonical = key * HTSIZE + bucket (src/hashTable_hh.hh:469).  off = exclusive
+// scan of the chunk's bucket sizes, nzrank = inclusive scan of (size != 0); with -s sampling only every
+// sampling-th non-empty bucket of the whole file is kept (src/CuClarkDB.cu:503-513).
 template <typename KEY>
 __global__ void k_insert_ref_chunk(uint64_t* buckets, uint32_t* flags, uint32_t* status,
                                    unsigned long long* counts, HashParams hp,
                                    uint64_t htsize, uint64_t r0, uint32_t nbk,
-                                   const uint8_t* sz, const uint32_t* off,
+                                   const uint8_t* sz, const uint32_t* off, const uint32_t* nzrank,
+                                   uint64_t rank_base, uint32_t sampling,
                                    const KEY* keys, const uint16_t* labels)
 {
     uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
     for (; i < nbk; i += stride) {
         uint32_t n = sz[i];
+        if (n == 0) continue;
+        if (sampling > 1 && (rank_base + nzrank[i]) % sampling != 0) continue;
         uint32_t o = off[i];
         for (uint32_t j = 0; j < n; j++) {
             uint64_t c = (uint64_t)keys[o + j] * htsize + (r0 + i);
@@ -42,6 +49,9 @@ __global__ void k_insert_ref_chunk(uint64_t* buckets, uint32_t* flags, uint32_t*
         }
     }
 }
+
+struct NonZero { __host__ __device__ uint32_t operator()(uint8_t v) const { return v ? 1u : 0u; } };
+struct Widen   { __host__ __device__ uint32_t operator()(uint8_t v) const { return v; } };
 
 // Order the entries of every full bucket so that (e0 > e1) == A, (e2 > e3) == B.
 __global__ void k_finalize(ulonglong4* b, const uint32_t* flags, uint64_t n)
@@ -109,21 +119,36 @@ int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_lab
     return 0;
 }
 
-int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
-                           const uint8_t* d_sz, const uint32_t* d_off,
+size_t table_ref_chunk_scratch(uint32_t max_buckets)
+{
+    size_t a = 0, b = 0;
+    auto in1 = thrust::make_transform_iterator((const uint8_t*)nullptr, Widen());
+    auto in2 = thrust::make_transform_iterator((const uint8_t*)nullptr, NonZero());
+    cub::DeviceScan::ExclusiveSum(nullptr, a, in1, (uint32_t*)nullptr, max_buckets);
+    cub::DeviceScan::InclusiveSum(nullptr, b, in2, (uint32_t*)nullptr, max_buckets);
+    return (a > b ? a : b) + 256;
+}
+
+int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk, const uint8_t* d_sz,
+                           uint32_t* d_off, uint32_t* d_rank, void* d_scratch, size_t scratch_bytes,
+                           uint64_t rank_base, uint32_t sampling,
                            const void* d_keys, int key_bytes, const uint16_t* d_labels, cudaStream_t s)
 {
     if (t.finalized || !t.d_buckets) return -11;
     if (nbk == 0) return 0;
+    auto in1 = thrust::make_transform_iterator(d_sz, Widen());
+    auto in2 = thrust::make_transform_iterator(d_sz, NonZero());
+    CK(cub::DeviceScan::ExclusiveSum(d_scratch, scratch_bytes, in1, d_off, nbk, s));
+    if (sampling > 1) CK(cub::DeviceScan::InclusiveSum(d_scratch, scratch_bytes, in2, d_rank, nbk, s));
     int g = grid_for(nbk, 256);
     uint64_t* b = (uint64_t*)t.d_buckets - t.lo * kSlots;   // indexed by global bucket
     uint32_t* fl = t.d_flags - t.lo / 16;
     if (key_bytes == 2)
-        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint16_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint16_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, d_rank, rank_base, sampling, (const uint16_t*)d_keys, d_labels);
     else if (key_bytes == 4)
-        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint32_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint32_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, d_rank, rank_base, sampling, (const uint32_t*)d_keys, d_labels);
     else if (key_bytes == 8)
-        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, (const uint64_t*)d_keys, d_labels);
+        k_insert_ref_chunk<uint64_t><<<g, 256, 0, s>>>(b, fl, t.d_status, t.d_counts, t.hp, htsize, r0, nbk, d_sz, d_off, d_rank, rank_base, sampling, (const uint64_t*)d_keys, d_labels);
     else return -12;
     CK(cudaGetLastError());
     return 0;

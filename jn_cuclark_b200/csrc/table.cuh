@@ -157,10 +157,13 @@ struct Table {
 int table_create(Table& t, int k, uint64_t expected_entries, double load_factor, cudaStream_t s,
                  uint32_t n_shards = 1, uint32_t shard = 0);
 int table_insert_device(Table& t, const uint64_t* d_canon, const uint16_t* d_labels, uint64_t n, cudaStream_t s);
-// reference on-disk layout chunk (A9): buckets [r0, r0+nbk) with per-bucket
-// size (0 when skipped by -s sampling) and key offset relative to d_keys.
-int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk,
-                           const uint8_t* d_sz, const uint32_t* d_off,
+// reference on-disk layout chunk (A9): buckets [r0, r0+nbk) with their sizes as in the .sz file; keys and
+// labels of the chunk in file order.  d_off / d_rank: nbk u32 each, d_scratch: table_ref_chunk_scratch().
+// rank_base = non-empty buckets before r0 in the file; sampling = -s factor (<= 1: every bucket).
+size_t table_ref_chunk_scratch(uint32_t max_buckets);
+int table_insert_ref_chunk(Table& t, uint64_t htsize, uint64_t r0, uint32_t nbk, const uint8_t* d_sz,
+                           uint32_t* d_off, uint32_t* d_rank, void* d_scratch, size_t scratch_bytes,
+                           uint64_t rank_base, uint32_t sampling,
                            const void* d_keys, int key_bytes, const uint16_t* d_labels, cudaStream_t s);
 int table_finalize(Table& t, cudaStream_t s);   // orders entries (flags), frees build scratch, checks status
 void table_destroy(Table& t);

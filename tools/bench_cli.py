@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""End-to-end wall time of the drop-in binary (file -> CSV), rows A1/A2/A7/F2: synthetic genomes as FASTA
+targets (database built by the CLI itself on first use), reads as a FASTQ file, then `bin/cuCLARK -n T`."""
+import argparse, json, os, re, subprocess, sys, tempfile, time
+import numpy as np
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--genomes", type=int, default=100)
+ap.add_argument("--genome-len", type=int, default=4_000_000)
+ap.add_argument("--reads", type=int, default=10_000_000)
+ap.add_argument("--threads", default="1,4,16")
+ap.add_argument("--dir", default=None)
+a = ap.parse_args()
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+d = a.dir or tempfile.mkdtemp(prefix="ccb_cli_")
+os.makedirs(d, exist_ok=True)
+rng = np.random.default_rng(7)
+lut = np.frombuffer(b"ACGT", dtype=np.uint8)
+t0 = time.time()
+genomes = []
+with open(os.path.join(d, "targets.txt"), "w") as tf:
+    for g in range(a.genomes):
+        seq = lut[rng.integers(0, 4, a.genome_len, dtype=np.uint8)]
+        genomes.append(seq)
+        p = os.path.join(d, f"g{g}.fa")
+        rows = seq[: a.genome_len // 80 * 80].reshape(-1, 80)
+        with open(p, "wb") as f:
+            f.write(b">g%d\n" % g)
+            f.write(np.concatenate([rows, np.full((rows.shape[0], 1), 10, np.uint8)], axis=1).tobytes())
+            f.write(seq[a.genome_len // 80 * 80:].tobytes() + b"\n")
+        tf.write(f"{p}\tT{g}\n")
+# reads: 90 % windows of a genome with 1 % substitutions, 10 % random; fixed-width FASTQ records
+N, L = a.reads, 150
+rec = np.empty((N, 15 + 2 * L), dtype=np.uint8)
+ids = np.arange(N)
+rec[:, 0] = ord("@"); rec[:, 1] = ord("r")
+for j in range(8):
+    rec[:, 9 - j] = 48 + (ids // 10 ** j) % 10
+rec[:, 10 - 0] = 10  # newline after the 8-digit id (columns 2..9)
+allg = np.stack(genomes) if a.genomes * a.genome_len < 2_000_000_000 else None
+gi = rng.integers(0, a.genomes, N); pos = rng.integers(0, a.genome_len - L, N)
+CH = 1_000_000
+for s in range(0, N, CH):
+    e = min(N, s + CH)
+    idx = pos[s:e, None] + np.arange(L)[None, :]
+    seqs = (allg[gi[s:e, None], idx] if allg is not None else np.stack([genomes[g][p:p + L] for g, p in zip(gi[s:e], pos[s:e])]))
+    sub = rng.random(seqs.shape) < 0.01
+    seqs = np.where(sub, lut[rng.integers(0, 4, seqs.shape, dtype=np.uint8)], seqs)
+    rnd = rng.random(e - s) < 0.10
+    seqs[rnd] = lut[rng.integers(0, 4, (int(rnd.sum()), L), dtype=np.uint8)]
+    rec[s:e, 11:11 + L] = seqs
+rec[:, 11 + L] = 10; rec[:, 12 + L] = ord("+"); rec[:, 13 + L] = 10
+rec[:, 14 + L:14 + 2 * L] = ord("I"); rec[:, 14 + 2 * L] = 10
+fq = os.path.join(d, "reads.fq")
+rec.tofile(fq)
+t_gen = time.time() - t0
+dbdir = os.path.join(d, "db"); os.makedirs(dbdir, exist_ok=True)
+out = {"genomes": a.genomes, "genome_len": a.genome_len, "reads": N, "fastq_bytes": os.path.getsize(fq), "generate_s": t_gen, "runs": []}
+exe = os.path.join(ROOT, "bin", "cuCLARK")
+for i, T in enumerate([int(x) for x in a.threads.split(",")]):
+    t0 = time.time()
+    r = subprocess.run([exe, "-T", os.path.join(d, "targets.txt"), "-D", dbdir + "/", "-O", fq, "-R", os.path.join(d, f"res{T}"), "-n", str(T), "--verbose"],
+                       capture_output=True, text=True)
+    wall = time.time() - t0
+    m = re.search(r"Done in ([0-9.]+)s \((\d+) reads/min, (\d+) reads\)", r.stderr.replace("\n", " "))
+    out["runs"].append({"threads": T, "rc": r.returncode, "wall_s": wall, "built_db": "successfully stored" in r.stderr,
+                        "classify_s": float(m.group(1)) if m else None, "reads_per_min": int(m.group(2)) if m else None,
+                        "stderr_tail": r.stderr[-600:] if (r.returncode or not m) else None,
+                        "phases": [l.strip() for l in r.stderr.splitlines() if "build:" in l or "host pipeline" in l or "Loading time" in l][:12]})
+import hashlib
+hs = {T["threads"]: hashlib.sha256(open(os.path.join(d, f"res{T['threads']}.csv"), "rb").read()).hexdigest() for T in out["runs"] if T["rc"] == 0}
+out["csv_identical_across_threads"] = len(set(hs.values())) == 1
+print(json.dumps(out))
