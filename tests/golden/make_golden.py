@@ -31,17 +31,17 @@ WORLD = os.path.join(HERE, "world")
 REF = os.path.join(ROOT, "oracle", "_ref")
 
 
-def make_world():
+def make_world(n_genomes=6, length=12000, seed=21):
     shutil.rmtree(WORLD, ignore_errors=True)
-    tp, genomes, labels = synth.make_genomes(os.path.join(WORLD, "genomes"), 6, 12000, seed=21)
+    tp, genomes, labels = synth.make_genomes(os.path.join(WORLD, "genomes"), n_genomes, length, seed=seed)
     os.remove(tp)                                    # absolute paths: regenerated where used
     with open(os.path.join(WORLD, "labels.txt"), "w") as f:
         f.write("\n".join(labels) + "\n")
-    reads = synth.make_reads(genomes, 400, 150, seed=22, k=31)
+    reads = synth.make_reads(genomes, 400, 150, seed=seed + 1, k=31)
     synth.write_reads_fasta(os.path.join(WORLD, "reads.fa"), reads)
     synth.write_reads_fasta(os.path.join(WORLD, "reads_ml.fa"), reads, width=60)
     synth.write_reads_fastq(os.path.join(WORLD, "reads.fq"), [r for r in reads if " " not in r[0] and len(r[1])])
-    r1, r2 = synth.make_pairs(genomes, 150, seed=23)
+    r1, r2 = synth.make_pairs(genomes, 150, seed=seed + 2)
     synth.write_reads_fastq(os.path.join(WORLD, "p1.fq"), r1, "/1")
     synth.write_reads_fastq(os.path.join(WORLD, "p2.fq"), r2, "/2")
 
@@ -121,9 +121,54 @@ def make_gpu(out, suffix=""):
     log.close()
 
 
+def make_gpu32(out):
+    """The reference's GPU binaries on this box's GPU, world32 (32 targets).  With a number of targets that
+    is not a multiple of 32 their queryKernel never returns on sm_70+ (lanes beyond numTargets skip the
+    loop around `__ballot_sync(0xFFFFFFFF, ...)`, src/CuClarkDB.cu:1131-1136); with 32 it completes.  The
+    databases are written by bin/cuCLARK[-l] first (byte-identical to the reference's, test_build_gpu.py),
+    so the reference binaries only load them."""
+    os.makedirs(out, exist_ok=True)
+    log = open(os.path.join(out, "log32.txt"), "w")
+    for mode, binary, k in (("light", "cuCLARK-l", 27), ("full", "cuCLARK", 31)):
+        d = tempfile.mkdtemp()
+        tp = write_targets(d)
+        os.makedirs(os.path.join(d, "db"))
+        base = ["-k", str(k), "-T", tp, "-D", os.path.join(d, "db") + "/"]
+        r = subprocess.run([os.path.join(ROOT, "bin", binary)] + base + ["-O", os.path.join(WORLD, "reads.fa"), "-R", os.path.join(d, "mine")],
+                           capture_output=True, text=True, timeout=600)
+        log.write(f"== {mode} database by bin/{binary} rc={r.returncode}\n{r.stderr[-600:]}\n")
+        runs = [("fa", ["-O", os.path.join(WORLD, "reads.fa")]),
+                ("fq", ["-O", os.path.join(WORLD, "reads.fq")]),
+                ("pe", ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")]),
+                ("fa_ext", ["-O", os.path.join(WORLD, "reads.fa"), "--extended"])]
+        if mode == "full":
+            runs = [r_ for r_ in runs if r_[0] in ("fa", "pe")]
+        for name, extra in runs:
+            res = os.path.join(d, name)
+            t0 = time.time()
+            r = run_ref(binary, base + extra + ["-R", res], d, timeout=150)
+            log.write(f"-- {time.time() - t0:.1f} s\n== {mode} {name} rc={r.returncode}\n{r.stdout[-800:]}\n{r.stderr[-800:]}\n")
+            if r.returncode == 0 and os.path.exists(res + ".csv"):
+                shutil.copy(res + ".csv", os.path.join(out, f"w32_{mode}_{name}.csv"))
+            log.flush()
+            if r.returncode == -999:
+                break                                 # a hang: do not spend more GPU time on this mode
+        shutil.rmtree(d, ignore_errors=True)
+    log.close()
+
+
 if __name__ == "__main__":
     cmd = sys.argv[1]
-    if cmd == "world":
+    if cmd.endswith("32"):
+        WORLD = os.path.join(HERE, "world32")
+    if cmd == "world32":
+        make_world(33, 8000, seed=31)
+    elif cmd == "gpu32":
+        make_gpu32(sys.argv[2])
+        sys.exit(0)
+    if cmd == "world32":
+        pass
+    elif cmd == "world":
         make_world()
     elif cmd == "db":
         make_db()

@@ -144,3 +144,31 @@ def test_missing_db_and_unbuildable_targets_fail_like_reference(setup, tmp_path)
     r = subprocess.run([s["bin"], "-T", str(tp), "-D", str(tmp_path), "-O", os.path.join(WORLD, "reads.fa"), "-R", str(tmp_path / "o")],
                        capture_output=True, text=True)
     assert r.returncode == 255 and "Failed to find the database." in r.stderr
+
+
+# ---- against CSVs the reference's own CUDA kernels wrote on a B200 (tests/golden/ref_gpu/w32_*.csv) ----
+WORLD32 = os.path.join(HERE, "golden", "world32")
+REFGPU = os.path.join(HERE, "golden", "ref_gpu")
+W32 = {"fa": ["-O", "reads.fa"], "fq": ["-O", "reads.fq"], "fa_ext": ["-O", "reads.fa", "--extended"], "pe": ["-P", "p1.fq", "p2.fq"]}
+
+
+@pytest.mark.parametrize("mode", ["light", "full"])
+def test_cli_equals_reference_gpu_binary(tmp_path, mode):
+    """Same targets, same reads: bin/cuCLARK[-l] (database built by ccb_build_*) writes the CSV that the unmodified
+    reference binary wrote with its own kernels on a B200 (make_golden.py gpu32)."""
+    labels = open(os.path.join(WORLD32, "labels.txt")).read().split()
+    tp = str(tmp_path / "targets.txt")
+    with open(tp, "w") as f:
+        for i, lab in enumerate(labels):
+            f.write(f"{os.path.join(WORLD32, 'genomes', f'g{i}.fa')}\t{lab}\n")
+    (tmp_path / "db").mkdir()
+    exe = os.path.join(ROOT, "bin", "cuCLARK-l" if mode == "light" else "cuCLARK")
+    golden = sorted(glob.glob(os.path.join(REFGPU, f"w32_{mode}_*.csv")))
+    assert golden
+    for g in golden:
+        case = os.path.basename(g)[len(f"w32_{mode}_"):-4]
+        args = [a if a.startswith("-") else os.path.join(WORLD32, a) for a in W32[case]]
+        res = str(tmp_path / case)
+        r = subprocess.run([exe, "-T", tp, "-D", str(tmp_path / "db") + "/", "-R", res, "-n", "3"] + args, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-1500:]
+        assert open(res + ".csv", "rb").read() == open(g, "rb").read(), case

@@ -93,3 +93,52 @@ def test_oracle_csv_equals_reference_host_engine(oracle, golden_dbs, tmp_path, p
     out = str(tmp_path / "o.csv")
     ir.write_csv(out, k, paired, golden_dbs["names"], out5, rows if ext else None)
     assert open(out, "rb").read() == open(os.path.join(REF_CSV, path), "rb").read()
+
+
+# ---- CSVs written by the reference's own CUDA kernels on a B200 (tests/golden/ref_gpu/w32_*.csv) ----
+# make_golden.py gpu32: the UNMODIFIED reference binaries (oracle/_ref/cuCLARK, cuCLARK-l, sm_100 build) on
+# tests/golden/world32.  32 targets, because with a target count that is not a multiple of 32 the reference's
+# queryKernel deadlocks on sm_70+ (src/CuClarkDB.cu:1131-1136: __ballot_sync(0xFFFFFFFF) inside a loop that
+# lanes >= numTargets never enter).  These pin rows A3 and A6 (k-mer assembly, vote, result) by execution.
+WORLD32 = os.path.join(HERE, "golden", "world32")
+REF_GPU = os.path.join(HERE, "golden", "ref_gpu")
+GPU_CASES = {"fa": ("reads.fa", False, False), "fq": ("reads.fq", False, False), "fa_ext": ("reads.fa", False, True),
+             "pe": (None, True, False)}
+
+
+@pytest.fixture(scope="module")
+def golden_dbs32(oracle, tmp_path_factory):
+    d = tmp_path_factory.mktemp("gdb32")
+    labels = open(os.path.join(WORLD32, "labels.txt")).read().split()
+    tp = str(d / "targets.txt")
+    with open(tp, "w") as f:
+        for i, lab in enumerate(labels):
+            f.write(f"{os.path.join(WORLD32, 'genomes', f'g{i}.fa')}\t{lab}\n")
+    names = ["NA"]
+    for lab in labels:
+        if lab not in names:
+            names.append(lab)
+    assert len(names) - 1 == 32
+    return {"light": (oracle.OracleDb.build(tp, 27, oracle.HTSIZE_LIGHT, light=True), 27, 48),
+            "full": (oracle.OracleDb.build(tp, 31, oracle.HTSIZE_FULL), 31, 32), "names": names}
+
+
+@pytest.mark.parametrize("path", sorted(os.path.basename(p) for p in __import__("glob").glob(os.path.join(REF_GPU, "w32_*.csv"))))
+def test_oracle_csv_equals_reference_gpu_kernels(oracle, golden_dbs32, tmp_path, path):
+    _, mode, case = path[:-4].split("_", 2)
+    src, paired, ext = GPU_CASES[case]
+    db, k, stride = golden_dbs32[mode]
+    if paired:
+        m = str(tmp_path / "m.fa")
+        assert oracle.merge_paired(os.path.join(WORLD32, "p1.fq"), os.path.join(WORLD32, "p2.fq"), m) == 0
+        data = open(m, "rb").read()
+    else:
+        data = open(os.path.join(WORLD32, src), "rb").read()
+    ir = oracle.IndexedReads(data)
+    off, cont = ir.pack(k)
+    out5, rows, _ = db.query_packed(k, off, cont, row_stride=stride if ext else 0)
+    out = str(tmp_path / "o.csv")
+    ir.write_csv(out, k, paired, golden_dbs32["names"], out5, rows if ext else None)
+    got, want = open(out, "rb").read(), open(os.path.join(REF_GPU, path), "rb").read()
+    assert want.count(b"\n") > 100 and sum(1 for l in want.splitlines()[1:] if b",NA," not in l) > 50   # not vacuous
+    assert got == want
