@@ -10,6 +10,9 @@ ap.add_argument("--genome-len", type=int, default=4_000_000)
 ap.add_argument("--reads", type=int, default=10_000_000)
 ap.add_argument("--threads", default="1,4,16")
 ap.add_argument("--dir", default=None)
+ap.add_argument("--reference", default=None,
+                help="also run the reference GPU binary (oracle/_ref/cuCLARK) with these '-n,-b' pairs, e.g. 1:4,16:32 "
+                     "(needs a number of targets that is a multiple of 32, see tests/golden/ref_gpu/README.md)")
 a = ap.parse_args()
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 d = a.dir or tempfile.mkdtemp(prefix="ccb_cli_")
@@ -68,6 +71,27 @@ for i, T in enumerate([int(x) for x in a.threads.split(",")]):
                         "stderr_tail": r.stderr[-600:] if (r.returncode or not m) else None,
                         "phases": [l.strip() for l in r.stderr.splitlines() if "build:" in l or "host pipeline" in l or "Loading time" in l][:12]})
 import hashlib
+if a.reference:
+    ref = os.path.join(ROOT, "oracle", "_ref", "cuCLARK")
+    out["reference_runs"] = []
+    for pair in a.reference.split(","):
+        n, b = pair.split(":")
+        t0 = time.time()
+        try:
+            r = subprocess.run([ref, "-T", os.path.join(d, "targets.txt"), "-D", dbdir + "/", "-O", fq, "-R", os.path.join(d, f"ref{n}_{b}"),
+                                "-n", n, "-b", b], capture_output=True, text=True, timeout=600)
+            rc, err = r.returncode, r.stderr
+        except subprocess.TimeoutExpired as e:
+            rc, err = -999, "TIMEOUT " + str(e.stderr)[-300:]
+        wall = time.time() - t0
+        m = re.search(r"Done in ([0-9.]+)s \((\d+) reads/min, (\d+) reads\)", err.replace("\n", " "))
+        same = None
+        if rc == 0 and os.path.exists(os.path.join(d, f"ref{n}_{b}.csv")):
+            mine = os.path.join(d, f"res{out['runs'][0]['threads']}.csv")
+            same = open(mine, "rb").read() == open(os.path.join(d, f"ref{n}_{b}.csv"), "rb").read()
+        out["reference_runs"].append({"n": int(n), "b": int(b), "rc": rc, "wall_s": wall, "classify_s": float(m.group(1)) if m else None,
+                                      "reads_per_min": int(m.group(2)) if m else None, "csv_identical_to_ours": same,
+                                      "stderr_tail": err[-400:] if (rc or not m) else None})
 hs = {T["threads"]: hashlib.sha256(open(os.path.join(d, f"res{T['threads']}.csv"), "rb").read()).hexdigest() for T in out["runs"] if T["rc"] == 0}
 out["csv_identical_across_threads"] = len(set(hs.values())) == 1
 print(json.dumps(out))
