@@ -15,8 +15,9 @@
  * own hTable::find via oracle/_ref/ref_harness; parse/pack/pair-merge/print
  * (A1, A2, A7, A10) byte-for-byte against CSVs written by the reference's
  * unmodified host engine (tests/golden/ref_csv/, oracle/ref_cpu_device.cc).
- * The device kernels' k-mer assembly and vote (A3, A6) are restated only: the
- * reference GPU binary hangs on B200 (tests/golden/ref_gpu/README.md).
+ * The device kernels' k-mer assembly, counting and result (A3, A6) are pinned
+ * byte-for-byte against CSVs the reference's own CUDA kernels wrote on a B200
+ * (tests/golden/ref_gpu/w32_*.csv; see the README there).
  */
 #ifndef CUCLARK_ORACLE_H
 #define CUCLARK_ORACLE_H
