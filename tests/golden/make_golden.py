@@ -129,7 +129,13 @@ def make_gpu32(out):
     so the reference binaries only load them."""
     os.makedirs(out, exist_ok=True)
     log = open(os.path.join(out, "log32.txt"), "w")
-    for mode, binary, k in (("light", "cuCLARK-l", 27), ("full", "cuCLARK", 31)):
+    fa, fq, ml = (["-O", os.path.join(WORLD, f)] for f in ("reads.fa", "reads.fq", "reads_ml.fa"))
+    pe = ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")]
+    plans = [("light", "cuCLARK-l", 27, [("fa", fa), ("fq", fq), ("ml", ml), ("pe", pe), ("fa_ext", fa + ["--extended"]), ("pe_ext", pe + ["--extended"])]),
+             ("full", "cuCLARK", 31, [("fa", fa), ("fq", fq), ("pe", pe), ("fa_ext", fa + ["--extended"]),
+                                    ("fa_s2", fa + ["-s", "2"])]),      # kept as refbug_full_fa_s2.csv, see ref_gpu/README.md
+             ("fullk21", "cuCLARK", 21, [("fa", fa), ("pe", pe)])]
+    for mode, binary, k, runs in plans:
         d = tempfile.mkdtemp()
         tp = write_targets(d)
         os.makedirs(os.path.join(d, "db"))
@@ -137,12 +143,6 @@ def make_gpu32(out):
         r = subprocess.run([os.path.join(ROOT, "bin", binary)] + base + ["-O", os.path.join(WORLD, "reads.fa"), "-R", os.path.join(d, "mine")],
                            capture_output=True, text=True, timeout=600)
         log.write(f"== {mode} database by bin/{binary} rc={r.returncode}\n{r.stderr[-600:]}\n")
-        runs = [("fa", ["-O", os.path.join(WORLD, "reads.fa")]),
-                ("fq", ["-O", os.path.join(WORLD, "reads.fq")]),
-                ("pe", ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")]),
-                ("fa_ext", ["-O", os.path.join(WORLD, "reads.fa"), "--extended"])]
-        if mode == "full":
-            runs = [r_ for r_ in runs if r_[0] in ("fa", "pe")]
         for name, extra in runs:
             res = os.path.join(d, name)
             t0 = time.time()

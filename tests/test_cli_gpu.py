@@ -149,10 +149,11 @@ def test_missing_db_and_unbuildable_targets_fail_like_reference(setup, tmp_path)
 # ---- against CSVs the reference's own CUDA kernels wrote on a B200 (tests/golden/ref_gpu/w32_*.csv) ----
 WORLD32 = os.path.join(HERE, "golden", "world32")
 REFGPU = os.path.join(HERE, "golden", "ref_gpu")
-W32 = {"fa": ["-O", "reads.fa"], "fq": ["-O", "reads.fq"], "fa_ext": ["-O", "reads.fa", "--extended"], "pe": ["-P", "p1.fq", "p2.fq"]}
+W32 = {"fa": ["-O", "reads.fa"], "fq": ["-O", "reads.fq"], "ml": ["-O", "reads_ml.fa"], "fa_ext": ["-O", "reads.fa", "--extended"],
+       "pe": ["-P", "p1.fq", "p2.fq"], "pe_ext": ["-P", "p1.fq", "p2.fq", "--extended"]}
 
 
-@pytest.mark.parametrize("mode", ["light", "full"])
+@pytest.mark.parametrize("mode", ["light", "full", "fullk21"])
 def test_cli_equals_reference_gpu_binary(tmp_path, mode):
     """Same targets, same reads: bin/cuCLARK[-l] (database built by ccb_build_*) writes the CSV that the unmodified
     reference binary wrote with its own kernels on a B200 (make_golden.py gpu32)."""
@@ -163,12 +164,13 @@ def test_cli_equals_reference_gpu_binary(tmp_path, mode):
             f.write(f"{os.path.join(WORLD32, 'genomes', f'g{i}.fa')}\t{lab}\n")
     (tmp_path / "db").mkdir()
     exe = os.path.join(ROOT, "bin", "cuCLARK-l" if mode == "light" else "cuCLARK")
+    kflag = ["-k", "21"] if mode == "fullk21" else []
     golden = sorted(glob.glob(os.path.join(REFGPU, f"w32_{mode}_*.csv")))
     assert golden
     for g in golden:
         case = os.path.basename(g)[len(f"w32_{mode}_"):-4]
         args = [a if a.startswith("-") else os.path.join(WORLD32, a) for a in W32[case]]
         res = str(tmp_path / case)
-        r = subprocess.run([exe, "-T", tp, "-D", str(tmp_path / "db") + "/", "-R", res, "-n", "3"] + args, capture_output=True, text=True, timeout=600)
+        r = subprocess.run([exe, "-T", tp, "-D", str(tmp_path / "db") + "/", "-R", res, "-n", "3"] + kflag + args, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-1500:]
         assert open(res + ".csv", "rb").read() == open(g, "rb").read(), case

@@ -103,7 +103,8 @@ def test_oracle_csv_equals_reference_host_engine(oracle, golden_dbs, tmp_path, p
 WORLD32 = os.path.join(HERE, "golden", "world32")
 REF_GPU = os.path.join(HERE, "golden", "ref_gpu")
 GPU_CASES = {"fa": ("reads.fa", False, False), "fq": ("reads.fq", False, False), "fa_ext": ("reads.fa", False, True),
-             "pe": (None, True, False)}
+             "ml": ("reads_ml.fa", False, False), "pe": (None, True, False), "pe_ext": (None, True, True),
+             }
 
 
 @pytest.fixture(scope="module")
@@ -120,7 +121,8 @@ def golden_dbs32(oracle, tmp_path_factory):
             names.append(lab)
     assert len(names) - 1 == 32
     return {"light": (oracle.OracleDb.build(tp, 27, oracle.HTSIZE_LIGHT, light=True), 27, 48),
-            "full": (oracle.OracleDb.build(tp, 31, oracle.HTSIZE_FULL), 31, 32), "names": names}
+            "full": (oracle.OracleDb.build(tp, 31, oracle.HTSIZE_FULL), 31, 32),
+            "fullk21": (oracle.OracleDb.build(tp, 21, oracle.HTSIZE_FULL), 21, 32), "names": names}
 
 
 @pytest.mark.parametrize("path", sorted(os.path.basename(p) for p in __import__("glob").glob(os.path.join(REF_GPU, "w32_*.csv"))))
