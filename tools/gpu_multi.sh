@@ -1,8 +1,25 @@
 #!/bin/bash
-# N-GPU validation: tests that need >1 device, then the bench through torchrun
+# N-GPU validation: the bench through torchrun (both arms), then the sharded mode with the peer exchange
 N=${1:-2}
 mkdir -p gpurun_out
-nvidia-smi -L
-timeout 900 python -m pytest tests -m gpu -x -q -k "device or multi" > gpurun_out/pytest_multi.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_multi.log
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"; cut -c1-400 gpurun_out/bench_n$N.json
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > gpurun_out/bench_ref_n$N.json 2> gpurun_out/bench_ref_n$N.err; echo "benchref rc=$?"; cut -c1-200 gpurun_out/bench_ref_n$N.json
+nvidia-smi -L | head -8
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+timeout 600 $TR --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"
+python - <<PY
+import json
+try:
+    d=[json.loads(l) for l in open("gpurun_out/bench_n$N.json") if l.startswith("{")][0]
+    print(d["n_gpus"], d["ms_per_step"], d["value"]/1e9, d["e2e"]["value"]/1e9, d["clocks"])
+except Exception as e:
+    print("no line", e); print(open("gpurun_out/bench_n$N.err").read()[-1500:])
+PY
+timeout 300 $TR --master-port 29512 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > gpurun_out/bench_ref_n$N.json 2> gpurun_out/bench_ref_n$N.err; echo "benchref rc=$?"; cut -c1-160 gpurun_out/bench_ref_n$N.json
+timeout 400 $TR --master-port 29513 bench.py --gpus $N --sharded --exchange peer --steps 5 --warmup 2 > gpurun_out/bench_sharded_peer_n$N.json 2> gpurun_out/bench_sharded_peer_n$N.err; echo "sharded rc=$?"
+python - <<PY
+import json
+try:
+    d=[json.loads(l) for l in open("gpurun_out/bench_sharded_peer_n$N.json") if l.startswith("{")][0]
+    print(d["n_gpus"], d["ms_per_step"], d["value"]/1e9, d["e2e"]["ms_per_step"], d["config"]["phases_rank0"])
+except Exception as e:
+    print("no line", e); print(open("gpurun_out/bench_sharded_peer_n$N.err").read()[-1500:])
+PY
