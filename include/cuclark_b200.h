@@ -58,7 +58,7 @@ typedef struct ccb_stats {
     uint64_t dense_reads;   /* reads re-done by the dense exact path    */
 } ccb_stats;
 
-enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4 };
+enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8 };
 
 /* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
 int  ccb_create(const ccb_config* cfg, ccb_handle** out);
@@ -149,6 +149,25 @@ int  ccb_device_alloc(ccb_handle* h, uint64_t bytes, void** ptr);
 int  ccb_ipc_export(ccb_handle* h, void* ptr, unsigned char out[64]);
 int  ccb_ipc_open(ccb_handle* h, const unsigned char in[64], void** ptr);
 int  ccb_ipc_close(ccb_handle* h, void* ptr);
+
+/* Anchor index (no counterpart in the reference; results are unchanged by it).  The target sequences
+ * themselves are kept on the device (both strands, 2 bits per base) with one bit per position saying
+ * whether the k-mer starting there is in the table, and a small table of sampled k-mers -> position.
+ * A read whose sampled k-mer is found is compared base by base with the sequence; every k-mer window
+ * that matches is answered from the position bits without a table probe, every other window is probed
+ * as usual -- so the answer is exact whatever the index contains.  Built after the table is loaded;
+ * dropped when the table is replaced.  CCB_NO_ANCHOR in the query flags bypasses it.
+ *   ccb_anchor_synth   for the synthetic workload of ccb_synth_db (same seed / genomes / labels) */
+typedef struct ccb_anchor_info {
+    int      ready;
+    uint64_t bases;       /* bases per strand, incl. separators and padding */
+    uint64_t entries;     /* sampled k-mers stored   */
+    uint64_t dropped;     /* sampled k-mers that found their bucket full */
+    uint64_t bytes;       /* device bytes */
+} ccb_anchor_info;
+int  ccb_anchor_synth(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels);
+int  ccb_anchor_drop(ccb_handle* h);
+int  ccb_anchor_get_info(const ccb_handle* h, ccb_anchor_info* info);
 
 /* CuClarkDB::malloc (src/CuClarkDB.cu:322-421): pinned host + device buffers for
  * every slot, owned by the library; the caller fills offsets/containers in

@@ -106,6 +106,7 @@ extern "C" void ccb_destroy(ccb_handle* h)
     cudaDeviceSynchronize();
     free_slots(h);
     build_free(h);
+    anchor_free(h->anchor);
     table_destroy(h->table);
     cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense); cudaFree(h->shard_scan_tmp);
     if (h->db_stream) cudaStreamDestroy(h->db_stream);
@@ -120,6 +121,7 @@ extern "C" int ccb_db_begin(ccb_handle* h, uint64_t expected_entries)
     if (!h) return -1;
     USE_DEV(h);
     if (h->db_building || h->db_ready) { table_destroy(h->table); h->db_ready = h->db_building = false; }
+    anchor_free(h->anchor);                      // its "stored in the table" bits belong to the old table
     int rc = table_create(h->table, h->cfg.k, expected_entries, h->cfg.load_factor, h->db_stream, h->n_shards, h->shard);
     if (rc) {
         table_destroy(h->table);
@@ -360,7 +362,8 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
         rc = launch_query_dense(tv, d, nullptr, nullptr, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);
         return rc;
     }
-    rc = launch_query(tv, a, st);
+    if (h->anchor.ready && !(flags & CCB_NO_ANCHOR)) rc = launch_query_anchor(tv, a, h->anchor.view(), st);
+    else rc = launch_query(tv, a, st);
     if (rc) return rc;
     QueryArgs d = a; d.stats = nullptr;
     return launch_query_dense(tv, d, ovf_list, ovf_count, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);

@@ -66,6 +66,22 @@ int launch_vote_lists(const QueryArgs& a, const VoteArgs& va, cudaStream_t s);
 int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
                             uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s);
 
+// Anchor index (DESIGN.md "Anchor and verify"): the target sequences themselves, both strands, 2 bits per
+// base, plus per-position bits, plus a small table of sampled k-mers -> text position.  A read whose
+// sampled k-mer is found there is compared base by base with the text; every window that matches needs no
+// table probe -- its answer is the per-position bit "this text k-mer is in the table" and the label of the
+// record.  Windows that do not match are probed as usual, so the result is exact whatever the anchors say.
+struct AnchorView {
+    const uint32_t*   seq;      // text T = F . revcomp(F): 16 bases per word, first base in the top bits
+    const uint32_t*   valid;    // bit p: base p of T is a base (0: separator / N / padding)
+    const uint32_t*   disc;     // bit p: the k-mer starting at p is stored in the k-mer table
+    uint64_t          nF;       // bases in F (multiple of 32); T has 2 * nF
+    const ulonglong4* buckets;  // sampled k-mers: 4 x [fp15 | fwd1 | label16 | pos32], no overflow chains
+    uint64_t          nb;
+};
+// same as launch_query, but reads are first tried against the anchor index
+int launch_query_anchor(const TableView& t, const QueryArgs& a, const AnchorView& av, cudaStream_t s);
+
 // fast path: one warp per read, votes kept in registers
 int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s);
 // exact path for any number of distinct targets: one CTA per listed read, dense

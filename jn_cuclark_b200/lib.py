@@ -15,7 +15,7 @@ import os
 
 import numpy as np
 
-CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE = 1, 2, 4
+CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR = 1, 2, 4, 8
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -44,6 +44,10 @@ class DbInfo(C.Structure):
 class BuildInfo(C.Structure):
     _fields_ = [("bases", C.c_uint64), ("occurrences", C.c_uint64), ("distinct", C.c_uint64),
                 ("stored", C.c_uint64), ("max_bucket", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class AnchorInfo(C.Structure):
+    _fields_ = [("ready", C.c_int), ("bases", C.c_uint64), ("entries", C.c_uint64), ("dropped", C.c_uint64), ("bytes", C.c_uint64)]
 
 
 class Stats(C.Structure):
@@ -79,6 +83,9 @@ SYMBOLS = {
     "ccb_ipc_export": (C.c_int, [_H, _VP, C.c_char_p]),
     "ccb_ipc_open": (C.c_int, [_H, C.c_char_p, C.POINTER(_VP)]),
     "ccb_ipc_close": (C.c_int, [_H, _VP]),
+    "ccb_anchor_synth": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32]),
+    "ccb_anchor_drop": (C.c_int, [_H]),
+    "ccb_anchor_get_info": (C.c_int, [_H, C.POINTER(AnchorInfo)]),
     "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
     "ccb_batch_buffers": (C.c_int, [_H, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
     "ccb_batch_submit": (C.c_int, [_H, C.c_int, C.c_uint32, C.c_uint64, C.c_int]),
@@ -305,6 +312,19 @@ class CuClarkDB:
 
     def ipc_close(self, ptr: int):
         self._ck(self._lib.ccb_ipc_close(self._h, ptr))
+
+    # -- anchor index ---------------------------------------------------------------------------
+    def anchor_synth(self, db_seed: int, n_genomes: int, genome_len: int, n_labels: int) -> AnchorInfo:
+        self._ck(self._lib.ccb_anchor_synth(self._h, db_seed, n_genomes, genome_len, n_labels))
+        return self.anchor_info()
+
+    def anchor_drop(self):
+        self._ck(self._lib.ccb_anchor_drop(self._h))
+
+    def anchor_info(self) -> AnchorInfo:
+        info = AnchorInfo()
+        self._ck(self._lib.ccb_anchor_get_info(self._h, C.byref(info)))
+        return info
 
     def l2_fetch_granularity(self) -> int:
         return self._lib.ccb_l2_fetch_granularity(self._h)
