@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--sample-reads", type=int, default=200_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--anchor", action="store_true",
+                    help="build the anchor index (target sequences + sampled k-mer positions) in front of the table")
     ap.add_argument("--sharded", action="store_true",
                     help="row E2: the table sharded over the N GPUs (k-mer all-to-all) instead of replicated")
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
@@ -214,6 +216,9 @@ def run_b200(args):
     n_kmers = db.synth_db(DB_SEED, G, LG, min(G, 65534))
     t_db = time.time() - t0
     info = db.db_info()
+    anchor = None
+    if args.anchor:
+        t0 = time.time(); anchor = db.anchor_synth(DB_SEED, G, LG, min(G, 65534)); t_anchor = time.time() - t0
     d_off, d_cont, n_cont = db.synth_reads_packed(READS_SEED, DB_SEED, rank * NR, NR, L, G, LG)
     out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
