@@ -58,7 +58,8 @@ typedef struct ccb_stats {
     uint64_t dense_reads;   /* reads re-done by the dense exact path    */
 } ccb_stats;
 
-enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8 };
+enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8,
+       CCB_LANE_KERNEL = 16 /* thread-per-read kernel for short single-part reads, the rest as usual */ };
 
 /* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
 int  ccb_create(const ccb_config* cfg, ccb_handle** out);

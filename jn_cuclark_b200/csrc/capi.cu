@@ -321,7 +321,7 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
         ok(cudaMallocHost(&s.h_offsets, so)); ok(cudaMallocHost(&s.h_cont, sc)); ok(cudaMallocHost(&s.h_final5, sf));
         ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 16));
         ok(cudaMalloc(&s.d_offsets, so)); ok(cudaMalloc(&s.d_cont, sc)); ok(cudaMalloc(&s.d_final5, sf));
-        ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 4)); ok(cudaMalloc(&s.d_ovf_count, 4));
+        ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 8)); ok(cudaMalloc(&s.d_ovf_count, 8));   // [overflow list | redo list]
         ok(cudaMalloc(&s.d_dense_scratch, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
         ok(cudaMalloc(&s.d_stats, 16));
         if (extended) { ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
@@ -348,13 +348,15 @@ extern "C" int ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, ui
     return 0;
 }
 
-static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uint32_t* ovf_count,
+// ovf_list holds 2 * list_cap entries and ovf_count 2 words: [0] reads for the dense pass, [1] reads the
+// thread-per-read kernel handed back to the warp-per-read kernel
+static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uint32_t* ovf_count, uint32_t list_cap,
                      uint32_t* dense_scratch, int flags, cudaStream_t st)
 {
     QueryArgs a = a0;
     a.ovf_list = ovf_list; a.ovf_count = ovf_count;
     TableView tv = h->table.view();
-    cudaMemsetAsync(ovf_count, 0, 4, st);
+    cudaMemsetAsync(ovf_count, 0, 8, st);
     int rc;
     if (flags & CCB_FORCE_DENSE) {
         // every read through the dense exact path (cross-check of the fast path)
@@ -362,10 +364,18 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
         rc = launch_query_dense(tv, d, nullptr, nullptr, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);
         return rc;
     }
-    if (h->anchor.ready && !(flags & CCB_NO_ANCHOR)) rc = launch_query_anchor(tv, a, h->anchor.view(), st);
+    const bool use_anchor = h->anchor.ready && !(flags & CCB_NO_ANCHOR);
+    const AnchorView av = h->anchor.view();
+    if ((flags & CCB_LANE_KERNEL) && list_cap >= a.n_reads) {
+        uint32_t* redo_list = ovf_list + list_cap; uint32_t* redo_count = ovf_count + 1;
+        rc = launch_query_lane(tv, a, use_anchor ? &av : nullptr, redo_list, redo_count, st);
+        if (rc) return rc;
+        a.read_list = redo_list; a.n_list = redo_count;
+    }
+    if (use_anchor) rc = launch_query_anchor(tv, a, av, st);
     else rc = launch_query(tv, a, st);
     if (rc) return rc;
-    QueryArgs d = a; d.stats = nullptr;
+    QueryArgs d = a; d.stats = nullptr; d.read_list = nullptr; d.n_list = nullptr;
     return launch_query_dense(tv, d, ovf_list, ovf_count, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);
 }
 
@@ -388,7 +398,7 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
     a.out5 = s.d_final5; a.rows = (flags & CCB_EXTENDED) ? s.d_rows : nullptr; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr;
     if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 16, s.stream));
-    int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, s.d_dense_scratch, flags, s.stream);
+    int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, h->max_reads, s.d_dense_scratch, flags, s.stream);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     CU(h, cudaMemcpyAsync(s.h_final5, s.d_final5, (size_t)n_reads * 10, cudaMemcpyDeviceToHost, s.stream));
     if (flags & CCB_EXTENDED) CU(h, cudaMemcpyAsync(s.h_rows, s.d_rows, (size_t)n_reads * h->row_stride * 2, cudaMemcpyDeviceToHost, s.stream));
@@ -449,16 +459,16 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
     USE_DEV(h);
     if (h->q_ovf_cap < n_reads || !h->q_ovf_list) {
         cudaFree(h->q_ovf_list); h->q_ovf_list = nullptr;
-        CU(h, cudaMalloc(&h->q_ovf_list, (size_t)(n_reads ? n_reads : 1) * 4));
+        CU(h, cudaMalloc(&h->q_ovf_list, (size_t)(n_reads ? n_reads : 1) * 8));
         h->q_ovf_cap = n_reads;
     }
-    if (!h->q_ovf_count) CU(h, cudaMalloc(&h->q_ovf_count, 4));
+    if (!h->q_ovf_count) CU(h, cudaMalloc(&h->q_ovf_count, 8));
     if (!h->q_dense) CU(h, cudaMalloc(&h->q_dense, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
     QueryArgs a{};
     a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
     a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr;
-    int rc = run_query(h, a, h->q_ovf_list, h->q_ovf_count, h->q_dense, flags, (cudaStream_t)stream);
+    int rc = run_query(h, a, h->q_ovf_list, h->q_ovf_count, h->q_ovf_cap, h->q_dense, flags, (cudaStream_t)stream);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     return 0;
 }

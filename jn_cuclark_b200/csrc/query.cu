@@ -160,9 +160,13 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra, const AnchorVi
     // Software pipeline over the warp's reads: offsets are loaded two reads ahead, the first tile's
     // containers and the first part header one read ahead, so a read's three dependent loads
     // (offsets -> containers -> table) do not add up.
-    auto load_off = [&](uint32_t rr, uint32_t& b, int& n) {
+    const uint32_t n_items = a.read_list ? min(__ldg(a.n_list), a.n_reads) : a.n_reads;     // reads to do (all, or the listed ones)
+    auto load_off = [&](uint32_t idx, uint32_t& b, int& n) {
         b = 0; n = 0;
-        if (rr < a.n_reads) { b = __ldg(a.offsets + rr); n = (int)(__ldg(a.offsets + rr + 1) - b); }
+        if (idx < n_items) {
+            const uint32_t rr = a.read_list ? __ldg(a.read_list + idx) : idx;
+            b = __ldg(a.offsets + rr); n = (int)(__ldg(a.offsets + rr + 1) - b);
+        }
     };
     auto load_words = [&](uint32_t b, int n, uint32_t& xa, uint32_t& xb, uint32_t& xh) {
         const uint16_t* cc = a.containers + b;
@@ -183,13 +187,14 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra, const AnchorVi
     load_off(r_first + total_warps, nxt_beg, nxt_n);
     load_words(cur_beg, cur_n, pa, pb, ph);
 
-    for (uint32_t r = r_first; r < a.n_reads; r += total_warps) {
+    for (uint32_t idx = r_first; idx < n_items; idx += total_warps) {
+        const uint32_t r = a.read_list ? __ldg(a.read_list + idx) : idx;
         const uint32_t beg = cur_beg;
         const int nslots = cur_n;
         const uint32_t wa = pa, wb = pb, wh = ph;
         {
             uint32_t n2_beg; int n2_n;
-            load_off(r + 2 * total_warps, n2_beg, n2_n);
+            load_off(idx + 2 * total_warps, n2_beg, n2_n);
             load_words(nxt_beg, nxt_n, pa, pb, ph);
             cur_beg = nxt_beg; cur_n = nxt_n; nxt_beg = n2_beg; nxt_n = n2_n;
         }

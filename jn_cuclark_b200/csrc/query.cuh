@@ -20,6 +20,10 @@ struct QueryArgs {
     uint32_t*       ovf_count;
     // optional accounting [0]=k-mers probed [1]=32-byte sectors read
     unsigned long long* stats;
+    // optional: classify only the reads listed (read_list[0 .. min(*n_list, n_reads)) ), e.g. the ones the
+    // thread-per-read kernel handed back
+    const uint32_t* read_list;
+    const uint32_t* n_list;
 };
 
 // Sharded table: each read's mixed k-mers h = mix2k(canonical) are sent
@@ -81,6 +85,13 @@ struct AnchorView {
 };
 // same as launch_query, but reads are first tried against the anchor index
 int launch_query_anchor(const TableView& t, const QueryArgs& a, const AnchorView& av, cudaStream_t s);
+
+// Thread-per-read kernel for short single-part reads (<= 192 bases, <= 4 distinct targets hit): every lane
+// walks its own read, so nothing is coordinated across lanes.  Reads it does not take (several parts, long,
+// many targets) are appended to redo_list / *redo_count and must be classified by launch_query with
+// read_list = redo_list afterwards.  av may be null (no anchor index).
+int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* av, uint32_t* redo_list,
+                      uint32_t* redo_count, cudaStream_t s);
 
 // fast path: one warp per read, votes kept in registers
 int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s);

@@ -15,7 +15,7 @@ import os
 
 import numpy as np
 
-CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR = 1, 2, 4, 8
+CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_LANE_KERNEL = 1, 2, 4, 8, 16
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
