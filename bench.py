@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--sample-reads", type=int, default=200_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--lane", action="store_true", help="thread-per-read kernel for short reads (CCB_LANE_KERNEL)")
     ap.add_argument("--anchor", action="store_true",
                     help="build the anchor index (target sequences + sampled k-mer positions) in front of the table")
     ap.add_argument("--sharded", action="store_true",
@@ -222,7 +223,8 @@ def run_b200(args):
     d_off, d_cont, n_cont = db.synth_reads_packed(READS_SEED, DB_SEED, rank * NR, NR, L, G, LG)
     out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
-    db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS, stream)
+    QF = 16 if args.lane else 0                                  # CCB_LANE_KERNEL
+    db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS | QF, stream)
     torch.cuda.synchronize()
     lookups, sectors = int(stats[0]), int(stats[1])
     classified = int((out.view(-1, 5)[:, 1] != 0).sum())
@@ -241,13 +243,13 @@ def run_b200(args):
 
     # ---- kernel-only: batch resident in HBM ----------------------------------------------------
     for _ in range(args.warmup):
-        db.query_device(d_off, d_cont, NR, out.data_ptr(), stream=stream)
+        db.query_device(d_off, d_cont, NR, out.data_ptr(), flags=QF, stream=stream)
     barrier()
     sampler = ClockSampler(local); sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        db.query_device(d_off, d_cont, NR, out.data_ptr(), stream=stream)
+        db.query_device(d_off, d_cont, NR, out.data_ptr(), flags=QF, stream=stream)
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
@@ -305,7 +307,7 @@ def run_b200(args):
         for s, (n, nc) in enumerate(sizes):
             if busy[s]:
                 db.waitForBatch(s)
-            db.readyBatch(s, n, nc); db.queryBatch(s); busy[s] = True
+            db.readyBatch(s, n, nc); db.queryBatch(s, flags=QF); busy[s] = True
 
     def e2e_drain():
         for s in range(S):
