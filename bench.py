@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--lane", action="store_true", help="thread-per-read kernel for short reads (CCB_LANE_KERNEL)")
     ap.add_argument("--anchor", action="store_true",
                     help="build the anchor index (target sequences + sampled k-mer positions) in front of the table")
+    ap.add_argument("--no-anchor-leg", action="store_true", help="skip the second leg (anchor index in front of the table)")
     ap.add_argument("--sharded", action="store_true",
                     help="row E2: the table sharded over the N GPUs (k-mer all-to-all) instead of replicated")
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
@@ -242,19 +243,25 @@ def run_b200(args):
         return float(t[0])
 
     # ---- kernel-only: batch resident in HBM ----------------------------------------------------
-    for _ in range(args.warmup):
-        db.query_device(d_off, d_cont, NR, out.data_ptr(), flags=QF, stream=stream)
-    barrier()
-    sampler = ClockSampler(local); sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        db.query_device(d_off, d_cont, NR, out.data_ptr(), flags=QF, stream=stream)
-    e1.record()
-    barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
-    sampler.stop_flag = True; sampler.join()
-    clocks = sampler.summary()
+    def time_resident(qf, with_clocks):
+        for _ in range(args.warmup):
+            db.query_device(d_off, d_cont, NR, out.data_ptr(), flags=qf, stream=stream)
+        barrier()
+        smp = None
+        if with_clocks:
+            smp = ClockSampler(local); smp.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            db.query_device(d_off, d_cont, NR, out.data_ptr(), flags=qf, stream=stream)
+        e1.record()
+        barrier()
+        t_ms = max_over_ranks(e0.elapsed_time(e1))
+        if smp:
+            smp.stop_flag = True; smp.join()
+        return t_ms, (smp.summary() if smp else None)
+
+    ms, clocks = time_resident(QF, True)
     total_lookups = lookups * world
     if world > 1:
         t = torch.tensor([lookups], dtype=torch.int64, device="cuda"); dist.all_reduce(t); total_lookups = int(t[0])
@@ -303,32 +310,63 @@ def run_b200(args):
     # refilled, so the H2D of one batch overlaps the kernel of the previous one across steps too.
     busy = [False] * S
 
-    def e2e_step():
-        for s, (n, nc) in enumerate(sizes):
-            if busy[s]:
-                db.waitForBatch(s)
-            db.readyBatch(s, n, nc); db.queryBatch(s, flags=QF); busy[s] = True
+    def time_e2e(qf):
+        def e2e_step():
+            for s, (n, nc) in enumerate(sizes):
+                if busy[s]:
+                    db.waitForBatch(s)
+                db.readyBatch(s, n, nc); db.queryBatch(s, flags=qf); busy[s] = True
 
-    def e2e_drain():
-        for s in range(S):
-            if busy[s]:
-                db.waitForBatch(s); busy[s] = False
+        def e2e_drain():
+            for s in range(S):
+                if busy[s]:
+                    db.waitForBatch(s); busy[s] = False
 
-    for _ in range(args.warmup):
-        e2e_step()
-    e2e_drain()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    e2e_drain()
-    torch.cuda.synchronize()
-    t_e2e = max_over_ranks(time.perf_counter() - t0)
-    barrier()
+        for _ in range(args.warmup):
+            e2e_step()
+        e2e_drain()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        e2e_drain()
+        torch.cuda.synchronize()
+        t = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        # results of the e2e path equal the resident path
+        fin = np.concatenate([db.buffers(s)[2][:n] for s, (n, _) in enumerate(sizes)])
+        return t, bool(np.array_equal(fin, out_h))
+
+    out_h = out.cpu().numpy().view(np.uint16).reshape(-1, 5).copy()
+    t_e2e, same = time_e2e(QF)
     e2e_value = total_lookups * args.steps / t_e2e
-    # results of the e2e path equal the resident path
-    fin = np.concatenate([db.buffers(s)[2][:n] for s, (n, _) in enumerate(sizes)])
-    same = bool(np.array_equal(fin, out.cpu().numpy().view(np.uint16).reshape(-1, 5)))
+
+    # ---- second leg: the anchor index in front of the same table --------------
+    # Same reads, same table, same result words; windows that match the target text base by base are
+    # answered without a table probe.  Reported beside the headline, which stays the table-only path.
+    anchor_leg = None
+    if not args.anchor and not args.no_anchor_leg:
+        t0 = time.time(); ainfo = db.anchor_synth(DB_SEED, G, LG, min(G, 65534)); t_anchor = time.time() - t0
+        AQF = 16                                                   # CCB_LANE_KERNEL; the anchor is used because it exists
+        stats.zero_(); out.zero_()
+        db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS | AQF, stream)
+        torch.cuda.synchronize()
+        a_lookups, a_sectors = int(stats[0]), int(stats[1])
+        a_same = bool(np.array_equal(out.cpu().numpy().view(np.uint16).reshape(-1, 5), out_h))
+        a_ms, _ = time_resident(AQF, False)
+        a_t_e2e, a_same_e2e = time_e2e(AQF)
+        anchor_leg = {
+            "what": "anchor index (target text + sampled k-mer positions) in front of the same table, block-cooperative "
+                    "thread-per-read kernel; results compared word for word with the table-only path",
+            "value": total_lookups * args.steps / (a_ms * 1e-3), "unit": "lookups/s", "ms_per_step": a_ms / args.steps,
+            "reads_per_s": NR * world * args.steps / (a_ms * 1e-3),
+            "e2e": {"value": total_lookups * args.steps / a_t_e2e, "unit": "lookups/s", "ms_per_step": 1e3 * a_t_e2e / args.steps,
+                    "results_equal_table_only_path": a_same_e2e},
+            "results_equal_table_only_path": a_same, "lookups_per_step_per_gpu": a_lookups,
+            "sectors_per_lookup": a_sectors / max(a_lookups, 1),
+            "index_gb": ainfo.bytes / 1e9, "index_entries": ainfo.entries, "index_dropped": ainfo.dropped, "index_build_s": t_anchor,
+            "kernel": "ccb::k_query_block<anchor>",
+        }
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -361,6 +399,8 @@ def run_b200(args):
                          "kernel": "ccb::k_query", "gather32_gbs": gather and gather[32], "gather64_gbs": gather and gather[64],
                          "frac_of_gather32": (achieved / gather[32]) if gather else None},
         }
+        if anchor_leg:
+            line["anchor_index"] = anchor_leg
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
             line["parity_sample"] = parity
