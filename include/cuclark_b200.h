@@ -59,7 +59,8 @@ typedef struct ccb_stats {
 } ccb_stats;
 
 enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8,
-       CCB_LANE_KERNEL = 16 /* thread-per-read kernel for short single-part reads, the rest as usual */ };
+       CCB_LANE_KERNEL = 16 /* thread-per-read kernel for short single-part reads, the rest as usual
+                               (implied when the anchor index is in use) */ };
 
 /* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
 int  ccb_create(const ccb_config* cfg, ccb_handle** out);
@@ -158,6 +159,11 @@ int  ccb_ipc_close(ccb_handle* h, void* ptr);
  * that matches is answered from the position bits without a table probe, every other window is probed
  * as usual -- so the answer is exact whatever the index contains.  Built after the table is loaded;
  * dropped when the table is replaced.  CCB_NO_ANCHOR in the query flags bypasses it.
+ *   ccb_anchor_begin / ccb_anchor_add_fasta / ccb_anchor_end
+ *                      from the target FASTA texts the database was built from (the files of the targets
+ *                      definition, src/CuCLARK_hh.hh:1129-1198 gives the scan rules); label as in
+ *                      ccb_build_add_fasta; add_fasta may be called from several host threads; max_bases bounds
+ *                      the bytes of all texts together and must stay below 2^32 (positions are 32-bit)
  *   ccb_anchor_synth   for the synthetic workload of ccb_synth_db (same seed / genomes / labels) */
 typedef struct ccb_anchor_info {
     int      ready;
@@ -166,6 +172,9 @@ typedef struct ccb_anchor_info {
     uint64_t dropped;     /* sampled k-mers that found their bucket full */
     uint64_t bytes;       /* device bytes */
 } ccb_anchor_info;
+int  ccb_anchor_begin(ccb_handle* h, uint64_t max_bases);
+int  ccb_anchor_add_fasta(ccb_handle* h, const unsigned char* text, uint64_t len, uint16_t label);
+int  ccb_anchor_end(ccb_handle* h, ccb_anchor_info* info);
 int  ccb_anchor_synth(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels);
 int  ccb_anchor_drop(ccb_handle* h);
 int  ccb_anchor_get_info(const ccb_handle* h, ccb_anchor_info* info);

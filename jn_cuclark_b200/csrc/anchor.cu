@@ -2,13 +2,15 @@
 //
 // Input: the targets as one code stream F (0..3 = base in x-encoding, 4 = not a base: N, record
 // boundary), the same stream the database builder scans, and the label of every record.
-//   text   T = F . revcomp(F), 2 bits per base + a validity bit per base
-//   disc   bit p = the k-mer starting at T[p] is stored in the k-mer table (one table lookup per
-//          position, once, at build time)
-//   table  every 8th k-mer of F by hash (top three bits of mix2k zero) -> [fp15 | fwd | label16 | pos32];
-//          first come first served, a full bucket drops the newcomer: the index only ever SAVES probes,
-//          exactness never depends on it (k_query<kModeAnchor> verifies base by base).
+//   text    T = F . revcomp(F), per 32 positions: 2 words of bases, validity bits, and two bits per position
+//           from ONE table lookup at build time: "the k-mer starting here is stored under this record's
+//           label" / "... under another label" (light databases, databases built from other files)
+//   sampled every canonical k-mer of F with anchor_sampled() -> [fp15 | fwd | label16 | pos32] in a sector of
+//           four, overflowing into the neighbouring sector of the same line; first come first served, a
+//           k-mer that finds both full is dropped: the index only ever SAVES probes, exactness never depends
+//           on it (k_query_block verifies base by base).
 #include "capi_internal.cuh"
+#include "dbbuild.cuh"
 #include "../../include/ccb_synth.h"
 #include <algorithm>
 #include <vector>
@@ -23,7 +25,7 @@ namespace ccb {
 
 void anchor_free(Anchor& a)
 {
-    cudaFree(a.d_seq); cudaFree(a.d_valid); cudaFree(a.d_disc); cudaFree(a.d_buckets);
+    cudaFree(a.d_txt); cudaFree(a.d_buckets);
     a = Anchor{};
 }
 
@@ -31,9 +33,8 @@ namespace {
 
 struct ASeg { uint64_t start; uint32_t label; uint32_t pad; };
 
-// 32 bases of T per thread -> 2 sequence words + 1 validity word
-__global__ void k_pack_text(const uint8_t* __restrict__ codes, uint64_t n_codes, uint64_t nF,
-                            uint32_t* seq, uint32_t* valid)
+// 32 positions of T per thread -> 2 words of bases + 1 validity word
+__global__ void k_pack_text(const uint8_t* __restrict__ codes, uint64_t n_codes, uint64_t nF, uint32_t* txt)
 {
     const uint64_t nblk = 2 * nF / 32;
     for (uint64_t b = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; b < nblk; b += gridDim.x * (uint64_t)blockDim.x) {
@@ -47,24 +48,27 @@ __global__ void k_pack_text(const uint8_t* __restrict__ codes, uint64_t n_codes,
             if (c < 4u) v |= 1u << i;
             if (i < 16) w0 |= base << (30 - 2 * i); else w1 |= base << (30 - 2 * (i - 16));
         }
-        seq[2 * b] = w0; seq[2 * b + 1] = w1; valid[b] = v;
+        uint32_t* g = txt + kTextWords * b;
+        g[0] = w0; g[1] = w1; g[2] = v; g[3] = 0; g[4] = 0;
     }
 }
 
-__device__ __forceinline__ uint32_t text_code(const uint32_t* seq, uint64_t p) { return (seq[p >> 4] >> (30 - 2 * (int)(p & 15))) & 3u; }
-__device__ __forceinline__ bool text_valid(const uint32_t* valid, uint64_t p) { return (valid[p >> 5] >> (p & 31)) & 1u; }
+__device__ __forceinline__ uint32_t text_code(const uint32_t* txt, uint64_t p)
+{
+    return (txt[kTextWords * (p >> 5) + ((p >> 4) & 1)] >> (30 - 2 * (int)(p & 15))) & 3u;
+}
+__device__ __forceinline__ bool text_valid(const uint32_t* txt, uint64_t p) { return (txt[kTextWords * (p >> 5) + 2] >> (p & 31)) & 1u; }
 
 // For the 32 k-mer start positions of block b: roll over the text, call f(p, forward k-mer, reverse complement).
 template <typename F>
-__device__ __forceinline__ void for_kmers_of_block(const uint32_t* seq, const uint32_t* valid, uint64_t n_text, uint64_t b,
-                                                   int k, uint64_t mask, F&& f)
+__device__ __forceinline__ void for_kmers_of_block(const uint32_t* txt, uint64_t n_text, uint64_t b, int k, uint64_t mask, F&& f)
 {
     const uint64_t p_first = 32 * b;
     uint64_t x = 0, rc = 0; int run = 0;
     const int s2 = 2 * (k - 1);
     for (uint64_t e = p_first; e < p_first + 32 + (uint64_t)k - 1 && e < n_text; e++) {
-        if (!text_valid(valid, e)) { run = 0; x = 0; rc = 0; continue; }
-        const uint64_t c = text_code(seq, e);
+        if (!text_valid(txt, e)) { run = 0; x = 0; rc = 0; continue; }
+        const uint64_t c = text_code(txt, e);
         x = ((x << 2) | c) & mask;
         rc = (rc >> 2) | ((3ull - c) << s2);
         if (run < k) run++;
@@ -75,40 +79,51 @@ __device__ __forceinline__ void for_kmers_of_block(const uint32_t* seq, const ui
     }
 }
 
-__global__ void k_disc_bits(const TableView t, const uint32_t* __restrict__ seq, const uint32_t* __restrict__ valid,
-                            uint64_t n_text, uint32_t* disc)
+// label of the record that holds F position p (segs ascending by start)
+__device__ __forceinline__ uint32_t seg_label(const ASeg* __restrict__ segs, int nseg, uint64_t p)
 {
-    const uint64_t nblk = n_text / 32;
+    int lo = 0, hi = nseg - 1;
+    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (segs[mid].start <= p) lo = mid; else hi = mid - 1; }
+    return segs[lo].label & 0xFFFFu;
+}
+
+__global__ void k_text_bits(const TableView t, uint32_t* txt, uint64_t nF, const ASeg* __restrict__ segs, int nseg)
+{
+    const uint64_t nblk = 2 * nF / 32;
     for (uint64_t b = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; b < nblk; b += gridDim.x * (uint64_t)blockDim.x) {
-        uint32_t bits = 0;
-        for_kmers_of_block(seq, valid, n_text, b, t.hp.k, t.hp.mask, [&](uint64_t p, uint64_t x, uint64_t rc) {
-            if (lookup(t, x < rc ? x : rc) != kLabelNone) bits |= 1u << (p - 32 * b);
+        uint32_t same = 0, other = 0;
+        for_kmers_of_block(txt, 2 * nF, b, t.hp.k, t.hp.mask, [&](uint64_t p, uint64_t x, uint64_t rc) {
+            const uint32_t l = lookup(t, x < rc ? x : rc);
+            if (l >= kLabelTomb) return;                                        // absent, or stored as not discriminative
+            const uint64_t pf = p < nF ? p : nF - 1 - (p - nF);                 // an F position inside the k-mer
+            if (l == seg_label(segs, nseg, pf)) same |= 1u << (p - 32 * b); else other |= 1u << (p - 32 * b);
         });
-        disc[b] = bits;
+        txt[kTextWords * b + 3] = same; txt[kTextWords * b + 4] = other;
     }
 }
 
-__global__ void k_anchor_insert(const HashParams hp, const uint32_t* __restrict__ seq, const uint32_t* __restrict__ valid,
-                                uint64_t nF, const ASeg* __restrict__ segs, int nseg,
+__global__ void k_anchor_insert(const HashParams hp, const uint32_t* __restrict__ txt, uint64_t nF,
+                                const ASeg* __restrict__ segs, int nseg,
                                 unsigned long long* buckets, uint64_t nb, unsigned long long* counts)
 {
     const uint64_t nblk = nF / 32;
     const int k = hp.k;
     for (uint64_t b = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; b < nblk; b += gridDim.x * (uint64_t)blockDim.x) {
-        int lo = 0, hi = nseg - 1;
-        while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (segs[mid].start <= 32 * b) lo = mid; else hi = mid - 1; }
-        for_kmers_of_block(seq, valid, nF, b, k, hp.mask, [&](uint64_t p, uint64_t x, uint64_t rc) {
-            const uint64_t h = mix2k(x < rc ? x : rc, k, hp.mask);
-            if ((h >> (2 * k - 3)) != 0) return;
-            while (lo + 1 < nseg && segs[lo + 1].start <= p) lo++;
-            const uint64_t ent = ((uint64_t)((uint32_t)(h >> 3) & 0x7FFFu) << 49) | ((uint64_t)(x <= rc ? 1u : 0u) << 48) |
-                                 ((uint64_t)(segs[lo].label & 0xFFFFu) << 32) | p;
-            const uint64_t bi = mulhi64(((h << 3) & hp.mask) << hp.shift, nb);
-            unsigned long long* s = buckets + bi * 4;
-            for (int i = 0; i < 4; i++) {
-                if (s[i] == ~0ull && atomicCAS(s + i, ~0ull, (unsigned long long)ent) == ~0ull) { atomicAdd(counts, 1ull); return; }
+        for_kmers_of_block(txt, nF, b, k, hp.mask, [&](uint64_t p, uint64_t x, uint64_t rc) {
+            const uint64_t c = x < rc ? x : rc;
+            if (!anchor_sampled(c)) return;
+            const uint64_t h = mix2k(c, k, hp.mask);
+            const uint64_t ent = ((uint64_t)((uint32_t)h & 0x7FFFu) << 49) | ((uint64_t)(x <= rc ? 1u : 0u) << 48) |
+                                 ((uint64_t)seg_label(segs, nseg, p) << 32) | p;
+            const uint64_t bi = mulhi64(h << hp.shift, nb);
+#pragma unroll
+            for (int alt = 0; alt < 2; alt++) {
+                unsigned long long* s = buckets + (bi ^ (uint64_t)alt) * 4;
+                for (int i = 0; i < 4; i++) {
+                    if (s[i] == ~0ull && atomicCAS(s + i, ~0ull, (unsigned long long)ent) == ~0ull) { atomicAdd(counts, 1ull); return; }
+                }
             }
-            atomicAdd(counts + 1, 1ull);          // bucket full: dropped
+            atomicAdd(counts + 1, 1ull);          // both sectors full: dropped
         });
     }
 }
@@ -129,28 +144,28 @@ int anchor_build(ccb_handle* h, const uint8_t* d_codes, uint64_t n_codes, const 
 {
     if (!h->db_ready) return ccb_fail(h, -70, "anchor index: the k-mer table must be loaded first");
     if (h->n_shards > 1) return ccb_fail(h, -70, "anchor index: not with a sharded table");
+    if (segs.empty()) return ccb_fail(h, -70, "anchor index: no records");
     anchor_free(h->anchor);
     const uint64_t nF = (n_codes + 64 + 31) / 32 * 32;
-    if (2 * nF >= (1ull << 32) * 2 || nF >= (1ull << 32)) return ccb_fail(h, -71, "anchor index: %llu bases do not fit 32-bit positions", (unsigned long long)n_codes);
+    if (nF >= (1ull << 32)) return ccb_fail(h, -71, "anchor index: %llu bases do not fit 32-bit positions", (unsigned long long)n_codes);
     cudaStream_t s = h->db_stream;
     Anchor& a = h->anchor;
     a.nF = nF;
-    const uint64_t seq_words = 2 * nF / 16 + 64, bit_words = 2 * nF / 32 + 64;
-    CU(h, cudaMalloc(&a.d_seq, seq_words * 4)); CU(h, cudaMalloc(&a.d_valid, bit_words * 4)); CU(h, cudaMalloc(&a.d_disc, bit_words * 4));
-    CU(h, cudaMemsetAsync(a.d_seq, 0, seq_words * 4, s)); CU(h, cudaMemsetAsync(a.d_valid, 0, bit_words * 4, s));
-    CU(h, cudaMemsetAsync(a.d_disc, 0, bit_words * 4, s));
-    k_pack_text<<<148 * 16, 256, 0, s>>>(d_codes, n_codes, nF, a.d_seq, a.d_valid);
-    k_disc_bits<<<148 * 32, 256, 0, s>>>(h->table.view(), a.d_seq, a.d_valid, 2 * nF, a.d_disc);
-    a.nb = std::max<uint64_t>(1024, nF / 16);                  // nF/8 sampled k-mers at most, 4 per bucket, half full
-    CU(h, cudaMalloc(&a.d_buckets, a.nb * 32));
-    CU(h, cudaMemsetAsync(a.d_buckets, 0xFF, a.nb * 32, s));
+    const uint64_t txt_words = (2 * nF / 32 + 16) * kTextWords;              // 16 groups of slack: the kernel reads ahead
+    CU(h, cudaMalloc(&a.d_txt, txt_words * 4));
+    CU(h, cudaMemsetAsync(a.d_txt, 0, txt_words * 4, s));
     std::vector<ASeg> hs(segs.size());
     for (size_t i = 0; i < segs.size(); i++) hs[i] = ASeg{segs[i].first, segs[i].second, 0};
     ASeg* d_segs = nullptr; unsigned long long* d_cnt = nullptr;
-    CU(h, cudaMalloc(&d_segs, std::max<size_t>(1, hs.size()) * sizeof(ASeg))); CU(h, cudaMalloc(&d_cnt, 16));
+    CU(h, cudaMalloc(&d_segs, hs.size() * sizeof(ASeg))); CU(h, cudaMalloc(&d_cnt, 16));
     CU(h, cudaMemcpyAsync(d_segs, hs.data(), hs.size() * sizeof(ASeg), cudaMemcpyHostToDevice, s));
     CU(h, cudaMemsetAsync(d_cnt, 0, 16, s));
-    k_anchor_insert<<<148 * 32, 256, 0, s>>>(h->table.hp, a.d_seq, a.d_valid, nF, d_segs, (int)hs.size(),
+    k_pack_text<<<148 * 16, 256, 0, s>>>(d_codes, n_codes, nF, a.d_txt);
+    k_text_bits<<<148 * 32, 256, 0, s>>>(h->table.view(), a.d_txt, nF, d_segs, (int)hs.size());
+    a.nb = std::max<uint64_t>(1024, nF / 16) & ~1ull;          // nF/8 sampled k-mers expected, 4 per sector, half full
+    CU(h, cudaMalloc(&a.d_buckets, a.nb * 32));
+    CU(h, cudaMemsetAsync(a.d_buckets, 0xFF, a.nb * 32, s));
+    k_anchor_insert<<<148 * 32, 256, 0, s>>>(h->table.hp, a.d_txt, nF, d_segs, (int)hs.size(),
                                             (unsigned long long*)a.d_buckets, a.nb, d_cnt);
     unsigned long long cnt[2] = {0, 0};
     CU(h, cudaMemcpyAsync(cnt, d_cnt, 16, cudaMemcpyDeviceToHost, s));
@@ -158,7 +173,7 @@ int anchor_build(ccb_handle* h, const uint8_t* d_codes, uint64_t n_codes, const 
     CU(h, cudaGetLastError());
     cudaFree(d_segs); cudaFree(d_cnt);
     a.entries = cnt[0]; a.dropped = cnt[1];
-    a.bytes = seq_words * 4 + 2 * bit_words * 4 + a.nb * 32;
+    a.bytes = txt_words * 4 + a.nb * 32;
     a.ready = true;
     if (h->cfg.verbose) fprintf(stderr, "anchor index: %llu bases x 2 strands, %llu sampled k-mers (%llu dropped), %.2f GB\n",
                                 (unsigned long long)nF, cnt[0], cnt[1], a.bytes / 1e9);
@@ -179,6 +194,66 @@ extern "C" int ccb_anchor_synth(ccb_handle* h, uint64_t db_seed, uint32_t n_geno
     for (uint32_t g = 0; g < n_genomes; g++) segs[g] = {(uint64_t)g * (genome_len + 1), g % n_labels};
     int rc = anchor_build(h, d_codes, n, segs);
     cudaFree(d_codes);
+    return rc;
+}
+
+// ---- from the target FASTA files (the texts the database was built from) -------------------------------
+namespace ccb {
+struct AnchorBuild {
+    uint8_t* d_codes = nullptr; uint64_t cap = 0, n = 0;
+    std::vector<std::pair<uint64_t, uint32_t>> segs;
+};
+void anchor_build_free(ccb_handle* h)
+{
+    if (!h->anchor_build) return;
+    cudaFree(h->anchor_build->d_codes);
+    delete h->anchor_build; h->anchor_build = nullptr;
+}
+}  // namespace ccb
+
+extern "C" int ccb_anchor_begin(ccb_handle* h, uint64_t max_bases)
+{
+    if (!h) return -1;
+    USE_DEV(h);
+    if (!h->db_ready) return ccb_fail(h, -70, "anchor index: the k-mer table must be loaded first");
+    if (h->n_shards > 1) return ccb_fail(h, -70, "anchor index: not with a sharded table");
+    if (max_bases + 64 >= (1ull << 32)) return ccb_fail(h, -71, "anchor index: %llu bases do not fit 32-bit positions", (unsigned long long)max_bases);
+    std::lock_guard<std::mutex> g(h->build_mu);
+    anchor_build_free(h);
+    AnchorBuild* b = new AnchorBuild;
+    b->cap = max_bases + 64;
+    cudaError_t e = cudaMalloc(&b->d_codes, b->cap);
+    if (e != cudaSuccess) { delete b; return ccb_fail(h, (int)e, "anchor index: out of GPU memory (%llu bases): %s", (unsigned long long)max_bases, cudaGetErrorString(e)); }
+    h->anchor_build = b;
+    return 0;
+}
+
+extern "C" int ccb_anchor_add_fasta(ccb_handle* h, const unsigned char* text, uint64_t len, uint16_t label)
+{
+    if (!h || !h->anchor_build) return ccb_fail(h, -72, "ccb_anchor_add_fasta: call ccb_anchor_begin first");
+    if (!text || len == 0) return 0;
+    std::unique_ptr<uint8_t[]> codes; uint64_t bases = 0;
+    const size_t n = fasta_to_codes(text, len, codes, bases);      // outside the lock: several host threads scan at once
+    if (n == 0) return 0;
+    std::lock_guard<std::mutex> g(h->build_mu);
+    USE_DEV(h);
+    AnchorBuild* b = h->anchor_build;
+    if (b->n + n > b->cap) return ccb_fail(h, -73, "anchor index: more bases than announced in ccb_anchor_begin");
+    CU(h, cudaMemcpy(b->d_codes + b->n, codes.get(), n, cudaMemcpyHostToDevice));
+    b->segs.push_back({b->n, (uint32_t)label});
+    b->n += n;
+    return 0;
+}
+
+extern "C" int ccb_anchor_end(ccb_handle* h, ccb_anchor_info* info)
+{
+    if (!h || !h->anchor_build) return ccb_fail(h, -72, "ccb_anchor_end: call ccb_anchor_begin first");
+    USE_DEV(h);
+    std::lock_guard<std::mutex> g(h->build_mu);
+    AnchorBuild* b = h->anchor_build;
+    int rc = b->n ? anchor_build(h, b->d_codes, b->n, b->segs) : 0;
+    anchor_build_free(h);
+    if (rc == 0 && info) ccb_anchor_get_info(h, info);
     return rc;
 }
 

@@ -106,6 +106,7 @@ extern "C" void ccb_destroy(ccb_handle* h)
     cudaDeviceSynchronize();
     free_slots(h);
     build_free(h);
+    anchor_build_free(h);
     anchor_free(h->anchor);
     table_destroy(h->table);
     cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense); cudaFree(h->shard_scan_tmp);
@@ -366,14 +367,14 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
     }
     const bool use_anchor = h->anchor.ready && !(flags & CCB_NO_ANCHOR);
     const AnchorView av = h->anchor.view();
-    if ((flags & CCB_LANE_KERNEL) && list_cap >= a.n_reads) {
+    // short single-part reads: thread-per-read block kernel when asked for, and whenever the anchor index is used
+    if (((flags & CCB_LANE_KERNEL) || use_anchor) && list_cap >= a.n_reads) {
         uint32_t* redo_list = ovf_list + list_cap; uint32_t* redo_count = ovf_count + 1;
         rc = launch_query_lane(tv, a, use_anchor ? &av : nullptr, redo_list, redo_count, st);
         if (rc) return rc;
         a.read_list = redo_list; a.n_list = redo_count;
     }
-    if (use_anchor) rc = launch_query_anchor(tv, a, av, st);
-    else rc = launch_query(tv, a, st);
+    rc = launch_query(tv, a, st);
     if (rc) return rc;
     QueryArgs d = a; d.stats = nullptr; d.read_list = nullptr; d.n_list = nullptr;
     return launch_query_dense(tv, d, ovf_list, ovf_count, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);

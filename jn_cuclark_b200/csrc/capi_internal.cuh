@@ -32,13 +32,15 @@ constexpr uint32_t kDenseBlocks = 64;
 
 // anchor index owner (anchor.cu)
 struct Anchor {
-    uint32_t* d_seq = nullptr; uint32_t* d_valid = nullptr; uint32_t* d_disc = nullptr;
+    uint32_t* d_txt = nullptr;
     ulonglong4* d_buckets = nullptr;
     uint64_t nF = 0, nb = 0, entries = 0, dropped = 0, bytes = 0;
     bool ready = false;
-    AnchorView view() const { return AnchorView{d_seq, d_valid, d_disc, nF, d_buckets, nb}; }
+    AnchorView view() const { return AnchorView{d_txt, nF, d_buckets, nb}; }
 };
 void anchor_free(Anchor& a);
+struct AnchorBuild;                  // anchor.cu: target texts being collected (ccb_anchor_begin .. ccb_anchor_end)
+void anchor_build_free(ccb_handle* h);
 struct BuildState;                   // dbbuild.cu
 
 }  // namespace ccb
@@ -63,6 +65,7 @@ struct ccb_handle {
     uint32_t   n_shards = 1, shard = 0;
     void*      shard_scan_tmp = nullptr; size_t shard_scan_bytes = 0;
     ccb::Anchor anchor;              // optional: sequences + sampled k-mer positions in front of the table
+    ccb::AnchorBuild* anchor_build = nullptr;
     // database construction in progress (ccb_build_*)
     ccb::BuildState* build = nullptr;
     std::mutex  build_mu;

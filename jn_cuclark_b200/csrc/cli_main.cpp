@@ -240,6 +240,50 @@ struct Engine {
         return resident;
     }
 
+    // Optional (environment CCB_ANCHOR=1; no counterpart in the reference, results are unchanged): keep the
+    // target sequences on every device so that read windows which match a target base by base are answered
+    // without a table probe (include/cuclark_b200.h "Anchor index").  Any failure only costs the speed-up.
+    void build_anchor()
+    {
+        const char* env = getenv("CCB_ANCHOR");
+        if (!env || !*env || *env == '0' || tg.files.empty()) return;
+        struct timeval t0, t1;
+        gettimeofday(&t0, NULL);
+        uint64_t total = 0;
+        for (auto& f : tg.files) { struct stat sb; if (stat(f.first.c_str(), &sb) == 0) total += (uint64_t)sb.st_size; }
+        for (ccb_handle* h : devs)
+            if (ccb_anchor_begin(h, total)) { cerr << "Anchor index not built: " << ccb_last_error(h) << endl; return; }
+        std::atomic<size_t> next{0};
+        std::atomic<bool> failed{false};
+        auto work = [&] {
+            for (size_t t = next++; t < tg.files.size() && !failed; t = next++) {
+                const string& fn = tg.files[t].first;
+                int fd = open(fn.c_str(), O_RDONLY);
+                struct stat sb;
+                if (fd == -1 || fstat(fd, &sb) == -1 || sb.st_size == 0) { if (fd != -1) close(fd); continue; }
+                void* map = mmap(0, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+                if (map == MAP_FAILED) { close(fd); continue; }
+                for (ccb_handle* h : devs)
+                    if (ccb_anchor_add_fasta(h, (const unsigned char*)map, (uint64_t)sb.st_size, tg.files[t].second)) failed = true;
+                munmap(map, (size_t)sb.st_size); close(fd);
+            }
+        };
+        vector<std::thread> th;
+        for (size_t i = 0; i < std::max<size_t>(1, std::min<size_t>(cli.cpu, tg.files.size())); i++) th.emplace_back(work);
+        for (auto& t : th) t.join();
+        for (ccb_handle* h : devs) {
+            ccb_anchor_info ai;
+            memset(&ai, 0, sizeof ai);
+            if (failed) { ccb_anchor_end(h, NULL); ccb_anchor_drop(h); cerr << "Anchor index not built: " << ccb_last_error(h) << endl; continue; }
+            if (ccb_anchor_end(h, &ai)) { cerr << "Anchor index not built: " << ccb_last_error(h) << endl; continue; }
+            if (cli.verbose) {
+                gettimeofday(&t1, NULL);
+                cerr << "Anchor index: " << ai.bases << " bases, " << ai.entries << " sampled k-mers, " << ai.bytes / 1e9 << " GB, "
+                     << (t1.tv_sec - t0.tv_sec) + (t1.tv_usec - t0.tv_usec) / 1e6 << " s" << endl;
+            }
+        }
+    }
+
     // runSimple (src/CuCLARK_hh.hh:513-574) on a text already in memory or mapped
     void classify(const char* shown_name, const uint8_t* map, size_t nb, const char* result_prefix, bool paired)
     {
@@ -434,6 +478,7 @@ int main(int argc, char** argv)
     }
     e.open_devices();
     e.load_db();
+    e.build_anchor();
     e.run();
     for (ccb_handle* h : e.devs) ccb_destroy(h);
     return 0;

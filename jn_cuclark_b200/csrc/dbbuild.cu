@@ -393,6 +393,16 @@ int flush_codes(ccb_handle* h, BuildState* b) { return b->wide ? flush_codes_t<t
 
 }  // namespace
 
+namespace ccb {
+size_t fasta_to_codes(const unsigned char* text, uint64_t len, std::unique_ptr<uint8_t[]>& out, uint64_t& bases)
+{
+    CodeBuf b;
+    compact_fasta(text, len, b, bases);
+    out = std::move(b.p);
+    return b.n;
+}
+}  // namespace ccb
+
 extern "C" int ccb_build_begin(ccb_handle* h, uint64_t htsize, int key_bytes, int light, unsigned gap,
                                unsigned min_count, uint64_t max_bases)
 {

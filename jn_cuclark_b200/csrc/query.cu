@@ -82,21 +82,6 @@ __device__ __forceinline__ void vote_bulk(uint32_t L, uint32_t total, uint32_t& 
     }
 }
 
-// 16 bases compared: diff = text word ^ read word (2 bits per base, first base in the top bits)
-// -> 16 bits, bit b set iff base b differs
-__device__ __forceinline__ uint32_t mismatch16(uint32_t diff)
-{
-    uint32_t v = __brev((diff | (diff >> 1)) & 0x55555555u) >> 1;     // base b -> bit 2b
-    v &= 0x55555555u;
-    v = (v | (v >> 1)) & 0x33333333u;
-    v = (v | (v >> 2)) & 0x0F0F0F0Fu;
-    v = (v | (v >> 4)) & 0x00FF00FFu;
-    v = (v | (v >> 8)) & 0x0000FFFFu;
-    return v;
-}
-
-struct AnchorSmem { uint32_t good[8]; uint32_t disc[8]; };
-
 // Writes a read's result {sumN, idxBest, best, idxSecond, second} (src/CuClarkDB.cu:1370-1405), its
 // sparse row when asked for, and lists it for the dense pass when it overflowed the accumulators.
 __device__ __forceinline__ void finish_read(const QueryArgs& a, uint32_t r, uint32_t acc_lab, uint32_t acc_cnt,
@@ -138,16 +123,14 @@ __device__ __forceinline__ void finish_read(const QueryArgs& a, uint32_t r, uint
 // MODE 0: classify against a table held whole (the product path).
 // MODE 1/2: sharded table -- count, then write, each read's mixed k-mers per owner shard
 //           (same walk, so both passes see the k-mers in the same order).
-// MODE 3: MODE 0 with the anchor index in front (AnchorView).
-enum { kModeQuery = 0, kModeCount = 1, kModeRoute = 2, kModeAnchor = 3 };
+enum { kModeQuery = 0, kModeCount = 1, kModeRoute = 2 };
 
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 2)
-k_query(const TableView t, const QueryArgs a, const RouteArgs ra, const AnchorView av)
+k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
 {
-    constexpr bool kProbe = MODE == kModeQuery || MODE == kModeAnchor;     // modes that probe the table and vote
+    constexpr bool kProbe = MODE == kModeQuery;     // the mode that probes the table and votes
     __shared__ WarpSmem smem[kWarpsPerCta];
-    __shared__ AnchorSmem asmem[MODE == kModeAnchor ? kWarpsPerCta : 1];
     const int lane = threadIdx.x & 31;
     const int wid  = threadIdx.x >> 5;
     WarpSmem& sw = smem[wid];
@@ -277,97 +260,6 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra, const AnchorVi
                 uint64_t rc = revcomp(x, k);
                 uint64_t rest_hi = (hi << s2) | (lo >> (64 - s2)), rest_lo = lo << s2;
                 const int ngroups = chunk >> 2;
-                uint32_t ver = 0;                 // bit j: k-mer j of my chunk is answered by the anchor index
-                if (MODE == kModeAnchor && ntiles == 1 && chunk == 4 && 1 + (((int)wh + 7) >> 3) == nslots) {
-                    // ---- my four k-mers (on copies of the rolling state), which of them are sampled ----
-                    uint64_t ax = x, arc = rc, ah = rest_hi, al = rest_lo;
-                    uint64_t hs[4]; uint32_t okm = 0, fwdm = 0, samp = 0;
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        uint64_t code = ah >> 62;
-                        ah = (ah << 2) | (al >> 62); al <<= 2;
-                        ax = ((ax << 2) | code) & kmsk;
-                        arc = (arc >> 2) | ((3ull - code) << s2);
-                        const bool okj = (p0 + j < npos) && (((vm >> j) & validk) == validk);
-                        hs[j] = mix2k(ax < arc ? ax : arc, k, kmsk);
-                        okm |= (okj ? 1u : 0u) << j; fwdm |= (ax <= arc ? 1u : 0u) << j;
-                        if (okj && (hs[j] >> (2 * k - 3)) == 0) samp |= 1u << j;
-                    }
-                    // ---- the first and the last sampled k-mer of the read are looked up ----
-                    const uint32_t bl = __ballot_sync(0xFFFFFFFFu, samp != 0);
-                    if (bl) {
-                        const int l1 = __ffs(bl) - 1, l2 = 31 - __clz(bl);
-                        uint64_t ent = ~0ull; int aj = 0;
-                        if (lane == l1 || lane == l2) {
-                            aj = lane == l1 ? __ffs(samp) - 1 : 31 - __clz(samp);
-                            uint64_t h = hs[0];
-#pragma unroll
-                            for (int j = 1; j < 4; j++) if (aj == j) h = hs[j];
-                            const uint64_t hl = (h << 3) & kmsk;                         // the sampled bits are all zero
-                            const uint64_t bi = mulhi64(hl << t.hp.shift, av.nb);
-                            const uint32_t fp = (uint32_t)(h >> 3) & 0x7FFFu;
-                            uint64_t e[4];
-                            load_bucket(av.buckets + bi, e);
-                            if (STATS) st_sectors++;
-#pragma unroll
-                            for (int sl = 3; sl >= 0; sl--) if ((uint32_t)(e[sl] >> 49) == fp && e[sl] != ~0ull) ent = e[sl];
-                        }
-                        const uint64_t e1 = __shfl_sync(0xFFFFFFFFu, ent, l1), e2 = __shfl_sync(0xFFFFFFFFu, ent, l2);
-                        const int src = e1 != ~0ull ? l1 : l2;
-                        const uint64_t ae = e1 != ~0ull ? e1 : e2;
-                        if (ae != ~0ull) {
-                            const int apos = __shfl_sync(0xFFFFFFFFu, p0 + aj, src);                  // read position of the anchor k-mer
-                            const uint32_t afwd = __shfl_sync(0xFFFFFFFFu, (fwdm >> aj) & 1u, src);
-                            const uint32_t alab = (uint32_t)(ae >> 32) & 0xFFFFu;
-                            const uint64_t tpos = ae & 0xFFFFFFFFull;
-                            const bool same = afwd == ((uint32_t)(ae >> 48) & 1u);
-                            // text position of read base 0 (F half, or the reverse-complement half)
-                            const int64_t g0 = same ? (int64_t)tpos - apos
-                                                    : (int64_t)(2 * av.nF - tpos - (uint64_t)k) - apos;
-                            const int L = npos + k - 1;                                                 // bases of the read
-                            if (g0 >= 0 && (uint64_t)g0 + 192 + 32 <= 2 * av.nF) {
-                                // ---- compare the read with the text: lanes 0..11 take 16 bases each ----
-                                const uint64_t w0 = (uint64_t)g0 >> 4; const int sh = 2 * (int)(g0 & 15);
-                                uint32_t tw = lane < 13 ? __ldg(av.seq + w0 + lane) : 0u;
-                                const uint32_t tn = __shfl_down_sync(0xFFFFFFFFu, tw, 1);
-                                const uint32_t al16 = __funnelshift_l(tn, tw, sh);
-                                const uint32_t m16 = lane < 12 ? mismatch16(al16 ^ sw.base[min(lane, kBaseWords - 1)]) : 0u;
-                                const uint32_t mlo = __shfl_sync(0xFFFFFFFFu, m16, (2 * lane) & 31), mhi = __shfl_sync(0xFFFFFFFFu, m16, (2 * lane + 1) & 31);
-                                // ---- genome validity and "stored in the table" bits, 32 positions per lane (0..5) ----
-                                const uint64_t v0 = (uint64_t)g0 >> 5; const int vs = (int)(g0 & 31);
-                                uint32_t gv = 0, gd = 0;
-                                if (lane < 6) {
-                                    gv = __funnelshift_r(__ldg(av.valid + v0 + lane), __ldg(av.valid + v0 + lane + 1), vs);
-                                    gd = __funnelshift_r(__ldg(av.disc + v0 + lane), __ldg(av.disc + v0 + lane + 1), vs);
-                                }
-                                if (STATS) st_sectors += lane < 3 ? 1u : 0u;
-                                const int nb_here = L - 32 * lane;                                      // read bases in my 32-base word
-                                const uint32_t need = nb_here >= 32 ? 0xFFFFFFFFu : (nb_here > 0 ? (1u << nb_here) - 1u : 0u);
-                                const bool span_ok = lane >= 6 || (gv & need) == need;
-                                // a separator / N inside the span could put later windows into another record: no shortcut then
-                                if (__all_sync(0xFFFFFFFFu, span_ok)) {
-                                    AnchorSmem& as = asmem[wid];
-                                    if (lane < 6) { as.good[lane] = ~(mlo | (mhi << 16)) & gv; as.disc[lane] = gd; }
-                                    if (lane >= 6 && lane < 8) { as.good[lane] = 0; as.disc[lane] = 0; }
-                                    __syncwarp();
-                                    const int jm = p0 >> 5, shm = p0 & 31;
-                                    const uint64_t gw = ((uint64_t)__funnelshift_r(as.good[jm + 1], as.good[jm + 2], shm) << 32) |
-                                                        __funnelshift_r(as.good[jm], as.good[jm + 1], shm);
-                                    const uint32_t dw = __funnelshift_r(as.disc[jm], as.disc[jm + 1], shm);
-                                    uint32_t hits = 0;
-#pragma unroll
-                                    for (int j = 0; j < 4; j++) {
-                                        if (((okm >> j) & 1u) && ((gw >> j) & validk) == validk) { ver |= 1u << j; hits += (dw >> j) & 1u; }
-                                    }
-                                    const uint32_t total = __reduce_add_sync(0xFFFFFFFFu, hits);
-                                    if (total) vote_bulk(alab, total, acc_lab, acc_cnt, nacc, overflow, lane);
-                                    if (STATS) st_lookups += __popc(ver);
-                                    __syncwarp();
-                                }
-                            }
-                        }
-                    }
-                }
                 for (int g = 0; g < ngroups; g++) {
                     uint64_t e[4][4]; uint64_t home[4], q[4]; bool ok[4];
 #pragma unroll
@@ -378,7 +270,6 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra, const AnchorVi
                         x = ((x << 2) | code) & kmsk;
                         rc = (rc >> 2) | ((3ull - code) << s2);
                         ok[j] = (p0 + i < npos) && (((vm >> i) & validk) == validk);
-                        if (MODE == kModeAnchor && ((ver >> i) & 1u)) ok[j] = false;      // answered by the anchor index
                         uint64_t cn = x < rc ? x : rc;
                         uint64_t h = mix2k(cn, k, kmsk);
                         if (kProbe) {
@@ -454,23 +345,11 @@ int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s)
     uint32_t cap = 148u * 128u;
     if (ctas > cap) ctas = cap;
     const RouteArgs none{};
-    const AnchorView noav{};
-    if (a.stats) k_query<kModeQuery, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none, noav);
-    else         k_query<kModeQuery, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none, noav);
+    if (a.stats) k_query<kModeQuery, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none);
+    else         k_query<kModeQuery, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none);
     return (int)cudaGetLastError();
 }
 
-int launch_query_anchor(const TableView& t, const QueryArgs& a, const AnchorView& av, cudaStream_t s)
-{
-    if (a.n_reads == 0) return 0;
-    uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
-    uint32_t cap = 148u * 128u;
-    if (ctas > cap) ctas = cap;
-    const RouteArgs none{};
-    if (a.stats) k_query<kModeAnchor, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none, av);
-    else         k_query<kModeAnchor, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none, av);
-    return (int)cudaGetLastError();
-}
 
 int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s)
 {
@@ -479,9 +358,8 @@ int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bo
     uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
     uint32_t cap = 148u * 128u;
     if (ctas > cap) ctas = cap;
-    const AnchorView noav{};
-    if (write) k_query<kModeRoute, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra, noav);
-    else       k_query<kModeCount, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra, noav);
+    if (write) k_query<kModeRoute, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra);
+    else       k_query<kModeCount, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra);
     return (int)cudaGetLastError();
 }
 

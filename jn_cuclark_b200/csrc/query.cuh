@@ -70,26 +70,39 @@ int launch_vote_lists(const QueryArgs& a, const VoteArgs& va, cudaStream_t s);
 int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
                             uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s);
 
-// Anchor index (DESIGN.md "Anchor and verify"): the target sequences themselves, both strands, 2 bits per
-// base, plus per-position bits, plus a small table of sampled k-mers -> text position.  A read whose
-// sampled k-mer is found there is compared base by base with the text; every window that matches needs no
-// table probe -- its answer is the per-position bit "this text k-mer is in the table" and the label of the
-// record.  Windows that do not match are probed as usual, so the result is exact whatever the anchors say.
+// Anchor index (DESIGN.md "Anchor and verify"): the target sequences themselves, both strands, plus a small
+// table of sampled k-mers -> text position.  A read whose sampled k-mer is found there is compared base by
+// base with the text; a window that matches needs no table probe -- the text knows whether the k-mer starting
+// there is stored in the table under the record's own label ("same"), under another label ("other": probed
+// as usual) or not at all.  Windows that do not match are probed as usual, so the result is exact whatever
+// the sampled table holds.
+constexpr int kTextWords = 5;   // per 32 text positions
 struct AnchorView {
-    const uint32_t*   seq;      // text T = F . revcomp(F): 16 bases per word, first base in the top bits
-    const uint32_t*   valid;    // bit p: base p of T is a base (0: separator / N / padding)
-    const uint32_t*   disc;     // bit p: the k-mer starting at p is stored in the k-mer table
+    // text T = F . revcomp(F), group g = positions [32g, 32g+32), 5 words:
+    //   [0] bases 0..15, [1] bases 16..31   (2 bits per base, first base in the top bits)
+    //   [2] valid  bit i: position 32g+i is a base (0: separator / N / padding)
+    //   [3] same   bit i: the k-mer starting there is in the k-mer table under the label of its record
+    //   [4] other  bit i: ... is in the k-mer table under a different label
+    const uint32_t*   txt;
     uint64_t          nF;       // bases in F (multiple of 32); T has 2 * nF
-    const ulonglong4* buckets;  // sampled k-mers: 4 x [fp15 | fwd1 | label16 | pos32], no overflow chains
-    uint64_t          nb;
+    // sampled k-mers of F: 32-byte sectors of 4 x [fp15 | fwd1 | label16 | pos32]; sector b overflows into b ^ 1
+    // (same 128-byte line), a k-mer that finds both full is not indexed
+    const ulonglong4* buckets;
+    uint64_t          nb;       // sectors (even)
 };
-// same as launch_query, but reads are first tried against the anchor index
-int launch_query_anchor(const TableView& t, const QueryArgs& a, const AnchorView& av, cudaStream_t s);
+#if defined(__CUDACC__)
+// which canonical k-mers are sampled (1 in 8): cheap enough to evaluate for every window of a read
+__device__ __forceinline__ bool anchor_sampled(uint64_t c)
+{
+    return ((((uint32_t)c ^ (uint32_t)(c >> 32)) * 0x9E3779B1u) >> 29) == 0u;
+}
+#endif
 
-// Thread-per-read kernel for short single-part reads (<= 192 bases, <= 4 distinct targets hit): every lane
-// walks its own read, so nothing is coordinated across lanes.  Reads it does not take (several parts, long,
-// many targets) are appended to redo_list / *redo_count and must be classified by launch_query with
-// read_list = redo_list afterwards.  av may be null (no anchor index).
+// Thread-per-read kernel for short single-part reads (<= 192 bases, <= 4 distinct targets hit): phase A, every
+// thread takes one read: looks for an anchor, compares the read with the text; phase B, the windows still to
+// probe are dealt out over the block four at a time; phase C, one result per thread.  Reads it does not take
+// (several parts, long, many targets) are appended to redo_list / *redo_count and must be classified by
+// launch_query with read_list = redo_list afterwards.  av may be null (no anchor index).
 int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* av, uint32_t* redo_list,
                       uint32_t* redo_count, cudaStream_t s);
 

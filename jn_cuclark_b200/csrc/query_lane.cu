@@ -1,21 +1,29 @@
-// query_lane.cu -- thread-per-read classification of short reads.
+// query_lane.cu -- thread-per-read classification of short reads, block-cooperative.
 //
 // k_query (query.cu) gives a whole warp to one read; most of its instructions coordinate the 32 lanes
 // (tile staging, validity masks, shuffle-merged votes).  For the reads that dominate a metagenomic
-// sample -- one part, <= 192 bases, a handful of targets hit -- none of that is needed: here every lane
-// walks its own read with rolling forward / reverse-complement words, keeps 4 probes in flight, and votes
-// into four (label,count) register pairs.  A warp holds 32 reads, so there are 32x more independent
-// requests to hide the DRAM latency behind, and with the anchor index (query.cuh AnchorView) the windows
-// that match the target sequence base for base are answered without touching the table at all.
+// sample -- one part, <= 192 bases, a handful of targets hit -- none of that is needed.  k_query_block
+// gives every thread of a block one read and runs three phases per block of reads:
+//   A  per read: (with the anchor index, query.cuh AnchorView) roll over the read until two sampled k-mers
+//      are met, look both up in the sampled table at once, compare the read with the target text base by
+//      base; every window that matches is answered from the text's own bits.  The windows that remain are
+//      cut into work items of at most four windows of one 16-window chunk and queued in shared memory.
+//   B  the items are dealt out over the block: six containers give the 46 bases a chunk's windows can
+//      touch, each window's k-mer is cut out of them directly (no rolling state, no divergence between
+//      lanes), four probes are in flight per thread, votes go to the read's four (label,count) pairs in
+//      shared memory.
+//   C  per read: best / second best / sum, sparse row.
 // Anything else -- several parts, longer reads, a fifth distinct target -- is handed back on a list and
 // classified by k_query.  Results are the same u16[5] / sparse rows either way.
 #include "query.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 namespace ccb {
 
 constexpr int kLaneMaxBases = 192;
 constexpr int kLaneAcc = 4;
+constexpr int kItemsPerRead = 48;          // <= 191 windows -> 12 chunks of 16 -> <= 4 items each
 
 namespace {
 
@@ -32,6 +40,15 @@ __device__ __forceinline__ uint32_t mismatch16(uint32_t diff)
     return v;
 }
 
+// kmer.cuh revcomp() with the five swap stages replaced by two bit reversals and one swap inside the pairs
+__device__ __forceinline__ uint64_t revcomp_brev(uint64_t x, int k)
+{
+    uint32_t lo = __brev((uint32_t)(x >> 32)), hi = __brev((uint32_t)x);
+    lo = ((lo >> 1) & 0x55555555u) | ((lo & 0x55555555u) << 1);
+    hi = ((hi >> 1) & 0x55555555u) | ((hi & 0x55555555u) << 1);
+    return (~(((uint64_t)hi << 32) | lo)) >> (64 - 2 * k);
+}
+
 struct Bits192 {                       // bit i <-> position i, LSB first
     uint64_t w[3];
     __device__ __forceinline__ Bits192 shr(int s) const          // 0 < s < 64
@@ -43,249 +60,21 @@ struct Bits192 {                       // bit i <-> position i, LSB first
         return r;
     }
     __device__ __forceinline__ void and_with(const Bits192& o) { w[0] &= o.w[0]; w[1] &= o.w[1]; w[2] &= o.w[2]; }
-    __device__ __forceinline__ bool get(int i) const
-    {
-        const uint64_t v = i < 64 ? w[0] : (i < 128 ? w[1] : w[2]);
-        return (v >> (i & 63)) & 1ull;
-    }
 };
 
-struct LaneVotes {
-    uint32_t lab[kLaneAcc], cnt[kLaneAcc];
-    int n; bool overflow;
-    __device__ __forceinline__ void init() { n = 0; overflow = false;
-#pragma unroll
-        for (int i = 0; i < kLaneAcc; i++) { lab[i] = kLabelNone; cnt[i] = 0; } }
-    __device__ __forceinline__ void add(uint32_t L, uint32_t c)
-    {
-        bool done = false;
-#pragma unroll
-        for (int i = 0; i < kLaneAcc; i++) if (!done && i < n && lab[i] == L) { cnt[i] += c; done = true; }
-        if (!done) {
-            if (n < kLaneAcc) {
-#pragma unroll
-                for (int i = 0; i < kLaneAcc; i++) if (i == n) { lab[i] = L; cnt[i] = c; }
-                n++;
-            } else overflow = true;
-        }
-    }
-};
-
-}  // namespace
-
-template <bool ANCHOR, bool STATS>
-__global__ void __launch_bounds__(256) k_query_lane(const TableView t, const QueryArgs a, const AnchorView av,
-                                                    uint32_t* redo_list, uint32_t* redo_count)
-{
-    const int k = t.hp.k;
-    const uint64_t kmsk = t.hp.mask;
-    const int s2 = 2 * (k - 1);
-    unsigned long long st_lookups = 0, st_sectors = 0;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < a.n_reads; r += stride) {
-        const uint32_t beg = __ldg(a.offsets + r);
-        const int nslots = (int)(__ldg(a.offsets + r + 1) - beg);
-        const uint16_t* c = a.containers + beg;
-        const int len = nslots > 0 ? (int)__ldg(c) : 0;
-        if (nslots == 0) {                                     // no k-mer at all (read shorter than k, or all N)
-            uint16_t* o5 = a.out5 + (size_t)r * 5;
-            o5[0] = o5[1] = o5[2] = o5[3] = o5[4] = 0;
-            if (a.rows) a.rows[(size_t)r * a.row_stride] = 0;
-            continue;
-        }
-        if (1 + ((len + 7) >> 3) != nslots || len > kLaneMaxBases || len < k) {       // not for this kernel
-            redo_list[atomicAdd(redo_count, 1u)] = r;
-            continue;
-        }
-        const int npos = len - k + 1;
-        LaneVotes votes; votes.init();
-        Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;              // windows answered by the anchor index
-
-        if (ANCHOR) {
-            // ---- the first two sampled k-mers of the read are tried as anchors ----
-            uint64_t x = 0, rc = 0;
-            uint32_t cw = 0;
-            int tries = 0;
-            uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
-            for (int i = 0; i < len && tries < 2 && ae == ~0ull; i++) {
-                if ((i & 7) == 0) cw = __ldg(c + 1 + (i >> 3));
-                const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
-                x = ((x << 2) | code) & kmsk;
-                rc = (rc >> 2) | ((3ull - code) << s2);
-                if (i < k - 1) continue;
-                const uint64_t h = mix2k(x < rc ? x : rc, k, kmsk);
-                if ((h >> (2 * k - 3)) != 0) continue;
-                tries++;
-                const uint64_t bi = mulhi64(((h << 3) & kmsk) << t.hp.shift, av.nb);
-                const uint32_t fp = (uint32_t)(h >> 3) & 0x7FFFu;
-                uint64_t e[4];
-                load_bucket(av.buckets + bi, e);
-                if (STATS) st_sectors++;
-#pragma unroll
-                for (int sl = 3; sl >= 0; sl--) if ((uint32_t)(e[sl] >> 49) == fp && e[sl] != ~0ull) ae = e[sl];
-                apos = i - (k - 1); afwd = x <= rc ? 1u : 0u;
-            }
-            if (ae != ~0ull) {
-                const uint32_t alab = (uint32_t)(ae >> 32) & 0xFFFFu;
-                const uint64_t tpos = ae & 0xFFFFFFFFull;
-                const bool same = afwd == ((uint32_t)(ae >> 48) & 1u);
-                const int64_t g0 = same ? (int64_t)tpos - apos : (int64_t)(2 * av.nF - tpos - (uint64_t)k) - apos;
-                if (g0 >= 0 && (uint64_t)g0 + kLaneMaxBases + 64 <= 2 * av.nF) {
-                    // ---- read vs text, 16 bases at a time; validity and "stored" bits of the span ----
-                    const uint64_t w0 = (uint64_t)g0 >> 4; const int sh = 2 * (int)(g0 & 15);
-                    const uint64_t v0 = (uint64_t)g0 >> 5; const int vs = (int)(g0 & 31);
-                    uint32_t tprev = __ldg(av.seq + w0);
-                    uint32_t vprev = __ldg(av.valid + v0), dprev = __ldg(av.disc + v0);
-                    Bits192 good, D;
-                    bool span_ok = true;
-#pragma unroll
-                    for (int u = 0; u < 6; u++) {                  // 32 positions per step
-                        uint32_t mis = 0;
-#pragma unroll
-                        for (int hlf = 0; hlf < 2; hlf++) {
-                            const int w = 2 * u + hlf;             // 16-base unit
-                            const uint32_t tnext = __ldg(av.seq + w0 + w + 1);
-                            const uint32_t tw = __funnelshift_l(tnext, tprev, sh);
-                            tprev = tnext;
-                            const int s0 = 1 + 2 * w;
-                            const uint32_t r0 = s0 < nslots ? (uint32_t)__ldg(c + s0) : 0u, r1 = s0 + 1 < nslots ? (uint32_t)__ldg(c + s0 + 1) : 0u;
-                            mis |= mismatch16(tw ^ ((r0 << 16) | r1)) << (16 * hlf);
-                        }
-                        const uint32_t vnext = __ldg(av.valid + v0 + u + 1), dnext = __ldg(av.disc + v0 + u + 1);
-                        const uint32_t gv = __funnelshift_r(vprev, vnext, vs), gd = __funnelshift_r(dprev, dnext, vs);
-                        vprev = vnext; dprev = dnext;
-                        const int here = len - 32 * u;             // read bases in this word
-                        const uint32_t need = here >= 32 ? 0xFFFFFFFFu : (here > 0 ? (1u << here) - 1u : 0u);
-                        if ((gv & need) != need) span_ok = false;  // a separator / N in the span: other records may follow
-                        const uint32_t g32 = ~mis & gv & need;
-                        if (u & 1) { good.w[u >> 1] |= (uint64_t)g32 << 32; D.w[u >> 1] |= (uint64_t)gd << 32; }
-                        else       { good.w[u >> 1] = g32; D.w[u >> 1] = gd; }
-                    }
-                    if (STATS) st_sectors += 3;
-                    if (span_ok) {
-                        // windows of k good bases: runs of ones by doubling
-                        Bits192 run = good; int have = 1;
-                        while (2 * have <= k) { run.and_with(run.shr(have)); have *= 2; }
-                        if (have < k) run.and_with(run.shr(k - have));
-                        // only window starts < npos count (bits beyond are already 0: good is masked to len)
-                        W = run;
-                        const uint32_t hits = __popcll(W.w[0] & D.w[0]) + __popcll(W.w[1] & D.w[1]) + __popcll(W.w[2] & D.w[2]);
-                        if (hits) votes.add(alab, hits);
-                        if (STATS) st_lookups += __popcll(W.w[0]) + __popcll(W.w[1]) + __popcll(W.w[2]);
-                    }
-                }
-            }
-        }
-
-        // ---- walk the read: every window not answered above is probed, 4 in flight ----
-        {
-            uint64_t x = 0, rc = 0;
-            uint32_t cw = 0;
-            for (int i = 0; i < k - 1; i++) {
-                if ((i & 7) == 0) cw = __ldg(c + 1 + (i >> 3));
-                const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
-                x = (x << 2) | code;
-            }
-            x &= kmsk;
-            rc = revcomp(x, k);                                  // of the k-1 bases, as k_query does
-            for (int p0 = 0; p0 < npos && !votes.overflow; p0 += 4) {
-                uint64_t e[4][4], home[4], q[4]; bool need[4];
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const int p = p0 + j, i = p + k - 1;           // window start, its last base
-                    need[j] = false;
-                    if (p < npos) {
-                        if ((i & 7) == 0) cw = __ldg(c + 1 + (i >> 3));
-                        const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
-                        x = ((x << 2) | code) & kmsk;
-                        rc = (rc >> 2) | ((3ull - code) << s2);
-                        need[j] = !(ANCHOR && W.get(p));
-                        if (need[j]) {
-                            const uint64_t h = mix2k(x < rc ? x : rc, k, kmsk);
-                            home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
-                            load_bucket(t.buckets + home[j], e[j]);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    if (need[j]) {
-                        uint32_t probes = 1;
-                        const uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &probes : nullptr);
-                        if (STATS) { st_lookups++; st_sectors += probes; }
-                        if (l < kLabelTomb) votes.add(l, 1u);
-                    }
-                }
-            }
-        }
-        if (votes.overflow) {                                   // a fifth target: the warp-per-read kernel redoes it
-            redo_list[atomicAdd(redo_count, 1u)] = r;
-            continue;
-        }
-        // ---- result {sumN, idxBest, best, idxSecond, second}: top-2 under (count desc, target asc) ----
-        uint32_t sum = 0, k1 = 0, k2 = 0;
-#pragma unroll
-        for (int i = 0; i < kLaneAcc; i++) {
-            const uint32_t c16 = i < votes.n ? (votes.cnt[i] & 0xFFFFu) : 0u;     // reference counters are u16
-            if (!c16) continue;
-            sum += c16;
-            const uint32_t key = (c16 << 16) | (0xFFFFu - votes.lab[i]);
-            if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
-        }
-        uint16_t* o5 = a.out5 + (size_t)r * 5;
-        o5[0] = (uint16_t)sum;
-        o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
-        o5[2] = (uint16_t)(k1 >> 16);
-        o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
-        o5[4] = (uint16_t)(k2 >> 16);
-        if (a.rows) {                                           // sparse row {n,(target,count)*}, targets ascending
-            uint16_t* row = a.rows + (size_t)r * a.row_stride;
-            const int fit = (a.row_stride - 1) / 2;
-            row[0] = (uint16_t)min(votes.n, fit);
-#pragma unroll
-            for (int i = 0; i < kLaneAcc; i++) {
-                if (i < votes.n) {
-                    int rank = 0;
-#pragma unroll
-                    for (int j = 0; j < kLaneAcc; j++) if (j < votes.n && votes.lab[j] < votes.lab[i]) rank++;
-                    if (2 * rank + 2 < a.row_stride) { row[1 + 2 * rank] = (uint16_t)votes.lab[i]; row[2 + 2 * rank] = (uint16_t)votes.cnt[i]; }
-                }
-            }
-        }
-    }
-    if (STATS) {
-#pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            st_lookups += __shfl_xor_sync(0xFFFFFFFFu, st_lookups, o);
-            st_sectors += __shfl_xor_sync(0xFFFFFFFFu, st_sectors, o);
-        }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(a.stats + 0, st_lookups); atomicAdd(a.stats + 1, st_sectors); }
-    }
-}
-
-// ---------------------------------------------------------------------------
-// Block-cooperative variant: the same per-read work split into three uniform phases per block of 256
-// reads, so that lanes never wait for a neighbour whose read needs more probes.
-//   A  thread = read   : shape check, anchor lookup, read-vs-text comparison, bulk vote; the windows still
-//                        to be probed are cut into 16-aligned chunks and queued in shared memory
-//   B  thread = chunk  : k-mer of the chunk's first window extracted from the containers, then rolling;
-//                        4 probes in flight; votes into per-read accumulators in shared memory
-//   C  thread = read   : result from the accumulators (or back to k_query when a fifth target showed up)
-// ---------------------------------------------------------------------------
-constexpr int kBlkReads = 256;
-constexpr int kBlkQueue = kBlkReads * 12;        // <= 162 windows per read -> <= 11 chunks of 16
-
+template <int BLK>
 struct BlockSmem {
-    uint32_t beg[kBlkReads];
-    uint32_t acc_lab[kBlkReads][kLaneAcc];
-    uint32_t acc_cnt[kBlkReads][kLaneAcc];
-    uint8_t  state[kBlkReads];                   // 0 nothing to do, 1 handled here, 2 overflow
-    uint16_t len[kBlkReads];
-    uint32_t queue[kBlkQueue];                   // read << 20 | chunk << 16 | need mask
+    uint32_t beg[BLK];                           // first container of the read
+    uint32_t acc_lab[BLK][kLaneAcc];
+    uint32_t acc_cnt[BLK][kLaneAcc];
+    uint16_t len[BLK];
+    uint8_t  state[BLK];                         // 0 nothing to do, 1 handled here, 2 overflow
     uint32_t qn;
+    uint32_t queue[BLK * kItemsPerRead];         // read << 20 | chunk << 16 | mask of <= 4 windows of the chunk
 };
 
-__device__ __forceinline__ void vote_smem(BlockSmem& sm, uint32_t lr, uint32_t label, uint32_t count)
+template <int BLK>
+__device__ __forceinline__ void vote_smem(BlockSmem<BLK>& sm, uint32_t lr, uint32_t label, uint32_t count)
 {
 #pragma unroll
     for (int s = 0; s < kLaneAcc; s++) {
@@ -295,19 +84,31 @@ __device__ __forceinline__ void vote_smem(BlockSmem& sm, uint32_t lr, uint32_t l
     sm.state[lr] = 2;
 }
 
-template <bool ANCHOR, bool STATS>
-__global__ void __launch_bounds__(kBlkReads, 2) k_query_block(const TableView t, const QueryArgs a, const AnchorView av,
-                                                               uint32_t* redo_list, uint32_t* redo_count)
+// entry of sector e whose fingerprint is fp (~0 when there is none)
+__device__ __forceinline__ uint64_t match_anchor(const uint64_t (&e)[4], uint32_t fp)
 {
-    __shared__ BlockSmem sm;
+    uint64_t ae = ~0ull;
+#pragma unroll
+    for (int sl = 3; sl >= 0; sl--) if ((uint32_t)(e[sl] >> 49) == fp && e[sl] != ~0ull) ae = e[sl];
+    return ae;
+}
+
+}  // namespace
+
+template <int BLK, int MINB, bool ANCHOR, bool STATS>
+__global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, const QueryArgs a, const AnchorView av,
+                                                          uint32_t* redo_list, uint32_t* redo_count)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BlockSmem<BLK>& sm = *reinterpret_cast<BlockSmem<BLK>*>(smem_raw);
     const int k = t.hp.k;
     const uint64_t kmsk = t.hp.mask;
     const int s2 = 2 * (k - 1);
     const int tid = threadIdx.x;
     unsigned long long st_lookups = 0, st_sectors = 0;
-    const uint32_t nblocks = (a.n_reads + kBlkReads - 1) / kBlkReads;
+    const uint32_t nblocks = (a.n_reads + BLK - 1) / BLK;
     for (uint32_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        const uint32_t r = blk * kBlkReads + tid;
+        const uint32_t r = blk * BLK + tid;
         // ---------------- phase A ----------------
         if (tid == 0) sm.qn = 0;
 #pragma unroll
@@ -328,70 +129,112 @@ __global__ void __launch_bounds__(kBlkReads, 2) k_query_block(const TableView t,
             } else {
                 sm.state[tid] = 1; sm.beg[tid] = beg; sm.len[tid] = (uint16_t)len;
                 const int npos = len - k + 1;
-                Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;
+                Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;            // windows answered without a table probe
                 if (ANCHOR) {
-                    uint64_t x = 0, rc = 0;
-                    uint32_t cw = 0;
-                    int tries = 0;
-                    uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
-                    for (int i = 0; i < len && tries < 2 && ae == ~0ull; i++) {
-                        if ((i & 7) == 0) cw = __ldg(c + 1 + (i >> 3));
-                        const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
-                        x = ((x << 2) | code) & kmsk;
-                        rc = (rc >> 2) | ((3ull - code) << s2);
-                        if (i < k - 1) continue;
-                        const uint64_t h = mix2k(x < rc ? x : rc, k, kmsk);
-                        if ((h >> (2 * k - 3)) != 0) continue;
-                        tries++;
-                        const uint64_t bi = mulhi64(((h << 3) & kmsk) << t.hp.shift, av.nb);
-                        const uint32_t fp = (uint32_t)(h >> 3) & 0x7FFFu;
-                        uint64_t e[4];
-                        load_bucket(av.buckets + bi, e);
-                        if (STATS) st_sectors++;
+                    // rolling state after the first k-1 bases, cut out of the first four containers
+                    uint64_t x, rc;
+                    {
+                        uint64_t v = 0;
 #pragma unroll
-                        for (int sl = 3; sl >= 0; sl--) if ((uint32_t)(e[sl] >> 49) == fp && e[sl] != ~0ull) ae = e[sl];
-                        apos = i - (k - 1); afwd = x <= rc ? 1u : 0u;
+                        for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)__ldg(c + 1 + j) : 0ull);
+                        x = k > 1 ? v >> (64 - s2) : 0ull;
+                        rc = revcomp_brev(x, k);
+                    }
+                    uint32_t cw = 0;
+                    int i = k - 1;
+                    if (i & 7) cw = __ldg(c + 1 + (i >> 3));
+                    uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
+                    // up to two rounds; a round = the next two sampled k-mers of the read, looked up together
+                    for (int round = 0; round < 2 && ae == ~0ull && i < len; round++) {
+                        uint64_t c0 = 0, c1 = 0; int p0 = 0, p1 = 0; uint32_t f0 = 0, f1 = 0; int nc = 0;
+                        for (; i < len && nc < 2; i++) {
+                            if ((i & 7) == 0) cw = __ldg(c + 1 + (i >> 3));
+                            const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
+                            x = ((x << 2) | code) & kmsk;
+                            rc = (rc >> 2) | ((3ull - code) << s2);
+                            const uint64_t cn = x < rc ? x : rc;
+                            if (anchor_sampled(cn)) {
+                                if (nc == 0) { c0 = cn; p0 = i - (k - 1); f0 = x <= rc ? 1u : 0u; }
+                                else         { c1 = cn; p1 = i - (k - 1); f1 = x <= rc ? 1u : 0u; }
+                                nc++;
+                            }
+                        }
+                        if (nc == 0) break;
+                        const uint64_t h0 = mix2k(c0, k, kmsk), h1 = mix2k(c1, k, kmsk);
+                        const uint64_t b0 = mulhi64(h0 << t.hp.shift, av.nb), b1 = mulhi64(h1 << t.hp.shift, av.nb);
+                        const uint32_t fp0 = (uint32_t)h0 & 0x7FFFu, fp1 = (uint32_t)h1 & 0x7FFFu;
+                        uint64_t e0[4], e1[4];
+                        load_bucket(av.buckets + b0, e0);
+                        if (nc > 1) load_bucket(av.buckets + b1, e1);
+                        if (STATS) st_sectors += nc;
+                        uint64_t m = match_anchor(e0, fp0);
+                        if (m == ~0ull && e0[3] != ~0ull) {                       // full sector: its neighbour may hold it
+                            load_bucket(av.buckets + (b0 ^ 1ull), e0);
+                            if (STATS) st_sectors++;
+                            m = match_anchor(e0, fp0);
+                        }
+                        if (m != ~0ull) { ae = m; apos = p0; afwd = f0; }
+                        else if (nc > 1) {
+                            m = match_anchor(e1, fp1);
+                            if (m == ~0ull && e1[3] != ~0ull) {
+                                load_bucket(av.buckets + (b1 ^ 1ull), e1);
+                                if (STATS) st_sectors++;
+                                m = match_anchor(e1, fp1);
+                            }
+                            if (m != ~0ull) { ae = m; apos = p1; afwd = f1; }
+                        }
                     }
                     if (ae != ~0ull) {
                         const uint32_t alab = (uint32_t)(ae >> 32) & 0xFFFFu;
                         const uint64_t tpos = ae & 0xFFFFFFFFull;
                         const bool same = afwd == ((uint32_t)(ae >> 48) & 1u);
+                        // text position of read base 0 (F half, or the reverse-complement half)
                         const int64_t g0 = same ? (int64_t)tpos - apos : (int64_t)(2 * av.nF - tpos - (uint64_t)k) - apos;
                         if (g0 >= 0 && (uint64_t)g0 + kLaneMaxBases + 64 <= 2 * av.nF) {
-                            const uint64_t w0 = (uint64_t)g0 >> 4; const int sh = 2 * (int)(g0 & 15);
-                            const uint64_t v0 = (uint64_t)g0 >> 5; const int vs = (int)(g0 & 31);
-                            uint32_t tprev = __ldg(av.seq + w0);
-                            uint32_t vprev = __ldg(av.valid + v0), dprev = __ldg(av.disc + v0);
-                            Bits192 good, D;
+                            const int sft = (int)(g0 & 31);
+                            const int ngr = (sft + len + 31) >> 5;                                    // text groups the read spans (<= 7)
+                            const uint32_t* tg = av.txt + (size_t)kTextWords * ((uint64_t)g0 >> 5);
+                            uint32_t pw0, pw1, pv, pd, po;                                            // group u
+                            pw0 = __ldg(tg); pw1 = __ldg(tg + 1); pv = __ldg(tg + 2); pd = __ldg(tg + 3); po = __ldg(tg + 4);
+                            Bits192 good, D, O;
+                            good.w[0] = good.w[1] = good.w[2] = 0; D = good; O = good;
                             bool span_ok = true;
 #pragma unroll
                             for (int u = 0; u < 6; u++) {
-                                uint32_t mis = 0;
-#pragma unroll
-                                for (int hlf = 0; hlf < 2; hlf++) {
-                                    const int w = 2 * u + hlf;
-                                    const uint32_t tnext = __ldg(av.seq + w0 + w + 1);
-                                    const uint32_t tw = __funnelshift_l(tnext, tprev, sh);
-                                    tprev = tnext;
-                                    const int s0 = 1 + 2 * w;
-                                    const uint32_t r0 = s0 < nslots ? (uint32_t)__ldg(c + s0) : 0u, r1 = s0 + 1 < nslots ? (uint32_t)__ldg(c + s0 + 1) : 0u;
-                                    mis |= mismatch16(tw ^ ((r0 << 16) | r1)) << (16 * hlf);
+                                uint32_t nw0 = 0, nw1 = 0, nv = 0, nd = 0, no = 0;                    // group u + 1
+                                if (u + 1 < ngr) {
+                                    const uint32_t* g = tg + kTextWords * (u + 1);
+                                    nw0 = __ldg(g); nw1 = __ldg(g + 1); nv = __ldg(g + 2); nd = __ldg(g + 3); no = __ldg(g + 4);
                                 }
-                                const uint32_t vnext = __ldg(av.valid + v0 + u + 1), dnext = __ldg(av.disc + v0 + u + 1);
-                                const uint32_t gv = __funnelshift_r(vprev, vnext, vs), gd = __funnelshift_r(dprev, dnext, vs);
-                                vprev = vnext; dprev = dnext;
-                                const int here = len - 32 * u;
-                                const uint32_t need = here >= 32 ? 0xFFFFFFFFu : (here > 0 ? (1u << here) - 1u : 0u);
-                                if ((gv & need) != need) span_ok = false;
-                                const uint32_t g32 = ~mis & gv & need;
-                                if (u & 1) { good.w[u >> 1] |= (uint64_t)g32 << 32; D.w[u >> 1] |= (uint64_t)gd << 32; }
-                                else       { good.w[u >> 1] = g32; D.w[u >> 1] = gd; }
+                                const int here = len - 32 * u;                                        // read bases from 32u on
+                                if (here > 0) {
+                                    // text bases at read positions 32u .. 32u+31
+                                    const uint64_t tcur = ((uint64_t)pw0 << 32) | pw1, tnxt = ((uint64_t)nw0 << 32) | nw1;
+                                    const uint64_t tt = sft ? (tcur << (2 * sft)) | (tnxt >> (64 - 2 * sft)) : tcur;
+                                    uint64_t rd = 0;
+#pragma unroll
+                                    for (int j = 0; j < 4; j++) {
+                                        const int sl = 1 + 4 * u + j;
+                                        rd = (rd << 16) | (sl < nslots ? (uint64_t)__ldg(c + sl) : 0ull);
+                                    }
+                                    const uint64_t df = tt ^ rd;
+                                    const uint32_t mis = mismatch16((uint32_t)(df >> 32)) | (mismatch16((uint32_t)df) << 16);
+                                    const uint32_t gv = __funnelshift_r(pv, nv, sft), gd = __funnelshift_r(pd, nd, sft),
+                                                   go = __funnelshift_r(po, no, sft);
+                                    const uint32_t need = here >= 32 ? 0xFFFFFFFFu : (1u << here) - 1u;
+                                    if ((gv & need) != need) span_ok = false;     // a separator inside the span: another record may follow
+                                    const uint32_t g32 = ~mis & gv & need;
+                                    if (u & 1) { good.w[u >> 1] |= (uint64_t)g32 << 32; D.w[u >> 1] |= (uint64_t)gd << 32; O.w[u >> 1] |= (uint64_t)go << 32; }
+                                    else       { good.w[u >> 1] = g32; D.w[u >> 1] = gd; O.w[u >> 1] = go; }
+                                }
+                                pw0 = nw0; pw1 = nw1; pv = nv; pd = nd; po = no;
                             }
-                            if (STATS) st_sectors += 3;
+                            if (STATS) st_sectors += (uint32_t)(ngr * kTextWords * 4 + 31) / 32u;
                             if (span_ok) {
                                 Bits192 run = good; int have = 1;
                                 while (2 * have <= k) { run.and_with(run.shr(have)); have *= 2; }
                                 if (have < k) run.and_with(run.shr(k - have));
+                                run.w[0] &= ~O.w[0]; run.w[1] &= ~O.w[1]; run.w[2] &= ~O.w[2];       // stored under another label: probe
                                 W = run;
                                 const uint32_t hits = __popcll(W.w[0] & D.w[0]) + __popcll(W.w[1] & D.w[1]) + __popcll(W.w[2] & D.w[2]);
                                 if (hits) { sm.acc_lab[tid][0] = alab; sm.acc_cnt[tid][0] = hits; }
@@ -400,8 +243,8 @@ __global__ void __launch_bounds__(kBlkReads, 2) k_query_block(const TableView t,
                         }
                     }
                 }
-                // ---- the windows still to probe, as 16-aligned chunks ----
-                uint32_t items[12]; int ni = 0;
+                // ---- the windows still to probe: items of <= 4 windows of one 16-window chunk ----
+                uint32_t nitems = 0;
 #pragma unroll
                 for (int ch = 0; ch < 12; ch++) {
                     const int p = 16 * ch;
@@ -409,70 +252,74 @@ __global__ void __launch_bounds__(kBlkReads, 2) k_query_block(const TableView t,
                         const uint64_t wv = ch < 4 ? W.w[0] : (ch < 8 ? W.w[1] : W.w[2]);
                         const int left = npos - p;
                         const uint32_t in = left >= 16 ? 0xFFFFu : ((1u << left) - 1u);
-                        const uint32_t needm = ~(uint32_t)(wv >> (16 * (ch & 3))) & in;
-                        if (needm) items[ni++] = ((uint32_t)tid << 20) | ((uint32_t)ch << 16) | needm;
+                        nitems += (__popc(~(uint32_t)(wv >> (16 * (ch & 3))) & in) + 3) >> 2;
                     }
                 }
-                if (ni) {
-                    const uint32_t at = atomicAdd(&sm.qn, (uint32_t)ni);
+                if (nitems) {
+                    uint32_t at = atomicAdd(&sm.qn, nitems);
 #pragma unroll
-                    for (int j = 0; j < 12; j++) if (j < ni) sm.queue[at + j] = items[j];
+                    for (int ch = 0; ch < 12; ch++) {
+                        const int p = 16 * ch;
+                        if (p < npos) {
+                            const uint64_t wv = ch < 4 ? W.w[0] : (ch < 8 ? W.w[1] : W.w[2]);
+                            const int left = npos - p;
+                            const uint32_t in = left >= 16 ? 0xFFFFu : ((1u << left) - 1u);
+                            uint32_t needm = ~(uint32_t)(wv >> (16 * (ch & 3))) & in;
+                            while (needm) {
+                                uint32_t rest = needm & (needm - 1);
+                                rest &= rest - 1; rest &= rest - 1; rest &= rest - 1;                 // lowest four set bits removed
+                                sm.queue[at++] = ((uint32_t)tid << 20) | ((uint32_t)ch << 16) | (needm ^ rest);
+                                needm = rest;
+                            }
+                        }
+                    }
                 }
             }
         }
         __syncthreads();
         // ---------------- phase B ----------------
         const uint32_t qn = sm.qn;
-        for (uint32_t it = tid; it < qn; it += kBlkReads) {
+        for (uint32_t it = tid; it < qn; it += BLK) {
             const uint32_t item = sm.queue[it];
-            const uint32_t lr = item >> 20, ch = (item >> 16) & 15u, needm = item & 0xFFFFu;
+            const uint32_t lr = item >> 20, ch = (item >> 16) & 15u;
+            uint32_t m4 = item & 0xFFFFu;
             const uint16_t* c = a.containers + sm.beg[lr];
-            const int first = 16 * (int)ch + (__ffs(needm) - 1), last = 16 * (int)ch + (31 - __clz(needm));
-            // k-1 bases starting at `first`, taken from five containers
-            uint64_t x, rc;
+            // the 48 bases from the chunk's first window on
+            uint64_t bhi = 0, blo = 0;
             {
-                const int s0 = 1 + (first >> 3);
+                const int s0 = 1 + 2 * (int)ch;
                 const int nsl = 1 + ((sm.len[lr] + 7) >> 3);
-                uint64_t v = 0;
 #pragma unroll
-                for (int j = 0; j < 4; j++) v = (v << 16) | (s0 + j < nsl ? (uint64_t)__ldg(c + s0 + j) : 0ull);
-                const uint64_t c4 = s0 + 4 < nsl ? (uint64_t)__ldg(c + s0 + 4) : 0ull;
-                const int sh = 2 * (first & 7);
-                const uint64_t full = sh ? ((v << sh) | (c4 >> (16 - sh))) : v;       // 32 bases from `first`
-                x = k > 1 ? full >> (64 - s2) : 0ull;
-                rc = revcomp(x, k);
+                for (int j = 0; j < 4; j++) bhi = (bhi << 16) | (s0 + j < nsl ? (uint64_t)__ldg(c + s0 + j) : 0ull);
+#pragma unroll
+                for (int j = 4; j < 6; j++) blo = (blo << 16) | (s0 + j < nsl ? (uint64_t)__ldg(c + s0 + j) : 0ull);
+                blo <<= 32;
+            }
+            uint64_t e[4][4], home[4], q[4]; bool need[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                need[j] = m4 != 0;
+                if (need[j]) {
+                    const int o = __ffs(m4) - 1;
+                    m4 &= m4 - 1;
+                    const uint64_t w64 = o ? (bhi << (2 * o)) | (blo >> (64 - 2 * o)) : bhi;
+                    const uint64_t x = w64 >> (64 - 2 * k);
+                    const uint64_t rc = revcomp_brev(x, k);
+                    const uint64_t h = mix2k(x < rc ? x : rc, k, kmsk);
+                    home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
+                    load_bucket(t.buckets + home[j], e[j]);
+                }
             }
             uint32_t run_lab = kLabelNone, run_cnt = 0;
-            uint32_t cw = 0; bool have_cw = false;
-            for (int p0 = first; p0 <= last; p0 += 4) {
-                uint64_t e[4][4], home[4], q[4]; bool need[4];
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const int p = p0 + j, i = p + k - 1;
-                    need[j] = false;
-                    if (p <= last) {
-                        if (!have_cw || (i & 7) == 0) { cw = __ldg(c + 1 + (i >> 3)); have_cw = true; }
-                        const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
-                        x = ((x << 2) | code) & kmsk;
-                        rc = (rc >> 2) | ((3ull - code) << s2);
-                        need[j] = (needm >> (p - 16 * (int)ch)) & 1u;
-                        if (need[j]) {
-                            const uint64_t h = mix2k(x < rc ? x : rc, k, kmsk);
-                            home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
-                            load_bucket(t.buckets + home[j], e[j]);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    if (need[j]) {
-                        uint32_t probes = 1;
-                        const uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &probes : nullptr);
-                        if (STATS) { st_lookups++; st_sectors += probes; }
-                        if (l < kLabelTomb) {
-                            if (l == run_lab) run_cnt++;
-                            else { if (run_cnt) vote_smem(sm, lr, run_lab, run_cnt); run_lab = l; run_cnt = 1; }
-                        }
+            for (int j = 0; j < 4; j++) {
+                if (need[j]) {
+                    uint32_t probes = 1;
+                    const uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &probes : nullptr);
+                    if (STATS) { st_lookups++; st_sectors += probes; }
+                    if (l < kLabelTomb) {
+                        if (l == run_lab) run_cnt++;
+                        else { if (run_cnt) vote_smem(sm, lr, run_lab, run_cnt); run_lab = l; run_cnt = 1; }
                     }
                 }
             }
@@ -530,32 +377,41 @@ __global__ void __launch_bounds__(kBlkReads, 2) k_query_block(const TableView t,
     }
 }
 
+namespace {
+
+template <int BLK, int MINB>
+int launch_block(const TableView& t, const QueryArgs& a, const AnchorView* av, uint32_t* redo_list, uint32_t* redo_count,
+                 cudaStream_t s)
+{
+    const size_t smem = sizeof(BlockSmem<BLK>);
+    uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
+    const uint32_t cap = 148u * 64u * (256u / BLK);
+    if (ctas > cap) ctas = cap;
+    const AnchorView none{};
+#define CCB_LAUNCH_BLOCK(AN, ST, AV)                                                                                   \
+    do {   /* the attribute is per device: set it on every launch (microseconds) rather than remember who has it */   \
+        cudaError_t e = cudaFuncSetAttribute(k_query_block<BLK, MINB, AN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return (int)e;                                                                           \
+        k_query_block<BLK, MINB, AN, ST><<<ctas, BLK, smem, s>>>(t, a, AV, redo_list, redo_count);                      \
+    } while (0)
+    if (av) { if (a.stats) CCB_LAUNCH_BLOCK(true, true, *av); else CCB_LAUNCH_BLOCK(true, false, *av); }
+    else    { if (a.stats) CCB_LAUNCH_BLOCK(false, true, none); else CCB_LAUNCH_BLOCK(false, false, none); }
+#undef CCB_LAUNCH_BLOCK
+    return (int)cudaGetLastError();
+}
+
+}  // namespace
+
 int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* av, uint32_t* redo_list,
                       uint32_t* redo_count, cudaStream_t s)
 {
     if (a.n_reads == 0) return 0;
-    uint32_t ctas = (a.n_reads + 255) / 256;
-    if (ctas > 148u * 64u) ctas = 148u * 64u;
-    const AnchorView none{};
-    static const bool simple = getenv("CCB_LANE_SIMPLE") != nullptr;      // the one-phase kernel, kept for comparison
-    if (!simple) {
-        if (av) {
-            if (a.stats) k_query_block<true, true><<<ctas, kBlkReads, 0, s>>>(t, a, *av, redo_list, redo_count);
-            else         k_query_block<true, false><<<ctas, kBlkReads, 0, s>>>(t, a, *av, redo_list, redo_count);
-        } else {
-            if (a.stats) k_query_block<false, true><<<ctas, kBlkReads, 0, s>>>(t, a, none, redo_list, redo_count);
-            else         k_query_block<false, false><<<ctas, kBlkReads, 0, s>>>(t, a, none, redo_list, redo_count);
-        }
-        return (int)cudaGetLastError();
-    }
-    if (av) {
-        if (a.stats) k_query_lane<true, true><<<ctas, 256, 0, s>>>(t, a, *av, redo_list, redo_count);
-        else         k_query_lane<true, false><<<ctas, 256, 0, s>>>(t, a, *av, redo_list, redo_count);
-    } else {
-        if (a.stats) k_query_lane<false, true><<<ctas, 256, 0, s>>>(t, a, none, redo_list, redo_count);
-        else         k_query_lane<false, false><<<ctas, 256, 0, s>>>(t, a, none, redo_list, redo_count);
-    }
-    return (int)cudaGetLastError();
+    // block shape: 256 threads x 2 blocks per SM unless CCB_BLOCK_SHAPE says otherwise (measurements)
+    static const char* shape = getenv("CCB_BLOCK_SHAPE");
+    if (shape && !strcmp(shape, "128x4")) return launch_block<128, 4>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "256x3")) return launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "128x6")) return launch_block<128, 6>(t, a, av, redo_list, redo_count, s);
+    return launch_block<256, 2>(t, a, av, redo_list, redo_count, s);
 }
 
 }  // namespace ccb

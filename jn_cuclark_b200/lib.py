@@ -84,6 +84,9 @@ SYMBOLS = {
     "ccb_ipc_open": (C.c_int, [_H, C.c_char_p, C.POINTER(_VP)]),
     "ccb_ipc_close": (C.c_int, [_H, _VP]),
     "ccb_anchor_synth": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32]),
+    "ccb_anchor_begin": (C.c_int, [_H, C.c_uint64]),
+    "ccb_anchor_add_fasta": (C.c_int, [_H, C.c_char_p, C.c_uint64, C.c_uint16]),
+    "ccb_anchor_end": (C.c_int, [_H, C.POINTER(AnchorInfo)]),
     "ccb_anchor_drop": (C.c_int, [_H]),
     "ccb_anchor_get_info": (C.c_int, [_H, C.POINTER(AnchorInfo)]),
     "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
@@ -317,6 +320,16 @@ class CuClarkDB:
     def anchor_synth(self, db_seed: int, n_genomes: int, genome_len: int, n_labels: int) -> AnchorInfo:
         self._ck(self._lib.ccb_anchor_synth(self._h, db_seed, n_genomes, genome_len, n_labels))
         return self.anchor_info()
+
+    def anchor_from_fasta(self, texts) -> AnchorInfo:
+        """texts: iterable of (FASTA bytes, 0-based label) -- the target files the database was built from."""
+        texts = list(texts)
+        self._ck(self._lib.ccb_anchor_begin(self._h, sum(len(t) for t, _ in texts)))
+        for t, label in texts:
+            self._ck(self._lib.ccb_anchor_add_fasta(self._h, t, len(t), label))
+        info = AnchorInfo()
+        self._ck(self._lib.ccb_anchor_end(self._h, C.byref(info)))
+        return info
 
     def anchor_drop(self):
         self._ck(self._lib.ccb_anchor_drop(self._h))

@@ -73,7 +73,10 @@ def _oracle_csv(s, oracle, data, path, paired=False, extended=False):
 CASES = [("fa", ["-O", "reads.fa"], {}), ("ml", ["-O", "reads_ml.fa"], {}), ("fq", ["-O", "reads.fq"], {}),
          ("fa_ext", ["-O", "reads.fa", "--extended"], {"extended": True}),
          ("fa_b4n4", ["-O", "reads.fa", "-n", "4", "-b", "4"], {}),
-         ("fq_m", ["-O", "reads.fq", "-m", "0", "--verbose"], {})]
+         ("fq_m", ["-O", "reads.fq", "-m", "0", "--verbose"], {}),
+         # CCB_ANCHOR=1: the target texts on the device in front of the table -- same bytes out
+         ("fa_anchor", ["-O", "reads.fa", "--verbose"], {"env": {"CCB_ANCHOR": "1"}}),
+         ("fa_ext_anchor", ["-O", "reads.fa", "--extended", "-n", "3"], {"extended": True, "env": {"CCB_ANCHOR": "1"}})]
 
 
 @pytest.mark.parametrize("name,args,kw", CASES, ids=[c[0] for c in CASES])
@@ -82,14 +85,16 @@ def test_single_end(setup, oracle, tmp_path, name, args, kw):
     args = [os.path.join(WORLD, a) if a.startswith("reads") else a for a in args]
     res = str(tmp_path / "out")
     dump = str(tmp_path / "final5.bin")
-    r = _run(s, args, res, {"CCB_DUMP_FINAL5": dump})
+    r = _run(s, args, res, dict({"CCB_DUMP_FINAL5": dump}, **kw.get("env", {})))
+    if kw.get("env", {}).get("CCB_ANCHOR") and "--verbose" in args:
+        assert "Anchor index: " in r.stderr
     assert "Classifying: " in r.stderr and "reads/min" in r.stderr and "Results: " + res + ".csv" in r.stderr
     data = open(args[1], "rb").read()
     want5 = _oracle_csv(s, oracle, data, str(tmp_path / "want.csv"), extended=kw.get("extended", False))
     assert open(res + ".csv", "rb").read() == open(str(tmp_path / "want.csv"), "rb").read()
     got5 = np.fromfile(dump, np.uint16).reshape(-1, 5)
     assert np.array_equal(got5, want5)                   # includes second best, which the CSV does not print
-    ref = os.path.join(REFCSV, f"{s['mode']}_{'fa_b4' if name == 'fa_b4n4' else name}.csv")
+    ref = os.path.join(REFCSV, f"{s['mode']}_{'fa_b4' if name == 'fa_b4n4' else name.replace('_anchor', '')}.csv")
     if os.path.exists(ref):
         assert open(res + ".csv", "rb").read() == open(ref, "rb").read(), "differs from the reference host engine's CSV"
 
@@ -153,8 +158,9 @@ W32 = {"fa": ["-O", "reads.fa"], "fq": ["-O", "reads.fq"], "ml": ["-O", "reads_m
        "pe": ["-P", "p1.fq", "p2.fq"], "pe_ext": ["-P", "p1.fq", "p2.fq", "--extended"]}
 
 
+@pytest.mark.parametrize("anchor", [False, True], ids=["table", "anchor"])
 @pytest.mark.parametrize("mode", ["light", "full", "fullk21"])
-def test_cli_equals_reference_gpu_binary(tmp_path, mode):
+def test_cli_equals_reference_gpu_binary(tmp_path, mode, anchor):
     """Same targets, same reads: bin/cuCLARK[-l] (database built by ccb_build_*) writes the CSV that the unmodified
     reference binary wrote with its own kernels on a B200 (make_golden.py gpu32)."""
     labels = open(os.path.join(WORLD32, "labels.txt")).read().split()
@@ -171,6 +177,7 @@ def test_cli_equals_reference_gpu_binary(tmp_path, mode):
         case = os.path.basename(g)[len(f"w32_{mode}_"):-4]
         args = [a if a.startswith("-") else os.path.join(WORLD32, a) for a in W32[case]]
         res = str(tmp_path / case)
-        r = subprocess.run([exe, "-T", tp, "-D", str(tmp_path / "db") + "/", "-R", res, "-n", "3"] + kflag + args, capture_output=True, text=True, timeout=600)
+        env = dict(os.environ, CCB_ANCHOR="1") if anchor else None
+        r = subprocess.run([exe, "-T", tp, "-D", str(tmp_path / "db") + "/", "-R", res, "-n", "3"] + kflag + args, capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stderr[-1500:]
         assert open(res + ".csv", "rb").read() == open(g, "rb").read(), case
