@@ -45,7 +45,8 @@ def parse():
     ap.add_argument("--sample-reads", type=int, default=200_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
-    ap.add_argument("--lane", action="store_true", help="thread-per-read kernel for short reads (CCB_LANE_KERNEL)")
+    ap.add_argument("--lane", action="store_true", help="(default now) thread-per-read block kernel for short reads")
+    ap.add_argument("--warp", action="store_true", help="warp-per-read kernel for every read (CCB_WARP_KERNEL)")
     ap.add_argument("--anchor", action="store_true",
                     help="build the anchor index (target sequences + sampled k-mer positions) in front of the table")
     ap.add_argument("--no-anchor-leg", action="store_true", help="skip the second leg (anchor index in front of the table)")
@@ -224,7 +225,7 @@ def run_b200(args):
     d_off, d_cont, n_cont = db.synth_reads_packed(READS_SEED, DB_SEED, rank * NR, NR, L, G, LG)
     out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
-    QF = 16 if args.lane else 0                                  # CCB_LANE_KERNEL
+    QF = 32 if args.warp else 0                                  # CCB_WARP_KERNEL; default: block kernel + warp kernel for the rest
     db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS | QF, stream)
     torch.cuda.synchronize()
     lookups, sectors = int(stats[0]), int(stats[1])
@@ -347,7 +348,7 @@ def run_b200(args):
     anchor_leg = None
     if not args.anchor and not args.no_anchor_leg:
         t0 = time.time(); ainfo = db.anchor_synth(DB_SEED, G, LG, min(G, 65534)); t_anchor = time.time() - t0
-        AQF = 16                                                   # CCB_LANE_KERNEL; the anchor is used because it exists
+        AQF = 0                                                    # default path; the anchor is used because it exists
         stats.zero_(); out.zero_()
         db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS | AQF, stream)
         torch.cuda.synchronize()
@@ -375,7 +376,7 @@ def run_b200(args):
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get("k_query_dram_bytes_per_launch")
+                traffic = json.load(open(tp)).get("k_query_dram_bytes_per_launch" if args.warp else "k_query_block_dram_bytes_per_launch")
             except Exception:
                 pass
         line = {
@@ -393,10 +394,10 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": "lookups/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "reads_per_s": NR * world * args.steps / t_e2e, "ms_per_step": 1e3 * t_e2e / args.steps,
                     "slots": S, "results_equal_resident_path": same},
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": (2 if args.warp else 3) * args.steps,      # k_query_block, k_query (handed-back reads), k_query_dense
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "bytes_per_lookup": 32,
-                         "kernel": "ccb::k_query", "gather32_gbs": gather and gather[32], "gather64_gbs": gather and gather[64],
+                         "kernel": "ccb::k_query" if args.warp else "ccb::k_query_block", "gather32_gbs": gather and gather[32], "gather64_gbs": gather and gather[64],
                          "frac_of_gather32": (achieved / gather[32]) if gather else None},
         }
         if anchor_leg:

@@ -59,8 +59,8 @@ typedef struct ccb_stats {
 } ccb_stats;
 
 enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8,
-       CCB_LANE_KERNEL = 16 /* thread-per-read kernel for short single-part reads, the rest as usual
-                               (implied when the anchor index is in use) */ };
+       CCB_LANE_KERNEL = 16 /* (default since the block kernel became the product path; kept for callers that pass it) */,
+       CCB_WARP_KERNEL = 32 /* warp-per-read kernel for every read (no block kernel, hence no anchor index) */ };
 
 /* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
 int  ccb_create(const ccb_config* cfg, ccb_handle** out);

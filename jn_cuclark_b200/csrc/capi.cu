@@ -367,8 +367,9 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
     }
     const bool use_anchor = h->anchor.ready && !(flags & CCB_NO_ANCHOR);
     const AnchorView av = h->anchor.view();
-    // short single-part reads: thread-per-read block kernel when asked for, and whenever the anchor index is used
-    if (((flags & CCB_LANE_KERNEL) || use_anchor) && list_cap >= a.n_reads) {
+    // short single-part reads go through the thread-per-read block kernel (query_lane.cu), everything it hands
+    // back (several parts, long reads, many targets) through the warp-per-read kernel
+    if (!(flags & CCB_WARP_KERNEL) && list_cap >= a.n_reads) {
         uint32_t* redo_list = ovf_list + list_cap; uint32_t* redo_count = ovf_count + 1;
         rc = launch_query_lane(tv, a, use_anchor ? &av : nullptr, redo_list, redo_count, st);
         if (rc) return rc;

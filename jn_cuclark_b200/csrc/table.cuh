@@ -47,7 +47,9 @@ __device__ __forceinline__ uint32_t match_bucket(const uint64_t (&e)[4], uint64_
 #pragma unroll
     for (int s = 0; s < 4; s++) {
         uint64_t d = e[s] ^ q;
-        if (d < 0x10000ull && e[s] != kEmpty) lab = (uint32_t)d;   // d == label when key bits agree
+        // key bits agree <=> d < 2^16, and then d is the label; an empty slot (all ones) can only agree with an
+        // all-ones key, where d = 0xFFFF, the one label no entry carries
+        if (d < 0xFFFFull) lab = (uint32_t)d;
     }
     return lab;
 }

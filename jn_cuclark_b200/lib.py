@@ -15,7 +15,8 @@ import os
 
 import numpy as np
 
-CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_LANE_KERNEL = 1, 2, 4, 8, 16
+CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_LANE_KERNEL, CCB_WARP_KERNEL = 1, 2, 4, 8, 16, 32
+default_flags = 0          # ORed into every query (tests run the parity suite once per kernel with it)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -241,7 +242,7 @@ class CuClarkDB:
     def queryBatch(self, batchId: int, isExtended: bool = False, flags: int = 0) -> bool:
         """CuClarkDB::queryBatch (src/CuClarkDB.cu:836); asynchronous."""
         n, c = self._n[batchId]
-        self._ck(self._lib.ccb_batch_submit(self._h, batchId, n, c, flags | (CCB_EXTENDED if isExtended else 0)))
+        self._ck(self._lib.ccb_batch_submit(self._h, batchId, n, c, flags | default_flags | (CCB_EXTENDED if isExtended else 0)))
         return True
 
     def waitForBatch(self, batchId: int) -> bool:
@@ -264,7 +265,7 @@ class CuClarkDB:
     def query_device(self, d_offsets: int, d_containers: int, n_reads: int, d_final5: int,
                      d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
         self._ck(self._lib.ccb_query_device(self._h, d_offsets, d_containers, n_reads, d_final5,
-                                            d_rows or None, d_stats or None, flags, stream or None))
+                                            d_rows or None, d_stats or None, flags | default_flags, stream or None))
 
     # -- sharded table (row E2): raw device pointers, the caller owns buffers and the exchange ----
     def shard_config(self, n_shards: int, shard: int):

@@ -18,14 +18,14 @@ def _classify(db, d_off, d_cont, n, flags):
 @pytest.mark.parametrize("k,L,G,LG", [(31, 150, 6, 60000), (31, 100, 3, 30000), (21, 140, 5, 50000), (31, 151, 4, 40000), (31, 200, 4, 40000)])
 def test_anchor_path_equals_plain_path_and_oracle(oracle, k, L, G, LG):
     import torch
-    from jn_cuclark_b200 import CuClarkDB, CCB_STATS, CCB_NO_ANCHOR
+    from jn_cuclark_b200 import CuClarkDB, CCB_STATS, CCB_NO_ANCHOR, CCB_WARP_KERNEL
     NR = 6000
     db = CuClarkDB(1, k, 1, G)
     db.synth_db(11, G, LG, G)
     info = db.anchor_synth(11, G, LG, G)
     assert info.ready and info.entries > 0.08 * G * LG and info.dropped < 0.08 * info.entries
     d_off, d_cont, nc = db.synth_reads_packed(22, 11, 0, NR, L, G, LG)
-    plain, l0, s0 = _classify(db, d_off, d_cont, NR, CCB_STATS | CCB_NO_ANCHOR)
+    plain, l0, s0 = _classify(db, d_off, d_cont, NR, CCB_STATS | CCB_WARP_KERNEL)      # warp-per-read kernel, table only
     # the index in use: the block kernel takes the short reads, the warp kernel the rest
     fast, l1, s1 = _classify(db, d_off, d_cont, NR, CCB_STATS)
     assert np.array_equal(fast, plain)
@@ -35,8 +35,7 @@ def test_anchor_path_equals_plain_path_and_oracle(oracle, k, L, G, LG):
     else:
         assert 0.99 * s0 < s1 <= s0                   # longer reads take the plain path (all but a few cut short by an N)
     # thread-per-read kernel without the index: same probes, same sectors
-    from jn_cuclark_b200 import CCB_LANE_KERNEL
-    lane, l2, s2_ = _classify(db, d_off, d_cont, NR, CCB_STATS | CCB_LANE_KERNEL | CCB_NO_ANCHOR)
+    lane, l2, s2_ = _classify(db, d_off, d_cont, NR, CCB_STATS | CCB_NO_ANCHOR)
     assert np.array_equal(lane, plain) and l2 == l0 and s2_ == s0
     # against the oracle
     off = torch.empty(NR + 1, dtype=torch.int32, device="cuda"); cont = torch.empty(nc, dtype=torch.int16, device="cuda")

@@ -6,6 +6,16 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
+
+@pytest.fixture(autouse=True, params=["block", "warp"])
+def kernel_flavour(request):
+    """Every parity case runs twice: the default path (thread-per-read block kernel for short single-part reads,
+    warp-per-read kernel for the rest) and the warp-per-read kernel for every read."""
+    from jn_cuclark_b200 import lib
+    lib.default_flags = lib.CCB_WARP_KERNEL if request.param == "warp" else 0
+    yield
+    lib.default_flags = 0
+
 HT_SMALL = 1000003
 
 
