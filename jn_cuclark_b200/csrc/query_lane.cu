@@ -109,25 +109,45 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
     const uint32_t nblocks = (a.n_reads + BLK - 1) / BLK;
     for (uint32_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const uint32_t r = blk * BLK + tid;
-        // ---------------- phase A ----------------
+        // ---------------- the read: one part, or two (a pair joined by N, an N inside) ----------------
         if (tid == 0) sm.qn = 0;
 #pragma unroll
         for (int s = 0; s < kLaneAcc; s++) { sm.acc_lab[tid][s] = kLabelNone; sm.acc_cnt[tid][s] = 0; }
-        sm.state[tid] = 0;
-        __syncthreads();
+        uint32_t rbeg = 0; int plen0 = 0, plen1 = 0, pn0 = 0; bool mine = false;
         if (r < a.n_reads) {
-            const uint32_t beg = __ldg(a.offsets + r);
-            const int nslots = (int)(__ldg(a.offsets + r + 1) - beg);
-            const uint16_t* c = a.containers + beg;
-            const int len = nslots > 0 ? (int)__ldg(c) : 0;
-            if (nslots == 0) {
+            rbeg = __ldg(a.offsets + r);
+            const int rslots = (int)(__ldg(a.offsets + r + 1) - rbeg);
+            const uint16_t* c = a.containers + rbeg;
+            if (rslots == 0) {
                 uint16_t* o5 = a.out5 + (size_t)r * 5;
                 o5[0] = o5[1] = o5[2] = o5[3] = o5[4] = 0;
                 if (a.rows) a.rows[(size_t)r * a.row_stride] = 0;
-            } else if (1 + ((len + 7) >> 3) != nslots || len > kLaneMaxBases || len < k) {
-                redo_list[atomicAdd(redo_count, 1u)] = r;
             } else {
-                sm.state[tid] = 1; sm.beg[tid] = beg; sm.len[tid] = (uint16_t)len;
+                plen0 = (int)__ldg(c); pn0 = 1 + ((plen0 + 7) >> 3);
+                mine = plen0 >= k && plen0 <= kLaneMaxBases && pn0 <= rslots;
+                if (mine && pn0 < rslots) {
+                    plen1 = (int)__ldg(c + pn0);
+                    mine = plen1 >= k && plen1 <= kLaneMaxBases && pn0 + 1 + ((plen1 + 7) >> 3) == rslots;
+                }
+                if (!mine) redo_list[atomicAdd(redo_count, 1u)] = r;      // more parts, longer, shorter than k
+            }
+        }
+        sm.state[tid] = mine ? 1 : 0;
+        for (int part = 0; part < 2; part++) {
+        if (part == 1) {
+            if (tid == 0) sm.qn = 0;
+            if (!__syncthreads_or(mine && plen1 > 0)) break;               // nobody in the block has a second part
+        } else {
+            __syncthreads();
+        }
+        // ---------------- phase A ----------------
+        {
+            const int len = part ? plen1 : plen0;
+            if (mine && len > 0) {
+                const uint32_t beg = rbeg + (part ? (uint32_t)pn0 : 0u);
+                const int nslots = 1 + ((len + 7) >> 3);
+                const uint16_t* c = a.containers + beg;
+                sm.beg[tid] = beg; sm.len[tid] = (uint16_t)len;
                 const int npos = len - k + 1;
                 Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;            // windows answered without a table probe
                 if (ANCHOR) {
@@ -237,7 +257,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                                 run.w[0] &= ~O.w[0]; run.w[1] &= ~O.w[1]; run.w[2] &= ~O.w[2];       // stored under another label: probe
                                 W = run;
                                 const uint32_t hits = __popcll(W.w[0] & D.w[0]) + __popcll(W.w[1] & D.w[1]) + __popcll(W.w[2] & D.w[2]);
-                                if (hits) { sm.acc_lab[tid][0] = alab; sm.acc_cnt[tid][0] = hits; }
+                                if (hits) vote_smem(sm, (uint32_t)tid, alab, hits);
                                 if (STATS) st_lookups += __popcll(W.w[0]) + __popcll(W.w[1]) + __popcll(W.w[2]);
                             }
                         }
@@ -326,6 +346,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
             if (run_cnt) vote_smem(sm, lr, run_lab, run_cnt);
         }
         __syncthreads();
+        }   // part
         // ---------------- phase C ----------------
         if (r < a.n_reads && sm.state[tid]) {
             if (sm.state[tid] == 2) {

@@ -112,8 +112,8 @@ def _world_texts(small_world, odb):
 
 
 @pytest.mark.parametrize("light", [False, True])
-@pytest.mark.parametrize("fname", ["reads.fa", "reads.fq"])
-def test_anchor_from_fasta_targets(small_world, oracle, fname, light):
+@pytest.mark.parametrize("fname", ["reads.fa", "reads.fq", "pairs"])
+def test_anchor_from_fasta_targets(small_world, oracle, fname, light, tmp_path):
     """The index built from the target FASTA files (N runs, lower case, several records per file, sequence
     shared between targets, two files under one label).  In a light database a text k-mer can be stored under
     ANOTHER target's label (it was sampled there, not here): those windows must still be probed."""
@@ -121,7 +121,13 @@ def test_anchor_from_fasta_targets(small_world, oracle, fname, light):
     from jn_cuclark_b200 import CuClarkDB, CCB_STATS, CCB_NO_ANCHOR
     k = 27 if light else 31
     odb = oracle.OracleDb.build(small_world["targets"], k, 1000003, light=light, gap=4)
-    ir = oracle.IndexedReads(open(os.path.join(small_world["dir"], fname), "rb").read())
+    if fname == "pairs":      # two parts per read (mates joined by N): both go through the block kernel, hence the index
+        m = str(tmp_path / "m.fa")
+        assert oracle.merge_paired(os.path.join(small_world["dir"], "p1.fq"), os.path.join(small_world["dir"], "p2.fq"), m) == 0
+        data = open(m, "rb").read()
+    else:
+        data = open(os.path.join(small_world["dir"], fname), "rb").read()
+    ir = oracle.IndexedReads(data)
     off, cont = ir.pack(k)
     want, wrows, nl = odb.query_packed(k, off, cont, row_stride=32)
     db = CuClarkDB(1, k, 2, len(odb.labels))

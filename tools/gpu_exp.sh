@@ -1,5 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for shape in 256x2 256x3 128x6 128x4; do
-  CCB_BLOCK_SHAPE=$shape timeout 300 python bench.py --kernel-only --steps 10 --warmup 3 > gpurun_out/ko_plain_$shape.log 2>&1; echo "$shape plain rc=$? $(tail -1 gpurun_out/ko_plain_$shape.log)"
-done
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_exp.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_exp.log
+timeout 300 python bench.py --kernel-only --steps 10 --warmup 3 > gpurun_out/ko_exp_plain.log 2>&1; echo "plain $(tail -1 gpurun_out/ko_exp_plain.log)"
+timeout 300 python bench.py --kernel-only --anchor --steps 10 --warmup 3 > gpurun_out/ko_exp_anchor.log 2>&1; echo "anchor $(tail -1 gpurun_out/ko_exp_anchor.log)"
