@@ -351,8 +351,9 @@ extern "C" int ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, ui
 
 // ovf_list holds 2 * list_cap entries and ovf_count 2 words: [0] reads for the dense pass, [1] reads the
 // thread-per-read kernel handed back to the warp-per-read kernel
+// n_containers: u16 units of the batch when the caller knows them (-1 otherwise): tells long-read batches apart
 static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uint32_t* ovf_count, uint32_t list_cap,
-                     uint32_t* dense_scratch, int flags, cudaStream_t st)
+                     uint32_t* dense_scratch, int flags, cudaStream_t st, int64_t n_containers = -1)
 {
     QueryArgs a = a0;
     a.ovf_list = ovf_list; a.ovf_count = ovf_count;
@@ -369,13 +370,17 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
     const AnchorView av = h->anchor.view();
     // short single-part reads go through the thread-per-read block kernel (query_lane.cu), everything it hands
     // back (several parts, long reads, many targets) through the warp-per-read kernel
-    if (!(flags & CCB_WARP_KERNEL) && list_cap >= a.n_reads) {
+    // (a batch that averages more than 50 containers per read holds long reads only: straight to the warp kernel)
+    const bool long_reads = n_containers >= 0 && n_containers > 50ll * (int64_t)a.n_reads;
+    uint32_t redo_grid = 0;
+    if (!(flags & CCB_WARP_KERNEL) && !long_reads && list_cap >= a.n_reads) {
         uint32_t* redo_list = ovf_list + list_cap; uint32_t* redo_count = ovf_count + 1;
         rc = launch_query_lane(tv, a, use_anchor ? &av : nullptr, redo_list, redo_count, st);
         if (rc) return rc;
         a.read_list = redo_list; a.n_list = redo_count;
+        if (n_containers >= 0) redo_grid = 148u * 16u;      // short reads on average: the list is short
     }
-    rc = launch_query(tv, a, st);
+    rc = launch_query(tv, a, st, redo_grid);
     if (rc) return rc;
     QueryArgs d = a; d.stats = nullptr; d.read_list = nullptr; d.n_list = nullptr;
     return launch_query_dense(tv, d, ovf_list, ovf_count, a.n_reads, (uint32_t)h->cfg.n_targets, dense_scratch, kDenseBlocks, st);
@@ -400,7 +405,7 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
     a.out5 = s.d_final5; a.rows = (flags & CCB_EXTENDED) ? s.d_rows : nullptr; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr;
     if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 16, s.stream));
-    int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, h->max_reads, s.d_dense_scratch, flags, s.stream);
+    int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, h->max_reads, s.d_dense_scratch, flags, s.stream, (int64_t)n_containers);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     CU(h, cudaMemcpyAsync(s.h_final5, s.d_final5, (size_t)n_reads * 10, cudaMemcpyDeviceToHost, s.stream));
     if (flags & CCB_EXTENDED) CU(h, cudaMemcpyAsync(s.h_rows, s.d_rows, (size_t)n_reads * h->row_stride * 2, cudaMemcpyDeviceToHost, s.stream));

@@ -67,21 +67,6 @@ __device__ __forceinline__ void vote4(const uint32_t (&lab)[4], uint32_t& acc_la
     }
 }
 
-// One label with a count, folded into the accumulators (the tail of vote4).
-__device__ __forceinline__ void vote_bulk(uint32_t L, uint32_t total, uint32_t& acc_lab, uint32_t& acc_cnt,
-                                          int& nacc, bool& overflow, int lane)
-{
-    uint32_t hit = __ballot_sync(0xFFFFFFFFu, lane < nacc && acc_lab == L);
-    if (hit) {
-        if (lane == __ffs(hit) - 1) acc_cnt += total;
-    } else if (nacc < 32) {
-        if (lane == nacc) { acc_lab = L; acc_cnt = total; }
-        nacc++;
-    } else {
-        overflow = true;
-    }
-}
-
 // Writes a read's result {sumN, idxBest, best, idxSecond, second} (src/CuClarkDB.cu:1370-1405), its
 // sparse row when asked for, and lists it for the dense pass when it overflowed the accumulators.
 __device__ __forceinline__ void finish_read(const QueryArgs& a, uint32_t r, uint32_t acc_lab, uint32_t acc_cnt,
@@ -335,14 +320,14 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
     if (MODE == kModeRoute) __threadfence_system();      // the stores may have gone to a peer GPU
 }
 
-int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s)
+int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s, uint32_t max_ctas)
 {
     if (a.n_reads == 0) return 0;
     uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
     // 2 CTAs are resident per SM; the grid holds 64x that many so the block scheduler
     // rebalances between fast and slow SMs (measured: 2/SM 36.1 ms, 8/SM 31.9, 128/SM 29.2
     // per 10 M reads -- a static split leaves the slower SMs as the tail).
-    uint32_t cap = 148u * 128u;
+    uint32_t cap = max_ctas ? max_ctas : 148u * 128u;
     if (ctas > cap) ctas = cap;
     const RouteArgs none{};
     if (a.stats) k_query<kModeQuery, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, none);

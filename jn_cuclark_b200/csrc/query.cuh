@@ -107,7 +107,9 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
                       uint32_t* redo_count, cudaStream_t s);
 
 // fast path: one warp per read, votes kept in registers
-int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s);
+// max_ctas: grid cap (0 = the default, 128 CTAs per SM); a pass over a short read_list wants a small grid --
+// 19 k CTAs that find nothing to do still cost 56 us
+int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s, uint32_t max_ctas = 0);
 // exact path for any number of distinct targets: one CTA per listed read, dense
 // per-CTA counters in global scratch (n_scratch_blocks * n_targets u32)
 int launch_query_dense(const TableView& t, const QueryArgs& a, const uint32_t* read_list,

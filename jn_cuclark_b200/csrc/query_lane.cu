@@ -427,14 +427,17 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
                       uint32_t* redo_count, cudaStream_t s)
 {
     if (a.n_reads == 0) return 0;
-    // block shape (measured): with the anchor index 256 threads x 2 blocks per SM (114 registers;
-    // three blocks spill), table only 256 x 3 (78 registers); CCB_BLOCK_SHAPE overrides for measurements
+    // block shape (measured): with the anchor index 128 threads x 4 blocks per SM (120 registers;
+    // more blocks spill and are slower, 256 x 2 is 1-2 % slower at the barriers), table only 256 x 3 (79 registers);
+    // CCB_BLOCK_SHAPE overrides for measurements
     static const char* shape = getenv("CCB_BLOCK_SHAPE");
     if (shape && !strcmp(shape, "128x4")) return launch_block<128, 4>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "256x3")) return launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "128x6")) return launch_block<128, 6>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "256x2")) return launch_block<256, 2>(t, a, av, redo_list, redo_count, s);
-    return av ? launch_block<256, 2>(t, a, av, redo_list, redo_count, s) : launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "64x8")) return launch_block<64, 8>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "128x5")) return launch_block<128, 5>(t, a, av, redo_list, redo_count, s);
+    return av ? launch_block<128, 4>(t, a, av, redo_list, redo_count, s) : launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
 }
 
 }  // namespace ccb

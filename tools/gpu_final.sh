@@ -9,6 +9,7 @@ a)  # full tests, smoke, bench (both arms), launch lists
     timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_final.json 2> gpurun_out/bench_final.err; echo "bench rc=$?"; cut -c1-300 gpurun_out/bench_final.json
     timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref_final.json 2> gpurun_out/bench_ref_final.err; echo "benchref rc=$?"
     timeout 300 python bench.py --kernel-only --warp --steps 10 --warmup 3 > gpurun_out/ko_warp.log 2>&1; echo "warp kernel: $(tail -1 gpurun_out/ko_warp.log)"
+    timeout 300 python bench.py --kernel-only --read-len 10000 --reads 125000 --steps 10 --warmup 3 > gpurun_out/ko_long.log 2>&1; echo "10-kbp reads (C4 shape, 125 k reads per GPU): $(tail -1 gpurun_out/ko_long.log)"
     timeout 600 $KO > gpurun_out/ko_block.log 2>&1 && \
     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches_final.csv $KO > gpurun_out/ncu_launches.log 2>&1
     echo "launch list rc=$?"
