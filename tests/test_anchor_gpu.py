@@ -15,7 +15,8 @@ def _classify(db, d_off, d_cont, n, flags):
     return out.cpu().numpy().view(np.uint16).reshape(n, 5), int(st[0]), int(st[1])
 
 
-@pytest.mark.parametrize("k,L,G,LG", [(31, 150, 6, 60000), (31, 100, 3, 30000), (21, 140, 5, 50000), (31, 151, 4, 40000), (31, 200, 4, 40000)])
+@pytest.mark.parametrize("k,L,G,LG", [(31, 150, 6, 60000), (31, 100, 3, 30000), (21, 140, 5, 50000), (31, 151, 4, 40000), (31, 200, 4, 40000),
+                                       (32, 192, 4, 30000), (12, 120, 3, 20000), (27, 33, 3, 20000)])
 def test_anchor_path_equals_plain_path_and_oracle(oracle, k, L, G, LG):
     import torch
     from jn_cuclark_b200 import CuClarkDB, CCB_STATS, CCB_NO_ANCHOR, CCB_WARP_KERNEL
@@ -30,8 +31,10 @@ def test_anchor_path_equals_plain_path_and_oracle(oracle, k, L, G, LG):
     fast, l1, s1 = _classify(db, d_off, d_cont, NR, CCB_STATS)
     assert np.array_equal(fast, plain)
     assert l1 == l0                                   # every k-mer is still accounted for
-    if L <= 192:
+    if 100 <= L <= 192:
         assert s1 < 0.6 * s0, (s0, s1)                # and most of them no longer touch the table
+    elif L < 100:
+        pass                                          # a handful of windows: the index's own sectors outweigh the saving
     else:
         assert 0.99 * s0 < s1 <= s0                   # longer reads take the plain path (all but a few cut short by an N)
     # thread-per-read kernel without the index: same probes, same sectors
