@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                 sm.beg[tid] = beg; sm.len[tid] = (uint16_t)len;
                 const int npos = len - k + 1;
                 Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;            // windows answered without a table probe
-                if (ANCHOR) {
+                if (ANCHOR && npos >= 16) {      // fewer windows: the index's own line fetches (3-4) outweigh what it can save
                     // rolling state after the first k-1 bases, cut out of the first four containers
                     uint64_t x, rc;
                     {
