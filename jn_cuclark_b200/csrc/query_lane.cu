@@ -107,12 +107,15 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
     const int tid = threadIdx.x;
     unsigned long long st_lookups = 0, st_sectors = 0;
     const uint32_t nblocks = (a.n_reads + BLK - 1) / BLK;
+    // the queue is empty and every read's vote pairs are clear at the top of an iteration: phase C leaves them so
+    // (three barriers per iteration: A|B, B|C, C|next A)
+    if (tid == 0) sm.qn = 0;
+#pragma unroll
+    for (int s = 0; s < kLaneAcc; s++) { sm.acc_lab[tid][s] = kLabelNone; sm.acc_cnt[tid][s] = 0; }
+    __syncthreads();
     for (uint32_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const uint32_t r = blk * BLK + tid;
         // ---------------- the read: one part, or two (a pair joined by N, an N inside) ----------------
-        if (tid == 0) sm.qn = 0;
-#pragma unroll
-        for (int s = 0; s < kLaneAcc; s++) { sm.acc_lab[tid][s] = kLabelNone; sm.acc_cnt[tid][s] = 0; }
         uint32_t rbeg = 0; int plen0 = 0, plen1 = 0, pn0 = 0; bool mine = false;
         if (r < a.n_reads) {
             rbeg = __ldg(a.offsets + r);
@@ -133,13 +136,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
             }
         }
         sm.state[tid] = mine ? 1 : 0;
-        for (int part = 0; part < 2; part++) {
-        if (part == 1) {
-            if (tid == 0) sm.qn = 0;
-            if (!__syncthreads_or(mine && plen1 > 0)) break;               // nobody in the block has a second part
-        } else {
-            __syncthreads();
-        }
+        for (int part = 0; ; part++) {
         // ---------------- phase A ----------------
         {
             const int len = part ? plen1 : plen0;
@@ -345,6 +342,9 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
             }
             if (run_cnt) vote_smem(sm, lr, run_lab, run_cnt);
         }
+        // B|C barrier, and at the same time: does any read of the block have a second part?
+        if (!__syncthreads_or(part == 0 && mine && plen1 > 0)) break;
+        if (tid == 0) sm.qn = 0;
         __syncthreads();
         }   // part
         // ---------------- phase C ----------------
@@ -386,6 +386,9 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                 }
             }
         }
+#pragma unroll
+        for (int s = 0; s < kLaneAcc; s++) { sm.acc_lab[tid][s] = kLabelNone; sm.acc_cnt[tid][s] = 0; }
+        if (tid == 0) sm.qn = 0;
         __syncthreads();
     }
     if (STATS) {

@@ -1,9 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-CCB_BLOCK_SHAPE=128x4p timeout 900 python -m pytest tests/test_anchor_gpu.py tests/test_parity_gpu.py -x -q 2>&1 | tail -2
-for shape in 128x4 128x4p 256x2p 128x3p; do
-  CCB_BLOCK_SHAPE=$shape timeout 300 python bench.py --kernel-only --anchor --steps 10 --warmup 3 > gpurun_out/ko_anchor_$shape.log 2>&1; echo "$shape anchor rc=$? $(tail -1 gpurun_out/ko_anchor_$shape.log)"
-done
-for shape in 256x3 128x4p 256x2p; do
-  CCB_BLOCK_SHAPE=$shape timeout 300 python bench.py --kernel-only --steps 10 --warmup 3 > gpurun_out/ko_plain_$shape.log 2>&1; echo "$shape plain rc=$? $(tail -1 gpurun_out/ko_plain_$shape.log)"
+timeout 900 python -m pytest tests/test_anchor_gpu.py tests/test_parity_gpu.py tests/test_cli_gpu.py -x -q 2>&1 | tail -2
+for i in 1 2; do
+timeout 300 python bench.py --kernel-only --anchor --steps 10 --warmup 3 > gpurun_out/ko_exp_anchor.log 2>&1; echo "anchor $(tail -1 gpurun_out/ko_exp_anchor.log)"
+timeout 300 python bench.py --kernel-only --steps 10 --warmup 3 > gpurun_out/ko_exp_plain.log 2>&1; echo "plain $(tail -1 gpurun_out/ko_exp_plain.log)"
 done
