@@ -1,7 +1,9 @@
 // query.cu -- fused k-mer extraction -> canonicalise -> probe -> vote.
 //
 // Replaces the reference's queryKernel + mergeKernel + resultKernel
-// (src/CuClarkDB.cu:1000-1183, 1261-1355, 1361-1411) by one kernel:
+// (src/CuClarkDB.cu:1000-1183, 1261-1355, 1361-1411) by one kernel.  k_query is the general kernel: reads of
+// any length and any number of parts.  Short reads of one or two parts are taken by k_query_block
+// (query_lane.cu) first, which hands everything else to k_query on a list (QueryArgs::read_list).
 //
 //  * one warp per read, the read is walked in tiles of 512 k-mer start
 //    positions; each lane owns a CONTIGUOUS chunk of positions, so forward and
