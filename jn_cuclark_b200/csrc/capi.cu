@@ -3,8 +3,11 @@
 #include "capi_internal.cuh"
 #include "dbbuild.cuh"
 #include <algorithm>
+#include <atomic>
 #include <memory>
 #include <thread>
+#include <fcntl.h>
+#include <unistd.h>
 
 #include <stdarg.h>
 #include <stdio.h>
@@ -200,22 +203,42 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
     USE_DEV(h);
     if (key_bytes != 2 && key_bytes != 4 && key_bytes != 8) return ccb_fail(h, -2, "key_bytes must be 2, 4 or 8");
     std::string p = prefix;
-    FILE* fs = fopen((p + ".sz").c_str(), "rb");
-    if (!fs) return ccb_fail(h, -20, "Failed to open %s.sz", prefix);          // src/CuClarkDB.cu:483-488
-    FILE* fk = fopen((p + ".ky").c_str(), "rb");
-    if (!fk) { fclose(fs); return ccb_fail(h, -20, "Failed to open %s.ky", prefix); }
-    FILE* fl = fopen((p + ".lb").c_str(), "rb");
-    if (!fl) { fclose(fs); fclose(fk); return ccb_fail(h, -20, "Failed to open %s.lb", prefix); }
+    // the three files are read with pread() from several threads: one thread copies out of the page cache at
+    // 2-3 GB/s, the .sz file alone is HTSIZE = 1.6 GB
+    const unsigned nthr = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    auto pread_all = [&](int fd, void* dst, uint64_t bytes, uint64_t off) -> bool {
+        const uint64_t grain = 4ull << 20;
+        const unsigned T = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(nthr, (bytes + grain - 1) / grain));
+        std::atomic<bool> ok(true);
+        auto part = [&](unsigned t) {
+            uint64_t lo = bytes / T * t, hi = t + 1 == T ? bytes : bytes / T * (t + 1);
+            while (lo < hi) {
+                const ssize_t r = pread(fd, (char*)dst + lo, (size_t)std::min<uint64_t>(hi - lo, 64ull << 20), (off_t)(off + lo));
+                if (r <= 0) { ok = false; return; }
+                lo += (uint64_t)r;
+            }
+        };
+        if (T == 1) { part(0); return ok; }
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < T; t++) th.emplace_back(part, t);
+        for (auto& x : th) x.join();
+        return ok;
+    };
+    const int fs = open((p + ".sz").c_str(), O_RDONLY);
+    if (fs < 0) return ccb_fail(h, -20, "Failed to open %s.sz", prefix);          // src/CuClarkDB.cu:483-488
+    const int fk = open((p + ".ky").c_str(), O_RDONLY);
+    if (fk < 0) { close(fs); return ccb_fail(h, -20, "Failed to open %s.ky", prefix); }
+    const int fl = open((p + ".lb").c_str(), O_RDONLY);
+    if (fl < 0) { close(fs); close(fk); return ccb_fail(h, -20, "Failed to open %s.lb", prefix); }
 
     std::unique_ptr<uint8_t[]> sz(new uint8_t[htsize]);
-    if (fread(sz.get(), 1, htsize, fs) != htsize) { fclose(fs); fclose(fk); fclose(fl); return ccb_fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
-    fclose(fs);
+    if (!pread_all(fs, sz.get(), htsize, 0)) { close(fs); close(fk); close(fl); return ccb_fail(h, -21, "%s.sz is shorter than HTSIZE=%llu", prefix, (unsigned long long)htsize); }
+    close(fs);
     // per block of 64 Ki buckets: keys and non-empty buckets (all host threads), then the blocks are
     // grouped into chunks the staging buffers can hold
     const uint64_t BS = 1ull << 16;
     const uint64_t nblk = (htsize + BS - 1) / BS;
     std::vector<uint64_t> blk_keys(nblk), blk_nz(nblk), blk_rank(nblk + 1, 0), blk_kept(nblk, 0);
-    const unsigned nthr = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
     auto par = [&](auto&& fn) {
         std::vector<std::thread> th;
         for (unsigned t = 0; t < nthr; t++) th.emplace_back([&, t] { for (uint64_t b = t; b < nblk; b += nthr) fn(b); });
@@ -242,10 +265,10 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
         for (uint64_t b = 0; b < nblk; b++) n_keep += blk_kept[b];
     }
     int rc = ccb_db_begin(h, n_keep);
-    if (rc) { fclose(fk); fclose(fl); return rc; }
+    if (rc) { close(fk); close(fl); return rc; }
 
     const uint32_t CB = 1u << 24;               // max buckets per chunk
-    const uint64_t CK = 1ull << 25;             // max keys per chunk (a block holds at most 255 * 64 Ki < CK)
+    const uint64_t CK = 1ull << 24;             // max keys per chunk (a block holds at most 255 * 64 Ki < CK); pinned staging is 2 x 112 MB
     const size_t scratch_bytes = table_ref_chunk_scratch(CB);
     uint32_t* d_off = nullptr; uint32_t* d_rank = nullptr; void* d_scratch = nullptr;
     CU(h, cudaMalloc(&d_off, CB * 4ull)); CU(h, cudaMalloc(&d_rank, CB * 4ull)); CU(h, cudaMalloc(&d_scratch, scratch_bytes));
@@ -256,7 +279,7 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
         CU(h, cudaMallocHost(&x.h_sz, CB)); CU(h, cudaMallocHost(&x.h_keys, CK * key_bytes)); CU(h, cudaMallocHost(&x.h_lab, CK * 2));
         CU(h, cudaEventCreateWithFlags(&x.done, cudaEventDisableTiming));
     }
-    uint64_t blk = 0; rc = 0; int cur = 0;
+    uint64_t blk = 0, keys_read = 0; rc = 0; int cur = 0;
     while (blk < nblk && !rc) {
         uint64_t nk = 0, e = blk;
         while (e < nblk && (e - blk) * BS < CB && nk + blk_keys[e] <= CK) { nk += blk_keys[e]; e++; }
@@ -265,7 +288,9 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
         Stage& x = st[cur];
         if (x.busy) { cudaEventSynchronize(x.done); x.busy = false; }      // the copy engines are done with this stage
         if (nk) {
-            if (fread(x.h_keys, (size_t)key_bytes, nk, fk) != nk || fread(x.h_lab, 2, nk, fl) != nk) { rc = -22; break; }
+            if (!pread_all(fk, x.h_keys, nk * (uint64_t)key_bytes, keys_read * (uint64_t)key_bytes) ||
+                !pread_all(fl, x.h_lab, nk * 2, keys_read * 2)) { rc = -22; break; }
+            keys_read += nk;
             memcpy(x.h_sz, sz.get() + b0, nb);
             cudaMemcpyAsync(x.d_keys, x.h_keys, nk * key_bytes, cudaMemcpyHostToDevice, h->db_stream);
             cudaMemcpyAsync(x.d_lab, x.h_lab, nk * 2, cudaMemcpyHostToDevice, h->db_stream);
@@ -278,7 +303,7 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
         blk = e;
     }
     cudaStreamSynchronize(h->db_stream);
-    fclose(fk); fclose(fl);
+    close(fk); close(fl);
     cudaFree(d_off); cudaFree(d_rank); cudaFree(d_scratch);
     for (auto& x : st) { cudaFree(x.d_sz); cudaFree(x.d_keys); cudaFree(x.d_lab); cudaFreeHost(x.h_sz); cudaFreeHost(x.h_keys); cudaFreeHost(x.h_lab); if (x.done) cudaEventDestroy(x.done); }
     if (rc == -22) { table_destroy(h->table); h->db_building = false; return ccb_fail(h, rc, "%s.ky/.lb are shorter than the bucket sizes in .sz announce", prefix); }

@@ -112,15 +112,6 @@ void index_sequential(const uint8_t* m, size_t nb, bool fasta, ReadSet& o)
     }
 }
 
-void append(ReadSet& o, const ReadSet& a)
-{
-    o.name_s.insert(o.name_s.end(), a.name_s.begin(), a.name_s.end());
-    o.name_e.insert(o.name_e.end(), a.name_e.begin(), a.name_e.end());
-    o.seq_s.insert(o.seq_s.end(), a.seq_s.begin(), a.seq_s.end());
-    o.seq_e.insert(o.seq_e.end(), a.seq_e.begin(), a.seq_e.end());
-    o.len.insert(o.len.end(), a.len.begin(), a.len.end());
-}
-
 }  // namespace
 
 int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
@@ -198,10 +189,24 @@ int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
         for (auto& x : th) x.join();
     }
     if (odd) { out.clear(); index_sequential(m, nb, fasta, out); return 0; }
-    size_t total = 0;
-    for (auto& p : part) total += p.n();
-    out.name_s.reserve(total); out.name_e.reserve(total); out.seq_s.reserve(total); out.seq_e.reserve(total); out.len.reserve(total);
-    for (auto& p : part) append(out, p);
+    // concatenate: sizes first, then every thread copies its own part (which also spreads the first touch)
+    std::vector<size_t> at((size_t)T + 1, 0);
+    for (int t = 0; t < T; t++) at[(size_t)t + 1] = at[(size_t)t] + part[(size_t)t].n();
+    const size_t total = at[(size_t)T];
+    out.name_s.resize(total); out.name_e.resize(total); out.seq_s.resize(total); out.seq_e.resize(total); out.len.resize(total);
+    {
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; t++) th.emplace_back([&, t] {
+            const ReadSet& p = part[(size_t)t];
+            const size_t o = at[(size_t)t], n = p.n();
+            if (!n) return;
+            memcpy(out.name_s.data() + o, p.name_s.data(), n * 8); memcpy(out.name_e.data() + o, p.name_e.data(), n * 8);
+            memcpy(out.seq_s.data() + o, p.seq_s.data(), n * 8);   memcpy(out.seq_e.data() + o, p.seq_e.data(), n * 8);
+            memcpy(out.len.data() + o, p.len.data(), n * 8);
+            part[(size_t)t].clear();
+        });
+        for (auto& x : th) x.join();
+    }
     return 0;
 }
 
@@ -456,8 +461,22 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
 {
     auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = now();
+    const size_t kMaxBatchReads = 1u << 17, kMaxBatchBytes = 32u << 20;
+    // For a large input the pinned slots are allocated while the file is being indexed (0.1 s of cudaHostAlloc
+    // next to 0.3 s of indexing per 10 M reads).  Their size is the most a batch can need -- bytes/8 containers,
+    // two more per part, a part at least k bases and a separator long -- unless a single read is larger than a
+    // batch; the exact figures are checked below and the slots re-made if they do not fit.
+    const bool early = nb >= ((size_t)256 << 20);
+    const size_t spec_reads = kMaxBatchReads,
+                 spec_cont = kMaxBatchBytes / 8 + 2 * (kMaxBatchBytes / (size_t)(opt.k + 1) + kMaxBatchReads) + 64;
+    std::vector<int> early_rc(devs.size(), 0);
+    std::thread early_alloc;
+    if (early) early_alloc = std::thread([&] {
+        for (size_t d = 0; d < devs.size(); d++) early_rc[d] = ccb_batch_alloc(devs[d], (uint32_t)spec_reads, spec_cont, opt.extended);
+    });
     ReadSet rs;
-    if (index_reads(map, nb, opt.threads, rs) != 0) { err = "Failed to recognize the format of the file."; return 255; }
+    const int irc = index_reads(map, nb, opt.threads, rs);
+    if (irc != 0) { if (early) early_alloc.join(); err = "Failed to recognize the format of the file."; return 255; }
     stats.seconds_index = now() - t0;
     const size_t n = rs.n();
     stats.reads = n;
@@ -465,7 +484,6 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     // batches: bounded by sequence bytes and read count so that pinned slots stay modest and
     // there are enough of them in flight to hide packing behind the GPU and vice versa
     // (and small enough that every worker gets several: 10 M x 150 bp reads -> 77 batches)
-    const size_t kMaxBatchReads = 1u << 17, kMaxBatchBytes = 32u << 20;
     std::vector<size_t> bstart{0};
     {
         size_t bytes = 0, cnt = 0;
@@ -487,8 +505,16 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     const int workers = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(opt.threads, 1), nbatches));
     const double t_alloc0 = now();
     std::vector<std::unique_ptr<DevSlots>> ds;
+    bool reuse = false;
+    if (early) {
+        early_alloc.join();
+        reuse = max_reads <= spec_reads && max_cont <= spec_cont;
+        for (int rc : early_rc) reuse = reuse && rc == 0;
+        if (reuse) { max_reads = spec_reads; max_cont = spec_cont; }
+    }
     for (ccb_handle* h : devs) {
-        if (int rc = ccb_batch_alloc(h, (uint32_t)max_reads, max_cont, opt.extended)) { err = ccb_last_error(h); return rc; }
+        if (!reuse)
+            if (int rc = ccb_batch_alloc(h, (uint32_t)max_reads, max_cont, opt.extended)) { err = ccb_last_error(h); return rc; }
         ds.emplace_back(new DevSlots());
         ds.back()->h = h;
         for (int s = 0; s < ccb_batch_slots(h); s++) ds.back()->free_slots.push_back(s);

@@ -13,6 +13,7 @@
 #pragma once
 #include <stddef.h>
 #include <stdint.h>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -20,14 +21,26 @@ struct ccb_handle;
 
 namespace ccbh {
 
+// std::vector whose resize() leaves new elements uninitialised: the index of 10 M reads is 400 MB, filling it
+// with zeros on one thread before the parallel copy costs as much as the copy
+template <typename T>
+struct NoInitAlloc : std::allocator<T> {
+    template <typename U> struct rebind { using other = NoInitAlloc<U>; };
+    NoInitAlloc() = default;
+    template <typename U> NoInitAlloc(const NoInitAlloc<U>&) {}
+    template <typename U> void construct(U* p) noexcept { ::new ((void*)p) U; }
+    template <typename U, typename... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+};
+using OffsetVec = std::vector<uint64_t, NoInitAlloc<uint64_t>>;
+
 // One entry per read, byte offsets into the mapped text (A1, src/CuCLARK_hh.hh:1364-1394, 1496-1524)
 struct ReadSet {
     const uint8_t* map = nullptr;
     size_t nb = 0;
     bool fasta = true;
-    std::vector<uint64_t> name_s, name_e;   // name bytes [name_s, name_e)
-    std::vector<uint64_t> seq_s, seq_e;     // sequence bytes [seq_s, seq_e) (may contain newlines)
-    std::vector<uint64_t> len;              // length used for gamma
+    OffsetVec name_s, name_e;   // name bytes [name_s, name_e)
+    OffsetVec seq_s, seq_e;     // sequence bytes [seq_s, seq_e) (may contain newlines)
+    OffsetVec len;              // length used for gamma
     size_t n() const { return len.size(); }
     void clear() { name_s.clear(); name_e.clear(); seq_s.clear(); seq_e.clear(); len.clear(); }
 };

@@ -10,6 +10,7 @@ ap.add_argument("--genome-len", type=int, default=4_000_000)
 ap.add_argument("--reads", type=int, default=10_000_000)
 ap.add_argument("--threads", default="1,4,16")
 ap.add_argument("--dir", default=None)
+ap.add_argument("--anchor", action="store_true", help="one more run with CCB_ANCHOR=1 (target texts on the device), CSV compared")
 ap.add_argument("--reference", default=None,
                 help="also run the reference GPU binary (oracle/_ref/cuCLARK) with these '-n,-b' pairs, e.g. 1:4,16:32 "
                      "(needs a number of targets that is a multiple of 32, see tests/golden/ref_gpu/README.md)")
@@ -71,6 +72,19 @@ for i, T in enumerate([int(x) for x in a.threads.split(",")]):
                         "stderr_tail": r.stderr[-600:] if (r.returncode or not m) else None,
                         "phases": [l.strip() for l in r.stderr.splitlines() if "build:" in l or "host pipeline" in l or "Loading time" in l][:12]})
 import hashlib
+if a.anchor:
+    T = max(int(x) for x in a.threads.split(","))
+    t0 = time.time()
+    r = subprocess.run([exe, "-T", os.path.join(d, "targets.txt"), "-D", dbdir + "/", "-O", fq, "-R", os.path.join(d, "res_anchor"), "-n", str(T), "--verbose"],
+                       capture_output=True, text=True, env=dict(os.environ, CCB_ANCHOR="1"))
+    wall = time.time() - t0
+    m = re.search(r"Done in ([0-9.]+)s \((\d+) reads/min, (\d+) reads\)", r.stderr.replace("\n", " "))
+    first = os.path.join(d, f"res{a.threads.split(',')[0]}.csv")
+    out["anchor_run"] = {"threads": T, "rc": r.returncode, "wall_s": wall, "classify_s": float(m.group(1)) if m else None,
+                         "reads_per_min": int(m.group(2)) if m else None,
+                         "csv_identical_to_table_only": r.returncode == 0 and open(first, "rb").read() == open(os.path.join(d, "res_anchor.csv"), "rb").read(),
+                         "phases": [l.strip() for l in r.stderr.splitlines() if "Anchor index" in l or "host pipeline" in l or "Loading time" in l][:6],
+                         "stderr_tail": r.stderr[-600:] if (r.returncode or not m) else None}
 if a.reference:
     ref = os.path.join(ROOT, "oracle", "_ref", "cuCLARK")
     out["reference_runs"] = []

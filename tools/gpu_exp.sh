@@ -1,7 +1,10 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_anchor_gpu.py tests/test_parity_gpu.py tests/test_cli_gpu.py -x -q 2>&1 | tail -2
-for i in 1 2; do
-timeout 300 python bench.py --kernel-only --anchor --steps 10 --warmup 3 > gpurun_out/ko_exp_anchor.log 2>&1; echo "anchor $(tail -1 gpurun_out/ko_exp_anchor.log)"
-timeout 300 python bench.py --kernel-only --steps 10 --warmup 3 > gpurun_out/ko_exp_plain.log 2>&1; echo "plain $(tail -1 gpurun_out/ko_exp_plain.log)"
-done
+timeout 900 python tools/bench_cli.py --threads 16,16,4 --anchor > gpurun_out/cli_e2e.json 2> gpurun_out/cli_e2e.err; echo "cli rc=$?"
+python - <<'P'
+import json
+d=json.load(open('gpurun_out/cli_e2e.json'))
+for r in d['runs']: print(r['threads'], r['wall_s'], r['classify_s'], r['phases'][-2:])
+print(d.get('anchor_run')); print(d['csv_identical_across_threads'])
+P
+timeout 600 python -m pytest tests/test_cli_gpu.py tests/test_parity_gpu.py -x -q 2>&1 | tail -2
