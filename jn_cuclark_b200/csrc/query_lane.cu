@@ -84,6 +84,19 @@ __device__ __forceinline__ void vote_smem(BlockSmem<BLK>& sm, uint32_t lr, uint3
     sm.state[lr] = 2;
 }
 
+// Staging of a block's containers (STAGE): the packed reads of a block are one contiguous run of the batch, so one
+// elected thread asks the TMA engine for the whole run (cp.async.bulk, completion on an mbarrier) one block ahead;
+// phases A and B then read containers from shared memory instead of issuing 2-byte global loads.
+template <int BLK>
+struct StageSmem {
+    static constexpr int kCap = BLK * 44;        // u16 per buffer: two parts of 150 bases per read on average (else: global loads)
+    alignas(16) uint16_t cbuf[2][kCap];
+    unsigned long long bar[2];
+    int      sbase[2];                           // container index of cbuf[b][0]
+    uint32_t staged[2];
+};
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 // entry of sector e whose fingerprint is fp (~0 when there is none)
 __device__ __forceinline__ uint64_t match_anchor(const uint64_t (&e)[4], uint32_t fp)
 {
@@ -95,12 +108,13 @@ __device__ __forceinline__ uint64_t match_anchor(const uint64_t (&e)[4], uint32_
 
 }  // namespace
 
-template <int BLK, int MINB, bool ANCHOR, bool STATS>
+template <int BLK, int MINB, bool ANCHOR, bool STATS, bool STAGE>
 __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, const QueryArgs a, const AnchorView av,
                                                           uint32_t* redo_list, uint32_t* redo_count)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BlockSmem<BLK>& sm = *reinterpret_cast<BlockSmem<BLK>*>(smem_raw);
+    StageSmem<BLK>& st = *reinterpret_cast<StageSmem<BLK>*>(smem_raw + ((sizeof(BlockSmem<BLK>) + 15) & ~(size_t)15));
     const int k = t.hp.k;
     const uint64_t kmsk = t.hp.mask;
     const int s2 = 2 * (k - 1);
@@ -112,24 +126,67 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
     if (tid == 0) sm.qn = 0;
 #pragma unroll
     for (int s = 0; s < kLaneAcc; s++) { sm.acc_lab[tid][s] = kLabelNone; sm.acc_cnt[tid][s] = 0; }
+    // thread 0: ask for the containers of block nb into buffer b (16-byte granules around the run)
+    auto stage_issue = [&](int b, uint32_t nb) {
+        const uint32_t r0 = nb * BLK, r1 = min(r0 + (uint32_t)BLK, a.n_reads);
+        const uint32_t o0 = __ldg(a.offsets + r0), o1 = __ldg(a.offsets + r1);
+        const uintptr_t base = (uintptr_t)a.containers;
+        const uintptr_t p0 = (base + 2ull * o0) & ~(uintptr_t)15, p1 = (base + 2ull * o1 + 15) & ~(uintptr_t)15;
+        const uint32_t nbytes = (uint32_t)(p1 - p0);
+        if (o1 > o0 && p0 >= base && nbytes <= (uint32_t)StageSmem<BLK>::kCap * 2u) {
+            st.sbase[b] = (int)((p0 - base) >> 1);
+            st.staged[b] = 1;
+            const uint32_t bar = smem_addr(&st.bar[b]);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(nbytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         :: "r"(smem_addr(st.cbuf[b])), "l"(p0), "r"(nbytes), "r"(bar) : "memory");
+        } else {
+            st.staged[b] = 0;
+        }
+    };
+    if (STAGE && tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_addr(&st.bar[0])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_addr(&st.bar[1])));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (blockIdx.x < nblocks) stage_issue(0, blockIdx.x);
+    }
     __syncthreads();
+    uint32_t stage_it = 0, stage_par = 0;
     for (uint32_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const uint32_t r = blk * BLK + tid;
+        // containers of this block: from the staged copy when there is one
+        const uint16_t* sb = nullptr; int sbase = 0;
+        if (STAGE) {
+            const int cur = (int)(stage_it & 1u);
+            if (tid == 0 && blk + gridDim.x < nblocks) stage_issue(cur ^ 1, blk + gridDim.x);
+            if (st.staged[cur]) {
+                const uint32_t bar = smem_addr(&st.bar[cur]);
+                uint32_t ok = 0;
+                while (!ok)
+                    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                                 : "=r"(ok) : "r"(bar), "r"((stage_par >> cur) & 1u) : "memory");
+                stage_par ^= 1u << cur;
+                sb = st.cbuf[cur]; sbase = st.sbase[cur];
+            }
+            stage_it++;
+        }
+        auto ldc = [&](uint32_t idx) -> uint32_t {
+            return (STAGE && sb) ? (uint32_t)sb[(int)idx - sbase] : (uint32_t)__ldg(a.containers + idx);
+        };
         // ---------------- the read: one part, or two (a pair joined by N, an N inside) ----------------
         uint32_t rbeg = 0; int plen0 = 0, plen1 = 0, pn0 = 0; bool mine = false;
         if (r < a.n_reads) {
             rbeg = __ldg(a.offsets + r);
             const int rslots = (int)(__ldg(a.offsets + r + 1) - rbeg);
-            const uint16_t* c = a.containers + rbeg;
             if (rslots == 0) {
                 uint16_t* o5 = a.out5 + (size_t)r * 5;
                 o5[0] = o5[1] = o5[2] = o5[3] = o5[4] = 0;
                 if (a.rows) a.rows[(size_t)r * a.row_stride] = 0;
             } else {
-                plen0 = (int)__ldg(c); pn0 = 1 + ((plen0 + 7) >> 3);
+                plen0 = (int)ldc(rbeg); pn0 = 1 + ((plen0 + 7) >> 3);
                 mine = plen0 >= k && plen0 <= kLaneMaxBases && pn0 <= rslots;
                 if (mine && pn0 < rslots) {
-                    plen1 = (int)__ldg(c + pn0);
+                    plen1 = (int)ldc(rbeg + (uint32_t)pn0);
                     mine = plen1 >= k && plen1 <= kLaneMaxBases && pn0 + 1 + ((plen1 + 7) >> 3) == rslots;
                 }
                 if (!mine) redo_list[atomicAdd(redo_count, 1u)] = r;      // more parts, longer, shorter than k
@@ -143,7 +200,6 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
             if (mine && len > 0) {
                 const uint32_t beg = rbeg + (part ? (uint32_t)pn0 : 0u);
                 const int nslots = 1 + ((len + 7) >> 3);
-                const uint16_t* c = a.containers + beg;
                 sm.beg[tid] = beg; sm.len[tid] = (uint16_t)len;
                 const int npos = len - k + 1;
                 Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;            // windows answered without a table probe
@@ -153,19 +209,19 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                     {
                         uint64_t v = 0;
 #pragma unroll
-                        for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)__ldg(c + 1 + j) : 0ull);
+                        for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)ldc(beg + 1 + j) : 0ull);
                         x = k > 1 ? v >> (64 - s2) : 0ull;
                         rc = revcomp_brev(x, k);
                     }
                     uint32_t cw = 0;
                     int i = k - 1;
-                    if (i & 7) cw = __ldg(c + 1 + (i >> 3));
+                    if (i & 7) cw = ldc(beg + 1 + (i >> 3));
                     uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
                     // up to two rounds; a round = the next two sampled k-mers of the read, looked up together
                     for (int round = 0; round < 2 && ae == ~0ull && i < len; round++) {
                         uint64_t c0 = 0, c1 = 0; int p0 = 0, p1 = 0; uint32_t f0 = 0, f1 = 0; int nc = 0;
                         for (; i < len && nc < 2; i++) {
-                            if ((i & 7) == 0) cw = __ldg(c + 1 + (i >> 3));
+                            if ((i & 7) == 0) cw = ldc(beg + 1 + (i >> 3));
                             const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
                             x = ((x << 2) | code) & kmsk;
                             rc = (rc >> 2) | ((3ull - code) << s2);
@@ -232,7 +288,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
 #pragma unroll
                                     for (int j = 0; j < 4; j++) {
                                         const int sl = 1 + 4 * u + j;
-                                        rd = (rd << 16) | (sl < nslots ? (uint64_t)__ldg(c + sl) : 0ull);
+                                        rd = (rd << 16) | (sl < nslots ? (uint64_t)ldc(beg + sl) : 0ull);
                                     }
                                     const uint64_t df = tt ^ rd;
                                     const uint32_t mis = mismatch16((uint32_t)(df >> 32)) | (mismatch16((uint32_t)df) << 16);
@@ -300,16 +356,16 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
             const uint32_t item = sm.queue[it];
             const uint32_t lr = item >> 20, ch = (item >> 16) & 15u;
             uint32_t m4 = item & 0xFFFFu;
-            const uint16_t* c = a.containers + sm.beg[lr];
+            const uint32_t cb = sm.beg[lr];
             // the 48 bases from the chunk's first window on
             uint64_t bhi = 0, blo = 0;
             {
                 const int s0 = 1 + 2 * (int)ch;
                 const int nsl = 1 + ((sm.len[lr] + 7) >> 3);
 #pragma unroll
-                for (int j = 0; j < 4; j++) bhi = (bhi << 16) | (s0 + j < nsl ? (uint64_t)__ldg(c + s0 + j) : 0ull);
+                for (int j = 0; j < 4; j++) bhi = (bhi << 16) | (s0 + j < nsl ? (uint64_t)ldc(cb + s0 + j) : 0ull);
 #pragma unroll
-                for (int j = 4; j < 6; j++) blo = (blo << 16) | (s0 + j < nsl ? (uint64_t)__ldg(c + s0 + j) : 0ull);
+                for (int j = 4; j < 6; j++) blo = (blo << 16) | (s0 + j < nsl ? (uint64_t)ldc(cb + s0 + j) : 0ull);
                 blo <<= 32;
             }
             uint64_t e[4][4], home[4], q[4]; bool need[4];
@@ -403,20 +459,22 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
 
 namespace {
 
-template <int BLK, int MINB>
+template <int BLK, int MINB, bool STAGE = false>
 int launch_block(const TableView& t, const QueryArgs& a, const AnchorView* av, uint32_t* redo_list, uint32_t* redo_count,
                  cudaStream_t s)
 {
-    const size_t smem = sizeof(BlockSmem<BLK>);
+    // the staged copy moves 16-byte granules: it needs the batch's containers to start on one
+    if (STAGE && ((uintptr_t)a.containers & 15u)) return launch_block<BLK, MINB, false>(t, a, av, redo_list, redo_count, s);
+    const size_t smem = ((sizeof(BlockSmem<BLK>) + 15) & ~(size_t)15) + (STAGE ? sizeof(StageSmem<BLK>) : 0);
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
     const uint32_t cap = 148u * 64u * (256u / BLK);
     if (ctas > cap) ctas = cap;
     const AnchorView none{};
 #define CCB_LAUNCH_BLOCK(AN, ST, AV)                                                                                   \
     do {   /* the attribute is per device: set it on every launch (microseconds) rather than remember who has it */   \
-        cudaError_t e = cudaFuncSetAttribute(k_query_block<BLK, MINB, AN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        cudaError_t e = cudaFuncSetAttribute(k_query_block<BLK, MINB, AN, ST, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return (int)e;                                                                           \
-        k_query_block<BLK, MINB, AN, ST><<<ctas, BLK, smem, s>>>(t, a, AV, redo_list, redo_count);                      \
+        k_query_block<BLK, MINB, AN, ST, STAGE><<<ctas, BLK, smem, s>>>(t, a, AV, redo_list, redo_count);                      \
     } while (0)
     if (av) { if (a.stats) CCB_LAUNCH_BLOCK(true, true, *av); else CCB_LAUNCH_BLOCK(true, false, *av); }
     else    { if (a.stats) CCB_LAUNCH_BLOCK(false, true, none); else CCB_LAUNCH_BLOCK(false, false, none); }
@@ -438,6 +496,9 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
     if (shape && !strcmp(shape, "256x3")) return launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "128x6")) return launch_block<128, 6>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "256x2")) return launch_block<256, 2>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "128x4s")) return launch_block<128, 4, true>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "64x8s")) return launch_block<64, 8, true>(t, a, av, redo_list, redo_count, s);
+    if (shape && !strcmp(shape, "256x2s")) return launch_block<256, 2, true>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "64x8")) return launch_block<64, 8>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "128x5")) return launch_block<128, 5>(t, a, av, redo_list, redo_count, s);
     return av ? launch_block<128, 4>(t, a, av, redo_list, redo_count, s) : launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
