@@ -55,6 +55,9 @@ def parse():
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"],
                     help="--sharded: NCCL all-to-all, or kernels storing into peer inboxes (CUDA IPC over NVLink)")
     ap.add_argument("--chunks", type=int, default=1, help="--sharded: split each rank's batch into this many exchange rounds")
+    ap.add_argument("--overlap", action="store_true",
+                    help="--sharded --exchange peer: rounds alternate between two streams, each with its own inboxes and barrier "
+                         "group, so one round's probe (HBM-bound) runs under the next round's count/route (issue- and NVLink-bound)")
     ap.add_argument("--kernel-only", action="store_true", help="profiling runs: resident-batch loop only (prints no bench line)")
     return ap.parse_args()
 
@@ -446,10 +449,26 @@ def run_sharded(args):
     else:
         sc = ShardedClassifier(db)
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+    overlap = bool(args.overlap and peer and nch >= 2)
+    if overlap:
+        # second pipeline: own inboxes / label boxes / counts, own barrier group (its all-reduces run on another stream)
+        g2 = dist.new_group(list(range(world))) if world > 1 else None
+        sc2 = PeerShardedClassifier(db, cap, group=g2)
+        scs, streams = [sc, sc2], [torch.cuda.Stream(), torch.cuda.Stream()]
 
     def step(st=None):
-        for o, cc, nc, n, out in batches:
-            sc.classify(o, cc, n, out, stats=st)
+        if not overlap:
+            for o, cc, nc, n, out in batches:
+                sc.classify(o, cc, n, out, stats=st)
+            return
+        cur = torch.cuda.current_stream()
+        for s_ in streams:
+            s_.wait_stream(cur)
+        for i, (o, cc, nc, n, out) in enumerate(batches):
+            with torch.cuda.stream(streams[i & 1]):
+                scs[i & 1].classify(o, cc, n, out, stats=st)
+        for s_ in streams:
+            cur.wait_stream(s_)
 
     def barrier():
         if world > 1:
@@ -537,7 +556,7 @@ def run_sharded(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic", "reads_per_s": NR * world * args.steps / (ms * 1e-3),
             "config": {"workload": f"cuCLARK full k={k}, synthetic {G} x {LG} bp DB ({n_kmers} {k}-mers), {NR} x {L} bp SE reads per GPU",
-                       "parallelism": f"table sharded x{world} by hash range, k-mer exchange = " + ("kernel stores into peer inboxes (CUDA IPC over NVLink)" if peer else "NCCL all-to-all") + f", {nch} exchange round(s) per step",
+                       "parallelism": f"table sharded x{world} by hash range, k-mer exchange = " + ("kernel stores into peer inboxes (CUDA IPC over NVLink)" if peer else "NCCL all-to-all") + f", {nch} exchange round(s) per step" + (", two rounds in flight on two streams" if overlap else ""),
                        "l2": "inputs larger than L2 (shard %.1f GB, random access)" % (info.bytes / 1e9),
                        "shard_gb": info.bytes / 1e9, "shard_entries": info.entries, "db_build_s": t_db,
                        "kmers_sent_per_step_rank0": sent_rank0, "probes_per_step_rank0": lookups_here, "phases_rank0": phases},
@@ -548,6 +567,8 @@ def run_sharded(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src, "bytes_per_lookup": 32, "kernel": "ccb::k_probe_list", "probe_ms": probe_ms,
                          "probes": n_in}}))
+    if overlap:
+        sc2.close()
     if peer:
         sc.close()
     for o, cc, nc, n, out in batches:

@@ -112,7 +112,8 @@ extern "C" void ccb_destroy(ccb_handle* h)
     anchor_build_free(h);
     anchor_free(h->anchor);
     table_destroy(h->table);
-    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense); cudaFree(h->shard_scan_tmp);
+    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense);
+    for (auto& x : h->shard_scratch) { cudaFree(x.scan_tmp); cudaFree(x.ovf_list); cudaFree(x.ovf_count); cudaFree(x.dense); }
     if (h->db_stream) cudaStreamDestroy(h->db_stream);
     delete h;
 }

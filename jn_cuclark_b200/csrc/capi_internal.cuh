@@ -63,7 +63,11 @@ struct ccb_handle {
     uint32_t  q_ovf_cap = 0;
     // sharded table (ccb_shard_*): this handle holds shard `shard` of `n_shards`
     uint32_t   n_shards = 1, shard = 0;
-    void*      shard_scan_tmp = nullptr; size_t shard_scan_bytes = 0;
+    // scratch of ccb_shard_count / ccb_shard_vote, one set per stream they were called on (batches of a
+    // sharded pipeline overlap on two streams); never shared with ccb_query_device's q_* buffers
+    struct ShardScratch { void* stream = nullptr; bool used = false; void* scan_tmp = nullptr; size_t scan_bytes = 0;
+                          uint32_t* ovf_list = nullptr; uint32_t ovf_cap = 0; uint32_t* ovf_count = nullptr; uint32_t* dense = nullptr; };
+    ShardScratch shard_scratch[4];
     ccb::Anchor anchor;              // optional: sequences + sampled k-mer positions in front of the table
     ccb::AnchorBuild* anchor_build = nullptr;
     // database construction in progress (ccb_build_*)

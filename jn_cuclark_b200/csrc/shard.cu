@@ -43,6 +43,15 @@ static int hp_for_routing(ccb_handle* h, int n_shards, TableView& tv)
     return 0;
 }
 
+// the scratch set of a stream (first use claims one of four)
+static ccb_handle::ShardScratch* shard_scratch_for(ccb_handle* h, void* stream)
+{
+    std::lock_guard<std::mutex> g(h->mu);
+    for (auto& x : h->shard_scratch) if (x.used && x.stream == stream) return &x;
+    for (auto& x : h->shard_scratch) if (!x.used) { x.used = true; x.stream = stream; return &x; }
+    return nullptr;
+}
+
 extern "C" int ccb_shard_count(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
                                int n_shards, void* d_pos, void* stream)
 {
@@ -59,11 +68,13 @@ extern "C" int ccb_shard_count(ccb_handle* h, const void* d_offsets, const void*
     if (rc) return ccb_fail(h, rc, "count launch failed");
     size_t need = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, need, (uint32_t*)d_pos, (uint32_t*)d_pos, n, s);
-    if (need > h->shard_scan_bytes) {
-        cudaFree(h->shard_scan_tmp); h->shard_scan_tmp = nullptr; h->shard_scan_bytes = 0;
-        CU(h, cudaMalloc(&h->shard_scan_tmp, need)); h->shard_scan_bytes = need;
+    ccb_handle::ShardScratch* x = shard_scratch_for(h, stream);
+    if (!x) return ccb_fail(h, -64, "ccb_shard_*: more than 4 streams in use on one handle");
+    if (need > x->scan_bytes) {
+        cudaFree(x->scan_tmp); x->scan_tmp = nullptr; x->scan_bytes = 0;
+        CU(h, cudaMalloc(&x->scan_tmp, need)); x->scan_bytes = need;
     }
-    CU(h, cub::DeviceScan::ExclusiveSum(h->shard_scan_tmp, need, (uint32_t*)d_pos, (uint32_t*)d_pos, n, s));
+    CU(h, cub::DeviceScan::ExclusiveSum(x->scan_tmp, need, (uint32_t*)d_pos, (uint32_t*)d_pos, n, s));
     return 0;
 }
 
@@ -99,21 +110,23 @@ extern "C" int ccb_shard_vote(ccb_handle* h, uint32_t n_reads, int n_shards, con
     if (n_shards < 1 || n_shards > kMaxShards) return ccb_fail(h, -60, "at most %d shards", kMaxShards);
     USE_DEV(h);
     cudaStream_t s = (cudaStream_t)stream;
-    if (h->q_ovf_cap < n_reads || !h->q_ovf_list) {
-        cudaFree(h->q_ovf_list); h->q_ovf_list = nullptr;
-        CU(h, cudaMalloc(&h->q_ovf_list, (size_t)(n_reads ? n_reads : 1) * 4));
-        h->q_ovf_cap = n_reads;
+    ccb_handle::ShardScratch* x = shard_scratch_for(h, stream);
+    if (!x) return ccb_fail(h, -64, "ccb_shard_*: more than 4 streams in use on one handle");
+    if (x->ovf_cap < n_reads || !x->ovf_list) {
+        cudaFree(x->ovf_list); x->ovf_list = nullptr;
+        CU(h, cudaMalloc(&x->ovf_list, (size_t)(n_reads ? n_reads : 1) * 4));
+        x->ovf_cap = n_reads;
     }
-    if (!h->q_ovf_count) CU(h, cudaMalloc(&h->q_ovf_count, 4));
-    if (!h->q_dense) CU(h, cudaMalloc(&h->q_dense, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
+    if (!x->ovf_count) CU(h, cudaMalloc(&x->ovf_count, 8));
+    if (!x->dense) CU(h, cudaMalloc(&x->dense, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
     QueryArgs a{}; a.n_reads = n_reads; a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
-    a.ovf_list = h->q_ovf_list; a.ovf_count = h->q_ovf_count;
+    a.ovf_list = x->ovf_list; a.ovf_count = x->ovf_count;
     VoteArgs va{}; va.n_shards = (uint32_t)n_shards; va.pos = (const uint32_t*)d_pos;
     va.derive_base = seg_base ? 0u : 1u;
     for (int g = 0; g < n_shards; g++) { va.seg_base[g] = seg_base ? seg_base[g] : 0; va.src[g] = (const uint16_t*)src[g]; }
-    CU(h, cudaMemsetAsync(h->q_ovf_count, 0, 4, s));
+    CU(h, cudaMemsetAsync(x->ovf_count, 0, 4, s));
     int rc = launch_vote_lists(a, va, s);
-    if (!rc) rc = launch_vote_lists_dense(a, va, h->q_ovf_list, h->q_ovf_count, n_reads, (uint32_t)h->cfg.n_targets, h->q_dense, kDenseBlocks, s);
+    if (!rc) rc = launch_vote_lists_dense(a, va, x->ovf_list, x->ovf_count, n_reads, (uint32_t)h->cfg.n_targets, x->dense, kDenseBlocks, s);
     if (rc) return ccb_fail(h, rc, "vote launch failed");
     return 0;
 }
