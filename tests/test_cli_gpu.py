@@ -181,3 +181,21 @@ def test_cli_equals_reference_gpu_binary(tmp_path, mode, anchor):
         r = subprocess.run([exe, "-T", tp, "-D", str(tmp_path / "db") + "/", "-R", res, "-n", "3"] + kflag + args, capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stderr[-1500:]
         assert open(res + ".csv", "rb").read() == open(g, "rb").read(), case
+
+
+@pytest.mark.parametrize("anchor", [False, True], ids=["table", "anchor"])
+def test_two_devices_give_the_same_csv(setup, oracle, tmp_path, anchor):
+    """-d 2 (row E1 at the process boundary): the table is replicated, batches are dealt round-robin over the
+    devices, rows come out in input order -- byte-identical to the one-device CSV and to the oracle's."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    s = setup
+    reads = os.path.join(WORLD, "reads.fq")
+    env = {"CCB_ANCHOR": "1"} if anchor else None
+    r = _run(s, ["-O", reads, "-d", "2", "-n", "4", "-b", "8", "--verbose"], str(tmp_path / "two"), env)
+    assert "Using 2 CUDA devices as requested." in r.stderr
+    _run(s, ["-O", reads, "-n", "4"], str(tmp_path / "one"), env)
+    _oracle_csv(s, oracle, open(reads, "rb").read(), str(tmp_path / "want.csv"))
+    two = open(str(tmp_path / "two.csv"), "rb").read()
+    assert two == open(str(tmp_path / "one.csv"), "rb").read() == open(str(tmp_path / "want.csv"), "rb").read()
