@@ -229,6 +229,20 @@ struct CodeTable {
 };
 const CodeTable kCodes;
 
+// two characters at once: (code << 2 | code) of a pair of bases, 0xFF when either is not a base
+struct PairTable {
+    uint8_t t[65536];
+    PairTable()
+    {
+        for (int a = 0; a < 256; a++)
+            for (int b = 0; b < 256; b++) {
+                const uint8_t ca = kCodes.t[a], cb = kCodes.t[b];
+                t[a | (b << 8)] = (ca < 4 && cb < 4) ? (uint8_t)((ca << 2) | cb) : (uint8_t)0xFF;     // little endian: first char in the low byte
+            }
+    }
+};
+const PairTable kPairs;
+
 struct PartWriter {
     uint16_t* c; size_t cc, cap; int k;
     size_t hdr = 0; uint32_t plen = 0; uint32_t acc = 0, cnt = 0; bool open = false; uint64_t hist = 0;
@@ -282,8 +296,22 @@ int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
         offsets[j] = (uint32_t)w.cc;
         if (r.len[i] < (uint64_t)k) continue;       // :1632, reads without a k-mer store nothing
         const uint8_t* p = m + r.seq_s[i]; const uint8_t* e = m + r.seq_e[i];
-        for (; p < e; p++) {
-            const uint32_t code = kCodes.t[*p];
+        while (p < e) {
+            // fast path: the writer sits on a container boundary and the next eight characters are bases
+            if (w.cnt == 0 && p + 8 <= e && w.cc < w.cap && (!w.open || w.plen + 8 <= kMaxPart)) {
+                uint16_t q[4];
+                memcpy(q, p, 8);
+                const uint32_t v0 = kPairs.t[q[0]], v1 = kPairs.t[q[1]], v2 = kPairs.t[q[2]], v3 = kPairs.t[q[3]];
+                if (!((v0 | v1 | v2 | v3) & 0x80u)) {
+                    if (!w.open) { w.begin(); if (w.overflow) break; }
+                    const uint32_t c16 = (v0 << 12) | (v1 << 8) | (v2 << 4) | v3;
+                    if (w.cc < w.cap) w.c[w.cc++] = (uint16_t)c16; else w.overflow = true;
+                    w.hist = (w.hist << 16) | c16; w.plen += 8;
+                    p += 8;
+                    continue;
+                }
+            }
+            const uint32_t code = kCodes.t[*p++];
             if (code < 4) w.base(code);
             else if (code == 5) w.end();
         }
