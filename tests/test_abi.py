@@ -66,3 +66,14 @@ def test_product_does_not_reference_oracle():
                 if re.search(r"oracle|ccbo_", s):
                     bad.append(os.path.join(d, f))
     assert not bad, bad
+
+
+def test_flag_values_match_the_header():
+    """The query flags of include/cuclark_b200.h and their mirror in lib.py are the same numbers."""
+    from jn_cuclark_b200 import lib
+    h = open(os.path.join(ROOT, "include", "cuclark_b200.h")).read()
+    h = re.sub(r"/\*.*?\*/", "", h, flags=re.S)
+    flags = dict((n, int(v)) for n, v in re.findall(r"\b(CCB_[A-Z_]+)\s*=\s*(\d+)", h))
+    assert {"CCB_EXTENDED", "CCB_STATS", "CCB_FORCE_DENSE", "CCB_NO_ANCHOR", "CCB_LANE_KERNEL", "CCB_WARP_KERNEL"} <= set(flags)
+    for n, v in flags.items():
+        assert getattr(lib, n) == v, n
