@@ -335,6 +335,13 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
     USE_DEV(h);
     if (max_containers > 0xFFFFFFFFull)
         return ccb_fail(h, -30, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>).");  // CuCLARK_hh.hh:1709-1713
+    // slots that are large enough are kept (the next file of a list; pinning and unpinning 250 MB costs ~0.1 s each)
+    if (!h->slots.empty() && (int)h->slots.size() == h->cfg.n_slots && h->max_reads >= max_reads && h->max_cont >= max_containers &&
+        h->batch_extended == (extended != 0)) {
+        bool idle = true;
+        for (const Slot& s : h->slots) idle = idle && !s.in_flight;
+        if (idle) return 0;
+    }
     free_slots(h);
     h->max_reads = max_reads; h->max_cont = max_containers; h->batch_extended = extended != 0;
     h->slots.resize((size_t)h->cfg.n_slots);

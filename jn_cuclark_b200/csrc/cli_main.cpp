@@ -477,7 +477,15 @@ int main(int argc, char** argv)
         if (c.sfactor > 2) cerr << "Sampling factor is " << c.sfactor << endl;
     }
     e.open_devices();
+    // a large reads file: pin the batch slots while the database loads (hostpipe.hpp reserve_slots)
+    std::thread slots;
+    {
+        struct stat sb;
+        if (stat(c.objects, &sb) == 0 && (uint64_t)sb.st_size >= (256ull << 20))
+            slots = std::thread([&] { ccbh::reserve_slots(e.devs, (int)e.cli.k, e.cli.ext); });
+    }
     e.load_db();
+    if (slots.joinable()) slots.join();
     e.build_anchor();
     e.run();
     for (ccb_handle* h : e.devs) ccb_destroy(h);

@@ -484,19 +484,30 @@ struct OrderedSink {
 
 }  // namespace
 
+namespace {
+constexpr size_t kMaxBatchReads = 1u << 17, kMaxBatchBytes = 32u << 20;
+// the most a batch can need: bytes/8 containers, two more per part, a part at least k bases and a separator long
+inline size_t spec_containers(int k) { return kMaxBatchBytes / 8 + 2 * (kMaxBatchBytes / (size_t)(k + 1) + kMaxBatchReads) + 64; }
+}  // namespace
+
+int reserve_slots(const std::vector<ccb_handle*>& devs, int k, bool extended)
+{
+    int rc = 0;
+    for (ccb_handle* h : devs) { const int r = ccb_batch_alloc(h, (uint32_t)kMaxBatchReads, spec_containers(k), extended); if (r && !rc) rc = r; }
+    return rc;
+}
+
 int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size_t nb, const char* result_csv,
                   const std::vector<std::string>& names, const ClassifyOptions& opt, ClassifyStats& stats, std::string& err)
 {
     auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = now();
-    const size_t kMaxBatchReads = 1u << 17, kMaxBatchBytes = 32u << 20;
     // For a large input the pinned slots are allocated while the file is being indexed (0.1 s of cudaHostAlloc
     // next to 0.3 s of indexing per 10 M reads).  Their size is the most a batch can need -- bytes/8 containers,
     // two more per part, a part at least k bases and a separator long -- unless a single read is larger than a
     // batch; the exact figures are checked below and the slots re-made if they do not fit.
     const bool early = nb >= ((size_t)256 << 20);
-    const size_t spec_reads = kMaxBatchReads,
-                 spec_cont = kMaxBatchBytes / 8 + 2 * (kMaxBatchBytes / (size_t)(opt.k + 1) + kMaxBatchReads) + 64;
+    const size_t spec_reads = kMaxBatchReads, spec_cont = spec_containers(opt.k);
     std::vector<int> early_rc(devs.size(), 0);
     std::thread early_alloc;
     if (early) early_alloc = std::thread([&] {
@@ -513,10 +524,12 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     // there are enough of them in flight to hide packing behind the GPU and vice versa
     // (and small enough that every worker gets several: 10 M x 150 bp reads -> 77 batches)
     std::vector<size_t> bstart{0};
+    bool oversize = false;                     // some read alone exceeds the batch byte limit
     {
         size_t bytes = 0, cnt = 0;
         for (size_t i = 0; i < n; i++) {
             size_t b = (size_t)(rs.seq_e[i] - rs.seq_s[i]);
+            oversize = oversize || b > kMaxBatchBytes;
             if (cnt && (cnt >= kMaxBatchReads || bytes + b > kMaxBatchBytes)) { bstart.push_back(i); bytes = 0; cnt = 0; }
             bytes += b; cnt++;
         }
@@ -525,9 +538,12 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     const size_t nbatches = bstart.size() - 1;
     stats.batches = nbatches;
     size_t max_reads = 1, max_cont = 1;
+    // with slots sized for the largest batch the rule allows, the per-batch bound (one more pass over the index) is
+    // only needed when a single read is larger than that
+    const bool need_bound = !early || oversize;
     for (size_t b = 0; b < nbatches; b++) {
         max_reads = std::max(max_reads, bstart[b + 1] - bstart[b]);
-        max_cont = std::max(max_cont, pack_bound(rs, bstart[b], bstart[b + 1] - bstart[b], opt.k));
+        if (need_bound) max_cont = std::max(max_cont, pack_bound(rs, bstart[b], bstart[b + 1] - bstart[b], opt.k));
     }
 
     const int workers = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(opt.threads, 1), nbatches));
@@ -614,7 +630,7 @@ int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size
     for (auto& t : th) t.join();
     const bool io_err = sink.io_error || fclose(sink.f) != 0;
     if (sink.dump) fclose(sink.dump);
-    for (auto& d : ds) ccb_batch_free(d->h);
+    // the slots stay with the handles: the next file of a list reuses them (ccb_batch_alloc), ccb_destroy releases them
     stats.seconds_total = now() - t0;
     if (failed) return failed;
     if (io_err) { err = std::string("Failed to write ") + result_csv; return 1; }

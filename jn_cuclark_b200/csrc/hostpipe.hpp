@@ -82,6 +82,10 @@ struct ClassifyStats {
     double   seconds_alloc = 0, cpu_pack = 0, cpu_wait = 0, cpu_format = 0, cpu_sink = 0;
 };
 
+// Allocate every handle's pinned slots for the largest batch classify_text forms (0.1-0.25 s of pinning): a caller
+// that knows a large input is coming does this while the database loads; classify_text then finds them in place.
+int reserve_slots(const std::vector<ccb_handle*>& devs, int k, bool extended);
+
 // Classify the reads of one mapped text with the given device handles (one per GPU, replicated
 // table; batches are dealt round-robin) and write <result_csv>.  0 = ok; err set otherwise.
 int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size_t nb, const char* result_csv,
