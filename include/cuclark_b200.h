@@ -181,7 +181,8 @@ int  ccb_anchor_get_info(const ccb_handle* h, ccb_anchor_info* info);
 
 /* CuClarkDB::malloc (src/CuClarkDB.cu:322-421): pinned host + device buffers for
  * every slot, owned by the library; the caller fills offsets/containers in
- * place and reads final5/rows in place after ccb_batch_wait. */
+ * place and reads final5/rows in place after ccb_batch_wait.  Slots that are
+ * already large enough (and idle) are kept: the call is then free. */
 int  ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended);
 int  ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers,
                        uint16_t** final5, uint16_t** rows);
