@@ -148,3 +148,25 @@ def test_long_part_is_split_not_wrapped():
         n = int(cont[p]); lens.append(n); total_kmers += n - k + 1; p += 1 + (n + 7) // 8
     assert lens == [65528, 65528, L - 2 * (65528 - (k - 1))]
     assert total_kmers == L - k + 1
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_pack_random_texts_equal_oracle(oracle, seed):
+    """Random FASTA with ragged line widths, N runs, lower case, U, stray characters and reads of every length around
+    the container size: the packer's eight-bases-per-step path and its byte path write the oracle's containers."""
+    from jn_cuclark_b200 import host
+    rng = np.random.default_rng(seed)
+    alphabet = np.frombuffer(b"ACGTACGTACGTACGTACGTACGTacgtuUN.-", dtype=np.uint8)
+    recs = []
+    for i in range(400):
+        n = int(rng.integers(0, 260)) if i % 7 else int(rng.integers(0, 20))
+        seq = alphabet[rng.integers(0, alphabet.size if i % 3 == 0 else 24, n)].tobytes()
+        width = int(rng.integers(1, 90))
+        lines = b"\n".join(seq[j:j + width] for j in range(0, len(seq), width)) if i % 2 else seq
+        recs.append(b">r%d x\n" % i + lines + b"\n")
+    data = b"".join(recs)
+    a, b = _same_index(oracle, host, data)
+    for k in (2, 8, 9, 21, 31, 32):
+        oa, ca = a.pack(k)
+        ob, cb = b.pack(k)
+        assert np.array_equal(oa, ob) and np.array_equal(ca[:int(oa[-1])], cb[:int(ob[-1])]), k
