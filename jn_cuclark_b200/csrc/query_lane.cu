@@ -2,8 +2,9 @@
 //
 // k_query (query.cu) gives a whole warp to one read; most of its instructions coordinate the 32 lanes
 // (tile staging, validity masks, shuffle-merged votes).  For the reads that dominate a metagenomic
-// sample -- one part, <= 192 bases, a handful of targets hit -- none of that is needed.  k_query_block
-// gives every thread of a block one read and runs three phases per block of reads:
+// sample -- one or two parts (a pair joined by N) of <= 192 bases, a handful of targets hit -- none of that
+// is needed.  k_query_block gives every thread of a block one read and runs three phases per block of reads
+// (phases A and B once more for the second parts, when any read of the block has one):
 //   A  per read: (with the anchor index, query.cuh AnchorView) roll over the read until two sampled k-mers
 //      are met, look both up in the sampled table at once, compare the read with the target text base by
 //      base; every window that matches is answered from the text's own bits.  The windows that remain are
@@ -12,9 +13,11 @@
 //      touch, each window's k-mer is cut out of them directly (no rolling state, no divergence between
 //      lanes), four probes are in flight per thread, votes go to the read's four (label,count) pairs in
 //      shared memory.
-//   C  per read: best / second best / sum, sparse row.
-// Anything else -- several parts, longer reads, a fifth distinct target -- is handed back on a list and
+//   C  per read: best / second best / sum, sparse row; queue and vote pairs are left clear for the next block.
+// Anything else -- three or more parts, longer parts, a fifth distinct target -- is handed back on a list and
 // classified by k_query.  Results are the same u16[5] / sparse rows either way.
+// Measurements, the rejected variants (L2 prefetch of the next item, TMA staging of the containers = STAGE)
+// and the block shapes are in DESIGN.md section 11.
 #include "query.cuh"
 #include <stdlib.h>
 #include <string.h>
