@@ -154,6 +154,11 @@ int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
             ReadSet& o = part[(size_t)t];
             const size_t b = cut[(size_t)t], e = cut[(size_t)t + 1];
             Rec r;
+            {   // room for the records of this range up front (FASTQ: a quarter of its lines; FASTA: a guess), so the
+                // five vectors are not copied over and over while they grow; untouched reservation costs nothing
+                const size_t guess = (fasta ? (e - b) / 100 : (size_t)newlines[(size_t)t] / 4) + 16;
+                o.name_s.reserve(guess); o.name_e.reserve(guess); o.seq_s.reserve(guess); o.seq_e.reserve(guess); o.len.reserve(guess);
+            }
             if (fasta) {
                 size_t p = b;
                 while (p < e) {                     // next '>' that starts a line, inside [b, e)
