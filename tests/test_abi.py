@@ -77,3 +77,20 @@ def test_flag_values_match_the_header():
     assert {"CCB_EXTENDED", "CCB_STATS", "CCB_FORCE_DENSE", "CCB_NO_ANCHOR", "CCB_LANE_KERNEL", "CCB_WARP_KERNEL"} <= set(flags)
     for n, v in flags.items():
         assert getattr(lib, n) == v, n
+
+
+def test_library_holds_sm_100a_code_only():
+    """Every device image in the library is sm_100a (no other architecture, no PTX-only fallback), and the block
+    kernel's optional container staging really is the TMA bulk copy (UBLKCP) -- checked on the build, no GPU needed."""
+    import shutil
+    import subprocess
+    import pytest
+    from jn_cuclark_b200 import lib
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    r = subprocess.run(["cuobjdump", "-lelf", lib.lib_path()], capture_output=True, text=True)
+    elfs = [l for l in r.stdout.splitlines() if l.startswith("ELF file")]
+    assert elfs and all("sm_100a" in l for l in elfs), elfs
+    sass = subprocess.run(["cuobjdump", "-sass", lib.lib_path()], capture_output=True, text=True).stdout
+    assert "UBLKCP" in sass and "SYNCS" in sass        # cp.async.bulk + mbarrier (STAGE variant of k_query_block)
+    assert "ENL2.256" in sass                          # LDG ... .256: one 32-byte table sector per probe in a single load
