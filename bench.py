@@ -403,11 +403,15 @@ def run_b200(args):
         achieved = (lookups * 32 / (ms * 1e-3 / args.steps)) / 1e9          # this rank's kernel
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
+        default_workload = (G, LG, NR, L, k) == (1000, 4_000_000, 10_000_000, 150, 31)      # what the ncu capture was taken on
+        if os.path.exists(tp) and default_workload:
             try:
                 traffic = json.load(open(tp)).get("k_query_dram_bytes_per_launch" if args.warp else "k_query_block_dram_bytes_per_launch")
             except Exception:
                 pass
+        # real DRAM bytes per launch (ncu) over this run's launch time: how close to HBM the kernel runs on the bytes
+        # the memory system moves (a 128-byte line per 32-byte sector), next to `frac` on the algorithmic bytes
+        dram_gbs = (traffic / (ms * 1e-3 / args.steps)) / 1e9 if traffic else None
         line = {
             "metric": "kmer_lookups_per_s", "value": value, "unit": "lookups/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -425,7 +429,8 @@ def run_b200(args):
                     "slots": S, "results_equal_resident_path": same},
             "gpu_launches": (2 if args.warp else 3) * args.steps,      # k_query_block, k_query (handed-back reads), k_query_dense
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "bytes_per_lookup": 32,
+                         "traffic": traffic, "dram_gbs": dram_gbs, "dram_frac": (dram_gbs / peak) if dram_gbs else None,
+                         "peak_source": peak_src, "bytes_per_lookup": 32,
                          "kernel": "ccb::k_query" if args.warp else "ccb::k_query_block", "gather32_gbs": gather and gather[32], "gather64_gbs": gather and gather[64],
                          "frac_of_gather32": (achieved / gather[32]) if gather else None},
         }
