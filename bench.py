@@ -45,7 +45,6 @@ def parse():
     ap.add_argument("--sample-reads", type=int, default=200_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
-    ap.add_argument("--lane", action="store_true", help="(default now) thread-per-read block kernel for short reads")
     ap.add_argument("--warp", action="store_true", help="warp-per-read kernel for every read (CCB_WARP_KERNEL)")
     ap.add_argument("--anchor", action="store_true",
                     help="build the anchor index (target sequences + sampled k-mer positions) in front of the table")
@@ -313,6 +312,7 @@ def run_b200(args):
     # rolling pipeline, as the CLI drives it: a slot is waited for only when it is about to be
     # refilled, so the H2D of one batch overlaps the kernel of the previous one across steps too.
     busy = [False] * S
+    e2e_steps_ms = []
 
     def time_e2e(qf):
         def e2e_step():
@@ -331,12 +331,15 @@ def run_b200(args):
         e2e_drain()
         barrier()
         t0 = time.perf_counter()
+        marks = []
         for _ in range(args.steps):
-            e2e_step()
+            e2e_step(); marks.append(time.perf_counter())
         e2e_drain()
         torch.cuda.synchronize()
         t = max_over_ranks(time.perf_counter() - t0)
         barrier()
+        # host-side pace of the pipeline, step by step (a one-off stall shows up as one long step)
+        e2e_steps_ms.append([round(1e3 * (b - a), 2) for a, b in zip([t0] + marks[:-1], marks)])
         # results of the e2e path equal the resident path
         fin = np.concatenate([db.buffers(s)[2][:n] for s, (n, _) in enumerate(sizes)])
         return t, bool(np.array_equal(fin, out_h))
@@ -426,7 +429,7 @@ def run_b200(args):
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "lookups/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "reads_per_s": NR * world * args.steps / t_e2e, "ms_per_step": 1e3 * t_e2e / args.steps,
-                    "slots": S, "results_equal_resident_path": same},
+                    "slots": S, "results_equal_resident_path": same, "host_step_ms": e2e_steps_ms[0]},
             "gpu_launches": (2 if args.warp else 3) * args.steps,      # k_query_block, k_query (handed-back reads), k_query_dense
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "dram_gbs": dram_gbs, "dram_frac": (dram_gbs / peak) if dram_gbs else None,

@@ -59,7 +59,6 @@ typedef struct ccb_stats {
 } ccb_stats;
 
 enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8,
-       CCB_LANE_KERNEL = 16 /* (default since the block kernel became the product path; kept for callers that pass it) */,
        CCB_WARP_KERNEL = 32 /* warp-per-read kernel for every read (no block kernel, hence no anchor index) */ };
 
 /* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
@@ -186,6 +185,15 @@ int  ccb_anchor_get_info(const ccb_handle* h, ccb_anchor_info* info);
 int  ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended);
 int  ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers,
                        uint16_t** final5, uint16_t** rows);
+/* CuClarkDB::malloc with its own result layout (src/CuClarkDB.cu:322-421): ONE pinned final-result array of
+ * num_reads x 5 u16 (and, when extended, ONE full-result array of num_reads x (2*max_hits+2) u16) for the whole file;
+ * slot b (= batch b, n_batches == ccb_config.n_slots) delivers its results at row index_batches[b]
+ * (h_resultsFinal[i] = _finalResults + rowSize * _indexBatches[i], :412-416), so the reference's print loop
+ * (src/CuCLARK_hh.hh:2096-2118) indexes by global read number unchanged.  full_results may be NULL.  The arrays
+ * belong to the library (ccb_batch_free); ccb_batch_buffers still hands out the slots' input buffers. */
+int  ccb_batch_alloc_ref(ccb_handle* h, uint64_t num_reads, uint32_t max_reads, uint64_t max_containers,
+                         const uint64_t* index_batches, int n_batches, int extended,
+                         uint16_t** full_results, uint16_t** final_results);
 /* CuClarkDB::readyBatch + queryBatch (src/CuClarkDB.cu:821-828, 836-987):
  * async H2D, query, D2H on the slot's stream; returns immediately. */
 int  ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint64_t n_containers, int flags);
@@ -231,8 +239,8 @@ int  ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, int mode, 
 int  ccb_device_count(void);
 int  ccb_batch_slots(const ccb_handle* h);
 
-/* cudaLimitMaxL2FetchGranularity in effect on the handle's device (ccb_create asks for 32 B so
- * that a probe costs one DRAM sector, not a 128-byte line; env CCB_L2_FETCH=0|32|64|128 overrides) */
+/* cudaLimitMaxL2FetchGranularity in effect on the handle's device (left at the driver's default;
+ * env CCB_L2_FETCH=32|64|128 sets it for measurements -- it changes nothing on B200) */
 int  ccb_l2_fetch_granularity(const ccb_handle* h);
 
 /* library / build identification, e.g. "cuclark_b200 0.1 sm_100a" */

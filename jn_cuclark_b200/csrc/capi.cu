@@ -60,16 +60,13 @@ extern "C" int ccb_create(const ccb_config* cfg, ccb_handle** out)
         ccb_fail(nullptr, -6, "cannot initialise CUDA device %d: %s", cfg->device, cudaGetErrorString(cudaGetLastError()));
         delete h; return -6;
     }
-    // A probe touches ONE 32-byte sector of a random line; by default the L2 fills the whole
-    // 128-byte line from HBM on a miss (ncu r01: 4.0 DRAM sectors per requested sector), which
-    // makes DRAM bytes, not lookups, the bound.  Ask for sector-granular fills.
+    // cudaLimitMaxL2FetchGranularity is left alone: it was measured to change nothing on this part (every L2 miss
+    // fills the whole 128-byte line whatever the limit says).  CCB_L2_FETCH=32|64|128 still sets
+    // it for measurements; the limit is device-wide, so a library should not touch it unasked.
     {
-        size_t want = 32;
-        if (const char* e = getenv("CCB_L2_FETCH")) want = (size_t)atoi(e);
-        if (want) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, want);
+        if (const char* e = getenv("CCB_L2_FETCH")) { const size_t want = (size_t)atoi(e); if (want) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, want); }
         size_t got = 0; cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
         h->l2_fetch = (int)got;
-        if (h->cfg.verbose) fprintf(stderr, "L2 fetch granularity: %zu B\n", got);
         cudaGetLastError();
     }
     *out = h;
@@ -91,7 +88,8 @@ static void free_slots(ccb_handle* h)
 {
     for (Slot& s : h->slots) {
         if (s.stream) cudaStreamSynchronize(s.stream);
-        cudaFreeHost(s.h_offsets); cudaFreeHost(s.h_cont); cudaFreeHost(s.h_final5); cudaFreeHost(s.h_rows);
+        cudaFreeHost(s.h_offsets); cudaFreeHost(s.h_cont);
+        if (!s.shared_results) { cudaFreeHost(s.h_final5); cudaFreeHost(s.h_rows); }
         cudaFreeHost(s.h_ovf_count); cudaFreeHost(s.h_stats);
         cudaFree(s.d_offsets); cudaFree(s.d_cont); cudaFree(s.d_final5); cudaFree(s.d_rows);
         cudaFree(s.d_ovf_list); cudaFree(s.d_ovf_count); cudaFree(s.d_dense_scratch); cudaFree(s.d_stats);
@@ -99,6 +97,7 @@ static void free_slots(ccb_handle* h)
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     h->slots.clear();
+    cudaFreeHost(h->ref_final); cudaFreeHost(h->ref_full); h->ref_final = h->ref_full = nullptr;
     cudaGetLastError();
 }
 
@@ -329,15 +328,42 @@ extern "C" int ccb_batch_free(ccb_handle* h)
     return 0;
 }
 
+static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended,
+                       uint64_t num_reads, const uint64_t* index_batches);
+
 extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended)
+{
+    return batch_alloc(h, max_reads, max_containers, extended, 0, nullptr);
+}
+
+extern "C" int ccb_batch_alloc_ref(ccb_handle* h, uint64_t num_reads, uint32_t max_reads, uint64_t max_containers,
+                                   const uint64_t* index_batches, int n_batches, int extended,
+                                   uint16_t** full_results, uint16_t** final_results)
+{
+    if (!h || !index_batches || !final_results) return ccb_fail(h, -1, "ccb_batch_alloc_ref: null argument");
+    if (n_batches != h->cfg.n_slots) return ccb_fail(h, -35, "ccb_batch_alloc_ref: %d batches but the handle was created with %d slots", n_batches, h->cfg.n_slots);
+    for (int b = 0; b < n_batches; b++)
+        if (index_batches[b] > num_reads) return ccb_fail(h, -36, "ccb_batch_alloc_ref: batch %d starts at read %llu of %llu", b, (unsigned long long)index_batches[b], (unsigned long long)num_reads);
+    const int rc = batch_alloc(h, max_reads, max_containers, extended, num_reads ? num_reads : 1, index_batches);
+    if (rc) return rc;
+    *final_results = h->ref_final;
+    if (full_results) *full_results = h->ref_full;
+    return 0;
+}
+
+// index_batches == NULL: every slot owns its result buffers (ccb_batch_alloc).  Otherwise (ccb_batch_alloc_ref) slot b's
+// results land at row index_batches[b] of one contiguous array of num_reads rows, the way CuClarkDB::malloc lays
+// h_resultsFinal[i] = _finalResults + rowSize * _indexBatches[i] (src/CuClarkDB.cu:412-416).
+static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended,
+                       uint64_t num_reads, const uint64_t* index_batches)
 {
     if (!h) return -1;
     USE_DEV(h);
     if (max_containers > 0xFFFFFFFFull)
         return ccb_fail(h, -30, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>).");  // CuCLARK_hh.hh:1709-1713
     // slots that are large enough are kept (the next file of a list; pinning and unpinning 250 MB costs ~0.1 s each)
-    if (!h->slots.empty() && (int)h->slots.size() == h->cfg.n_slots && h->max_reads >= max_reads && h->max_cont >= max_containers &&
-        h->batch_extended == (extended != 0)) {
+    if (!index_batches && !h->ref_final && !h->slots.empty() && (int)h->slots.size() == h->cfg.n_slots && h->max_reads >= max_reads &&
+        h->max_cont >= max_containers && h->batch_extended == (extended != 0)) {
         bool idle = true;
         for (const Slot& s : h->slots) idle = idle && !s.in_flight;
         if (idle) return 0;
@@ -347,18 +373,32 @@ extern "C" int ccb_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_c
     h->slots.resize((size_t)h->cfg.n_slots);
     const size_t so = ((size_t)max_reads + 1) * 4, sc = (size_t)(max_containers ? max_containers : 1) * 2,
                  sf = (size_t)(max_reads ? max_reads : 1) * 10, sr = (size_t)(max_reads ? max_reads : 1) * h->row_stride * 2;
+    if (index_batches) {
+        cudaError_t e = cudaMallocHost(&h->ref_final, (size_t)num_reads * 10);
+        if (e == cudaSuccess && extended) e = cudaMallocHost(&h->ref_full, (size_t)num_reads * h->row_stride * 2);
+        if (e != cudaSuccess) { free_slots(h); return ccb_fail(h, (int)e, "result allocation failed: %s", cudaGetErrorString(e)); }
+    }
+    size_t slot_no = 0;
     for (Slot& s : h->slots) {
         cudaError_t e = cudaSuccess;
         auto ok = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
         ok(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         ok(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming | cudaEventBlockingSync));
-        ok(cudaMallocHost(&s.h_offsets, so)); ok(cudaMallocHost(&s.h_cont, sc)); ok(cudaMallocHost(&s.h_final5, sf));
+        ok(cudaMallocHost(&s.h_offsets, so)); ok(cudaMallocHost(&s.h_cont, sc));
+        if (index_batches) {
+            s.shared_results = true;
+            s.h_final5 = h->ref_final + 5 * index_batches[slot_no];
+            if (extended) s.h_rows = h->ref_full + (size_t)h->row_stride * index_batches[slot_no];
+        } else {
+            ok(cudaMallocHost(&s.h_final5, sf));
+        }
+        slot_no++;
         ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 16));
         ok(cudaMalloc(&s.d_offsets, so)); ok(cudaMalloc(&s.d_cont, sc)); ok(cudaMalloc(&s.d_final5, sf));
         ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 8)); ok(cudaMalloc(&s.d_ovf_count, 8));   // [overflow list | redo list]
         ok(cudaMalloc(&s.d_dense_scratch, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
         ok(cudaMalloc(&s.d_stats, 16));
-        if (extended) { ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
+        if (extended) { if (!index_batches) ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
         if (e != cudaSuccess) {
             free_slots(h);
             if (e == cudaErrorMemoryAllocation)   // src/CuClarkDB.cu:65-73

@@ -24,6 +24,7 @@ struct Slot {
     uint32_t* h_ovf_count = nullptr;           // pinned
     unsigned long long* h_stats = nullptr;     // pinned
     bool      in_flight = false;
+    bool      shared_results = false;          // h_final5 / h_rows point into the handle's contiguous result arrays
     uint32_t  n_reads = 0;
     int       flags = 0;
 };
@@ -52,6 +53,8 @@ struct ccb_handle {
     cudaStream_t db_stream = nullptr;
     std::vector<ccb::Slot> slots;
     uint32_t   max_reads = 0; uint64_t max_cont = 0; bool batch_extended = false;
+    // ccb_batch_alloc_ref: ONE pinned final / full result array for all reads of a file, as CuClarkDB::malloc hands out
+    uint16_t*  ref_final = nullptr; uint16_t* ref_full = nullptr;
     int        row_stride = 0;
     ccb_stats  stats{};
     uint64_t   tombstones = 0; uint32_t max_disp = 0;

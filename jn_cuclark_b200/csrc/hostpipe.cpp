@@ -286,7 +286,9 @@ size_t pack_bound(const ReadSet& r, size_t first, size_t count, int k)
     for (size_t i = first; i < first + count; i++) {
         if (r.len[i] < (uint64_t)k) continue;
         size_t b = (size_t)(r.seq_e[i] - r.seq_s[i]);
-        tot += b / 8 + b / (size_t)k + 4 + (b / kMaxPart) * 8;
+        // bytes/8 containers, two more u16 per kept part (header + rounding); a part is at least k bases and one
+        // separator long -- the same worst case as spec_containers()
+        tot += b / 8 + 2 * (b / (size_t)(k + 1) + 1) + 4 + (b / kMaxPart) * 8;
     }
     return tot + 8;
 }

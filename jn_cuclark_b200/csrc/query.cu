@@ -430,7 +430,7 @@ k_query_dense(const TableView t, const QueryArgs a, const uint32_t* read_list, c
             for (int j = threadIdx.x; j + k <= len; j += blockDim.x) {
                 uint64_t x = kmer_at(data, j, k, t.hp.mask);
                 uint32_t lab = lookup(t, canonical(x, k));
-                if (lab != kLabelNone) atomicAdd(cnt + lab, 1u);
+                if (lab != kLabelNone && lab < n_targets) atomicAdd(cnt + lab, 1u);   // a label the handle was not sized for is ignored
             }
         }
         __syncthreads();

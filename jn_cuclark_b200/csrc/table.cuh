@@ -32,11 +32,27 @@ struct TableView {
 
 struct alignas(32) Bucket { uint64_t e[4]; };
 
+// One 256-bit read-only load = one 32-byte sector.  Without a size hint an L2 miss fills the whole 128-byte line
+// from HBM (126 B of DRAM reads per probe, ncu); with .L2::64B it fills 64 bytes (63 B per probe) at the same
+// request rate -- profiles/r02_probe_fill_ncu.csv, DESIGN.md section 3.  CCB_LD_HINT: 0 none, 64, 128, 256.
+#ifndef CCB_LD_HINT
+#define CCB_LD_HINT 64
+#endif
 __device__ __forceinline__ void load_bucket(const ulonglong4* p, uint64_t (&e)[4])
 {
-    // one 256-bit read-only load = one 32-byte sector
+#if CCB_LD_HINT == 64
+    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+#elif CCB_LD_HINT == 128
+    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+#elif CCB_LD_HINT == 256
+    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+#else
     asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+#endif
 }
 
 // Match the 4 entries of a bucket against q = key48 << 16.

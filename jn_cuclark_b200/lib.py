@@ -15,14 +15,15 @@ import os
 
 import numpy as np
 
-CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_LANE_KERNEL, CCB_WARP_KERNEL = 1, 2, 4, 8, 16, 32
+CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_WARP_KERNEL = 1, 2, 4, 8, 32
 default_flags = 0          # ORed into every query (tests run the parity suite once per kernel with it)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 def lib_path() -> str:
-    return os.path.join(_HERE, "libcuclark_b200.so")
+    # CCB_LIBRARY: a variant build of the same library (measurements: `make -C jn_cuclark_b200 VARIANT=...`)
+    return os.environ.get("CCB_LIBRARY") or os.path.join(_HERE, "libcuclark_b200.so")
 
 
 class CcbError(RuntimeError):
@@ -91,6 +92,8 @@ SYMBOLS = {
     "ccb_anchor_drop": (C.c_int, [_H]),
     "ccb_anchor_get_info": (C.c_int, [_H, C.POINTER(AnchorInfo)]),
     "ccb_batch_alloc": (C.c_int, [_H, C.c_uint32, C.c_uint64, C.c_int]),
+    "ccb_batch_alloc_ref": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, C.c_int,
+                                      C.POINTER(_VP), C.POINTER(_VP)]),
     "ccb_batch_buffers": (C.c_int, [_H, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
     "ccb_batch_submit": (C.c_int, [_H, C.c_int, C.c_uint32, C.c_uint64, C.c_int]),
     "ccb_batch_wait": (C.c_int, [_H, C.c_int]),
@@ -224,6 +227,18 @@ class CuClarkDB:
         """CuClarkDB::malloc (src/CuClarkDB.cu:322): library-owned pinned buffers."""
         self._ck(self._lib.ccb_batch_alloc(self._h, maxReads, maxContainers, int(isExtended)))
         self._max_reads, self._max_cont, self._ext = maxReads, maxContainers, isExtended
+
+    def malloc_ref(self, numReads: int, maxReads: int, maxContainers: int, indexBatches, isExtended: bool = False):
+        """CuClarkDB::malloc with the reference's result layout (src/CuClarkDB.cu:322-421): one contiguous final (and
+        full) result array for all numReads reads; batch b delivers at row indexBatches[b].  Returns (final5, rows|None)."""
+        idx = (C.c_uint64 * len(indexBatches))(*[int(x) for x in indexBatches])
+        full, fin = _VP(), _VP()
+        self._ck(self._lib.ccb_batch_alloc_ref(self._h, numReads, maxReads, maxContainers, idx, len(indexBatches), int(isExtended),
+                                               C.byref(full), C.byref(fin)))
+        self._max_reads, self._max_cont, self._ext = maxReads, maxContainers, isExtended
+        f = _np_view(fin.value, numReads * 5, np.uint16).reshape(-1, 5)
+        r = _np_view(full.value, numReads * self.row_stride, np.uint16).reshape(-1, self.row_stride) if (isExtended and full.value) else None
+        return f, r
 
     def buffers(self, batchId: int):
         """(offsets u32[maxReads+1], containers u16[maxContainers], final5 u16[maxReads,5], rows|None)"""

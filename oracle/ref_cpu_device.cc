@@ -2,9 +2,9 @@
  * ref_cpu_device.cc -- CPU stand-in for the reference's device layer
  * (test infrastructure, NOT product code).
  *
- * The reference's GPU binaries, compiled for sm_100, hang on a B200 (see
- * tests/golden/ref_gpu/README.md), so golden CSVs cannot come from them.  This
- * file defines the member functions of the reference's `class CuClarkDB<HKMERr>`
+ * The reference's GPU binaries need a B200 (and, there, a number of targets that is a
+ * multiple of 32: tests/golden/ref_gpu/README.md); their CSVs are the ref_gpu goldens.
+ * For everything that can be pinned WITHOUT a GPU this file defines the member functions of the reference's `class CuClarkDB<HKMERr>`
  * -- declared in the reference's own, unmodified src/CuClarkDB.cuh -- on the CPU,
  * so that the reference's UNMODIFIED host engine (src/main.cc, src/CuCLARK_hh.hh,
  * src/file.cc, ...: flag parsing, targets, DB build/load decision, read indexing,

@@ -74,7 +74,7 @@ def test_flag_values_match_the_header():
     h = open(os.path.join(ROOT, "include", "cuclark_b200.h")).read()
     h = re.sub(r"/\*.*?\*/", "", h, flags=re.S)
     flags = dict((n, int(v)) for n, v in re.findall(r"\b(CCB_[A-Z_]+)\s*=\s*(\d+)", h))
-    assert {"CCB_EXTENDED", "CCB_STATS", "CCB_FORCE_DENSE", "CCB_NO_ANCHOR", "CCB_LANE_KERNEL", "CCB_WARP_KERNEL"} <= set(flags)
+    assert {"CCB_EXTENDED", "CCB_STATS", "CCB_FORCE_DENSE", "CCB_NO_ANCHOR", "CCB_WARP_KERNEL"} <= set(flags)
     for n, v in flags.items():
         assert getattr(lib, n) == v, n
 

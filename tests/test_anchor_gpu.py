@@ -61,7 +61,7 @@ def test_lane_kernel_on_files_with_quirks(small_world, oracle, fname, tmp_path):
     """Short reads, N runs (several parts), reads shorter than k, lower case, paired reads joined by N: the
     thread-per-read kernel takes what it can and hands the rest back; u16[5] and sparse rows equal the oracle's."""
     import os
-    from jn_cuclark_b200 import CuClarkDB, CCB_LANE_KERNEL, CCB_STATS
+    from jn_cuclark_b200 import CuClarkDB, CCB_STATS
     odb = oracle.OracleDb.build(small_world["targets"], 31, 1000003)
     if fname == "pairs":
         m = str(tmp_path / "m.fa")
@@ -76,7 +76,7 @@ def test_lane_kernel_on_files_with_quirks(small_world, oracle, fname, tmp_path):
     c, l = odb.pairs()
     db.load_pairs(c, l)
     before = db.stats().lookups
-    got, rows = db.classify_packed(off, cont, extended=True, flags=CCB_LANE_KERNEL | CCB_STATS)
+    got, rows = db.classify_packed(off, cont, extended=True, flags=CCB_STATS)
     assert db.stats().lookups - before == nl
     db.close()
     assert np.array_equal(got, want)
@@ -87,7 +87,7 @@ def test_lane_kernel_on_files_with_quirks(small_world, oracle, fname, tmp_path):
 
 def test_lane_kernel_many_targets_goes_back_to_warp_kernel(oracle, tmp_path):
     import synth
-    from jn_cuclark_b200 import CuClarkDB, CCB_LANE_KERNEL
+    from jn_cuclark_b200 import CuClarkDB
     tp, genomes, _ = synth.make_genomes(str(tmp_path / "g"), 48, 6000, seed=5, shared=False, quirks=False, same_label_pair=False)
     odb = oracle.OracleDb.build(tp, 31, 1000003)
     reads = [("five", np.concatenate([g[100:136] for g in genomes[:5]])),            # 5 targets in 180 bases
@@ -101,7 +101,7 @@ def test_lane_kernel_many_targets_goes_back_to_warp_kernel(oracle, tmp_path):
     db = CuClarkDB(1, 31, 1, len(odb.labels))
     c, l = odb.pairs()
     db.load_pairs(c, l)
-    got, _ = db.classify_packed(off, cont, flags=CCB_LANE_KERNEL)
+    got, _ = db.classify_packed(off, cont)
     db.close()
     assert np.array_equal(got, want)
 

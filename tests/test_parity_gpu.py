@@ -213,3 +213,39 @@ def test_synthetic_workload_matches_oracle(oracle):
     assert 0.85 < frac_hit < 0.95                      # 90 % of reads come from a genome
     db.device_free(d_off); db.device_free(d_cont)
     db.close()
+
+
+@pytest.mark.parametrize("extended", [False, True])
+def test_malloc_ref_contiguous_results(small_world, oracle, full_db, extended):
+    """ccb_batch_alloc_ref = CuClarkDB::malloc's own result layout (src/CuClarkDB.cu:412-416): the batches of a file
+    deliver into ONE final / full result array at row indexBatches[b], in any submission order."""
+    from jn_cuclark_b200 import CuClarkDB
+    ir = _reads(small_world, "reads.fa", oracle)
+    off, cont = ir.pack(31)
+    n = off.size - 1
+    want, wrows, _ = full_db.query_packed(31, off, cont, row_stride=32)
+    nb = 3
+    db = CuClarkDB(1, 31, nb, len(full_db.labels))
+    c, l = full_db.pairs()
+    db.load_pairs(c, l)
+    index = [0, n // 5, n // 2]                       # uneven batches
+    ends = index[1:] + [n]
+    max_reads = max(e - s for s, e in zip(index, ends))
+    max_cont = max(int(off[e]) - int(off[s]) for s, e in zip(index, ends))
+    fin, rows = db.malloc_ref(n, max_reads, max_cont, index, extended)
+    for b in (2, 0, 1):
+        s, e = index[b], ends[b]
+        o, cc, _, _ = db.buffers(b)
+        o[: e - s + 1] = off[s:e + 1] - off[s]
+        cc[: int(off[e]) - int(off[s])] = cont[int(off[s]):int(off[e])]
+        db.readyBatch(b, e - s, int(off[e]) - int(off[s]))
+        db.queryBatch(b, extended)
+    for b in range(nb):
+        db.waitForBatch(b)
+    assert np.array_equal(fin, want)
+    if extended:
+        cnt = wrows[:, 0].astype(int)
+        for i in range(n):
+            assert rows[i, 0] == cnt[i] and np.array_equal(rows[i, 1:1 + 2 * cnt[i]], wrows[i, 1:1 + 2 * cnt[i]])
+    db.freeBatchMemory()
+    db.close()
