@@ -129,27 +129,54 @@ int  ccb_shard_route(ccb_handle* h, const void* d_offsets, const void* d_contain
 int  ccb_shard_probe(ccb_handle* h, const void* d_hashes, uint64_t n, void* d_labels, void* d_stats, void* stream);
 int  ccb_shard_vote(ccb_handle* h, uint32_t n_reads, int n_shards, const void* d_pos, const uint64_t* seg_base,
                     const void* const* src, void* d_final5, void* d_rows, void* stream);
-/* Peer exchange -- the same phases with NVLink stores instead of a collective and no host round trip:
- * seg_base == NULL in ccb_shard_route / ccb_shard_vote means "segment g starts at d_pos[g*n_reads]",
- * read on the device.
- *   ccb_shard_route_peer   dst[g] = this rank's region (cap k-mers) of owner g's inbox, mapped here;
- *                          afterwards *count_dst[g] (u64 in owner g's memory) = k-mers sent to g.
- *                          More than cap k-mers for one owner: the excess is dropped, *d_error (u32) = 1
+/* Peer exchange -- NVLink stores instead of a collective and no host round trip (route side: ccb_shard_route2 below):
  *   ccb_shard_probe_inbox  inbox = n_shards regions of cap k-mers, region s holds d_counts_in[s] (u64) k-mers
  *                          from rank s; the label of inbox[s][i] is stored at lab_dst[s][i] (rank s's memory)
  *   ccb_device_alloc / ccb_ipc_export / ccb_ipc_open / ccb_ipc_close
  *                          buffers another process may map (cudaIpc*; 64-byte handles)
  * A barrier across the ranks (any stream-ordered one, e.g. an NCCL all-reduce of one word) must separate
- * route_peer from probe_inbox and probe_inbox from vote. */
-int  ccb_shard_route_peer(ccb_handle* h, const void* d_offsets, const void* d_containers, uint32_t n_reads,
-                          int n_shards, const void* d_pos, void* const* dst, uint64_t cap,
-                          void* const* count_dst, void* d_error, void* stream);
+ * the route from probe_inbox and probe_inbox from the vote. */
 int  ccb_shard_probe_inbox(ccb_handle* h, int n_shards, const void* d_inbox, uint64_t cap, const void* d_counts_in,
                            void* const* lab_dst, void* d_stats, void* stream);
+/* One-pass pipeline (the product path of the sharded mode; the calls above remain for callers that want every
+ * (read, owner) pair in its own segment).  A block of 256 reads shares one contiguous segment per owner, reserved
+ * with one atomic on a cursor in the requester's memory, so the reads are walked once and no scan is needed; reads
+ * the block kernel does not take (three or more parts, parts over 192 bases) follow behind through count/route.
+ *   ccb_shardws_create   device scratch of ONE batch in flight: max_reads reads, n_shards regions of cap k-mers
+ *   ccb_shard_route2     dst[g] = this requester's region of owner g (cap x u64: a local send segment or a peer's
+ *                        inbox), count_dst[g] = where owner g reads how many k-mers it got (u64, owner's memory
+ *                        or local); n_containers = u16 units of the batch (-1 unknown).  More than cap k-mers for
+ *                        one owner: the excess is dropped and the workspace's error word set (ccb_shardws_error)
+ *   ccb_shard_probe_inbox / ccb_shard_probe   owner side, unchanged: labels come back at the same indices
+ *   ccb_shard_vote2      src[g] = labels of region g (cap x u16); writes u16[5] per read (+ rows)
+ * The same stream-ordered barriers as above separate route2 from the probe and the probe from vote2. */
+typedef struct ccb_shardws ccb_shardws;
+int  ccb_shardws_create(ccb_handle* h, uint32_t max_reads, int n_shards, uint64_t cap, ccb_shardws** out);
+void ccb_shardws_destroy(ccb_handle* h, ccb_shardws* ws);
+int  ccb_shardws_error(ccb_handle* h, ccb_shardws* ws, void* stream, int* out);
+int  ccb_shard_route2(ccb_handle* h, ccb_shardws* ws, const void* d_offsets, const void* d_containers, uint32_t n_reads,
+                      int64_t n_containers, void* const* dst, void* const* count_dst, void* stream);
+int  ccb_shard_vote2(ccb_handle* h, ccb_shardws* ws, uint32_t n_reads, const void* const* src, void* d_final5, void* d_rows,
+                     void* stream);
 int  ccb_device_alloc(ccb_handle* h, uint64_t bytes, void** ptr);
 int  ccb_ipc_export(ccb_handle* h, void* ptr, unsigned char out[64]);
 int  ccb_ipc_open(ccb_handle* h, const unsigned char in[64], void** ptr);
 int  ccb_ipc_close(ccb_handle* h, void* ptr);
+
+/* Device group: ONE process, n_devices GPUs, the table sharded over them (shard g on devices[g]) -- what
+ * bin/cuCLARK --sharded (or a database that does not fit one GPU) uses in place of the reference's part swapping.
+ * ccb_group_create returns a LEADER handle; on it ccb_db_load_files loads every shard, and ccb_batch_alloc /
+ * ccb_batch_buffers / ccb_batch_submit / ccb_batch_wait / ccb_batch_poll / ccb_batch_free / ccb_sync / ccb_destroy work as
+ * on a one-device handle: slot s is homed on devices[s mod n]; its k-mers travel to the owners' inboxes and the labels
+ * back through peer mappings (NVLink), the stages chained by events, nothing synchronised on the host in between.
+ * cfg->device is ignored.  The devices must be able to map each other's memory (a device may be listed more than
+ * once: several shards then share it -- tests on a one-GPU box).  Results are identical to a
+ * one-device handle holding the whole table.  A batch whose k-mers for one owner exceed the exchange region fails
+ * in ccb_batch_wait with the reference's "increase the number of batches" message (nothing is read or written out of
+ * bounds).  Not available on a leader: ccb_query_device, ccb_batch_alloc_ref, the anchor index, ccb_build_*. */
+int  ccb_group_create(const int* devices, int n_devices, const ccb_config* cfg, ccb_handle** out);
+int  ccb_group_size(const ccb_handle* h);                 /* 0 for an ordinary handle */
+ccb_handle* ccb_group_member(ccb_handle* h, int i);       /* the handle that holds shard i (owned by the leader) */
 
 /* Anchor index (no counterpart in the reference; results are unchanged by it).  The target sequences
  * themselves are kept on the device (both strands, 2 bits per base) with one bit per position saying
@@ -237,6 +264,8 @@ int  ccb_bench_gather_ex(ccb_handle* h, uint64_t n_probes, int bytes, int mode, 
 
 /* number of CUDA devices visible (0 when there is none or no driver); slots of a handle */
 int  ccb_device_count(void);
+/* free and total bytes of a device's memory (cudaMemGetInfo); 0 = ok */
+int  ccb_device_memory(int device, uint64_t* free_bytes, uint64_t* total_bytes);
 int  ccb_batch_slots(const ccb_handle* h);
 
 /* cudaLimitMaxL2FetchGranularity in effect on the handle's device (left at the driver's default;

@@ -261,6 +261,7 @@ extern "C" int ccb_anchor_drop(ccb_handle* h)
 {
     if (!h) return -1;
     USE_DEV(h);
+    anchor_build_free(h);                        // texts collected so far, if a build was under way
     anchor_free(h->anchor);
     return 0;
 }

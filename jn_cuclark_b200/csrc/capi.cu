@@ -80,6 +80,15 @@ extern "C" int ccb_device_count(void)
     return n;
 }
 
+extern "C" int ccb_device_memory(int device, uint64_t* free_bytes, uint64_t* total_bytes)
+{
+    size_t f = 0, t = 0;
+    if (cudaSetDevice(device) != cudaSuccess || cudaMemGetInfo(&f, &t) != cudaSuccess) { cudaGetLastError(); return -1; }
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+    return 0;
+}
+
 extern "C" int ccb_batch_slots(const ccb_handle* h) { return h ? h->cfg.n_slots : 0; }
 
 extern "C" int ccb_l2_fetch_granularity(const ccb_handle* h) { return h ? h->l2_fetch : -1; }
@@ -104,6 +113,7 @@ static void free_slots(ccb_handle* h)
 extern "C" void ccb_destroy(ccb_handle* h)
 {
     if (!h) return;
+    if (h->group) group_destroy(h);
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     free_slots(h);
@@ -187,6 +197,7 @@ extern "C" int ccb_db_end(ccb_handle* h)
 
 extern "C" int ccb_db_get_info(const ccb_handle* h, ccb_db_info* info)
 {
+    if (h && h->group && info) return group_db_get_info(h, info);
     if (!h || !info || !h->db_ready) return -1;
     info->entries = h->table.n_inserted; info->buckets = h->table.nb; info->bytes = h->table.bytes();
     info->tombstones = h->tombstones; info->max_displacement = h->max_disp;
@@ -200,6 +211,7 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
                                  unsigned sampling, uint64_t* n_loaded)
 {
     if (!h || !prefix) return -1;
+    if (h->group) return group_db_load_files(h, prefix, htsize, key_bytes, sampling, n_loaded);
     USE_DEV(h);
     if (key_bytes != 2 && key_bytes != 4 && key_bytes != 8) return ccb_fail(h, -2, "key_bytes must be 2, 4 or 8");
     std::string p = prefix;
@@ -322,6 +334,7 @@ extern "C" int ccb_db_load_files(ccb_handle* h, const char* prefix, uint64_t hts
 extern "C" int ccb_batch_free(ccb_handle* h)
 {
     if (!h) return -1;
+    if (h->group) return group_batch_free(h);
     cudaSetDevice(h->cfg.device);
     free_slots(h);
     h->max_reads = 0; h->max_cont = 0;
@@ -341,6 +354,7 @@ extern "C" int ccb_batch_alloc_ref(ccb_handle* h, uint64_t num_reads, uint32_t m
                                    uint16_t** full_results, uint16_t** final_results)
 {
     if (!h || !index_batches || !final_results) return ccb_fail(h, -1, "ccb_batch_alloc_ref: null argument");
+    if (h->group) return ccb_fail(h, -37, "ccb_batch_alloc_ref: not on a device group");
     if (n_batches != h->cfg.n_slots) return ccb_fail(h, -35, "ccb_batch_alloc_ref: %d batches but the handle was created with %d slots", n_batches, h->cfg.n_slots);
     for (int b = 0; b < n_batches; b++)
         if (index_batches[b] > num_reads) return ccb_fail(h, -36, "ccb_batch_alloc_ref: batch %d starts at read %llu of %llu", b, (unsigned long long)index_batches[b], (unsigned long long)num_reads);
@@ -358,6 +372,7 @@ static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_container
                        uint64_t num_reads, const uint64_t* index_batches)
 {
     if (!h) return -1;
+    if (h->group) return group_batch_alloc(h, max_reads, max_containers, extended);
     USE_DEV(h);
     if (max_containers > 0xFFFFFFFFull)
         return ccb_fail(h, -30, "ERROR: Batch overflow. Please increase the number of batches (-b <numberofbatches>).");  // CuCLARK_hh.hh:1709-1713
@@ -413,6 +428,7 @@ static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_container
 extern "C" int ccb_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers,
                                  uint16_t** final5, uint16_t** rows)
 {
+    if (h && h->group) return group_batch_buffers(h, slot, offsets, containers, final5, rows);
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     Slot& s = h->slots[(size_t)slot];
     if (offsets) *offsets = s.h_offsets;
@@ -461,6 +477,7 @@ static int run_query(ccb_handle* h, const QueryArgs& a0, uint32_t* ovf_list, uin
 
 extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint64_t n_containers, int flags)
 {
+    if (h && h->group) return group_batch_submit(h, slot, n_reads, n_containers, flags);
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
     if (h->n_shards > 1) return ccb_fail(h, -63, "this handle holds one shard of the table: use the ccb_shard_* calls");
@@ -500,6 +517,7 @@ static void harvest(ccb_handle* h, Slot& s)
 
 extern "C" int ccb_batch_wait(ccb_handle* h, int slot)
 {
+    if (h && h->group) return group_batch_wait(h, slot);
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     Slot& s = h->slots[(size_t)slot];
     if (!s.in_flight) return 0;
@@ -511,6 +529,7 @@ extern "C" int ccb_batch_wait(ccb_handle* h, int slot)
 
 extern "C" int ccb_batch_poll(ccb_handle* h, int slot)
 {
+    if (h && h->group) return group_batch_poll(h, slot);
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return ccb_fail(h, -31, "bad slot %d", slot);
     Slot& s = h->slots[(size_t)slot];
     if (!s.in_flight) return 0;
@@ -524,6 +543,7 @@ extern "C" int ccb_batch_poll(ccb_handle* h, int slot)
 extern "C" int ccb_sync(ccb_handle* h)
 {
     if (!h) return -1;
+    if (h->group) return group_sync(h);
     USE_DEV(h);
     CU(h, cudaDeviceSynchronize());
     return 0;
@@ -535,6 +555,7 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
 {
     if (!h) return -1;
     if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    if (h->group) return ccb_fail(h, -63, "this handle leads a device group: use the ccb_batch_* calls");
     if (h->n_shards > 1) return ccb_fail(h, -63, "this handle holds one shard of the table: use the ccb_shard_* calls");
     USE_DEV(h);
     if (h->q_ovf_cap < n_reads || !h->q_ovf_list) {

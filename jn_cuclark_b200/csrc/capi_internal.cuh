@@ -43,6 +43,18 @@ void anchor_free(Anchor& a);
 struct AnchorBuild;                  // anchor.cu: target texts being collected (ccb_anchor_begin .. ccb_anchor_end)
 void anchor_build_free(ccb_handle* h);
 struct BuildState;                   // dbbuild.cu
+// group.cu: several devices, one sharded table, behind one leader handle
+struct Group;
+void group_destroy(ccb_handle* h);
+int  group_db_load_files(ccb_handle* h, const char* prefix, uint64_t htsize, int key_bytes, unsigned sampling, uint64_t* n_loaded);
+int  group_db_get_info(const ccb_handle* h, ccb_db_info* info);
+int  group_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers, int extended);
+int  group_batch_buffers(ccb_handle* h, int slot, uint32_t** offsets, uint16_t** containers, uint16_t** final5, uint16_t** rows);
+int  group_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint64_t n_containers, int flags);
+int  group_batch_wait(ccb_handle* h, int slot);
+int  group_batch_poll(ccb_handle* h, int slot);
+int  group_batch_free(ccb_handle* h);
+int  group_sync(ccb_handle* h);
 
 }  // namespace ccb
 
@@ -71,6 +83,7 @@ struct ccb_handle {
     struct ShardScratch { void* stream = nullptr; bool used = false; void* scan_tmp = nullptr; size_t scan_bytes = 0;
                           uint32_t* ovf_list = nullptr; uint32_t ovf_cap = 0; uint32_t* ovf_count = nullptr; uint32_t* dense = nullptr; };
     ShardScratch shard_scratch[4];
+    ccb::Group* group = nullptr;     // leader of a device group (ccb_group_create): the batch calls go to group.cu
     ccb::Anchor anchor;              // optional: sequences + sampled k-mer positions in front of the table
     ccb::AnchorBuild* anchor_build = nullptr;
     // database construction in progress (ccb_build_*)

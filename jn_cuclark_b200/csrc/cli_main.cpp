@@ -18,6 +18,7 @@
 #include <sys/stat.h>
 #include <sys/time.h>
 #include <unistd.h>
+#include <zlib.h>
 
 #include <algorithm>
 #include <atomic>
@@ -68,6 +69,9 @@ static void printUsage()
     cout << "-s <factor>,         \t sampling factor value (for CuCLARK only).\n";
     cout << "--extended,          \t extended output (one column of hit counts per target).\n";
     cout << "--verbose,           \t progress messages.\n";
+    cout << "--gzipped,           \t the objects are gzip files (inflated in memory; classify_metagenome.sh strips the flag and gunzips itself).\n";
+    cout << "--sharded,           \t with -d N: ONE copy of the database, cut into N shards over the N devices (k-mers travel over NVLink),\n";
+    cout << "                     \t instead of N copies; chosen automatically when a copy does not fit a device's memory.\n";
     cout << "\n";
     cout << "--help,              \t to print help/options.\n";
     cout << "--version,           \t to print the version info.\n";
@@ -145,7 +149,7 @@ static void read_targets(const char* path, Targets& t)
 struct Cli {
     size_t k = 31, cpu = 1, iterKmers = 0, batches = 1, devices = 0;
     unsigned minT = 0, sfactor = 1;
-    bool tsk = false, ext = false, verbose = false;
+    bool tsk = false, ext = false, verbose = false, sharded = false, gzipped = false;
     const char *targets = NULL, *folder = NULL, *objects = NULL, *objects2 = NULL, *results = NULL;
 };
 
@@ -156,13 +160,51 @@ struct Engine {
     int key_bytes = 4;
     string dbname;
 
+    bool sharded = false;          // one table cut over the devices (ccb_group_create) instead of a copy per device
+
+    // k-mers of the database on disk (0 when it is still to be built)
+    uint64_t db_kmers() const
+    {
+        struct stat sb;
+        return stat((db_prefix() + ".ky").c_str(), &sb) == 0 ? (uint64_t)sb.st_size / (uint64_t)key_bytes : 0;
+    }
+
     void open_devices()
     {
         int ndev = ccb_device_count();
         if (ndev <= 0) { cerr << "No CUDA devices found. Abort.\n"; exit(1); }                       // src/CuClarkDB.cu:126-129
-        if ((size_t)ndev < cli.devices) { cerr << cli.devices << " CUDA devices requested. Insufficient devices found. Abort.\n"; exit(1); }
+        // CCB_SHARD_SAME_DEVICE=1 (tests on a one-GPU box): -d N --sharded may list a device more than once
+        const bool same_dev = cli.sharded && getenv("CCB_SHARD_SAME_DEVICE") && (size_t)ndev < cli.devices;
+        if ((size_t)ndev < cli.devices && !same_dev) { cerr << cli.devices << " CUDA devices requested. Insufficient devices found. Abort.\n"; exit(1); }
+        const int have = ndev;
         if (cli.devices > 0) { cerr << "Using " << cli.devices << " CUDA devices as requested.\n"; ndev = (int)cli.devices; }
         const int workers = (int)std::max<size_t>(cli.cpu, (size_t)ndev);
+        // The reference cuts a database that does not fit one device into parts and swaps them through the GPUs
+        // (src/CuClarkDB.cu:531-559, 776-815).  Here: one shard per device, all resident (--sharded, or by itself when a
+        // copy of the table -- 16 bytes per k-mer at the default fill -- would not fit beside the batch buffers).
+        sharded = cli.sharded && ndev > 1;
+        if (!sharded && ndev > 1 && cli.sfactor <= 1) {
+            uint64_t fr = 0, tot = 0;
+            const uint64_t need = db_kmers() * 16ull + (4ull << 30);
+            if (ccb_device_memory(0, &fr, &tot) == 0 && need > fr) {
+                sharded = true;
+                cerr << "The database does not fit one device (" << need / 1000000000.0 << " GB needed, " << fr / 1000000000.0
+                     << " GB free): sharding it over the " << ndev << " devices.\n";
+            }
+        }
+        if (sharded) {
+            vector<int> dv;
+            for (int d = 0; d < ndev; d++) dv.push_back(d % have);
+            ccb_config c;
+            memset(&c, 0, sizeof c);
+            c.k = (int)cli.k; c.n_targets = (int)std::max<size_t>(tg.n_labels, 1); c.max_hits = MAXHITS;
+            c.n_slots = workers + ndev; c.load_factor = 0; c.verbose = cli.verbose;
+            ccb_handle* h = NULL;
+            if (ccb_group_create(dv.data(), ndev, &c, &h)) { cerr << ccb_last_error(NULL) << endl; exit(1); }
+            if (cli.verbose) cerr << "Database sharded over " << ndev << " devices (k-mer exchange over peer memory).\n";
+            devs.push_back(h);
+            return;
+        }
         for (int d = 0; d < ndev; d++) {
             ccb_config c;
             memset(&c, 0, sizeof c);
@@ -174,12 +216,17 @@ struct Engine {
         }
     }
 
-    void load_db()
-    {   // getdbName (src/CuCLARK_hh.hh:581-592) + loadSpecificTargetSets (:599-632)
+    string db_prefix() const
+    {   // getdbName (src/CuCLARK_hh.hh:581-592)
         char name[4096];
         if (kLight) snprintf(name, sizeof name, "%s/db_central_k%lu_t%lu_s%lu_m%lu_light_%lu.tsk", cli.folder, cli.k, tg.n_labels, (size_t)HTSIZE, (size_t)cli.minT, cli.iterKmers);
         else        snprintf(name, sizeof name, "%s/db_central_k%lu_t%lu_s%lu_m%lu.tsk", cli.folder, cli.k, tg.n_labels, (size_t)HTSIZE, (size_t)cli.minT);
-        dbname = name;
+        return name;
+    }
+
+    void load_db()
+    {   // loadSpecificTargetSets (src/CuCLARK_hh.hh:599-632)
+        dbname = db_prefix();
         bool present = true;
         for (const char* e : {".sz", ".ky", ".lb"}) present = present && validFile((dbname + e).c_str());
         if (!present && build_db()) return;          // built on the device and already resident
@@ -229,7 +276,7 @@ struct Engine {
         for (size_t i = 0; i < std::max<size_t>(1, std::min<size_t>(cli.cpu, tg.files.size())); i++) th.emplace_back(work);
         for (auto& t : th) t.join();
         if (failed) exit(1);
-        const bool resident = devs.size() == 1 && cli.sfactor <= 1;
+        const bool resident = devs.size() == 1 && cli.sfactor <= 1 && !sharded;
         ccb_build_info bi;
         memset(&bi, 0, sizeof bi);
         cerr << endl << "Creating database in disk..." << endl;
@@ -240,19 +287,35 @@ struct Engine {
         return resident;
     }
 
-    // Optional (environment CCB_ANCHOR=1; no counterpart in the reference, results are unchanged): keep the
-    // target sequences on every device so that read windows which match a target base by base are answered
-    // without a table probe (include/cuclark_b200.h "Anchor index").  Any failure only costs the speed-up.
+    // The anchor index (no counterpart in the reference, results are unchanged): the target sequences are kept on
+    // every device so that read windows which match a target base by base are answered without a table probe
+    // (include/cuclark_b200.h "Anchor index").  On by default whenever the target FASTA files are there to build it from
+    // and fit (at most 4 Gbp of text per device, memory permitting; not with a sharded table); CCB_ANCHOR=0 turns it
+    // off, CCB_ANCHOR=1 reports why it could not be built.  Any failure only costs the speed-up.
     void build_anchor()
     {
         const char* env = getenv("CCB_ANCHOR");
-        if (!env || !*env || *env == '0' || tg.files.empty()) return;
+        if ((env && *env == '0') || tg.files.empty() || sharded) return;
+        const bool loud = (env && *env && *env != '0') || cli.verbose;
+        {   // room for it beside the table and the batch slots?  (text 1.25 B + sampled k-mers 2 B + build scratch 1 B per base)
+            uint64_t total_b = 0, fr = 0, tot = 0;
+            for (auto& f : tg.files) { struct stat sb; if (stat(f.first.c_str(), &sb) == 0) total_b += (uint64_t)sb.st_size; }
+            for (size_t d = 0; d < devs.size(); d++)
+                if (ccb_device_memory((int)d, &fr, &tot) == 0 && total_b * 9 / 2 + (6ull << 30) > fr) {
+                    if (loud) cerr << "Anchor index not built: not enough device memory left beside the database." << endl;
+                    return;
+                }
+        }
         struct timeval t0, t1;
         gettimeofday(&t0, NULL);
         uint64_t total = 0;
         for (auto& f : tg.files) { struct stat sb; if (stat(f.first.c_str(), &sb) == 0) total += (uint64_t)sb.st_size; }
         for (ccb_handle* h : devs)
-            if (ccb_anchor_begin(h, total)) { cerr << "Anchor index not built: " << ccb_last_error(h) << endl; return; }
+            if (ccb_anchor_begin(h, total)) {
+                if (loud) cerr << "Anchor index not built: " << ccb_last_error(h) << endl;
+                for (ccb_handle* x : devs) ccb_anchor_drop(x);
+                return;
+            }
         std::atomic<size_t> next{0};
         std::atomic<bool> failed{false};
         auto work = [&] {
@@ -274,8 +337,8 @@ struct Engine {
         for (ccb_handle* h : devs) {
             ccb_anchor_info ai;
             memset(&ai, 0, sizeof ai);
-            if (failed) { ccb_anchor_end(h, NULL); ccb_anchor_drop(h); cerr << "Anchor index not built: " << ccb_last_error(h) << endl; continue; }
-            if (ccb_anchor_end(h, &ai)) { cerr << "Anchor index not built: " << ccb_last_error(h) << endl; continue; }
+            if (failed) { ccb_anchor_end(h, NULL); ccb_anchor_drop(h); if (loud) cerr << "Anchor index not built: " << ccb_last_error(h) << endl; continue; }
+            if (ccb_anchor_end(h, &ai)) { if (loud) cerr << "Anchor index not built: " << ccb_last_error(h) << endl; continue; }
             if (cli.verbose) {
                 gettimeofday(&t1, NULL);
                 cerr << "Anchor index: " << ai.bases << " bases, " << ai.entries << " sampled k-mers, " << ai.bytes / 1e9 << " GB, "
@@ -311,9 +374,39 @@ struct Engine {
         (void)shown_name;
     }
 
+    // --gzipped: the whole file inflated in memory (zlib; concatenated members are fine, a plain text passes through).
+    // The reference leaves this to classify_metagenome.sh, which copies the file, gunzips the copy and hands the binary
+    // the text (scripts/classify_metagenome.sh:118-137); through the script nothing changes, directly it saves the copy.
+    static bool inflate_file(const char* file, vector<char>& out)
+    {
+        gzFile g = gzopen(file, "rb");
+        if (!g) return false;
+        gzbuffer(g, 1u << 20);
+        struct stat sb;
+        out.clear();
+        if (stat(file, &sb) == 0) out.reserve((size_t)sb.st_size * 4);
+        size_t n = 0;
+        for (;;) {
+            if (out.size() < n + (8u << 20)) out.resize(std::max(out.size() * 2, n + (size_t)(16u << 20)));
+            const int r = gzread(g, out.data() + n, (unsigned)std::min<size_t>(out.size() - n, 1u << 30));
+            if (r < 0) { gzclose(g); return false; }
+            if (r == 0) break;
+            n += (size_t)r;
+        }
+        gzclose(g);
+        out.resize(n);
+        return true;
+    }
+
     void run_file(const char* file, const char* result_prefix)
     {
         cerr << "Classifying: " << file << "\n";
+        if (cli.gzipped) {
+            vector<char> text;
+            if (!inflate_file(file, text) || text.empty()) { cerr << "Failed to uncompress input objects." << endl; return; }
+            classify(file, (const uint8_t*)text.data(), text.size(), result_prefix, false);
+            return;
+        }
         int fd = open(file, O_RDONLY);
         struct stat sb;
         if (fd == -1 || fstat(fd, &sb) != 0 || sb.st_size == 0) { cerr << "Failed to open " << file << endl; if (fd != -1) close(fd); return; }
@@ -329,7 +422,11 @@ struct Engine {
     {   // the reference writes <f1>_ConcatenatedByCLARK.fa, classifies it as FASTA and deletes it
         // (src/CuCLARK_hh.hh:442-452); the same text is built in memory here.
         vector<char> text; string err;
-        if (ccbh::join_pairs(f1, f2, text, err)) { cerr << err << endl; exit(1); }
+        if (cli.gzipped) {
+            vector<char> a, b;
+            if (!inflate_file(f1, a) || !inflate_file(f2, b) || a.empty() || b.empty()) { cerr << "Failed to uncompress input objects." << endl; exit(1); }
+            if (ccbh::join_pairs_streams(fmemopen(a.data(), a.size(), "r"), fmemopen(b.data(), b.size(), "r"), text, err)) { cerr << err << endl; exit(1); }
+        } else if (ccbh::join_pairs(f1, f2, text, err)) { cerr << err << endl; exit(1); }
         cerr << "Classifying: " << f1 << "_ConcatenatedByCLARK.fa" << "\n";
         if (text.empty()) { cerr << "Failed to open " << f1 << "_ConcatenatedByCLARK.fa" << endl; return; }
         classify(f1, (const uint8_t*)text.data(), text.size(), result_prefix, true);
@@ -448,6 +545,8 @@ int main(int argc, char** argv)
             continue;
         }
         if (val == "--verbose") { c.verbose = true; continue; }
+        if (val == "--sharded") { c.sharded = true; continue; }
+        if (val == "--gzipped") { c.gzipped = true; continue; }
         if (val == "-m") { need(i, "Please specify the mode!"); continue; }      // tolerated, ignored
         cerr << "Failed to recognize option: " << val << endl;
         exit(1);

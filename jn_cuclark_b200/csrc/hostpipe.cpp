@@ -364,8 +364,15 @@ inline void pair_id(const char* s, size_t n, const char*& b, size_t& len)
 
 int join_pairs(const char* file1, const char* file2, std::vector<char>& out, std::string& err)
 {
-    LineReader a(fopen(file1, "r")), b(fopen(file2, "r"));
-    if (!a.f || !b.f) { err = std::string("Failed to find/read ") + (!a.f ? file1 : file2); return 1; }
+    FILE* fa = fopen(file1, "r"); FILE* fb = fopen(file2, "r");
+    if (!fa || !fb) { err = std::string("Failed to find/read ") + (!fa ? file1 : file2); if (fa) fclose(fa); if (fb) fclose(fb); return 1; }
+    return join_pairs_streams(fa, fb, out, err);
+}
+
+int join_pairs_streams(FILE* fa, FILE* fb, std::vector<char>& out, std::string& err)
+{
+    LineReader a(fa), b(fb);
+    if (!a.f || !b.f) { err = "Failed to find/read the paired-end reads"; return 1; }
     if (!a.next() || !b.next() || a.buf[0] != b.buf[0]) { err = "Error: the files have different format!"; return 1; }
     if (a.buf[0] != '@') { err = "Error: paired-end reads must be FASTQ files!"; return 1; }
     rewind(a.f); rewind(b.f);

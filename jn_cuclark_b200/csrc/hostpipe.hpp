@@ -13,6 +13,7 @@
 #pragma once
 #include <stddef.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <memory>
 #include <string>
 #include <vector>
@@ -58,6 +59,8 @@ int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
 
 // A10 (src/file.cc:205-268): ">id\n<mate1>N<mate2>\n" per pair, in memory.  0 = ok, otherwise err is set.
 int join_pairs(const char* file1, const char* file2, std::vector<char>& out, std::string& err);
+// the same on two open streams (files, or fmemopen over texts inflated in memory); both are closed
+int join_pairs_streams(FILE* a, FILE* b, std::vector<char>& out, std::string& err);
 
 // A7 (src/CuCLARK_hh.hh:1952-1967, 2096-2118)
 void csv_header(std::string& out, bool extended, const std::vector<std::string>& target_names);

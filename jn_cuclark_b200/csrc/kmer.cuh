@@ -83,6 +83,14 @@ struct HashParams {
 
 #if defined(__CUDACC__)
 __device__ __forceinline__ uint64_t mulhi64(uint64_t a, uint64_t b) { return __umul64hi(a, b); }
+// revcomp() with the five swap stages replaced by two bit reversals and one swap inside the pairs (14 instructions)
+__device__ __forceinline__ uint64_t revcomp_brev(uint64_t x, int k)
+{
+    uint32_t lo = __brev((uint32_t)(x >> 32)), hi = __brev((uint32_t)x);
+    lo = ((lo >> 1) & 0x55555555u) | ((lo & 0x55555555u) << 1);
+    hi = ((hi >> 1) & 0x55555555u) | ((hi & 0x55555555u) << 1);
+    return (~(((uint64_t)hi << 32) | lo)) >> (64 - 2 * k);
+}
 #endif
 inline uint64_t mulhi64_host(uint64_t a, uint64_t b) { return (uint64_t)(((unsigned __int128)a * b) >> 64); }
 

@@ -20,6 +20,7 @@
 //    (count desc, target asc) == the reference's ascending scan
 //    (src/CuClarkDB.cu:1380-1399).
 #include "query.cuh"
+#include "vote.cuh"
 
 namespace ccb {
 
@@ -180,7 +181,7 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
             sent[g] = 0; out_g[g] = nullptr; room[g] = 0xFFFFFFFFu;
             if (MODE == kModeRoute && g < (int)ra.n_shards) {
                 const uint64_t base = ra.derive_base ? (uint64_t)__ldg(ra.pos + (size_t)g * a.n_reads) : ra.seg_base[g];
-                out_g[g] = ra.dst[g] + (__ldg(ra.pos + (size_t)g * a.n_reads + r) - base);
+                out_g[g] = ra.dst[g] + (ra.dst_off ? ra.dst_off[g] : 0ull) + (__ldg(ra.pos + (size_t)g * a.n_reads + r) - base);
                 if (ra.cap) {                            // elements of this read that still fit owner g's segment
                     const uint64_t first = (uint64_t)(out_g[g] - ra.dst[g]);
                     room[g] = first < ra.cap ? (uint32_t)min(ra.cap - first, (uint64_t)0xFFFFFFFFu) : 0u;
@@ -338,12 +339,12 @@ int launch_query(const TableView& t, const QueryArgs& a, cudaStream_t s, uint32_
 }
 
 
-int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s)
+int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s, uint32_t max_ctas)
 {
     if (a.n_reads == 0) return 0;
     if (ra.n_shards < 1 || ra.n_shards > (uint32_t)kMaxShards) return -60;
     uint32_t ctas = (a.n_reads + kWarpsPerCta - 1) / kWarpsPerCta;
-    uint32_t cap = 148u * 128u;
+    uint32_t cap = max_ctas ? max_ctas : 148u * 128u;
     if (ctas > cap) ctas = cap;
     if (write) k_query<kModeRoute, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra);
     else       k_query<kModeCount, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(t, a, ra);
@@ -363,49 +364,6 @@ __device__ __forceinline__ uint64_t kmer_at(const uint16_t* data, int j, int k, 
         x = (x << 2) | ((data[p >> 3] >> (2 * (7 - (p & 7)))) & 3u);
     }
     return x & mask;
-}
-
-// top-2 under (count desc, target asc) + sum over a CTA's dense counters, then the result row
-__device__ __forceinline__ void dense_result(const QueryArgs& a, uint32_t r, const uint32_t* cnt, uint32_t n_targets,
-                                             uint32_t (&s_key)[2][256], uint32_t (&s_sum)[256])
-{
-    uint32_t k1 = 0, k2 = 0, sum = 0;
-    for (uint32_t i = threadIdx.x; i < n_targets; i += blockDim.x) {
-        uint32_t c16 = cnt[i] & 0xFFFFu;
-        if (!c16) continue;
-        sum += c16;
-        uint32_t key = (c16 << 16) | (0xFFFFu - i);
-        if (key > k1) { k2 = k1; k1 = key; } else if (key > k2) k2 = key;
-    }
-    s_key[0][threadIdx.x] = k1; s_key[1][threadIdx.x] = k2; s_sum[threadIdx.x] = sum;
-    __syncthreads();
-    for (int o = 128; o; o >>= 1) {
-        if ((int)threadIdx.x < o) {
-            uint32_t a1 = s_key[0][threadIdx.x], a2 = s_key[1][threadIdx.x];
-            uint32_t b1 = s_key[0][threadIdx.x + o], b2 = s_key[1][threadIdx.x + o];
-            uint32_t m1 = max(a1, b1);
-            uint32_t m2 = max(min(a1, b1), max(a2, b2));
-            s_key[0][threadIdx.x] = m1; s_key[1][threadIdx.x] = m2;
-            s_sum[threadIdx.x] += s_sum[threadIdx.x + o];
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        k1 = s_key[0][0]; k2 = s_key[1][0];
-        uint16_t* o5 = a.out5 + (size_t)r * 5;
-        o5[0] = (uint16_t)s_sum[0];
-        o5[1] = (uint16_t)(k1 ? (0xFFFFu - (k1 & 0xFFFFu)) + 1u : 0u);
-        o5[2] = (uint16_t)(k1 >> 16);
-        o5[3] = (uint16_t)(k2 ? (0xFFFFu - (k2 & 0xFFFFu)) + 1u : 0u);
-        o5[4] = (uint16_t)(k2 >> 16);
-        if (a.rows) {
-            uint16_t* row = a.rows + (size_t)r * a.row_stride;
-            int n = 0, fit = (a.row_stride - 1) / 2;
-            for (uint32_t i = 0; i < n_targets && n < fit; i++)
-                if (cnt[i] & 0xFFFFu) { row[1 + 2 * n] = (uint16_t)i; row[2 + 2 * n] = (uint16_t)cnt[i]; n++; }
-            row[0] = (uint16_t)n;
-        }
-    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -502,20 +460,25 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_vote_lists(const QueryArg
 {
     const int lane = threadIdx.x & 31;
     const uint32_t total_warps = gridDim.x * kWarpsPerCta;
-    for (uint32_t r = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); r < a.n_reads; r += total_warps) {
+    const uint32_t n_items = a.read_list ? min(__ldg(a.n_list), a.n_reads) : a.n_reads;
+    for (uint32_t idx = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); idx < n_items; idx += total_warps) {
+        const uint32_t r = a.read_list ? __ldg(a.read_list + idx) : idx;
         uint32_t acc_lab = kLabelNone, acc_cnt = 0;
         int nacc = 0; bool overflow = false;
         for (uint32_t g = 0; g < va.n_shards; g++) {
             const size_t pi = (size_t)g * a.n_reads + r;
             const uint32_t b = __ldg(va.pos + pi), e = __ldg(va.pos + pi + 1);
             const uint64_t base = va.derive_base ? (uint64_t)__ldg(va.pos + (size_t)g * a.n_reads) : va.seg_base[g];
-            const uint16_t* src = va.src[g] + ((uint64_t)b - base);
-            for (uint32_t o = 0; o < e - b; o += 128) {
+            const uint64_t first = (va.src_off ? va.src_off[g] : 0ull) + ((uint64_t)b - base);
+            const uint16_t* src = va.src[g] + first;
+            uint32_t cnt = e - b;
+            if (va.cap) cnt = first < va.cap ? (uint32_t)min((uint64_t)cnt, va.cap - first) : 0u;
+            for (uint32_t o = 0; o < cnt; o += 128) {
                 uint32_t lab[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const uint32_t i = o + 32 * j + lane;
-                    lab[j] = i < e - b ? (uint32_t)__ldg(src + i) : kLabelNone;
+                    lab[j] = i < cnt ? (uint32_t)__ldg(src + i) : kLabelNone;
                     if (lab[j] >= kLabelTomb) lab[j] = kLabelNone;
                 }
                 vote4(lab, acc_lab, acc_cnt, nacc, overflow, lane);
@@ -551,8 +514,11 @@ k_vote_lists_dense(const QueryArgs a, const VoteArgs va, const uint32_t* read_li
             const size_t pi = (size_t)g * a.n_reads + r;
             const uint32_t b = va.pos[pi], e = va.pos[pi + 1];
             const uint64_t base = va.derive_base ? (uint64_t)va.pos[(size_t)g * a.n_reads] : va.seg_base[g];
-            const uint16_t* src = va.src[g] + ((uint64_t)b - base);
-            for (uint32_t i = threadIdx.x; i < e - b; i += blockDim.x) {
+            const uint64_t first = (va.src_off ? va.src_off[g] : 0ull) + ((uint64_t)b - base);
+            const uint16_t* src = va.src[g] + first;
+            uint32_t n_lab = e - b;
+            if (va.cap) n_lab = first < va.cap ? (uint32_t)min((uint64_t)n_lab, va.cap - first) : 0u;
+            for (uint32_t i = threadIdx.x; i < n_lab; i += blockDim.x) {
                 const uint32_t lab = src[i];
                 if (lab < kLabelTomb && lab < n_targets) atomicAdd(cnt + lab, 1u);
             }
@@ -578,22 +544,22 @@ int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32
 struct CountDst { unsigned long long* p[kMaxShards]; };
 
 __global__ void k_post_counts(const uint32_t* __restrict__ pos, uint32_t n_reads, uint32_t n_shards, uint64_t cap,
-                              CountDst dst, uint32_t* error)
+                              CountDst dst, uint32_t* error, const unsigned long long* first)
 {
     const uint32_t g = threadIdx.x;
     if (g >= n_shards) return;
-    const uint64_t n = (uint64_t)pos[(size_t)(g + 1) * n_reads] - pos[(size_t)g * n_reads];
+    const uint64_t n = (first ? first[g] : 0ull) + ((uint64_t)pos[(size_t)(g + 1) * n_reads] - pos[(size_t)g * n_reads]);
     if (cap && n > cap) { if (error) atomicExch(error, 1u); *dst.p[g] = cap; }
     else *dst.p[g] = n;
     __threadfence_system();
 }
 
 int launch_post_counts(const uint32_t* pos, uint32_t n_reads, uint32_t n_shards, uint64_t cap,
-                       unsigned long long* const* count_dst, uint32_t* error, cudaStream_t s)
+                       unsigned long long* const* count_dst, uint32_t* error, cudaStream_t s, const unsigned long long* first)
 {
     CountDst d{};
     for (uint32_t g = 0; g < n_shards; g++) d.p[g] = count_dst[g];
-    k_post_counts<<<1, 32, 0, s>>>(pos, n_reads, n_shards, cap, d, error);
+    k_post_counts<<<1, 32, 0, s>>>(pos, n_reads, n_shards, cap, d, error, first);
     return (int)cudaGetLastError();
 }
 

@@ -33,6 +33,8 @@ struct QueryArgs {
 constexpr int kMaxShards = 8;
 struct RouteArgs {
     uint32_t        n_shards;
+    const unsigned long long* dst_off;      // optional (device): owner g's segment starts dst_off[g] entries into dst[g]
+                                            // (the block path's k-mers come first, shard_block.cu)
     uint32_t*       counts;                 // count pass: u32[n_shards * n_reads]
     const uint32_t* pos;                    // u32[n_shards * n_reads + 1]
     uint64_t        seg_base[kMaxShards];   // pos of owner g's first k-mer (= pos[g * n_reads])
@@ -40,13 +42,16 @@ struct RouteArgs {
     uint32_t        derive_base;            // 1: take seg_base[g] from pos[g * n_reads] on the device (no host round trip)
     uint64_t        cap;                    // elements a segment may hold; stores beyond it are dropped (0 = unlimited)
 };
-int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s);
+int launch_route(const TableView& t, const QueryArgs& a, const RouteArgs& ra, bool write, cudaStream_t s, uint32_t max_ctas = 0);
 // owner side: labels[i] = label of mixed k-mer hashes[i] (0xFFFF: absent or not discriminative)
 int launch_probe_list(const TableView& t, const uint64_t* hashes, uint64_t n, uint16_t* labels,
                       unsigned long long* stats, cudaStream_t s);
 // requester side: vote from the returned label lists; overflowing reads go to ovf_list as in launch_query
 struct VoteArgs {
     uint32_t        n_shards;
+    const unsigned long long* src_off;      // optional (device): as RouteArgs::dst_off
+    uint64_t        cap;                    // entries a region holds (0 = unlimited): labels beyond it were never written
+                                            // (the route pass dropped the k-mers and raised the error word) and are not read
     const uint32_t* pos;
     uint64_t        seg_base[kMaxShards];
     const uint16_t* src[kMaxShards];
@@ -54,8 +59,10 @@ struct VoteArgs {
 };
 // Peer exchange (no NCCL on the data path): after the route pass, tell every owner how many k-mers it
 // got from this rank (count_dst[g] points into owner g's memory); over-capacity sets *error.
+// `first` (optional, device): entries the block path already put into each region
 int launch_post_counts(const uint32_t* pos, uint32_t n_reads, uint32_t n_shards, uint64_t cap,
-                       unsigned long long* const* count_dst, uint32_t* error, cudaStream_t s);
+                       unsigned long long* const* count_dst, uint32_t* error, cudaStream_t s,
+                       const unsigned long long* first = nullptr);
 // owner side over an inbox of n_shards regions of `cap` k-mers each, region s filled by rank s with
 // counts_in[s] k-mers; the label of inbox[s][i] is stored to lab_dst[s][i] (rank s's memory)
 struct InboxArgs {
@@ -68,6 +75,34 @@ struct InboxArgs {
 int launch_probe_inbox(const TableView& t, const InboxArgs& ia, unsigned long long* stats, cudaStream_t s);
 int launch_vote_lists(const QueryArgs& a, const VoteArgs& va, cudaStream_t s);
 int launch_vote_lists_dense(const QueryArgs& a, const VoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
+                            uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s);
+
+// One-pass routing and block-wise voting for short reads (shard_block.cu): a block of kRouteBlk reads owns one
+// contiguous segment per owner, reserved with one atomicAdd on the requester's cursor.
+constexpr int kRouteBlk = 256;
+struct BlockRouteArgs {
+    uint32_t  n_shards;
+    uint64_t* dst[kMaxShards];        // owner g's region for this requester (local send segment or a peer's inbox)
+    uint8_t*  rid[kMaxShards];        // local, same indices as dst[g]: which read of its block the k-mer belongs to
+    uint64_t  cap;                    // entries a region holds (< 2^32); the excess is dropped and *error set
+    unsigned long long* cursor;       // [kMaxShards] entries reserved per owner so far
+    uint32_t* blkseg;                 // [blocks][2 parts][kMaxShards][2]: first entry, entries of (block, part, owner)
+    uint8_t*  rstate;                 // per read: 0 no k-mers, 1 routed by the block kernel, 2 handed to the generic path
+    uint32_t* redo_list; uint32_t* redo_count;
+    uint32_t* error;
+};
+int launch_route_block(const HashParams& hp, const QueryArgs& a, const BlockRouteArgs& ra, cudaStream_t s);
+struct BlockVoteArgs {
+    uint32_t  n_shards;
+    const uint16_t* src[kMaxShards];  // labels, same indices as BlockRouteArgs::dst
+    const uint8_t*  rid[kMaxShards];
+    uint64_t  cap;
+    const uint32_t* blkseg;
+    const uint8_t*  rstate;
+};
+// reads with rstate 1 get their result; a read that met a fifth target goes to a.ovf_list / a.ovf_count
+int launch_vote_block(const QueryArgs& a, const BlockVoteArgs& va, cudaStream_t s);
+int launch_vote_block_dense(const QueryArgs& a, const BlockVoteArgs& va, const uint32_t* read_list, const uint32_t* d_n_list,
                             uint32_t max_list, uint32_t n_targets, uint32_t* scratch, uint32_t n_scratch_blocks, cudaStream_t s);
 
 // Anchor index (DESIGN.md "Anchor and verify"): the target sequences themselves, both strands, plus a small

@@ -43,15 +43,6 @@ __device__ __forceinline__ uint32_t mismatch16(uint32_t diff)
     return v;
 }
 
-// kmer.cuh revcomp() with the five swap stages replaced by two bit reversals and one swap inside the pairs
-__device__ __forceinline__ uint64_t revcomp_brev(uint64_t x, int k)
-{
-    uint32_t lo = __brev((uint32_t)(x >> 32)), hi = __brev((uint32_t)x);
-    lo = ((lo >> 1) & 0x55555555u) | ((lo & 0x55555555u) << 1);
-    hi = ((hi >> 1) & 0x55555555u) | ((hi & 0x55555555u) << 1);
-    return (~(((uint64_t)hi << 32) | lo)) >> (64 - 2 * k);
-}
-
 struct Bits192 {                       // bit i <-> position i, LSB first
     uint64_t w[3];
     __device__ __forceinline__ Bits192 shr(int s) const          // 0 < s < 64
@@ -493,7 +484,8 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
     if (a.n_reads == 0) return 0;
     // block shape (measured): with the anchor index 128 threads x 4 blocks per SM (120 registers;
     // more blocks spill and are slower, 256 x 2 is 1-2 % slower at the barriers), table only 256 x 3 (79 registers);
-    // CCB_BLOCK_SHAPE overrides for measurements
+    // CCB_BLOCK_SHAPE overrides in measurement builds
+#ifdef CCB_EXPERIMENTS     // the other shapes (and TMA staging of the containers) are measurement builds: make VARIANT=exp EXTRA=-DCCB_EXPERIMENTS
     static const char* shape = getenv("CCB_BLOCK_SHAPE");
     if (shape && !strcmp(shape, "128x4")) return launch_block<128, 4>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "256x3")) return launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
@@ -504,6 +496,7 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
     if (shape && !strcmp(shape, "256x2s")) return launch_block<256, 2, true>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "64x8")) return launch_block<64, 8>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "128x5")) return launch_block<128, 5>(t, a, av, redo_list, redo_count, s);
+#endif
     return av ? launch_block<128, 4>(t, a, av, redo_list, redo_count, s) : launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
 }
 

@@ -79,8 +79,15 @@ SYMBOLS = {
     "ccb_shard_route": (C.c_int, [_H, _VP, _VP, C.c_uint32, C.c_int, _VP, C.POINTER(C.c_uint64), C.POINTER(_VP), _VP]),
     "ccb_shard_probe": (C.c_int, [_H, _VP, C.c_uint64, _VP, _VP, _VP]),
     "ccb_shard_vote": (C.c_int, [_H, C.c_uint32, C.c_int, _VP, C.POINTER(C.c_uint64), C.POINTER(_VP), _VP, _VP, _VP]),
-    "ccb_shard_route_peer": (C.c_int, [_H, _VP, _VP, C.c_uint32, C.c_int, _VP, C.POINTER(_VP), C.c_uint64, C.POINTER(_VP), _VP, _VP]),
     "ccb_shard_probe_inbox": (C.c_int, [_H, C.c_int, _VP, C.c_uint64, _VP, C.POINTER(_VP), _VP, _VP]),
+    "ccb_shardws_create": (C.c_int, [_H, C.c_uint32, C.c_int, C.c_uint64, C.POINTER(_VP)]),
+    "ccb_shardws_destroy": (None, [_H, _VP]),
+    "ccb_shardws_error": (C.c_int, [_H, _VP, _VP, C.POINTER(C.c_int)]),
+    "ccb_shard_route2": (C.c_int, [_H, _VP, _VP, _VP, C.c_uint32, C.c_int64, C.POINTER(_VP), C.POINTER(_VP), _VP]),
+    "ccb_shard_vote2": (C.c_int, [_H, _VP, C.c_uint32, C.POINTER(_VP), _VP, _VP, _VP]),
+    "ccb_group_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_Config), C.POINTER(_H)]),
+    "ccb_group_size": (C.c_int, [_H]),
+    "ccb_group_member": (_H, [_H, C.c_int]),
     "ccb_device_alloc": (C.c_int, [_H, C.c_uint64, C.POINTER(_VP)]),
     "ccb_ipc_export": (C.c_int, [_H, _VP, C.c_char_p]),
     "ccb_ipc_open": (C.c_int, [_H, C.c_char_p, C.POINTER(_VP)]),
@@ -105,6 +112,7 @@ SYMBOLS = {
     "ccb_version": (C.c_char_p, []),
     "ccb_l2_fetch_granularity": (C.c_int, [_H]),
     "ccb_device_count": (C.c_int, []),
+    "ccb_device_memory": (C.c_int, [C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "ccb_batch_slots": (C.c_int, [_H]),
     "ccb_synth_db": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
     "ccb_synth_reads_packed": (C.c_int, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
@@ -164,6 +172,16 @@ class CuClarkDB:
         self._max_reads = 0
         self._n = {}
 
+    @classmethod
+    def _view(cls, lib, handle, k, numTargets, max_hits):
+        """Non-owning wrapper of a handle the library owns (a member of a device group)."""
+        o = cls.__new__(cls)
+        o._lib, o._h, o._borrowed = lib, _H(handle), True
+        o.k, o.numTargets, o.numBatches, o.max_hits = k, numTargets, 1, max_hits
+        o.row_stride = 2 * max_hits + 2
+        o._max_reads, o._n = 0, {}
+        return o
+
     # -- helpers ------------------------------------------------------------
     def _ck(self, rc: int):
         if rc:
@@ -171,7 +189,8 @@ class CuClarkDB:
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
-            self._lib.ccb_destroy(self._h)
+            if not getattr(self, "_borrowed", False):
+                self._lib.ccb_destroy(self._h)
             self._h = _H()
 
     def __del__(self):
@@ -276,6 +295,7 @@ class CuClarkDB:
 
     def freeBatchMemory(self):
         self._ck(self._lib.ccb_batch_free(self._h))
+        self._max_reads = 0
 
     def query_device(self, d_offsets: int, d_containers: int, n_reads: int, d_final5: int,
                      d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
@@ -303,16 +323,32 @@ class CuClarkDB:
         sp = (_VP * n_shards)(*[int(x) for x in src])
         self._ck(self._lib.ccb_shard_vote(self._h, n_reads, n_shards, d_pos, sb, sp, d_final5, d_rows or None, stream or None))
 
-    def shard_route_peer(self, d_offsets: int, d_containers: int, n_reads: int, n_shards: int, d_pos: int,
-                         dst, cap: int, count_dst, d_error: int = 0, stream: int = 0):
-        dp = (_VP * n_shards)(*[int(x) for x in dst])
-        cp = (_VP * n_shards)(*[int(x) for x in count_dst])
-        self._ck(self._lib.ccb_shard_route_peer(self._h, d_offsets, d_containers, n_reads, n_shards, d_pos, dp, cap, cp,
-                                                d_error or None, stream or None))
-
     def shard_probe_inbox(self, n_shards: int, d_inbox: int, cap: int, d_counts_in: int, lab_dst, d_stats: int = 0, stream: int = 0):
         lp = (_VP * n_shards)(*[int(x) for x in lab_dst])
         self._ck(self._lib.ccb_shard_probe_inbox(self._h, n_shards, d_inbox, cap, d_counts_in, lp, d_stats or None, stream or None))
+
+    # one-pass pipeline (shard_block.cu): a workspace per batch in flight
+    def shardws_create(self, max_reads: int, n_shards: int, cap: int) -> int:
+        p = _VP()
+        self._ck(self._lib.ccb_shardws_create(self._h, max_reads, n_shards, cap, C.byref(p)))
+        return p.value
+
+    def shardws_destroy(self, ws: int):
+        self._lib.ccb_shardws_destroy(self._h, ws)
+
+    def shardws_error(self, ws: int, stream: int = 0) -> bool:
+        v = C.c_int(0)
+        self._ck(self._lib.ccb_shardws_error(self._h, ws, stream or None, C.byref(v)))
+        return bool(v.value)
+
+    def shard_route2(self, ws: int, d_offsets: int, d_containers: int, n_reads: int, n_containers: int, dst, count_dst, stream: int = 0):
+        dp = (_VP * len(dst))(*[int(x) for x in dst])
+        cp = (_VP * len(count_dst))(*[int(x) for x in count_dst])
+        self._ck(self._lib.ccb_shard_route2(self._h, ws, d_offsets, d_containers, n_reads, n_containers, dp, cp, stream or None))
+
+    def shard_vote2(self, ws: int, n_reads: int, src, d_final5: int, d_rows: int = 0, stream: int = 0):
+        sp = (_VP * len(src))(*[int(x) for x in src])
+        self._ck(self._lib.ccb_shard_vote2(self._h, ws, n_reads, sp, d_final5, d_rows or None, stream or None))
 
     def device_alloc(self, nbytes: int) -> int:
         p = _VP()
@@ -404,3 +440,25 @@ class CuClarkDB:
         self.queryBatch(slot, extended, flags)
         self.waitForBatch(slot)
         return f[:n].copy(), (r[:n].copy() if extended else None)
+
+
+class CuClarkGroup(CuClarkDB):
+    """One process, several GPUs, the table sharded over them (ccb_group_create): the leader handle takes the same
+    batch calls as a one-device CuClarkDB (malloc / buffers / readyBatch / queryBatch / waitForBatch, classify_packed);
+    `members[g]` is the handle that holds shard g (load it with load_pairs / synth_db, or read() on the leader loads all)."""
+
+    def __init__(self, devices, k: int = 31, numBatches: int = 1, numTargets: int = 1, verbose: bool = False, *,
+                 max_hits: int = 15, load_factor: float = 0.0):
+        self._lib = load_library()
+        self._h = _H()
+        cfg = _Config(int(devices[0]), k, numTargets, max_hits, numBatches, load_factor, int(verbose))
+        dv = (C.c_int * len(devices))(*[int(d) for d in devices])
+        rc = self._lib.ccb_group_create(dv, len(devices), C.byref(cfg), C.byref(self._h))
+        if rc:
+            raise CcbError(rc, self._lib.ccb_last_error(None).decode())
+        self.k, self.numTargets, self.numBatches, self.max_hits = k, numTargets, numBatches, max_hits
+        self.row_stride = 2 * max_hits + 2
+        self._max_reads = 0
+        self._n = {}
+        self.members = [CuClarkDB._view(self._lib, self._lib.ccb_group_member(self._h, g), k, numTargets, max_hits)
+                        for g in range(self._lib.ccb_group_size(self._h))]

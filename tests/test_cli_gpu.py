@@ -199,3 +199,48 @@ def test_two_devices_give_the_same_csv(setup, oracle, tmp_path, anchor):
     _oracle_csv(s, oracle, open(reads, "rb").read(), str(tmp_path / "want.csv"))
     two = open(str(tmp_path / "two.csv"), "rb").read()
     assert two == open(str(tmp_path / "one.csv"), "rb").read() == open(str(tmp_path / "want.csv"), "rb").read()
+
+
+@pytest.mark.parametrize("case", ["fq", "pe_ext"])
+def test_sharded_table_gives_the_same_csv(setup, oracle, tmp_path, case):
+    """--sharded -d 2 (row E2 at the process boundary): ONE table cut into two shards (on two GPUs, or both on the one GPU
+    of the box), k-mers and labels exchanged through peer memory -- byte-identical to the one-device CSV and the oracle's."""
+    import torch
+    s = setup
+    env = {"CCB_SHARD_SAME_DEVICE": "1"} if torch.cuda.device_count() < 2 else {}
+    if case == "fq":
+        reads = os.path.join(WORLD, "reads.fq")
+        r = _run(s, ["-O", reads, "-d", "2", "--sharded", "-n", "4", "--verbose"], str(tmp_path / "sh"), env)
+        _oracle_csv(s, oracle, open(reads, "rb").read(), str(tmp_path / "want.csv"))
+    else:
+        p1, p2 = os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")
+        r = _run(s, ["-P", p1, p2, "--extended", "-d", "2", "--sharded", "-n", "2", "--verbose"], str(tmp_path / "sh"), env)
+        m = str(tmp_path / "m.fa")
+        assert oracle.merge_paired(p1, p2, m) == 0
+        _oracle_csv(s, oracle, open(m, "rb").read(), str(tmp_path / "want.csv"), paired=True, extended=True)
+    assert "Database sharded over 2 devices" in r.stderr
+    assert open(str(tmp_path / "sh.csv"), "rb").read() == open(str(tmp_path / "want.csv"), "rb").read()
+
+
+def test_gzipped_in_process(setup, tmp_path):
+    """--gzipped handed to the binary itself (classify_metagenome.sh strips it and gunzips first): inflated in memory."""
+    import gzip
+    s = setup
+    for f in ("reads.fq", "p1.fq", "p2.fq"):
+        with open(os.path.join(WORLD, f), "rb") as src, gzip.open(str(tmp_path / (f + ".gz")), "wb") as dst:
+            dst.write(src.read())
+    _run(s, ["-O", str(tmp_path / "reads.fq.gz"), "--gzipped"], str(tmp_path / "gz"))
+    _run(s, ["-O", os.path.join(WORLD, "reads.fq")], str(tmp_path / "plain"))
+    assert open(str(tmp_path / "gz.csv"), "rb").read() == open(str(tmp_path / "plain.csv"), "rb").read()
+    _run(s, ["-P", str(tmp_path / "p1.fq.gz"), str(tmp_path / "p2.fq.gz"), "--gzipped"], str(tmp_path / "gzp"))
+    _run(s, ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")], str(tmp_path / "plainp"))
+    assert open(str(tmp_path / "gzp.csv"), "rb").read() == open(str(tmp_path / "plainp.csv"), "rb").read()
+
+
+def test_anchor_is_the_default_and_can_be_turned_off(setup, tmp_path):
+    s = setup
+    reads = os.path.join(WORLD, "reads.fa")
+    r1 = _run(s, ["-O", reads, "--verbose"], str(tmp_path / "on"))
+    r0 = _run(s, ["-O", reads, "--verbose"], str(tmp_path / "off"), {"CCB_ANCHOR": "0"})
+    assert "Anchor index: " in r1.stderr and "Anchor index" not in r0.stderr
+    assert open(str(tmp_path / "on.csv"), "rb").read() == open(str(tmp_path / "off.csv"), "rb").read()

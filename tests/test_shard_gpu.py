@@ -135,7 +135,7 @@ def test_peer_exchange_kernels_one_gpu(small_world, oracle):
     peers = lambda r: {"rank": r, "inbox": [t.data_ptr() for t in inbox], "labbox": [t.data_ptr() for t in labbox],
                        "counts": [t.data_ptr() for t in counts]}
     try:
-        cls = [PeerShardedClassifier(shards[r], cap, peers=peers(r)) for r in range(G)]
+        cls = [PeerShardedClassifier(shards[r], cap, n, peers=peers(r)) for r in range(G)]
         # "rank" r classifies the r-th third of the reads
         cut = [0, n // 3, 2 * n // 3, n]
         parts = []
@@ -145,21 +145,28 @@ def test_peer_exchange_kernels_one_gpu(small_world, oracle):
             c = cont[int(off[a]):int(off[b])]
             parts.append((torch.from_numpy(o.view(np.int32)).to(dev), torch.from_numpy(np.ascontiguousarray(c).view(np.int16)).to(dev), b - a))
         stats = torch.zeros(2, dtype=torch.int64, device=dev)
-        pos = [cls[r].stage_route(parts[r][0].data_ptr(), parts[r][1].data_ptr(), parts[r][2]) for r in range(G)]
+        for r in range(G):
+            cls[r].stage_route(parts[r][0].data_ptr(), parts[r][1].data_ptr(), parts[r][2])
         for r in range(G):
             cls[r].stage_probe(stats)
         outs = [torch.zeros(parts[r][2] * 5, dtype=torch.int16, device=dev) for r in range(G)]
         for r in range(G):
-            cls[r].stage_vote(pos[r], parts[r][2], outs[r])
+            cls[r].stage_vote(parts[r][2], outs[r])
         torch.cuda.synchronize()
         got = np.concatenate([o.cpu().numpy().view(np.uint16).reshape(-1, 5) for o in outs])
         assert int(stats[0]) == nl and not any(c.overflowed() for c in cls)
         assert np.array_equal(got, want)
         assert int(sum(int(c.sum()) for c in counts)) == nl
-        # capacity too small: flagged, never written out of bounds
-        small = [PeerShardedClassifier(shards[r], 1000, peers=peers(r)) for r in range(G)]
-        small[0].stage_route(parts[0][0].data_ptr(), parts[0][1].data_ptr(), parts[0][2])
-        assert small[0].overflowed()
+        for c in cls:
+            c.close()
+        # capacity too small: flagged, nothing written or read out of bounds -- the whole classify(), vote included
+        small = [PeerShardedClassifier(shards[r], 1000, n, peers=peers(r)) for r in range(G)]
+        junk = torch.zeros(parts[0][2] * 5, dtype=torch.int16, device=dev)
+        small[0].classify(parts[0][0].data_ptr(), parts[0][1].data_ptr(), parts[0][2], junk)
+        torch.cuda.synchronize()
+        assert small[0].overflowed() and not small[0].overflowed()          # reading the flag clears it
+        for c in small:
+            c.close()
     finally:
         for s_ in shards:
             s_.close()
@@ -193,14 +200,18 @@ def _nccl_worker_body(rank, world, port, q):
     part = CuClarkDB(1, k, 1, G_, device=rank)
     part.shard_config(world, rank)
     part.synth_db(11, G_, LG, G_)
-    sc = ShardedClassifier(part)
+    cap = (4000 + 500 * world) * (L - k + 1)                                       # the same on every rank
+    sc = ShardedClassifier(part, cap, 4000 + 500 * world)
     out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
-    sc.classify(d_off, d_cont, NR, out)
+    for _ in range(2):
+        out.zero_()
+        sc.classify(d_off, d_cont, NR, out)
     torch.cuda.synchronize()
     same = bool(torch.equal(out, ref))
+    sc.close()
     # the same through the peer-store exchange (CUDA IPC inboxes, no collective on the data path)
     from jn_cuclark_b200.sharded import PeerShardedClassifier
-    pc = PeerShardedClassifier(part, cap=(4000 + 500 * world) * (L - k + 1))      # the same on every rank
+    pc = PeerShardedClassifier(part, cap, 4000 + 500 * world)
     for _ in range(3):                                   # buffers are reused batch after batch
         out2 = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
         pc.classify(d_off, d_cont, NR, out2)
@@ -233,3 +244,102 @@ def test_sharded_two_processes_nccl():
     assert all(g[1] for g in got), got                      # sharded == replicated, bit for bit
     assert all(g[2] > 1000 for g in got)
     assert got[0][3] + got[1][3] == got[0][4]               # shards partition the table
+
+
+def _classify_one_pass_one_gpu(shards, off, cont, cap, extended=False, n_containers=-1):
+    """The one-pass pipeline (ccb_shard_route2 / ccb_shard_vote2) with every shard on this device: requester = shard 0's
+    handle, owner g probes region g of the requester's send buffer."""
+    import torch
+    G = len(shards)
+    n = off.size - 1
+    dev = torch.device("cuda", 0)
+    d_off = torch.from_numpy(np.ascontiguousarray(off, dtype=np.uint32).view(np.int32)).to(dev)
+    d_cont = torch.from_numpy(np.ascontiguousarray(cont, dtype=np.uint16).view(np.int16)).to(dev) if cont.size else torch.zeros(1, dtype=torch.int16, device=dev)
+    rq = shards[0]
+    ws = rq.shardws_create(max(n, 1), G, cap)
+    send = torch.full((G * cap,), -1, dtype=torch.int64, device=dev)
+    sent = torch.zeros(G, dtype=torch.int64, device=dev)
+    labels = torch.full((G * cap,), 0x7777, dtype=torch.int16, device=dev)
+    stats = torch.zeros(2, dtype=torch.int64, device=dev)
+    rq.shard_route2(ws, d_off.data_ptr(), d_cont.data_ptr(), n, n_containers, [send.data_ptr() + 8 * g * cap for g in range(G)],
+                    [sent.data_ptr() + 8 * g for g in range(G)])
+    counts = [int(x) for x in sent.cpu().tolist()]
+    for g in range(G):
+        shards[g].shard_probe(send.data_ptr() + 8 * g * cap, min(counts[g], cap), labels.data_ptr() + 2 * g * cap, stats.data_ptr())
+    out = torch.full((max(n, 1) * 5,), 0x5555, dtype=torch.int16, device=dev)
+    rows = torch.zeros(max(n, 1) * rq.row_stride, dtype=torch.int16, device=dev) if extended else None
+    rq.shard_vote2(ws, n, [labels.data_ptr() + 2 * g * cap for g in range(G)], out.data_ptr(), rows.data_ptr() if extended else 0)
+    torch.cuda.synchronize()
+    err = rq.shardws_error(ws)
+    rq.shardws_destroy(ws)
+    o = out.cpu().numpy().view(np.uint16)[: n * 5].reshape(n, 5)
+    r = rows.cpu().numpy().view(np.uint16)[: n * rq.row_stride].reshape(n, rq.row_stride) if extended else None
+    return o, r, int(stats[0]), counts, err
+
+
+@pytest.mark.parametrize("G", [1, 2, 3, 8])
+@pytest.mark.parametrize("fname", ["reads.fa", "pairs"])
+def test_one_pass_pipeline_equals_oracle(small_world, oracle, tmp_path, G, fname):
+    """Short reads of one part and pairs joined by N (two parts) through k_route_block / k_vote_block; the odd reads of
+    the world (several parts, shorter than k) through the generic passes behind them; rows included."""
+    odb = oracle.OracleDb.build(small_world["targets"], 31, HT_SMALL)
+    if fname == "pairs":
+        m = str(tmp_path / "merged.fa")
+        assert oracle.merge_paired(os.path.join(small_world["dir"], "p1.fq"), os.path.join(small_world["dir"], "p2.fq"), m) == 0
+        data = open(m, "rb").read()
+    else:
+        data = open(os.path.join(small_world["dir"], fname), "rb").read()
+    ir = oracle.IndexedReads(data)
+    off, cont = ir.pack(31)
+    want, wrows, nl = odb.query_packed(31, off, cont, row_stride=32)
+    shards = _make_shards(odb, G)
+    try:
+        got, rows, lookups, counts, err = _classify_one_pass_one_gpu(shards, off, cont, cap=int(nl) + 64, extended=True, n_containers=int(off[-1]))
+        assert not err and lookups == nl and sum(counts) == nl
+        assert np.array_equal(got, want)
+        n = wrows[:, 0].astype(int)
+        for i in range(len(n)):
+            assert rows[i, 0] == n[i] and np.array_equal(rows[i, 1:1 + 2 * n[i]], wrows[i, 1:1 + 2 * n[i]])
+    finally:
+        for s in shards:
+            s.close()
+
+
+def test_one_pass_pipeline_odd_batches(oracle, tmp_path):
+    """Long reads (generic path only), a short read that meets more than four targets (block path -> dense re-vote), a read
+    that meets 48 (generic -> dense), reads without k-mers, an empty batch, a region that is too small."""
+    import synth
+    tp, genomes, _ = synth.make_genomes(str(tmp_path / "g"), 48, 12000, seed=5, shared=False, quirks=False, same_label_pair=False)
+    odb = oracle.OracleDb.build(tp, 31, HT_SMALL)
+    rng = np.random.default_rng(9)
+    short = [(f"s{i}", genomes[i % 48][1000 + 7 * i:1150 + 7 * i].copy()) for i in range(600)]
+    short.append(("mosaic6", np.concatenate([g[100:132] for g in genomes[:6]])))      # 192 bases, six targets: block path, fifth target
+    short.append(("mosaic5", np.concatenate([g[200:236] for g in genomes[3:8]])))
+    short.append(("tiny", genomes[0][:20])); short.append(("allN", np.full(150, ord("N"), np.uint8)))
+    long_ = []
+    for i in range(12):
+        s = genomes[i % 48][500:10500].copy()
+        m = rng.random(s.size) < 0.05
+        s[m] = synth.BASES[rng.integers(0, 4, size=int(m.sum()))]
+        long_.append((f"long{i}", s))
+    long_.append(("mosaic48", np.concatenate([g[100:180] for g in genomes])))
+    shards = _make_shards(odb, 4)
+    try:
+        for name, reads, hint in (("short", short, True), ("mixed", short + long_, True), ("long", long_, True), ("long_nohint", long_, False)):
+            synth.write_reads_fasta(str(tmp_path / f"{name}.fa"), reads)
+            ir = oracle.IndexedReads(open(str(tmp_path / f"{name}.fa"), "rb").read())
+            off, cont = ir.pack(31)
+            want, _, nl = odb.query_packed(31, off, cont)
+            got, _, lookups, counts, err = _classify_one_pass_one_gpu(shards, off, cont, cap=int(nl) + 64, n_containers=int(off[-1]) if hint else -1)
+            assert not err and lookups == nl, name
+            assert np.array_equal(got, want), name
+            if name == "short":
+                assert (want[-4:-2, 1] > 0).all()                                        # the mosaics are classified
+        got0, _, l0, _, err0 = _classify_one_pass_one_gpu(shards, np.zeros(1, np.uint32), np.zeros(0, np.uint16), cap=64)
+        assert got0.shape == (0, 5) and l0 == 0 and not err0
+        # a region that is too small: flagged; the vote reads nothing beyond the region
+        _, _, _, counts, err = _classify_one_pass_one_gpu(shards, off, cont, cap=1000)
+        assert err
+    finally:
+        for s in shards:
+            s.close()
