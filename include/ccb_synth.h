@@ -85,4 +85,82 @@ CCB_SYNTH_FN uint32_t ccb_read_code(const ccb_read_plan* p, uint64_t seed, uint3
 /* "TGCA"[code], 'N' for 4 */
 CCB_SYNTH_FN char ccb_code_char(uint32_t code) { return code > 3u ? 'N' : "TGCA"[code]; }
 
+/* ---- the other configurations of SURVEY D2 (C3 pairs, C4 long reads) --------------------------------
+ *   kind 1  pairs: a fragment of `insert` bases of a uniform genome / position / strand; mate 1 = its first
+ *           read_len bases, mate 2 = the reverse complement of its last read_len bases (opposite strands);
+ *           1 % iid substitutions per mate; 9.9 % of the pairs are random sequence, 0.1 % carry one N in
+ *           mate 1.  The read is "<mate1>N<mate2>", what mergePairedFiles writes (src/file.cc:205-268).
+ *   kind 2  long reads: read_len bases walked off a genome window with per-base errors -- ins_pm per mille
+ *           insertions (a random base, the genome does not advance), del_pm deletions (one genome base
+ *           skipped), sub_pm substitutions; 10 % of the reads are random sequence; no N.
+ * Light databases (C3) sample the genomes: the non-overlapping k-mers at positions 0, k, 2k, ... of which
+ * every gap-th is kept (src/CuCLARK_hh.hh:711-767) = one k-mer every gap*k bases. */
+typedef struct ccb_workload {
+    uint32_t kind;       /* 1 pairs, 2 long reads */
+    uint32_t read_len;   /* bases per mate / per read */
+    uint32_t insert;     /* pairs: fragment length (>= read_len) */
+    uint32_t sub_pm, ins_pm, del_pm;    /* per mille per base (pairs: sub_pm only) */
+} ccb_workload;
+
+/* bytes of the longest read text (no terminator) */
+CCB_SYNTH_FN uint32_t ccb_synth2_max_len(const ccb_workload* w) { return w->kind == 1u ? 2u * w->read_len + 1u : w->read_len; }
+/* genome bases a long read may consume */
+CCB_SYNTH_FN uint64_t ccb_synth2_span(const ccb_workload* w)
+{
+    return w->kind == 1u ? (uint64_t)w->insert : (uint64_t)w->read_len + w->read_len / 8u + 8u;
+}
+
+/* text of read i (bases as characters, 'N' between / inside mates); returns its length */
+CCB_SYNTH_FN uint32_t ccb_synth2_text(const ccb_workload* w, uint64_t reads_seed, uint64_t db_seed, uint64_t i,
+                                      uint32_t n_genomes, uint64_t genome_len, char* out)
+{
+    const uint64_t rs = ccb_sm64(reads_seed ^ (i * 0xA24BAED4963EE407ull));
+    const uint64_t a = ccb_sm64(rs + 1), b = ccb_sm64(rs + 2), c = ccb_sm64(rs + 3);
+    const uint32_t u = (uint32_t)(a % 1000u);
+    const uint32_t L = w->read_len;
+    const uint64_t span = ccb_synth2_span(w);
+    const uint64_t gs = ccb_genome_seed(db_seed, (uint32_t)((a >> 20) % n_genomes));
+    const uint64_t pos = b % (genome_len - span + 1);
+    const uint32_t rev = (uint32_t)(c & 1u);
+    if (w->kind == 1u) {
+        const uint32_t kind = u < 900u ? 0u : (u < 999u ? 1u : 2u);
+        const uint32_t n_pos = (uint32_t)((c >> 8) % L);
+        for (uint32_t m = 0; m < 2u; m++) {
+            for (uint32_t j = 0; j < L; j++) {
+                const uint64_t r = ccb_sm64(rs + 16 + m * (L + 1u) + j);
+                uint32_t code;
+                if (kind == 1u) code = (uint32_t)(r & 3u);
+                else {
+                    /* mate (m ^ rev) == 0 reads the fragment forward from its start, the other one backward from its end */
+                    code = (m ^ rev) == 0u ? ccb_genome_code(gs, pos + j) : 3u - ccb_genome_code(gs, pos + span - 1 - j);
+                    if ((r >> 8) % 1000u < w->sub_pm) code = (uint32_t)((r >> 40) & 3u);
+                    if (kind == 2u && m == 0u && j == n_pos) code = 4u;
+                }
+                out[m * (L + 1u) + j] = ccb_code_char(code);
+            }
+        }
+        out[L] = 'N';
+        return 2u * L + 1u;
+    }
+    {
+        const int random_read = u >= 900u;
+        uint64_t gp = 0;                                    /* genome bases consumed */
+        for (uint32_t j = 0; j < L; j++) {
+            const uint64_t r = ccb_sm64(rs + 16 + j);
+            const uint32_t e = (uint32_t)(r % 1000u);
+            uint32_t code;
+            if (random_read || e < w->ins_pm) code = (uint32_t)((r >> 12) & 3u);
+            else {
+                if (e < w->ins_pm + w->del_pm && gp + 2 < span) gp++;
+                if (gp >= span) gp = span - 1;
+                code = rev ? 3u - ccb_genome_code(gs, pos + span - 1 - gp) : ccb_genome_code(gs, pos + gp);
+                gp++;
+                if ((r >> 20) % 1000u < w->sub_pm) code = (uint32_t)((r >> 40) & 3u);
+            }
+            out[j] = ccb_code_char(code);
+        }
+        return L;
+    }
+}
+
 #endif

@@ -56,9 +56,13 @@ typedef struct ccb_stats {
     uint64_t lookups;       /* k-mers probed   (only with CCB_STATS)    */
     uint64_t sectors;       /* 32-byte table sectors read (CCB_STATS)   */
     uint64_t dense_reads;   /* reads re-done by the dense exact path    */
+    uint64_t table_probes;  /* k-mers that went to the k-mer table (the rest were answered by the anchor index); CCB_STATS */
 } ccb_stats;
 
-enum { CCB_EXTENDED = 1, CCB_STATS = 2, CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8,
+enum { CCB_EXTENDED = 1, CCB_STATS = 2 /* lookups = k-mers answered, sectors = 32-byte sectors requested from the table, the
+                                          anchor table and the target text together */,
+       CCB_FORCE_DENSE = 4, CCB_NO_ANCHOR = 8,
+       CCB_STATS_EX = 64 /* with CCB_STATS in ccb_query_device: d_stats holds 4 x u64 {lookups, sectors, table probes, 0} */,
        CCB_WARP_KERNEL = 32 /* warp-per-read kernel for every read (no block kernel, hence no anchor index) */ };
 
 /* CuClarkDB::CuClarkDB (src/CuClarkDB.cu:95-241) / ~CuClarkDB (:248-279) */
@@ -235,7 +239,8 @@ int  ccb_sync(ccb_handle* h);
 /* Device-resident variant of queryBatch for callers that already hold the batch
  * in HBM (multi-GPU pipelines, kernel-only timing): all pointers are device
  * pointers, stream is a cudaStream_t (NULL = default stream).  d_rows may be NULL.
- * d_stats (optional) = 2 x u64 device counters {lookups, sectors}, accumulated. */
+ * d_stats (optional) = 2 x u64 device counters {lookups, sectors}, accumulated (4 x u64 with CCB_STATS_EX:
+ * + {k-mers probed in the k-mer table, 0}). */
 int  ccb_query_device(ccb_handle* h, const void* d_offsets, const void* d_containers,
                       uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
                       int flags, void* stream);
@@ -256,6 +261,14 @@ int  ccb_synth_reads_packed(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed
 int  ccb_synth_reads_text(ccb_handle* h, uint64_t reads_seed, uint64_t db_seed, uint64_t first_read,
                           uint32_t n_reads, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len,
                           char* host_out);
+/* the other configurations (include/ccb_synth.h): a light database (every gap-th non-overlapping k-mer per genome) and
+ * reads of `struct ccb_workload` (kind 1 pairs joined by N, kind 2 long reads with indels), packed on the device */
+struct ccb_workload;
+int  ccb_synth_db_light(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len,
+                        uint32_t n_labels, uint32_t gap, uint64_t* n_kmers);
+int  ccb_synth2_reads_packed(ccb_handle* h, const struct ccb_workload* w, uint64_t reads_seed, uint64_t db_seed,
+                             uint64_t first_read, uint32_t n_reads, uint32_t n_genomes, uint64_t genome_len,
+                             void** d_offsets, void** d_containers, uint64_t* n_containers);
 int  ccb_device_free(ccb_handle* h, void* d_ptr);
 int  ccb_bench_gather(ccb_handle* h, uint64_t n_probes, int bytes, void* stream);
 /* mode 0 uniform / 1 one 2 MiB page per warp load / 2 lane pairs share a 64-B block / 3 lane quads

@@ -9,8 +9,8 @@ g.build()'`` or ``make -C jn_cuclark_b200``).
 """
 from . import host  # noqa: F401
 from .lib import (  # noqa: F401
-    CCB_EXTENDED, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_STATS, CCB_WARP_KERNEL, CcbError, CuClarkDB, CuClarkGroup, lib_path, load_library,
+    CCB_EXTENDED, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_STATS, CCB_STATS_EX, CCB_WARP_KERNEL, CcbError, CuClarkDB, CuClarkGroup, Workload, lib_path, load_library,
 )
 
-__all__ = ["CuClarkDB", "CuClarkGroup", "CcbError", "load_library", "lib_path",
-           "CCB_EXTENDED", "CCB_STATS", "CCB_FORCE_DENSE", "CCB_NO_ANCHOR", "CCB_WARP_KERNEL"]
+__all__ = ["CuClarkDB", "CuClarkGroup", "Workload", "CcbError", "load_library", "lib_path",
+           "CCB_EXTENDED", "CCB_STATS", "CCB_STATS_EX", "CCB_FORCE_DENSE", "CCB_NO_ANCHOR", "CCB_WARP_KERNEL"]

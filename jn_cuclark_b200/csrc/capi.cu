@@ -408,11 +408,11 @@ static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_container
             ok(cudaMallocHost(&s.h_final5, sf));
         }
         slot_no++;
-        ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 16));
+        ok(cudaMallocHost(&s.h_ovf_count, 4)); ok(cudaMallocHost(&s.h_stats, 32));
         ok(cudaMalloc(&s.d_offsets, so)); ok(cudaMalloc(&s.d_cont, sc)); ok(cudaMalloc(&s.d_final5, sf));
         ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 8)); ok(cudaMalloc(&s.d_ovf_count, 8));   // [overflow list | redo list]
         ok(cudaMalloc(&s.d_dense_scratch, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
-        ok(cudaMalloc(&s.d_stats, 16));
+        ok(cudaMalloc(&s.d_stats, 32));
         if (extended) { if (!index_batches) ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
         if (e != cudaSuccess) {
             free_slots(h);
@@ -420,7 +420,7 @@ static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_container
                 return ccb_fail(h, (int)e, "ERROR: Out of GPU memory.\nPlease increase the number of batches (-b <numberofbatches>).");
             return ccb_fail(h, (int)e, "batch allocation failed: %s", cudaGetErrorString(e));
         }
-        *s.h_ovf_count = 0; s.h_stats[0] = s.h_stats[1] = 0;
+        *s.h_ovf_count = 0; s.h_stats[0] = s.h_stats[1] = s.h_stats[2] = s.h_stats[3] = 0;
     }
     return 0;
 }
@@ -493,14 +493,14 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
     QueryArgs a{};
     a.offsets = s.d_offsets; a.containers = s.d_cont; a.n_reads = n_reads;
     a.out5 = s.d_final5; a.rows = (flags & CCB_EXTENDED) ? s.d_rows : nullptr; a.row_stride = h->row_stride;
-    a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr;
-    if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 16, s.stream));
+    a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr; a.stats_words = 4;
+    if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 32, s.stream));
     int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, h->max_reads, s.d_dense_scratch, flags, s.stream, (int64_t)n_containers);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     CU(h, cudaMemcpyAsync(s.h_final5, s.d_final5, (size_t)n_reads * 10, cudaMemcpyDeviceToHost, s.stream));
     if (flags & CCB_EXTENDED) CU(h, cudaMemcpyAsync(s.h_rows, s.d_rows, (size_t)n_reads * h->row_stride * 2, cudaMemcpyDeviceToHost, s.stream));
     CU(h, cudaMemcpyAsync(s.h_ovf_count, s.d_ovf_count, 4, cudaMemcpyDeviceToHost, s.stream));
-    if (flags & CCB_STATS) CU(h, cudaMemcpyAsync(s.h_stats, s.d_stats, 16, cudaMemcpyDeviceToHost, s.stream));
+    if (flags & CCB_STATS) CU(h, cudaMemcpyAsync(s.h_stats, s.d_stats, 32, cudaMemcpyDeviceToHost, s.stream));
     CU(h, cudaEventRecord(s.done, s.stream));
     s.in_flight = true;
     return 0;
@@ -511,7 +511,7 @@ static void harvest(ccb_handle* h, Slot& s)
     std::lock_guard<std::mutex> g(h->mu);          // slots may be waited on from several host threads
     h->stats.reads += s.n_reads;
     h->stats.dense_reads += (s.flags & CCB_FORCE_DENSE) ? s.n_reads : *s.h_ovf_count;
-    if (s.flags & CCB_STATS) { h->stats.lookups += s.h_stats[0]; h->stats.sectors += s.h_stats[1]; }
+    if (s.flags & CCB_STATS) { h->stats.lookups += s.h_stats[0]; h->stats.sectors += s.h_stats[1]; h->stats.table_probes += s.h_stats[2]; }
     s.in_flight = false;
 }
 
@@ -568,7 +568,7 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
     QueryArgs a{};
     a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
     a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
-    a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr;
+    a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr; a.stats_words = (flags & CCB_STATS_EX) ? 4 : 2;
     int rc = run_query(h, a, h->q_ovf_list, h->q_ovf_count, h->q_ovf_cap, h->q_dense, flags, (cudaStream_t)stream);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     return 0;

@@ -43,6 +43,9 @@ void anchor_free(Anchor& a);
 struct AnchorBuild;                  // anchor.cu: target texts being collected (ccb_anchor_begin .. ccb_anchor_end)
 void anchor_build_free(ccb_handle* h);
 struct BuildState;                   // dbbuild.cu
+// shard.cu: exclusive prefix sum of u32 in place (three small kernels); tmp holds scan_tmp_words(n) u32
+size_t scan_tmp_words(size_t n);
+int    exclusive_scan_u32(uint32_t* d, size_t n, uint32_t* tmp, cudaStream_t s);
 // group.cu: several devices, one sharded table, behind one leader handle
 struct Group;
 void group_destroy(ccb_handle* h);

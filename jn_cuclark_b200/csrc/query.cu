@@ -317,7 +317,7 @@ k_query(const TableView t, const QueryArgs a, const RouteArgs ra)
                 l += __shfl_xor_sync(0xFFFFFFFFu, l, o);
                 s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
             }
-            if (lane == 0) { atomicAdd(a.stats + 0, l); atomicAdd(a.stats + 1, s); }
+            if (lane == 0) { atomicAdd(a.stats + 0, l); atomicAdd(a.stats + 1, s); if (a.stats_words > 2) atomicAdd(a.stats + 2, l); }
         }
     }
     if (MODE == kModeRoute) __threadfence_system();      // the stores may have gone to a peer GPU

@@ -20,6 +20,7 @@ struct QueryArgs {
     uint32_t*       ovf_count;
     // optional accounting [0]=k-mers probed [1]=32-byte sectors read
     unsigned long long* stats;
+    int             stats_words;     // 2, or 4: [2] = k-mers probed in the k-mer table (not answered by the anchor index)
     // optional: classify only the reads listed (read_list[0 .. min(*n_list, n_reads)) ), e.g. the ones the
     // thread-per-read kernel handed back
     const uint32_t* read_list;

@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
     const uint64_t kmsk = t.hp.mask;
     const int s2 = 2 * (k - 1);
     const int tid = threadIdx.x;
-    unsigned long long st_lookups = 0, st_sectors = 0;
+    unsigned long long st_lookups = 0, st_sectors = 0, st_table = 0;
     const uint32_t nblocks = (a.n_reads + BLK - 1) / BLK;
     // the queue is empty and every read's vote pairs are clear at the top of an iteration: phase C leaves them so
     // (three barriers per iteration: A|B, B|C, C|next A)
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                 if (need[j]) {
                     uint32_t probes = 1;
                     const uint32_t l = resolve(t, home[j], q[j], e[j], STATS ? &probes : nullptr);
-                    if (STATS) { st_lookups++; st_sectors += probes; }
+                    if (STATS) { st_lookups++; st_table++; st_sectors += probes; }
                     if (l < kLabelTomb) {
                         if (l == run_lab) run_cnt++;
                         else { if (run_cnt) vote_smem(sm, lr, run_lab, run_cnt); run_lab = l; run_cnt = 1; }
@@ -446,8 +446,12 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
         for (int o = 16; o; o >>= 1) {
             st_lookups += __shfl_xor_sync(0xFFFFFFFFu, st_lookups, o);
             st_sectors += __shfl_xor_sync(0xFFFFFFFFu, st_sectors, o);
+            st_table += __shfl_xor_sync(0xFFFFFFFFu, st_table, o);
         }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(a.stats + 0, st_lookups); atomicAdd(a.stats + 1, st_sectors); }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(a.stats + 0, st_lookups); atomicAdd(a.stats + 1, st_sectors);
+            if (a.stats_words > 2) atomicAdd(a.stats + 2, st_table);
+        }
     }
 }
 

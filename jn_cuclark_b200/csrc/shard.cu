@@ -109,6 +109,9 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_apply(uint32_t* __restric
     for (int j = 0; j < kScanPer; j++) { if (base + j < n) d[base + j] = run; run += v[j]; }
 }
 
+}  // namespace
+
+namespace ccb {
 size_t scan_tmp_words(size_t n) { return (n + kScanTile - 1) / kScanTile + 1; }
 
 int exclusive_scan_u32(uint32_t* d, size_t n, uint32_t* tmp, cudaStream_t s)
@@ -120,7 +123,7 @@ int exclusive_scan_u32(uint32_t* d, size_t n, uint32_t* tmp, cudaStream_t s)
     k_scan_apply<<<nb, kScanThreads, 0, s>>>(d, n, tmp);
     return (int)cudaGetLastError();
 }
-}  // namespace
+}  // namespace ccb
 
 // the scratch set of a stream (first use claims one of four)
 static ccb_handle::ShardScratch* shard_scratch_for(ccb_handle* h, void* stream)

@@ -5,7 +5,6 @@
 #include "../../include/cuclark_b200.h"
 #include "../../include/ccb_synth.h"
 #include "capi_internal.cuh"
-#include <cub/device/device_scan.cuh>
 
 using namespace ccb;
 
@@ -133,9 +132,10 @@ extern "C" int ccb_synth_reads_packed(ccb_handle* h, uint64_t reads_seed, uint64
     cudaMemsetAsync(slots + n_reads, 0, 4, s);
     uint32_t g = (n_reads + 255) / 256;
     k_synth_count<<<g, 256, 0, s>>>(reads_seed, first_read, n_reads, read_len, h->cfg.k, n_genomes, genome_len, slots);
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, slots, off, n_reads + 1, s);
+    tmp_bytes = scan_tmp_words((size_t)n_reads + 1) * 4;
     cudaMalloc(&tmp, tmp_bytes);
-    cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, slots, off, n_reads + 1, s);
+    cudaMemcpyAsync(off, slots, ((size_t)n_reads + 1) * 4, cudaMemcpyDeviceToDevice, s);
+    exclusive_scan_u32(off, (size_t)n_reads + 1, (uint32_t*)tmp, s);
     uint32_t total = 0;
     cudaMemcpyAsync(&total, off + n_reads, 4, cudaMemcpyDeviceToHost, s);
     cudaStreamSynchronize(s);
@@ -163,6 +163,129 @@ extern "C" int ccb_synth_reads_text(ccb_handle* h, uint64_t reads_seed, uint64_t
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->db_stream);
     cudaFree(d);
     if (e != cudaSuccess) return ccb_fail(h, (int)e, "synth text: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// The other configurations (include/ccb_synth.h: C3 pairs on a light database, C4 long reads with indels)
+// ---------------------------------------------------------------------------
+namespace {
+
+// light database: of each genome the non-overlapping k-mers at 0, k, 2k, ... every gap-th (src/CuCLARK_hh.hh:711-767)
+__global__ void k_synth_db_light(uint64_t* buckets, uint32_t* flags, uint32_t* status, unsigned long long* counts,
+                                 HashParams hp, uint64_t seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels, uint32_t gap)
+{
+    const int k = hp.k;
+    const uint64_t step = (uint64_t)gap * k;
+    const uint64_t per_genome = (genome_len - k) / step + 1;
+    const uint64_t total = per_genome * n_genomes;
+    const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
+    for (uint64_t s = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; s < total; s += stride) {
+        const uint32_t g = (uint32_t)(s / per_genome);
+        const uint64_t p0 = (s % per_genome) * step;
+        const uint64_t gs = ccb_genome_seed(seed, g);
+        uint64_t x = 0;
+        for (int j = 0; j < k; j++) x = (x << 2) | ccb_genome_code(gs, p0 + j);
+        insert_one(buckets, flags, status, counts, hp, canonical(x & hp.mask, k), g % n_labels);
+    }
+}
+
+__global__ void k_synth2_text(ccb_workload w, uint64_t rseed, uint64_t dseed, uint64_t first, uint32_t n_reads,
+                              uint32_t n_genomes, uint64_t genome_len, uint32_t stride, char* text, uint32_t* len)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    len[i] = ccb_synth2_text(&w, rseed, dseed, first + i, n_genomes, genome_len, text + (size_t)i * stride);
+}
+
+// the reference's packing rules on a text (src/CuCLARK_hh.hh:1629-1707): maximal ACGT runs, runs shorter than k dropped
+template <bool FILL>
+__global__ void k_pack_text(const char* __restrict__ text, const uint32_t* __restrict__ len, uint32_t stride, uint32_t n_reads, int k,
+                            uint32_t* slots, const uint32_t* offsets, uint16_t* cont)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    const char* t = text + (size_t)i * stride;
+    const uint32_t L = len[i];
+    uint32_t total = 0;
+    uint16_t* o = FILL ? cont + offsets[i] : nullptr;
+    uint32_t q = 0;
+    while (q < L) {
+        while (q < L && t[q] == 'N') q++;
+        uint32_t e = q;
+        while (e < L && t[e] != 'N') e++;
+        const uint32_t run = e - q;
+        if (run >= (uint32_t)k) {
+            total += slots_of_part(run);
+            if (FILL) {
+                *o++ = (uint16_t)run;
+                uint32_t acc = 0, cnt = 0;
+                for (uint32_t x = q; x < e; x++) {
+                    const char c = t[x];
+                    acc = (acc << 2) | (c == 'A' ? 3u : c == 'C' ? 2u : c == 'G' ? 1u : 0u);
+                    if (++cnt == 8) { *o++ = (uint16_t)acc; acc = 0; cnt = 0; }
+                }
+                if (cnt) *o++ = (uint16_t)(acc << (2 * (8 - cnt)));
+            }
+        }
+        q = e;
+    }
+    if (!FILL) slots[i] = total;
+}
+
+}  // namespace
+
+extern "C" int ccb_synth_db_light(ccb_handle* h, uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len,
+                                  uint32_t n_labels, uint32_t gap, uint64_t* n_kmers)
+{
+    if (!h || n_genomes == 0 || genome_len < (uint64_t)h->cfg.k || n_labels == 0 || gap == 0) return ccb_fail(h, -40, "ccb_synth_db_light: bad arguments");
+    const uint64_t total = (uint64_t)n_genomes * ((genome_len - h->cfg.k) / ((uint64_t)gap * h->cfg.k) + 1);
+    int rc = ccb_db_begin(h, total);
+    if (rc) return rc;
+    Table& t = h->table;
+    k_synth_db_light<<<148 * 16, 256, 0, h->db_stream>>>((uint64_t*)t.d_buckets - t.lo * kSlots, t.d_flags - t.lo / 16, t.d_status, t.d_counts, t.hp,
+                                                          db_seed, n_genomes, genome_len, n_labels, gap);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ccb_fail(h, (int)e, "k_synth_db_light launch: %s", cudaGetErrorString(e));
+    rc = ccb_db_end(h);
+    if (rc) return rc;
+    if (n_kmers) *n_kmers = total;
+    return 0;
+}
+
+extern "C" int ccb_synth2_reads_packed(ccb_handle* h, const ccb_workload* w, uint64_t reads_seed, uint64_t db_seed, uint64_t first_read,
+                                       uint32_t n_reads, uint32_t n_genomes, uint64_t genome_len,
+                                       void** d_offsets, void** d_containers, uint64_t* n_containers)
+{
+    if (!h || !w || !d_offsets || !d_containers || n_reads == 0 || (w->kind != 1u && w->kind != 2u) || w->read_len == 0 ||
+        (w->kind == 1u && w->insert < w->read_len) || genome_len < ccb_synth2_span(w))
+        return ccb_fail(h, -41, "ccb_synth2_reads_packed: bad arguments");
+    cudaSetDevice(h->cfg.device);
+    cudaStream_t s = h->db_stream;
+    const uint32_t stride = ccb_synth2_max_len(w);
+    char* text = nullptr; uint32_t *len = nullptr, *off = nullptr, *tmp = nullptr; uint16_t* cont = nullptr;
+    cudaError_t e = cudaMalloc(&text, (size_t)n_reads * stride);
+    if (e == cudaSuccess) e = cudaMalloc(&len, (size_t)n_reads * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&off, ((size_t)n_reads + 1) * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&tmp, scan_tmp_words((size_t)n_reads + 1) * 4);
+    if (e != cudaSuccess) { cudaFree(text); cudaFree(len); cudaFree(off); cudaFree(tmp); return ccb_fail(h, (int)e, "cudaMalloc: %s", cudaGetErrorString(e)); }
+    const uint32_t g = (n_reads + 127) / 128;
+    k_synth2_text<<<g, 128, 0, s>>>(*w, reads_seed, db_seed, first_read, n_reads, n_genomes, genome_len, stride, text, len);
+    cudaMemsetAsync(off + n_reads, 0, 4, s);
+    k_pack_text<false><<<g, 128, 0, s>>>(text, len, stride, n_reads, h->cfg.k, off, nullptr, nullptr);
+    exclusive_scan_u32(off, (size_t)n_reads + 1, tmp, s);
+    uint32_t total = 0;
+    cudaMemcpyAsync(&total, off + n_reads, 4, cudaMemcpyDeviceToHost, s);
+    e = cudaStreamSynchronize(s);
+    if (e == cudaSuccess) e = cudaMalloc(&cont, ((size_t)total + 8) * 2);
+    if (e == cudaSuccess) {
+        k_pack_text<true><<<g, 128, 0, s>>>(text, len, stride, n_reads, h->cfg.k, nullptr, off, cont);
+        e = cudaStreamSynchronize(s);
+    }
+    cudaFree(text); cudaFree(len); cudaFree(tmp);
+    if (e != cudaSuccess) { cudaFree(off); cudaFree(cont); return ccb_fail(h, (int)e, "synth reads: %s", cudaGetErrorString(e)); }
+    *d_offsets = off; *d_containers = cont;
+    if (n_containers) *n_containers = total;
     return 0;
 }
 

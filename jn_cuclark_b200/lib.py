@@ -15,7 +15,7 @@ import os
 
 import numpy as np
 
-CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_WARP_KERNEL = 1, 2, 4, 8, 32
+CCB_EXTENDED, CCB_STATS, CCB_FORCE_DENSE, CCB_NO_ANCHOR, CCB_WARP_KERNEL, CCB_STATS_EX = 1, 2, 4, 8, 32, 64
 default_flags = 0          # ORed into every query (tests run the parity suite once per kernel with it)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -38,6 +38,12 @@ class _Config(C.Structure):
                 ("n_slots", C.c_int), ("load_factor", C.c_double), ("verbose", C.c_int)]
 
 
+class Workload(C.Structure):
+    """struct ccb_workload (include/ccb_synth.h): kind 1 pairs joined by N, kind 2 long reads with indels"""
+    _fields_ = [("kind", C.c_uint32), ("read_len", C.c_uint32), ("insert", C.c_uint32),
+                ("sub_pm", C.c_uint32), ("ins_pm", C.c_uint32), ("del_pm", C.c_uint32)]
+
+
 class DbInfo(C.Structure):
     _fields_ = [("entries", C.c_uint64), ("buckets", C.c_uint64), ("bytes", C.c_uint64),
                 ("tombstones", C.c_uint64), ("max_displacement", C.c_uint32)]
@@ -54,7 +60,7 @@ class AnchorInfo(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("reads", C.c_uint64), ("lookups", C.c_uint64), ("sectors", C.c_uint64),
-                ("dense_reads", C.c_uint64)]
+                ("dense_reads", C.c_uint64), ("table_probes", C.c_uint64)]
 
 
 _lib = None
@@ -119,6 +125,9 @@ SYMBOLS = {
                                          C.c_uint64, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(C.c_uint64)]),
     "ccb_synth_reads_text": (C.c_int, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
                                        C.c_uint64, _VP]),
+    "ccb_synth_db_light": (C.c_int, [_H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]),
+    "ccb_synth2_reads_packed": (C.c_int, [_H, _VP, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64,
+                                          C.POINTER(_VP), C.POINTER(_VP), C.POINTER(C.c_uint64)]),
     "ccb_device_free": (C.c_int, [_H, _VP]),
     "ccb_bench_gather": (C.c_int, [_H, C.c_uint64, C.c_int, _VP]),
     "ccb_bench_gather_ex": (C.c_int, [_H, C.c_uint64, C.c_int, C.c_int, C.c_uint64, _VP]),
@@ -411,6 +420,20 @@ class CuClarkDB:
         o, c, n = _VP(), _VP(), C.c_uint64(0)
         self._ck(self._lib.ccb_synth_reads_packed(self._h, reads_seed, db_seed, first, n_reads, read_len, n_genomes,
                                                   genome_len, C.byref(o), C.byref(c), C.byref(n)))
+        return o.value, c.value, n.value
+
+    def synth_db_light(self, db_seed: int, n_genomes: int, genome_len: int, n_labels: int, gap: int = 4) -> int:
+        """Light database of the synthetic genomes: every gap-th non-overlapping k-mer (src/CuCLARK_hh.hh:711-767)."""
+        n = C.c_uint64(0)
+        self._ck(self._lib.ccb_synth_db_light(self._h, db_seed, n_genomes, genome_len, n_labels, gap, C.byref(n)))
+        return n.value
+
+    def synth2_reads_packed(self, w: "Workload", reads_seed: int, db_seed: int, first: int, n_reads: int, n_genomes: int, genome_len: int):
+        """Reads of a ccb_workload (pairs joined by N / long reads with indels), packed on the device.
+        -> (d_offsets, d_containers, n_containers): raw device pointers owned by the caller (device_free)."""
+        o, c, n = _VP(), _VP(), C.c_uint64(0)
+        self._ck(self._lib.ccb_synth2_reads_packed(self._h, C.byref(w), reads_seed, db_seed, first, n_reads, n_genomes, genome_len,
+                                                   C.byref(o), C.byref(c), C.byref(n)))
         return o.value, c.value, n.value
 
     def synth_reads_text(self, reads_seed: int, db_seed: int, first: int, n_reads: int, read_len: int,

@@ -719,6 +719,13 @@ int ccbo_merge_paired(const char *f1, const char *f2, const char *outp)
 int ccbo_synth_db(uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels,
                   int k, uint64_t htsize, ccbo_db *db)
 {
+    return ccbo_synth_db_ex(db_seed, n_genomes, genome_len, n_labels, k, htsize, 0, 0, db);
+}
+
+/* light != 0: the light-mode scan (every gap-th non-overlapping k-mer, ccbo_extract_fasta) over the same genomes */
+int ccbo_synth_db_ex(uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels,
+                     int k, uint64_t htsize, int light, unsigned gap, ccbo_db *db)
+{
     ccbo_occ_vec occ = {0};
     unsigned char *txt = malloc(genome_len + 8);
     if (!txt) return -1;
@@ -726,7 +733,7 @@ int ccbo_synth_db(uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uin
     for (uint32_t g = 0; g < n_genomes; g++) {
         uint64_t gs = ccb_genome_seed(db_seed, g);
         for (uint64_t p = 0; p < genome_len; p++) txt[3 + p] = (unsigned char)ccb_code_char(ccb_genome_code(gs, p));
-        int rc = ccbo_extract_fasta(txt, 3 + genome_len, k, 0, 0, (uint16_t)(g % n_labels), &occ);
+        int rc = ccbo_extract_fasta(txt, 3 + genome_len, k, light, gap, (uint16_t)(g % n_labels), &occ);
         if (rc) { free(txt); free(occ.v); return rc; }
     }
     free(txt);
@@ -746,6 +753,23 @@ int ccbo_synth_reads_fasta(const char *path, uint64_t reads_seed, uint64_t db_se
         line[read_len] = '\n';
         fprintf(f, ">r%lu\n", (unsigned long)(first + i));
         fwrite(line, 1, read_len + 1, f);
+    }
+    free(line); fclose(f);
+    return 0;
+}
+
+/* FASTA text of the reads of a ccb_workload (include/ccb_synth.h: pairs joined by N, long reads with indels) */
+int ccbo_synth2_reads_fasta(const char *path, const ccb_workload *w, uint64_t reads_seed, uint64_t db_seed, uint64_t first,
+                            uint32_t n, uint32_t n_genomes, uint64_t genome_len)
+{
+    FILE *f = fopen(path, "wb");
+    if (!f) return -1;
+    char *line = malloc(ccb_synth2_max_len(w) + 2);
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t len = ccb_synth2_text(w, reads_seed, db_seed, first + i, n_genomes, genome_len, line);
+        line[len] = '\n';
+        fprintf(f, ">r%lu\n", (unsigned long)(first + i));
+        fwrite(line, 1, len + 1, f);
     }
     free(line); fclose(f);
     return 0;

@@ -161,6 +161,11 @@ int ccbo_merge_paired(const char *f1, const char *f2, const char *out);
 /* ---- synthetic benchmark workload (include/ccb_synth.h) ---------------- */
 int ccbo_synth_db(uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels,
                   int k, uint64_t htsize, ccbo_db *db);
+int ccbo_synth_db_ex(uint64_t db_seed, uint32_t n_genomes, uint64_t genome_len, uint32_t n_labels,
+                     int k, uint64_t htsize, int light, unsigned gap, ccbo_db *db);
+struct ccb_workload;
+int ccbo_synth2_reads_fasta(const char *path, const struct ccb_workload *w, uint64_t reads_seed, uint64_t db_seed, uint64_t first,
+                            uint32_t n, uint32_t n_genomes, uint64_t genome_len);
 int ccbo_synth_reads_fasta(const char *path, uint64_t reads_seed, uint64_t db_seed, uint64_t first,
                            uint32_t n, uint32_t read_len, uint32_t n_genomes, uint64_t genome_len);
 

@@ -73,8 +73,21 @@ def lib() -> C.CDLL:
         L.ccbo_db_from_occ.argtypes = [C.POINTER(OccVec), C.c_int, C.c_uint64, C.c_uint, C.POINTER(Db)]
         L.ccbo_synth_db.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_int, C.c_uint64, C.POINTER(Db)]
         L.ccbo_synth_reads_fasta.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64]
+        L.ccbo_synth_db_ex.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_int, C.c_uint64, C.c_int, C.c_uint, C.POINTER(Db)]
+        L.ccbo_synth2_reads_fasta.argtypes = [C.c_char_p, C.POINTER(Workload), C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64]
         _lib = L
     return _lib
+
+
+class Workload(C.Structure):
+    """struct ccb_workload (include/ccb_synth.h): kind 1 pairs joined by N, kind 2 long reads with indels"""
+    _fields_ = [("kind", C.c_uint32), ("read_len", C.c_uint32), ("insert", C.c_uint32),
+                ("sub_pm", C.c_uint32), ("ins_pm", C.c_uint32), ("del_pm", C.c_uint32)]
+
+
+def synth2_reads_fasta(path: str, w: "Workload", reads_seed: int, db_seed: int, first: int, n: int, n_genomes: int, genome_len: int):
+    rc = lib().ccbo_synth2_reads_fasta(path.encode(), C.byref(w), reads_seed, db_seed, first, n, n_genomes, genome_len)
+    assert rc == 0, rc
 
 
 class OracleDb:
@@ -114,9 +127,9 @@ class OracleDb:
         return self
 
     @classmethod
-    def synth(cls, db_seed: int, n_genomes: int, genome_len: int, n_labels: int, k: int, htsize: int):
+    def synth(cls, db_seed: int, n_genomes: int, genome_len: int, n_labels: int, k: int, htsize: int, light_gap: int = 0):
         self = cls()
-        rc = lib().ccbo_synth_db(db_seed, n_genomes, genome_len, n_labels, k, htsize, C.byref(self.db))
+        rc = lib().ccbo_synth_db_ex(db_seed, n_genomes, genome_len, n_labels, k, htsize, 1 if light_gap else 0, light_gap, C.byref(self.db))
         assert rc == 0, rc
         return self
 

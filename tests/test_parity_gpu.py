@@ -249,3 +249,51 @@ def test_malloc_ref_contiguous_results(small_world, oracle, full_db, extended):
             assert rows[i, 0] == cnt[i] and np.array_equal(rows[i, 1:1 + 2 * cnt[i]], wrows[i, 1:1 + 2 * cnt[i]])
     db.freeBatchMemory()
     db.close()
+
+
+@pytest.mark.parametrize("which", ["c3_pairs_light", "c4_long_indels"])
+def test_synthetic_c3_c4_workloads_match_oracle(oracle, tmp_path, which):
+    """The other bench workloads (include/ccb_synth.h: pairs joined by N on a light database = C3, long reads with 5 %
+    errors incl. indels = C4): the device generator's packed batch equals the oracle's text of the same reads packed with
+    the reference's rules, the database equals the oracle's scan of the same genomes, results are bit-exact, with and
+    without the anchor index."""
+    import ctypes as C
+    import torch
+    from jn_cuclark_b200 import CuClarkDB, Workload, CCB_STATS, CCB_NO_ANCHOR
+    if which == "c3_pairs_light":
+        G, LG, NR, k, gap = 6, 40000, 3000, 27, 4
+        w = Workload(1, 150, 400, 10, 0, 0); ow = oracle.Workload(1, 150, 400, 10, 0, 0)
+        db = CuClarkDB(1, k, 1, G, max_hits=23)
+        n = db.synth_db_light(0xC1A2C000, G, LG, G, gap)
+        odb = oracle.OracleDb.synth(0xC1A2C000, G, LG, G, k, HT_SMALL, light_gap=gap)
+        assert n == G * ((LG - k) // (gap * k) + 1)
+    else:
+        G, LG, NR, k = 5, 60000, 300, 31
+        w = Workload(2, 10000, 0, 30, 10, 10); ow = oracle.Workload(2, 10000, 0, 30, 10, 10)
+        db = CuClarkDB(1, k, 1, G)
+        db.synth_db(0xC1A2C000, G, LG, G)
+        odb = oracle.OracleDb.synth(0xC1A2C000, G, LG, G, k, HT_SMALL)
+    assert db.db_info().entries == odb.n
+    d_off, d_cont, nc = db.synth2_reads_packed(w, 0x5EED0003, 0xC1A2C000, 7, NR, G, LG)
+    off = torch.empty(NR + 1, dtype=torch.int32, device="cuda"); cont = torch.empty(nc, dtype=torch.int16, device="cuda")
+    rt = C.cdll.LoadLibrary("libcudart.so")
+    rt.cudaMemcpy(C.c_void_p(off.data_ptr()), C.c_void_p(d_off), C.c_size_t((NR + 1) * 4), 3)
+    rt.cudaMemcpy(C.c_void_p(cont.data_ptr()), C.c_void_p(d_cont), C.c_size_t(nc * 2), 3)
+    fa = str(tmp_path / "r.fa")
+    oracle.synth2_reads_fasta(fa, ow, 0x5EED0003, 0xC1A2C000, 7, NR, G, LG)
+    ir = oracle.IndexedReads(open(fa, "rb").read())
+    off_o, cont_o = ir.pack(k)
+    assert np.array_equal(off.cpu().numpy().view(np.uint32), off_o) and np.array_equal(cont.cpu().numpy().view(np.uint16), cont_o)
+    want, _, nl = odb.query_packed(k, off_o, cont_o)
+    assert (want[:, 1] > 0).mean() > 0.5
+    out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda"); stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, stats.data_ptr(), CCB_STATS, st)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint16).reshape(-1, 5), want) and int(stats[0]) == nl
+    db.anchor_synth(0xC1A2C000, G, LG, G)
+    out.zero_()
+    db.query_device(d_off, d_cont, NR, out.data_ptr(), 0, 0, 0, st)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint16).reshape(-1, 5), want)
+    db.device_free(d_off); db.device_free(d_cont); db.close()
