@@ -559,7 +559,7 @@ def sharded_leg(args, rank, world, local, d_off, d_cont, n_cont, out_h, total_lo
     import torch
     import torch.distributed as dist
     from jn_cuclark_b200 import CuClarkDB
-    from jn_cuclark_b200.sharded import ShardedClassifier, PeerShardedClassifier, region_size
+    from jn_cuclark_b200.sharded import ShardedClassifier, PeerShardedClassifier, PipelinedPeerClassifier, region_size
     k, G, LG, NR, L = args.k, args.genomes, args.genome_len, args.reads, args.read_len
     cudart = C.CDLL("libcudart.so")
     sdb = CuClarkDB(1, k, 1, min(G, 65534), device=local, load_factor=args.load_factor)
@@ -571,14 +571,23 @@ def sharded_leg(args, rank, world, local, d_off, d_cont, n_cont, out_h, total_lo
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
     leg = {"what": f"table sharded x{world} by hash range (shard {info.bytes / 1e9:.1f} GB per GPU), the same reads; one-pass route "
                    "(k_route_block) -> owner-side probe (k_probe_inbox / k_probe_list) -> block-wise vote (k_vote_block)",
-           "shard_gb": info.bytes / 1e9, "shard_entries": info.entries, "db_build_s": t_db, "region_kmers": cap, "exchanges": {}}
-    for exch in ("peer", "nccl"):
-        sc = PeerShardedClassifier(sdb, cap, NR) if exch == "peer" else ShardedClassifier(sdb, cap, NR)
+           "shard_gb": info.bytes / 1e9, "shard_entries": info.entries, "db_build_s": t_db, "region_kmers": cap,
+           "exchange_variants": {"peer": "kernels store k-mers / labels straight into peer memory (CUDA IPC over NVLink), one batch at a time",
+                                 "peer_pipelined": f"the same, the batch cut into {NCH} chunks through two pipelines on two streams: one chunk's probe runs beside the next one's route",
+                                 "nccl": "NCCL all-to-all of the k-mers and of the labels (one host sync per batch for the sizes)"},
+           "exchanges": {}}
+    NCH = 4                                                            # chunks of the pipelined variant, two in flight
+    per_chunk = (NR + NCH - 1) // NCH
+    for exch in ("peer_pipelined", "peer", "nccl"):
+        if exch == "peer_pipelined":
+            sc = PipelinedPeerClassifier(sdb, region_size(per_chunk, L - k + 1, world), per_chunk, n_pipes=2)
+        else:
+            sc = PeerShardedClassifier(sdb, cap, NR) if exch == "peer" else ShardedClassifier(sdb, cap, NR)
         stats.zero_(); out.zero_()
         sc.classify(d_off, d_cont, NR, out, stats=stats, n_containers=n_cont)
         torch.cuda.synchronize()
         same = bool(np.array_equal(out.cpu().numpy().view(np.uint16).reshape(-1, 5), out_h))
-        overflow = sc.overflowed() if exch == "peer" else False
+        overflow = sc.overflowed() if exch != "nccl" else False
         ok = torch.tensor([1 if (same and not overflow) else 0], dtype=torch.int32, device="cuda")
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         probes_here = int(stats[0])

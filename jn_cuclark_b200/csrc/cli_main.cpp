@@ -546,6 +546,10 @@ int main(int argc, char** argv)
         }
         if (val == "--verbose") { c.verbose = true; continue; }
         if (val == "--sharded") { c.sharded = true; continue; }
+        // `kent -c -P f1 f2 ...` ends its command line with --light, and classify_metagenome.sh:104-137 forwards everything
+        // after the second mate untouched (FILE2 is never reset): the reference's own cuCLARK-l then stops at
+        // "Failed to recognize option: --light".  The light binary takes its own name as a no-op instead.
+        if (val == "--light" && kLight) continue;
         if (val == "--gzipped") { c.gzipped = true; continue; }
         if (val == "-m") { need(i, "Please specify the mode!"); continue; }      // tolerated, ignored
         cerr << "Failed to recognize option: " << val << endl;

@@ -21,6 +21,7 @@
 //    (src/CuClarkDB.cu:1380-1399).
 #include "query.cuh"
 #include "vote.cuh"
+#include <stdlib.h>
 
 namespace ccb {
 
@@ -603,8 +604,11 @@ __global__ void __launch_bounds__(256) k_probe_inbox(const TableView t, const In
 
 int launch_probe_inbox(const TableView& t, const InboxArgs& ia, unsigned long long* stats, cudaStream_t s)
 {
-    if (stats) k_probe_inbox<true><<<148 * 32, 256, 0, s>>>(t, ia, stats);
-    else       k_probe_inbox<false><<<148 * 32, 256, 0, s>>>(t, ia, stats);
+    // two blocks per SM (2048 probes in flight per SM, several times what the DRAM request rate needs; 78 registers
+    // each) leave room for the route kernel of another batch on the same SMs (shard_block.cu launch_route_block)
+    static const int per_sm = getenv("CCB_PROBE_CTAS_PER_SM") ? atoi(getenv("CCB_PROBE_CTAS_PER_SM")) : 2;
+    if (stats) k_probe_inbox<true><<<148 * per_sm, 256, 0, s>>>(t, ia, stats);
+    else       k_probe_inbox<false><<<148 * per_sm, 256, 0, s>>>(t, ia, stats);
     return (int)cudaGetLastError();
 }
 

@@ -231,12 +231,12 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                         const uint64_t b0 = mulhi64(h0 << t.hp.shift, av.nb), b1 = mulhi64(h1 << t.hp.shift, av.nb);
                         const uint32_t fp0 = (uint32_t)h0 & 0x7FFFu, fp1 = (uint32_t)h1 & 0x7FFFu;
                         uint64_t e0[4], e1[4];
-                        load_bucket(av.buckets + b0, e0);
-                        if (nc > 1) load_bucket(av.buckets + b1, e1);
+                        load_bucket64(av.buckets + b0, e0);                      // a full sector overflows into b ^ 1: the same 64 bytes
+                        if (nc > 1) load_bucket64(av.buckets + b1, e1);
                         if (STATS) st_sectors += nc;
                         uint64_t m = match_anchor(e0, fp0);
                         if (m == ~0ull && e0[3] != ~0ull) {                       // full sector: its neighbour may hold it
-                            load_bucket(av.buckets + (b0 ^ 1ull), e0);
+                            load_bucket64(av.buckets + (b0 ^ 1ull), e0);
                             if (STATS) st_sectors++;
                             m = match_anchor(e0, fp0);
                         }
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                         else if (nc > 1) {
                             m = match_anchor(e1, fp1);
                             if (m == ~0ull && e1[3] != ~0ull) {
-                                load_bucket(av.buckets + (b1 ^ 1ull), e1);
+                                load_bucket64(av.buckets + (b1 ^ 1ull), e1);
                                 if (STATS) st_sectors++;
                                 m = match_anchor(e1, fp1);
                             }

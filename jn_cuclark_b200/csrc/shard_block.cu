@@ -19,6 +19,7 @@
 // k_query<count/route> passes on a list; a read that meets a fifth target is re-voted by k_vote_block_dense.
 #include "query.cuh"
 #include "vote.cuh"
+#include <stdlib.h>
 
 namespace ccb {
 
@@ -204,8 +205,12 @@ int launch_route_block(const HashParams& hp, const QueryArgs& a, const BlockRout
     if (ra.n_shards < 1 || ra.n_shards > (uint32_t)kMaxShards) return -60;
     constexpr int BLK = kRouteBlk;
     const size_t smem = sizeof(RouteSmem<BLK>);
+    // a persistent grid of two blocks per SM: the route of one batch is meant to run BESIDE the probe of another one
+    // (k_probe_inbox, two blocks per SM; the vote takes what is left) -- routing is issue- and NVLink-bound, probing
+    // HBM-bound, and two GPU-filling grids would just run one after the other
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
-    if (ctas > 148u * 64u) ctas = 148u * 64u;
+    static const uint32_t per_sm = getenv("CCB_ROUTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_ROUTE_CTAS_PER_SM")) : 2u;
+    if (ctas > 148u * per_sm) ctas = 148u * per_sm;
     cudaError_t e = cudaFuncSetAttribute(k_route_block<BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     k_route_block<BLK><<<ctas, BLK, smem, s>>>(hp, a, ra);
@@ -305,7 +310,8 @@ int launch_vote_block(const QueryArgs& a, const BlockVoteArgs& va, cudaStream_t 
     if (a.n_reads == 0) return 0;
     constexpr int BLK = kRouteBlk;
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
-    if (ctas > 148u * 64u) ctas = 148u * 64u;
+    static const uint32_t per_sm = getenv("CCB_VOTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_VOTE_CTAS_PER_SM")) : 2u;
+    if (ctas > 148u * per_sm) ctas = 148u * per_sm;
     k_vote_block<BLK><<<ctas, BLK, 0, s>>>(a, va);
     return (int)cudaGetLastError();
 }

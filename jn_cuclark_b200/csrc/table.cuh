@@ -34,24 +34,33 @@ struct alignas(32) Bucket { uint64_t e[4]; };
 
 // One 256-bit read-only load = one 32-byte sector.  Without a size hint an L2 miss fills the whole 128-byte line
 // from HBM (126 B of DRAM reads per probe, ncu); with .L2::64B it fills 64 bytes (63 B per probe) at the same
-// request rate -- profiles/r02_probe_fill_ncu.csv, DESIGN.md section 3.  CCB_LD_HINT: 0 none, 64, 128, 256.
+// request rate -- profiles/r02_probe_fill_ncu.csv, DESIGN.md section 3.  What the rest of the fill is good for is the
+// overflow bucket (the next one, 5.7 % of the lookups read it): a 64-byte fill holds it for even buckets, a 128-byte
+// fill also for the second bucket of a line, nothing helps the fourth.  CCB_LD_HINT: 1 (default) = the smallest fill
+// that still covers the next bucket (80 B of DRAM reads per probe on average, the overflow hit rate of whole lines),
+// 64 = always 64 bytes (1 % slower: profiles/r02_ld_hint_ab.json), 0 = no hint.
 #ifndef CCB_LD_HINT
-#define CCB_LD_HINT 64
+#define CCB_LD_HINT 1
 #endif
+__device__ __forceinline__ void load_bucket64(const ulonglong4* p, uint64_t (&e)[4])
+{
+    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+}
+__device__ __forceinline__ void load_bucket128(const ulonglong4* p, uint64_t (&e)[4])
+{
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+}
 __device__ __forceinline__ void load_bucket(const ulonglong4* p, uint64_t (&e)[4])
 {
 #if CCB_LD_HINT == 64
-    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];"
-                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
-#elif CCB_LD_HINT == 128
-    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u64 {%0,%1,%2,%3}, [%4];"
-                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
-#elif CCB_LD_HINT == 256
-    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.u64 {%0,%1,%2,%3}, [%4];"
-                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+    load_bucket64(p, e);
+#elif CCB_LD_HINT == 0
+    load_bucket128(p, e);
 #else
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
-                 : "=l"(e[0]), "=l"(e[1]), "=l"(e[2]), "=l"(e[3]) : "l"(p));
+    if (((unsigned)(uintptr_t)p & 0x60u) == 0x20u) load_bucket128(p, e);     // second bucket of a line: the third comes along
+    else load_bucket64(p, e);
 #endif
 }
 

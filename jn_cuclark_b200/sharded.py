@@ -192,3 +192,44 @@ class PeerShardedClassifier:
         if self.ws:
             self.db.shardws_destroy(self.ws); self.ws = 0
         self._opened, self._owned = [], []
+
+
+class PipelinedPeerClassifier:
+    """A batch cut into chunks that travel through `n_pipes` PeerShardedClassifier pipelines (own inboxes, label boxes,
+    workspaces, barrier groups and streams): while the owners probe chunk i, the requesters already route chunk i+1 and
+    vote chunk i-1.  The three kernels are launched on persistent grids that fit one SM together (two blocks each), so
+    the HBM-bound probe and the issue/NVLink-bound route really share the SMs instead of queueing behind each other.
+    max_reads = reads per CHUNK, cap = region size per chunk."""
+
+    def __init__(self, db: CuClarkDB, cap: int, max_reads: int, n_pipes: int = 2):
+        self.db, self.n_pipes = db, n_pipes
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        self.groups = [dist.new_group(list(range(world))) if world > 1 else None for _ in range(n_pipes)]
+        self.pipes = [PeerShardedClassifier(db, cap, max_reads, group=g) for g in self.groups]
+        self.streams = [torch.cuda.Stream() for _ in range(n_pipes)]
+        self.max_reads = max_reads
+
+    def classify(self, d_offsets: int, d_containers: int, n_reads: int, out5: torch.Tensor, stats=None, n_containers: int = -1):
+        per = self.max_reads
+        cur = torch.cuda.current_stream()
+        for s_ in self.streams:
+            s_.wait_stream(cur)
+        c = 0
+        for a in range(0, max(n_reads, 1), per):
+            n = min(per, n_reads - a)
+            p = c % self.n_pipes
+            with torch.cuda.stream(self.streams[p]):
+                # offsets are absolute container indices: a chunk is a window of the offsets array over the same containers
+                self.pipes[p].classify(d_offsets + 4 * a, d_containers, n, out5[5 * a:], stats=stats,
+                                       n_containers=(n_containers * n // max(n_reads, 1)) if n_containers >= 0 else -1)
+            c += 1
+        for s_ in self.streams:
+            cur.wait_stream(s_)
+        return out5
+
+    def overflowed(self) -> bool:
+        return any([p.overflowed() for p in self.pipes])
+
+    def close(self):
+        for p in self.pipes:
+            p.close()

@@ -67,7 +67,7 @@ def test_bench_two_ranks_carry_the_sharded_leg():
               "--master-port", str(port), "bench.py", "--gpus", "2"] + SMALL)
     assert d["n_gpus"] == 2 and "sharded" in d
     s = d["sharded"]
-    assert s["results_equal_replicated_path"] is True and set(s["exchanges"]) == {"peer", "nccl"}
+    assert s["results_equal_replicated_path"] is True and set(s["exchanges"]) == {"peer", "peer_pipelined", "nccl"}
     for x in s["exchanges"].values():
         assert x["results_equal_replicated_path"] is True and x["value"] > 0
     assert "route" in s["exchanges"]["peer"]["phases_rank0_ms"]
