@@ -567,6 +567,7 @@ def sharded_leg(args, rank, world, local, d_off, d_cont, n_cont, out_h, total_lo
     t0 = time.time(); sdb.synth_db(DB_SEED, G, LG, min(G, 65534)); t_db = time.time() - t0
     info = sdb.db_info()
     cap = region_size(NR, L - k + 1, world)
+    NCH = 4                                                            # chunks of the pipelined variant, two in flight
     out = torch.zeros(NR * 5, dtype=torch.int16, device="cuda")
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
     leg = {"what": f"table sharded x{world} by hash range (shard {info.bytes / 1e9:.1f} GB per GPU), the same reads; one-pass route "
@@ -576,7 +577,6 @@ def sharded_leg(args, rank, world, local, d_off, d_cont, n_cont, out_h, total_lo
                                  "peer_pipelined": f"the same, the batch cut into {NCH} chunks through two pipelines on two streams: one chunk's probe runs beside the next one's route",
                                  "nccl": "NCCL all-to-all of the k-mers and of the labels (one host sync per batch for the sizes)"},
            "exchanges": {}}
-    NCH = 4                                                            # chunks of the pipelined variant, two in flight
     per_chunk = (NR + NCH - 1) // NCH
     for exch in ("peer_pipelined", "peer", "nccl"):
         if exch == "peer_pipelined":

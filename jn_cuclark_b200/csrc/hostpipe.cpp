@@ -112,6 +112,127 @@ void index_sequential(const uint8_t* m, size_t nb, bool fasta, ReadSet& o)
     }
 }
 
+// ---- newline events, 256 bits at a time when the CPU can (hostscan_avx2.cpp), memchr otherwise ------------------
+extern "C" size_t ccbh_count_newlines_avx2(const uint8_t* p, size_t n);
+extern "C" size_t ccbh_newline_offsets_avx2(const uint8_t* p, size_t n, uint32_t* out);
+extern "C" int ccbh_has_bare_marker_avx2(const uint8_t* p, size_t n);
+
+const bool kAvx2 = __builtin_cpu_supports("avx2") && !getenv("CCB_NO_AVX2");
+
+size_t count_newlines(const uint8_t* p, size_t n)
+{
+    if (kAvx2) return ccbh_count_newlines_avx2(p, n);
+    size_t c = 0;
+    const uint8_t* e = p + n;
+    while (p < e) { const void* q = memchr(p, '\n', (size_t)(e - p)); if (!q) break; c++; p = (const uint8_t*)q + 1; }
+    return c;
+}
+
+// positions of the newlines from `pos` on, one window of text at a time
+struct NewlineStream {
+    static constexpr size_t kWin = 8192;
+    const uint8_t* m; size_t nb, pos;
+    uint32_t off[kWin]; size_t n = 0, at = 0, base = 0;
+    NewlineStream(const uint8_t* m_, size_t nb_, size_t from) : m(m_), nb(nb_), pos(from) {}
+    inline bool next(size_t& q)
+    {
+        while (at == n) {
+            if (pos >= nb) return false;
+            const size_t len = std::min(kWin, nb - pos);
+            base = pos; at = 0;
+            if (kAvx2) n = ccbh_newline_offsets_avx2(m + pos, len, off);
+            else {
+                n = 0;
+                const uint8_t* p = m + pos; const uint8_t* e = p + len;
+                while (p < e) { const void* x = memchr(p, '\n', (size_t)(e - p)); if (!x) break; off[n++] = (uint32_t)((const uint8_t*)x - (m + pos)); p = (const uint8_t*)x + 1; }
+            }
+            pos += len;
+        }
+        q = base + off[at++];
+        return true;
+    }
+};
+
+// first separator after ns, looking from ns + 1 on (name_end), when a newline is known to lie at q >= ns + 1
+inline size_t name_end_before(const uint8_t* m, size_t ns, size_t q)
+{
+    size_t i = ns + 1;
+    while (i < q && m[i] != ' ' && m[i] != '\t') i++;
+    return i;
+}
+
+// FASTQ records whose first byte lies in (b, e] at a line whose index is a multiple of four (`line` = index of the line
+// that holds byte b); the record at byte 0 belongs to the range that starts there.  Same records, same fields as
+// fastq_record() -- the newlines just come from one pass instead of four memchr calls per record.
+// returns false for a record whose marker stands alone on its line (only the sequential scan reproduces it)
+bool index_range_fastq(const uint8_t* m, size_t nb, size_t b, size_t e, uint64_t line, bool first, ReadSet& o)
+{
+    Rec r{};
+    NewlineStream nl(m, nb, b);
+    bool in_rec = false; int stage = 0; size_t rec_at = 0;
+    auto start = [&](size_t p) -> bool {           // a record begins at p
+        if (m[p + 1] == '\n') return false;
+        in_rec = true; stage = 0; rec_at = p; r.ns = p + 1;
+        return true;
+    };
+    if (first) { if (nb > 1 && !start(0)) return false; if (nb <= 1) { fastq_record(m, nb, 0, r); push(o, r); return true; } }
+    size_t q;
+    for (;;) {
+        if (!nl.next(q)) {                          // end of the text inside a record: the plain parser knows every corner
+            if (in_rec) { fastq_record(m, nb, rec_at, r); push(o, r); }
+            return true;
+        }
+        line++;
+        if (in_rec) {
+            stage++;
+            if (stage == 1) { r.ne = name_end_before(m, r.ns, q); r.ss = q + 1; }
+            else if (stage == 2) { r.se = q; r.len = q - r.ss; }
+            else if (stage == 4) { push(o, r); in_rec = false; }
+        }
+        if (!in_rec) {
+            if (q >= e) return true;
+            const size_t p = q + 1;
+            if ((line & 3) == 0 && p + 1 < nb && !start(p)) return false;
+        }
+    }
+}
+
+// FASTA records whose '>' starts a line inside [b, e)
+bool index_range_fasta(const uint8_t* m, size_t nb, size_t b, size_t e, ReadSet& o)
+{
+    Rec r{};
+    bool in_rec = false, header = false; size_t rec_at = 0; uint64_t lines = 0;
+    auto start = [&](size_t p) -> bool {
+        if (p + 1 >= nb || m[p + 1] == '\n') return false;
+        in_rec = true; header = true; rec_at = p; r.ns = p + 1; lines = 0;
+        return true;
+    };
+    size_t from = b;
+    if (b == 0 || m[b - 1] == '\n') { if (m[b] == '>' && !start(b)) return false; }
+    NewlineStream nl(m, nb, from);
+    size_t q;
+    for (;;) {
+        if (!nl.next(q)) {
+            if (in_rec) { fasta_record(m, nb, rec_at, r); push(o, r); }
+            return true;
+        }
+        const size_t c = q + 1;                     // the next line starts here
+        if (in_rec) {
+            if (header) { r.ne = name_end_before(m, r.ns, q); r.ss = r.se = c; header = false; }
+            else { lines++; r.se = q; }
+            if (c >= nb || m[c] == '>') {           // the record ends: at the end of the text, or where a line starts with '>'
+                r.len = (r.se - r.ss + 1) - lines;
+                push(o, r);
+                in_rec = false;
+            }
+        }
+        if (!in_rec) {
+            if (c >= e || c >= nb) return true;
+            if (m[c] == '>' && !start(c)) return false;
+        }
+    }
+}
+
 }  // namespace
 
 int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
@@ -139,9 +260,7 @@ int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
     if (!fasta) {
         std::vector<std::thread> th;
         for (int t = 0; t < T; t++) th.emplace_back([&, t] {
-            uint64_t c = 0;
-            const uint8_t* p = m + cut[(size_t)t]; const uint8_t* e = m + cut[(size_t)t + 1];
-            while (p < e) { const void* q = memchr(p, '\n', (size_t)(e - p)); if (!q) break; c++; p = (const uint8_t*)q + 1; }
+            const uint64_t c = count_newlines(m + cut[(size_t)t], cut[(size_t)t + 1] - cut[(size_t)t]);
             newlines[(size_t)t] = c;
         });
         for (auto& x : th) x.join();
@@ -159,37 +278,9 @@ int index_reads(const uint8_t* m, size_t nb, int threads, ReadSet& out)
                 const size_t guess = (fasta ? (e - b) / 100 : (size_t)newlines[(size_t)t] / 4) + 16;
                 o.name_s.reserve(guess); o.name_e.reserve(guess); o.seq_s.reserve(guess); o.seq_e.reserve(guess); o.len.reserve(guess);
             }
-            if (fasta) {
-                size_t p = b;
-                while (p < e) {                     // next '>' that starts a line, inside [b, e)
-                    const void* q = memchr(m + p, '>', e - p);
-                    if (!q) break;
-                    p = (size_t)((const uint8_t*)q - m);
-                    if (p == 0 || m[p - 1] == '\n') {
-                        if (p + 1 >= nb || m[p + 1] == '\n') { odd = true; return; }
-                        size_t nx = fasta_record(m, nb, p, r);
-                        push(o, r);
-                        p = nx;                     // may lie beyond e: the next thread owns it
-                    } else p++;
-                }
-            } else {
-                uint64_t line = line0[(size_t)t];
-                size_t p = b;
-                if (t == 0) {                       // line 0 starts at byte 0
-                    if (nb > 1 && m[1] == '\n') { odd = true; return; }
-                    fastq_record(m, nb, 0, r); push(o, r);
-                }
-                while (p < e) {
-                    const void* q = memchr(m + p, '\n', e - p);
-                    if (!q) break;
-                    p = (size_t)((const uint8_t*)q - m) + 1;     // start of line `line + 1`
-                    line++;
-                    if ((line & 3) == 0 && p + 1 < nb) {
-                        if (m[p + 1] == '\n') { odd = true; return; }
-                        fastq_record(m, nb, p, r); push(o, r);
-                    }
-                }
-            }
+            if (fasta) { if (!index_range_fasta(m, nb, b, e, o)) odd = true; }
+            else if (!index_range_fastq(m, nb, b, e, line0[(size_t)t], t == 0, o)) odd = true;
+            (void)r;
         });
         for (auto& x : th) x.join();
     }

@@ -411,10 +411,29 @@ int launch_query_dense(const TableView& t, const QueryArgs& a, const uint32_t* r
 // ---------------------------------------------------------------------------
 // sharded table: owner-side probe of a k-mer list, requester-side vote from label lists
 // ---------------------------------------------------------------------------
+// A table (or shard) larger than what the TLBs reach is probed range by range: measured with the table-only kernel,
+// 1.2 G random probes take 27.3 ms on a 64 GB table, 60.5 ms on 96 GB and 96.0 ms on 128 GB (profiles/r02_table_size.json)
+// -- beyond 64 GB every probe also misses the translation caches.  A list of k-mers can be walked once per range of
+// <= 48 GB instead (8 more bytes read per k-mer and range, against a probe that costs twice as much).
+static void probe_passes(const TableView& t, uint64_t& lo, uint64_t& per, int& passes)
+{
+    const uint64_t G = t.hp.n_shards > 1 ? t.hp.n_shards : 1;
+    const uint64_t held = t.hp.nb / G;                                   // home buckets held here
+    lo = held * (t.hp.n_shards > 1 ? t.hp.shard : 0);
+    const char* env = getenv("CCB_PROBE_RANGE_MB");                      // (tests: ranges of a few MB on a small table)
+    const uint64_t reach = env && atoll(env) > 0 ? (uint64_t)atoll(env) << 20 : 48ull << 30;
+    passes = (int)((held * 32 + reach - 1) / reach);
+    if (passes < 1) passes = 1;
+    per = (held + (uint64_t)passes - 1) / (uint64_t)passes;
+}
+
 // 4 independent probes in flight per thread, as in k_query.
+// home_lo / home_hi: only k-mers whose home bucket lies in [home_lo, home_hi) are probed by this launch (a shard larger
+// than the TLB reaches is probed range by range, see launch_probe_list)
 template <bool STATS>
 __global__ void __launch_bounds__(256) k_probe_list(const TableView t, const uint64_t* __restrict__ hashes, uint64_t n,
-                                                    uint16_t* __restrict__ labels, unsigned long long* stats)
+                                                    uint16_t* __restrict__ labels, unsigned long long* stats,
+                                                    const uint64_t home_lo, const uint64_t home_hi)
 {
     const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
     uint32_t sectors = 0; unsigned long long lookups = 0;
@@ -426,6 +445,7 @@ __global__ void __launch_bounds__(256) k_probe_list(const TableView t, const uin
             ok[j] = i < n;
             const uint64_t h = ok[j] ? __ldg(hashes + i) : 0;
             home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
+            ok[j] = ok[j] && home[j] >= home_lo && home[j] < home_hi;
             if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
         }
 #pragma unroll
@@ -451,8 +471,13 @@ int launch_probe_list(const TableView& t, const uint64_t* hashes, uint64_t n, ui
     if (n == 0) return 0;
     uint64_t g = (n + 1023) / 1024;
     if (g > 148ull * 64) g = 148ull * 64;
-    if (stats) k_probe_list<true><<<(uint32_t)g, 256, 0, s>>>(t, hashes, n, labels, stats);
-    else       k_probe_list<false><<<(uint32_t)g, 256, 0, s>>>(t, hashes, n, labels, stats);
+    uint64_t lo, per; int passes;
+    probe_passes(t, lo, per, passes);
+    for (int v = 0; v < passes; v++) {
+        const uint64_t a = lo + per * (uint64_t)v, b = v + 1 == passes ? ~0ull : a + per;
+        if (stats) k_probe_list<true><<<(uint32_t)g, 256, 0, s>>>(t, hashes, n, labels, stats, v ? a : 0ull, b);
+        else       k_probe_list<false><<<(uint32_t)g, 256, 0, s>>>(t, hashes, n, labels, stats, v ? a : 0ull, b);
+    }
     return (int)cudaGetLastError();
 }
 
@@ -565,7 +590,8 @@ int launch_post_counts(const uint32_t* pos, uint32_t n_reads, uint32_t n_shards,
 }
 
 template <bool STATS>
-__global__ void __launch_bounds__(256) k_probe_inbox(const TableView t, const InboxArgs ia, unsigned long long* stats)
+__global__ void __launch_bounds__(256) k_probe_inbox(const TableView t, const InboxArgs ia, unsigned long long* stats,
+                                                     const uint64_t home_lo, const uint64_t home_hi)
 {
     const uint64_t stride = gridDim.x * (uint64_t)blockDim.x;
     uint32_t sectors = 0; unsigned long long lookups = 0;
@@ -581,6 +607,7 @@ __global__ void __launch_bounds__(256) k_probe_inbox(const TableView t, const In
                 ok[j] = i < n;
                 const uint64_t h = ok[j] ? hashes[i] : 0;
                 home[j] = home_of(h, t.hp); q[j] = key48_of(h) << 16;
+                ok[j] = ok[j] && home[j] >= home_lo && home[j] < home_hi;
                 if (ok[j]) load_bucket(t.buckets + home[j], e[j]);
             }
 #pragma unroll
@@ -604,11 +631,17 @@ __global__ void __launch_bounds__(256) k_probe_inbox(const TableView t, const In
 
 int launch_probe_inbox(const TableView& t, const InboxArgs& ia, unsigned long long* stats, cudaStream_t s)
 {
-    // two blocks per SM (2048 probes in flight per SM, several times what the DRAM request rate needs; 78 registers
-    // each) leave room for the route kernel of another batch on the same SMs (shard_block.cu launch_route_block)
-    static const int per_sm = getenv("CCB_PROBE_CTAS_PER_SM") ? atoi(getenv("CCB_PROBE_CTAS_PER_SM")) : 2;
-    if (stats) k_probe_inbox<true><<<148 * per_sm, 256, 0, s>>>(t, ia, stats);
-    else       k_probe_inbox<false><<<148 * per_sm, 256, 0, s>>>(t, ia, stats);
+    // grid: 32 blocks per SM's worth (measured on one B200, 10 M reads: 2 per SM 36.8 ms, 4: 33.8, 8: 31.1, 32: 30.1 --
+    // small persistent grids that would leave room for another batch's route kernel cost more than the overlap returns,
+    // profiles/r02_sharded_grid_sweep.json)
+    static const int per_sm = getenv("CCB_PROBE_CTAS_PER_SM") ? atoi(getenv("CCB_PROBE_CTAS_PER_SM")) : 32;
+    uint64_t lo, per; int passes;
+    probe_passes(t, lo, per, passes);
+    for (int v = 0; v < passes; v++) {
+        const uint64_t a = lo + per * (uint64_t)v, b = v + 1 == passes ? ~0ull : a + per;
+        if (stats) k_probe_inbox<true><<<148 * per_sm, 256, 0, s>>>(t, ia, stats, v ? a : 0ull, b);
+        else       k_probe_inbox<false><<<148 * per_sm, 256, 0, s>>>(t, ia, stats, v ? a : 0ull, b);
+    }
     return (int)cudaGetLastError();
 }
 

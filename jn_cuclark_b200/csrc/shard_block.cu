@@ -205,11 +205,11 @@ int launch_route_block(const HashParams& hp, const QueryArgs& a, const BlockRout
     if (ra.n_shards < 1 || ra.n_shards > (uint32_t)kMaxShards) return -60;
     constexpr int BLK = kRouteBlk;
     const size_t smem = sizeof(RouteSmem<BLK>);
-    // a persistent grid of two blocks per SM: the route of one batch is meant to run BESIDE the probe of another one
-    // (k_probe_inbox, two blocks per SM; the vote takes what is left) -- routing is issue- and NVLink-bound, probing
-    // HBM-bound, and two GPU-filling grids would just run one after the other
+    // grid: many more blocks than are resident (three per SM) so that the block scheduler evens out the tail (measured:
+    // 11.2 ms per 10 M reads against 13.0 ms with 3 per SM and 14.0 ms with 2; small persistent grids meant to let another
+    // batch's probe run beside the route were tried and cost more than the overlap returned -- DESIGN.md section 9)
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
-    static const uint32_t per_sm = getenv("CCB_ROUTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_ROUTE_CTAS_PER_SM")) : 2u;
+    static const uint32_t per_sm = getenv("CCB_ROUTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_ROUTE_CTAS_PER_SM")) : 64u;
     if (ctas > 148u * per_sm) ctas = 148u * per_sm;
     cudaError_t e = cudaFuncSetAttribute(k_route_block<BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -310,7 +310,7 @@ int launch_vote_block(const QueryArgs& a, const BlockVoteArgs& va, cudaStream_t 
     if (a.n_reads == 0) return 0;
     constexpr int BLK = kRouteBlk;
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
-    static const uint32_t per_sm = getenv("CCB_VOTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_VOTE_CTAS_PER_SM")) : 2u;
+    static const uint32_t per_sm = getenv("CCB_VOTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_VOTE_CTAS_PER_SM")) : 64u;
     if (ctas > 148u * per_sm) ctas = 148u * per_sm;
     k_vote_block<BLK><<<ctas, BLK, 0, s>>>(a, va);
     return (int)cudaGetLastError();

@@ -36,11 +36,12 @@ struct alignas(32) Bucket { uint64_t e[4]; };
 // from HBM (126 B of DRAM reads per probe, ncu); with .L2::64B it fills 64 bytes (63 B per probe) at the same
 // request rate -- profiles/r02_probe_fill_ncu.csv, DESIGN.md section 3.  What the rest of the fill is good for is the
 // overflow bucket (the next one, 5.7 % of the lookups read it): a 64-byte fill holds it for even buckets, a 128-byte
-// fill also for the second bucket of a line, nothing helps the fourth.  CCB_LD_HINT: 1 (default) = the smallest fill
-// that still covers the next bucket (80 B of DRAM reads per probe on average, the overflow hit rate of whole lines),
-// 64 = always 64 bytes (1 % slower: profiles/r02_ld_hint_ab.json), 0 = no hint.
+// fill also for the second bucket of a line, nothing helps the fourth.  CCB_LD_HINT: 64 (default) = always 64 bytes
+// (1.2 % slower than whole lines, half the DRAM bytes: profiles/r02_ld_hint_ab.json), 0 = no hint, 1 = the smallest fill
+// that still covers the next bucket, chosen per load from the address (82 B per probe; the branch around two load
+// instructions costs the latency-bound kernels 8-20 %: 13.9 instead of 12.5 ms with the anchor index -- rejected).
 #ifndef CCB_LD_HINT
-#define CCB_LD_HINT 1
+#define CCB_LD_HINT 64
 #endif
 __device__ __forceinline__ void load_bucket64(const ulonglong4* p, uint64_t (&e)[4])
 {

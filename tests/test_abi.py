@@ -93,5 +93,5 @@ def test_library_holds_sm_100a_code_only():
     elfs = [l for l in r.stdout.splitlines() if l.startswith("ELF file")]
     assert elfs and all("sm_100a" in l for l in elfs), elfs
     sass = subprocess.run(["cuobjdump", "-sass", lib.lib_path()], capture_output=True, text=True).stdout
-    assert "ENL2.LTC64B.256" in sass and "NA.ENL2.256" in sass   # one 256-bit load per probe: 64-byte fill, or the whole line where the next bucket lies in it
+    assert "ENL2.LTC64B.256" in sass                   # LDG ... .256: one 32-byte table sector per probe, 64-byte fill on a miss
     assert "MATCH.ANY" in sass                         # the one-pass route kernel ranks k-mers per owner with __match_any_sync

@@ -343,3 +343,23 @@ def test_one_pass_pipeline_odd_batches(oracle, tmp_path):
     finally:
         for s in shards:
             s.close()
+
+
+def test_probe_range_by_range(small_world, oracle, monkeypatch):
+    """A shard larger than the TLBs reach is probed range by range (query.cu probe_passes): with the range set to 1 MB the
+    small table takes several passes -- every k-mer is still probed exactly once."""
+    odb = oracle.OracleDb.build(small_world["targets"], 31, HT_SMALL)
+    ir = oracle.IndexedReads(open(os.path.join(small_world["dir"], "reads.fa"), "rb").read())
+    off, cont = ir.pack(31)
+    want, _, nl = odb.query_packed(31, off, cont)
+    shards = _make_shards(odb, 2)
+    try:
+        assert shards[0].db_info().bytes > 3 * (1 << 20)
+        monkeypatch.setenv("CCB_PROBE_RANGE_MB", "1")
+        got, _, lookups, counts, err = _classify_one_pass_one_gpu(shards, off, cont, cap=int(nl) + 64)
+        assert not err and lookups == nl and np.array_equal(got, want)
+        got2, _, lookups2, _ = _classify_sharded_one_gpu(shards, off, cont)
+        assert lookups2 == nl and np.array_equal(got2, want)
+    finally:
+        for s in shards:
+            s.close()
