@@ -367,8 +367,8 @@ struct Engine {
         snprintf(buf, sizeof buf, "Done in %.1fs (%zu reads/min, %zu reads)\n", diff, (size_t)(((double)st.reads) / diff * 60.0), (size_t)st.reads);
         cerr << buf << "Results: " << res << "\n";
         if (cli.verbose) {
-            snprintf(buf, sizeof buf, "  host pipeline: index %.3f s, slots %.3f s, total %.3f s, %zu batches; worker seconds: pack %.3f, device wait %.3f, rows %.3f, writer %.3f\n",
-                     st.seconds_index, st.seconds_alloc, st.seconds_total, (size_t)st.batches, st.cpu_pack, st.cpu_wait, st.cpu_format, st.cpu_sink);
+            snprintf(buf, sizeof buf, "  host pipeline: index %.3f s, slots %.3f s, total %.3f s, %zu batches; worker seconds: index %.3f, pack %.3f, device wait %.3f, rows %.3f, writer %.3f\n",
+                     st.seconds_index, st.seconds_alloc, st.seconds_total, (size_t)st.batches, st.cpu_index, st.cpu_pack, st.cpu_wait, st.cpu_format, st.cpu_sink);
             cerr << buf;
         }
         (void)shown_name;

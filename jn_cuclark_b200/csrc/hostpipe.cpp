@@ -14,6 +14,10 @@
 #include <memory>
 #include <stdlib.h>
 
+#ifndef _GNU_SOURCE
+#define _GNU_SOURCE
+#endif
+
 namespace ccbh {
 
 // ---------------------------------------------------------------------------
@@ -602,9 +606,177 @@ int reserve_slots(const std::vector<ccb_handle*>& devs, int k, bool extended)
     return rc;
 }
 
+// ---------------------------------------------------------------------------
+// Streaming pipeline for large inputs: the text is cut into chunks of ~40 MB; a worker indexes ITS chunk, packs it,
+// submits it, formats its rows -- no global index, no serial stage in front of the GPU work.  What a chunk needs from the
+// rest of the file is one number (FASTQ: the index of the line it starts in), found by a newline count over all chunks
+// first (256-bit compares, memory speed).  Anything unusual -- a marker alone on its line, a chunk without a record
+// start (a read longer than a chunk), a record that does not fit a slot -- and the whole file goes through the two-phase
+// path below instead; both produce the same bytes.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr int kNotStreamable = -12345;
+constexpr size_t kStreamMinBytes = (size_t)128 << 20;
+
+int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size_t nb, const char* result_csv,
+                    const std::vector<std::string>& names, const ClassifyOptions& opt, ClassifyStats& stats, std::string& err)
+{
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    const bool fasta = m[0] == '>';
+    size_t chunk = fasta ? ((size_t)28 << 20) : ((size_t)40 << 20);            // <= kMaxBatchBytes of sequence, ~130 k short reads
+    if (const char* e = getenv("CCB_STREAM_CHUNK")) { const long long v = atoll(e); if (v >= 1024) chunk = (size_t)v; }    // (tests)
+    const size_t C = (nb + chunk - 1) / chunk;
+    const int T = std::max(1, opt.threads);
+    // slots first (pinning 17 MB x slots takes 0.1 s): on a thread of their own while the chunks are surveyed
+    std::vector<int> alloc_rc(devs.size(), 0);
+    std::thread alloc([&] {
+        for (size_t d = 0; d < devs.size(); d++) alloc_rc[d] = ccb_batch_alloc(devs[d], (uint32_t)kMaxBatchReads, spec_containers(opt.k), opt.extended);
+    });
+    // survey: newlines per chunk, markers alone on a line, chunks without a record start
+    std::vector<uint64_t> newlines(C, 0);
+    std::atomic<bool> unusual(false);
+    {
+        std::atomic<size_t> next(0);
+        auto survey = [&] {
+            for (size_t c = next++; c < C && !unusual; c = next++) {
+                const size_t b = c * chunk, e = std::min(nb, b + chunk);
+                const size_t lo = b ? b - 1 : 0, hi = std::min(nb, e + 1);          // patterns that straddle a chunk boundary
+                if (kAvx2 ? ccbh_has_bare_marker_avx2(m + lo, hi - lo) : 1) {
+                    if (kAvx2) { unusual = true; return; }
+                    for (size_t j = lo; j + 2 < hi; j++)
+                        if (m[j] == '\n' && (m[j + 1] == '@' || m[j + 1] == '>') && m[j + 2] == '\n') { unusual = true; return; }
+                }
+                if (fasta) {
+                    if (c && e - b >= 2 && !memmem(m + b - 1, e - b + 1, "\n>", 2)) { unusual = true; return; }
+                } else {
+                    newlines[c] = count_newlines(m + b, e - b);
+                    if (newlines[c] < 8 && c + 1 < C) { unusual = true; return; }
+                }
+            }
+        };
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; t++) th.emplace_back(survey);
+        for (auto& x : th) x.join();
+    }
+    if (nb > 1 && m[1] == '\n') unusual = true;
+    alloc.join();
+    for (size_t d = 0; d < devs.size(); d++)
+        if (alloc_rc[d]) { err = ccb_last_error(devs[d]); return alloc_rc[d]; }
+    if (unusual) return kNotStreamable;
+    std::vector<uint64_t> line0(C, 0);
+    for (size_t c = 1; c < C; c++) line0[c] = line0[c - 1] + newlines[c - 1];
+    stats.seconds_index = now() - t0;
+    stats.seconds_alloc = 0;
+    const size_t max_cont = spec_containers(opt.k);
+
+    std::vector<std::unique_ptr<DevSlots>> ds;
+    for (ccb_handle* h : devs) {
+        ds.emplace_back(new DevSlots());
+        ds.back()->h = h;
+        for (int s = 0; s < ccb_batch_slots(h); s++) ds.back()->free_slots.push_back(s);
+    }
+    OrderedSink sink;
+    sink.f = fopen(result_csv, "w");
+    if (!sink.f) { err = std::string("Failed to create/open file result: ") + result_csv; return 1; }
+    if (opt.dump_final5) sink.dump = fopen(opt.dump_final5, "wb");
+    {
+        std::string hdr; csv_header(hdr, opt.extended, names);
+        fwrite(hdr.data(), 1, hdr.size(), sink.f);
+    }
+    std::atomic<size_t> next_chunk(0);
+    std::atomic<uint64_t> n_reads(0), n_batches(0);
+    std::atomic<int> failed(0);
+    std::atomic<bool> give_up(false);
+    std::mutex err_mu, stat_mu;
+    auto fail = [&](int rc, const std::string& msg) { std::lock_guard<std::mutex> g(err_mu); if (!failed) { failed = rc ? rc : 1; err = msg; } };
+    auto work = [&](int wid) {
+        double c_idx = 0, c_pack = 0, c_wait = 0, c_fmt = 0, c_sink = 0;
+        struct Fold { std::mutex& mu; ClassifyStats& st; double &i, &a, &b, &c, &d;
+                      ~Fold() { std::lock_guard<std::mutex> g(mu); st.cpu_index += i; st.cpu_pack += a; st.cpu_wait += b; st.cpu_format += c; st.cpu_sink += d; } }
+            fold{stat_mu, stats, c_idx, c_pack, c_wait, c_fmt, c_sink};
+        ReadSet rs;
+        rs.map = m; rs.nb = nb; rs.fasta = fasta;
+        DevSlots& d = *ds[(size_t)wid % ds.size()];
+        for (;;) {
+            const size_t c = next_chunk.fetch_add(1);
+            if (c >= C || failed || give_up) return;
+            double t1 = now();
+            const size_t b = c * chunk, e = std::min(nb, b + chunk);
+            rs.clear();
+            const bool ok = fasta ? index_range_fasta(m, nb, b, e, rs) : index_range_fastq(m, nb, b, e, line0[c], c == 0, rs);
+            c_idx += now() - t1;
+            if (!ok) { give_up = true; sink.put(c, "", {}); return; }
+            const size_t n = rs.n();
+            std::string text; std::vector<uint16_t> raw;
+            text.reserve(n * 48);
+            size_t first = 0;
+            while (first < n && !failed && !give_up) {
+                size_t cnt = 0, bytes = 0;                      // a sub-batch within the slot's limits
+                while (first + cnt < n && cnt < kMaxBatchReads) {
+                    const size_t sb = (size_t)(rs.seq_e[first + cnt] - rs.seq_s[first + cnt]);
+                    if (cnt && bytes + sb > kMaxBatchBytes) break;
+                    bytes += sb; cnt++;
+                }
+                if (bytes > kMaxBatchBytes) { give_up = true; break; }          // one read larger than a slot: two-phase path
+                int slot;
+                {
+                    std::unique_lock<std::mutex> g(d.mu);
+                    d.cv.wait(g, [&] { return !d.free_slots.empty(); });
+                    slot = d.free_slots.back(); d.free_slots.pop_back();
+                }
+                auto release = [&] { { std::lock_guard<std::mutex> g(d.mu); d.free_slots.push_back(slot); } d.cv.notify_one(); };
+                uint32_t* off; uint16_t *cont, *fin, *rows;
+                ccb_batch_buffers(d.h, slot, &off, &cont, &fin, &rows);
+                t1 = now();
+                const int64_t nc = pack_reads(rs, first, cnt, opt.k, off, cont, max_cont);
+                c_pack += now() - t1; t1 = now();
+                if (nc < 0) { release(); give_up = true; break; }
+                int rc;
+                {
+                    std::lock_guard<std::mutex> g(d.submit_mu);
+                    rc = ccb_batch_submit(d.h, slot, (uint32_t)cnt, (uint64_t)nc, opt.extended ? CCB_EXTENDED : 0);
+                }
+                if (!rc) rc = ccb_batch_wait(d.h, slot);
+                if (rc) { fail(rc, ccb_last_error(d.h)); release(); break; }
+                c_wait += now() - t1; t1 = now();
+                csv_rows(text, rs, first, cnt, opt.k, opt.paired, opt.extended, names, fin, rows, opt.row_stride);
+                if (sink.dump) raw.insert(raw.end(), fin, fin + cnt * 5);
+                release();
+                c_fmt += now() - t1;
+                first += cnt; n_batches++;
+            }
+            n_reads += n;
+            t1 = now();
+            sink.put(c, std::move(text), std::move(raw));
+            c_sink += now() - t1;
+        }
+    };
+    const int workers = (int)std::max<size_t>(1, std::min<size_t>((size_t)T, C));
+    std::vector<std::thread> th;
+    for (int w = 0; w < workers; w++) th.emplace_back(work, w);
+    for (auto& t : th) t.join();
+    const bool io_err = sink.io_error || fclose(sink.f) != 0;
+    if (sink.dump) fclose(sink.dump);
+    if (failed) return failed;
+    if (give_up) return kNotStreamable;                  // nothing of the partial file is kept: the caller starts over
+    stats.reads = n_reads; stats.batches = n_batches;
+    stats.seconds_total = now() - t0;
+    if (io_err) { err = std::string("Failed to write ") + result_csv; return 1; }
+    return 0;
+}
+}  // namespace
+
 int classify_text(const std::vector<ccb_handle*>& devs, const uint8_t* map, size_t nb, const char* result_csv,
                   const std::vector<std::string>& names, const ClassifyOptions& opt, ClassifyStats& stats, std::string& err)
 {
+    size_t stream_min = kStreamMinBytes;
+    if (const char* e = getenv("CCB_STREAM_MIN_BYTES")) stream_min = (size_t)atoll(e);                                        // (tests)
+    if (nb >= stream_min && nb > 2 && map && (map[0] == '>' || map[0] == '@') && !getenv("CCB_NO_STREAM")) {
+        const int rc = classify_stream(devs, map, nb, result_csv, names, opt, stats, err);
+        if (rc != kNotStreamable) return rc;
+        stats = ClassifyStats();
+    }
     auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = now();
     // For a large input the pinned slots are allocated while the file is being indexed (0.1 s of cudaHostAlloc

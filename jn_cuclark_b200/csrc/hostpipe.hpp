@@ -82,7 +82,7 @@ struct ClassifyStats {
     double   seconds_index = 0, seconds_total = 0;
     // where the wall time of one file went: slot allocation, and summed over the workers:
     // packing, waiting for the device, formatting rows, waiting for the ordered writer
-    double   seconds_alloc = 0, cpu_pack = 0, cpu_wait = 0, cpu_format = 0, cpu_sink = 0;
+    double   seconds_alloc = 0, cpu_pack = 0, cpu_wait = 0, cpu_format = 0, cpu_sink = 0, cpu_index = 0;
 };
 
 // Allocate every handle's pinned slots for the largest batch classify_text forms (0.1-0.25 s of pinning): a caller

@@ -244,3 +244,25 @@ def test_anchor_is_the_default_and_can_be_turned_off(setup, tmp_path):
     r0 = _run(s, ["-O", reads, "--verbose"], str(tmp_path / "off"), {"CCB_ANCHOR": "0"})
     assert "Anchor index: " in r1.stderr and "Anchor index" not in r0.stderr
     assert open(str(tmp_path / "on.csv"), "rb").read() == open(str(tmp_path / "off.csv"), "rb").read()
+
+
+@pytest.mark.parametrize("chunk", ["3000", "20000", "1000000"])
+def test_streaming_pipeline_gives_the_same_csv(setup, tmp_path, chunk):
+    """Large inputs go through the streaming host pipeline (hostpipe.cpp classify_stream: chunks indexed, packed and
+    submitted by the worker that owns them); forced onto the small golden files here with small chunks.  FASTQ, multi-line
+    FASTA, pairs (joined in memory = FASTA), extended rows; a file with a marker alone on its line falls back."""
+    s = setup
+    env = {"CCB_STREAM_MIN_BYTES": "1", "CCB_STREAM_CHUNK": chunk}
+    off = {"CCB_NO_STREAM": "1"}
+    for i, args in enumerate((["-O", os.path.join(WORLD, "reads.fq"), "-n", "3"], ["-O", os.path.join(WORLD, "reads_ml.fa"), "-n", "4", "--extended"],
+                              ["-P", os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq"), "-n", "2"])):
+        r = _run(s, args + ["--verbose"], str(tmp_path / f"s{i}"), env)
+        _run(s, args, str(tmp_path / f"t{i}"), off)
+        assert open(str(tmp_path / f"s{i}.csv"), "rb").read() == open(str(tmp_path / f"t{i}.csv"), "rb").read(), args
+    odd = tmp_path / "odd.fq"
+    data = open(os.path.join(WORLD, "reads.fq"), "rb").read()
+    cut = data.index(b"\n@", len(data) // 2) + 1
+    odd.write_bytes(data[:cut] + b"@\nACGT\n+\nIIII\n" + data[cut:])
+    _run(s, ["-O", str(odd), "-n", "3"], str(tmp_path / "so"), env)
+    _run(s, ["-O", str(odd), "-n", "3"], str(tmp_path / "to"), off)
+    assert open(str(tmp_path / "so.csv"), "rb").read() == open(str(tmp_path / "to.csv"), "rb").read()
