@@ -54,7 +54,7 @@ def parse():
     ap.add_argument("--c4-read-len", type=int, default=10_000)
     ap.add_argument("--no-sharded-leg", action="store_true", help="N >= 2: skip the leg with the table sharded over the ranks")
     ap.add_argument("--no-cli-e2e", action="store_true", help="N = 1: skip the file -> CSV leg through bin/cuCLARK")
-    ap.add_argument("--cli-genomes", type=int, default=100, help="cli_e2e: genomes of its database (x genome-len, built by bin/cuCLARK itself)")
+    ap.add_argument("--cli-genomes", type=int, default=128, help="cli_e2e: genomes of its database (x genome-len, built by bin/cuCLARK itself)")
     ap.add_argument("--cli-reads", type=int, default=10_000_000)
     ap.add_argument("--sharded", action="store_true",
                     help="row E2: the table sharded over the N GPUs (k-mer all-to-all) instead of replicated")
@@ -695,7 +695,29 @@ def cli_e2e_leg(args, local):
         timed = [x for x in runs[1:] if x["classify_s"]]
         best = min(timed, key=lambda x: x["classify_s"])
         same_csv = open(os.path.join(d, "res1.csv"), "rb").read() == open(os.path.join(d, "res2.csv"), "rb").read()
-        return {"what": f"bin/cuCLARK -n {cores}: {NR} x {L} bp reads as one FASTQ file ({fq_bytes / 1e9:.2f} GB, page cache) -> CSV; database of "
+        # SURVEY D4 baseline 3: the reference's own cuCLARK build for this GPU (oracle/_ref/cuCLARK, unmodified sources, sm_100)
+        # on the same files; it only runs with a number of targets that is a multiple of 32 (tests/golden/ref_gpu/README.md)
+        ref_gpu = None
+        ref_exe = os.path.join(ROOT, "oracle", "_ref", "cuCLARK")
+        if not os.path.exists(ref_exe):
+            ref_gpu = {"unavailable": "oracle/_ref/cuCLARK not built"}
+        elif G % 32:
+            ref_gpu = {"unavailable": f"{G} targets: the reference kernels deadlock unless the number of targets is a multiple of 32"}
+        else:
+            t0 = time.time()
+            try:
+                r = subprocess.run([ref_exe, "-T", os.path.join(d, "targets.txt"), "-D", os.path.join(d, "db") + "/", "-O", fq, "-R", os.path.join(d, "ref"),
+                                    "-n", str(cores), "-b", "32"], capture_output=True, text=True, timeout=600, env=dict(os.environ, CUDA_VISIBLE_DEVICES=str(local)))
+                m = re.search(r"Done in ([0-9.]+)s \((\d+) reads/min", r.stderr.replace("\n", " "))
+                if r.returncode == 0 and m:
+                    ref_gpu = {"what": f"oracle/_ref/cuCLARK -n {cores} -b 32 on the same targets, database files and FASTQ; its own 'Done in' line",
+                               "classify_s": float(m.group(1)), "reads_per_s": int(m.group(2)) / 60.0, "process_wall_s": time.time() - t0,
+                               "csv_identical_to_ours": open(os.path.join(d, "ref.csv"), "rb").read() == open(os.path.join(d, "res1.csv"), "rb").read()}
+                else:
+                    ref_gpu = {"unavailable": "reference binary failed: " + r.stderr[-200:].replace("\n", " ")}
+            except subprocess.TimeoutExpired:
+                ref_gpu = {"unavailable": "reference binary did not finish in 600 s"}
+        return {"reference_gpu": ref_gpu,"what": f"bin/cuCLARK -n {cores}: {NR} x {L} bp reads as one FASTQ file ({fq_bytes / 1e9:.2f} GB, page cache) -> CSV; database of "
                         f"{G} x {LG} bp genomes built by the binary itself on the first run; anchor index on (product default)",
                 "reads_per_s": NR / best["classify_s"], "classify_s": best["classify_s"], "index_s": best["index_s"], "threads": cores,
                 "fastq_gbs": fq_bytes / best["classify_s"] / 1e9, "process_wall_s": best["wall_s"], "first_run_with_db_build_wall_s": runs[0]["wall_s"],

@@ -101,7 +101,7 @@ static void free_slots(ccb_handle* h)
         if (!s.shared_results) { cudaFreeHost(s.h_final5); cudaFreeHost(s.h_rows); }
         cudaFreeHost(s.h_ovf_count); cudaFreeHost(s.h_stats);
         cudaFree(s.d_offsets); cudaFree(s.d_cont); cudaFree(s.d_final5); cudaFree(s.d_rows);
-        cudaFree(s.d_ovf_list); cudaFree(s.d_ovf_count); cudaFree(s.d_dense_scratch); cudaFree(s.d_stats);
+        cudaFree(s.d_ovf_list); cudaFree(s.d_ovf_count); cudaFree(s.d_dense_scratch); cudaFree(s.d_stats); cudaFree(s.d_anchor_pre);
         if (s.done) cudaEventDestroy(s.done);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
@@ -121,7 +121,7 @@ extern "C" void ccb_destroy(ccb_handle* h)
     anchor_build_free(h);
     anchor_free(h->anchor);
     table_destroy(h->table);
-    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense);
+    cudaFree(h->q_ovf_list); cudaFree(h->q_ovf_count); cudaFree(h->q_dense); cudaFree(h->q_anchor_pre);
     for (auto& x : h->shard_scratch) { cudaFree(x.scan_tmp); cudaFree(x.ovf_list); cudaFree(x.ovf_count); cudaFree(x.dense); }
     if (h->db_stream) cudaStreamDestroy(h->db_stream);
     delete h;
@@ -413,6 +413,7 @@ static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_container
         ok(cudaMalloc(&s.d_ovf_list, (size_t)(max_reads ? max_reads : 1) * 8)); ok(cudaMalloc(&s.d_ovf_count, 8));   // [overflow list | redo list]
         ok(cudaMalloc(&s.d_dense_scratch, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
         ok(cudaMalloc(&s.d_stats, 32));
+        ok(cudaMalloc(&s.d_anchor_pre, (size_t)(max_reads ? max_reads : 1) * kAnchorPreBytes));
         if (extended) { if (!index_batches) ok(cudaMallocHost(&s.h_rows, sr)); ok(cudaMalloc(&s.d_rows, sr)); }
         if (e != cudaSuccess) {
             free_slots(h);
@@ -494,6 +495,7 @@ extern "C" int ccb_batch_submit(ccb_handle* h, int slot, uint32_t n_reads, uint6
     a.offsets = s.d_offsets; a.containers = s.d_cont; a.n_reads = n_reads;
     a.out5 = s.d_final5; a.rows = (flags & CCB_EXTENDED) ? s.d_rows : nullptr; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? s.d_stats : nullptr; a.stats_words = 4;
+    a.anchor_pre = s.d_anchor_pre;
     if (flags & CCB_STATS) CU(h, cudaMemsetAsync(s.d_stats, 0, 32, s.stream));
     int rc = run_query(h, a, s.d_ovf_list, s.d_ovf_count, h->max_reads, s.d_dense_scratch, flags, s.stream, (int64_t)n_containers);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
@@ -564,11 +566,17 @@ extern "C" int ccb_query_device(ccb_handle* h, const void* d_offsets, const void
         h->q_ovf_cap = n_reads;
     }
     if (!h->q_ovf_count) CU(h, cudaMalloc(&h->q_ovf_count, 8));
+    if (h->anchor.ready && !(flags & CCB_NO_ANCHOR) && (h->q_pre_cap < n_reads || !h->q_anchor_pre)) {
+        cudaFree(h->q_anchor_pre); h->q_anchor_pre = nullptr; h->q_pre_cap = 0;
+        CU(h, cudaMalloc(&h->q_anchor_pre, (size_t)(n_reads ? n_reads : 1) * kAnchorPreBytes));
+        h->q_pre_cap = n_reads;
+    }
     if (!h->q_dense) CU(h, cudaMalloc(&h->q_dense, (size_t)kDenseBlocks * h->cfg.n_targets * 4));
     QueryArgs a{};
     a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
     a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
     a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr; a.stats_words = (flags & CCB_STATS_EX) ? 4 : 2;
+    a.anchor_pre = h->q_anchor_pre;
     int rc = run_query(h, a, h->q_ovf_list, h->q_ovf_count, h->q_ovf_cap, h->q_dense, flags, (cudaStream_t)stream);
     if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
     return 0;

@@ -20,6 +20,7 @@ struct Slot {
     uint16_t* d_final5 = nullptr;  uint16_t* d_rows = nullptr;
     uint32_t* d_ovf_list = nullptr; uint32_t* d_ovf_count = nullptr;
     uint32_t* d_dense_scratch = nullptr;
+    void*     d_anchor_pre = nullptr;          // max_reads x kAnchorPreBytes: results of the anchor pass (query_lane.cu)
     unsigned long long* d_stats = nullptr;     // lookups, sectors
     uint32_t* h_ovf_count = nullptr;           // pinned
     unsigned long long* h_stats = nullptr;     // pinned
@@ -79,6 +80,7 @@ struct ccb_handle {
     // scratch for ccb_query_device
     uint32_t* q_ovf_list = nullptr; uint32_t* q_ovf_count = nullptr; uint32_t* q_dense = nullptr;
     uint32_t  q_ovf_cap = 0;
+    void*     q_anchor_pre = nullptr; uint32_t q_pre_cap = 0;
     // sharded table (ccb_shard_*): this handle holds shard `shard` of `n_shards`
     uint32_t   n_shards = 1, shard = 0;
     // scratch of ccb_shard_count / ccb_shard_vote, one set per stream they were called on (batches of a

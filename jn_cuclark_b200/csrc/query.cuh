@@ -25,7 +25,10 @@ struct QueryArgs {
     // thread-per-read kernel handed back
     const uint32_t* read_list;
     const uint32_t* n_list;
+    // optional scratch, n_reads x kAnchorPreBytes: with it the anchor pass runs as a kernel of its own (query_lane.cu)
+    void*           anchor_pre;
 };
+constexpr int kAnchorPreBytes = 64;
 
 // Sharded table: each read's mixed k-mers h = mix2k(canonical) are sent
 // to the shard that owns them.  Per read r and owner g the k-mers occupy

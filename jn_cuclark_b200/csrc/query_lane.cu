@@ -102,10 +102,189 @@ __device__ __forceinline__ uint64_t match_anchor(const uint64_t (&e)[4], uint32_
 
 }  // namespace
 
-template <int BLK, int MINB, bool ANCHOR, bool STATS, bool STAGE>
+// Phase A for one part of a read (with the anchor index): roll over the part until two sampled k-mers are met, look both
+// up in the sampled table at once, compare the part with the target text base by base.  W = the windows answered without
+// a table probe; vote_lab / vote_hits = the label those windows vote for and how many of them are stored k-mers.
+// ldc(i) = container i of the batch.
+template <bool STATS, typename LDC>
+__device__ __forceinline__ void anchor_part(const TableView& t, const AnchorView& av, LDC&& ldc, uint32_t beg, int len, int nslots,
+                                            int k, uint64_t kmsk, int s2, Bits192& W, uint32_t& vote_lab, uint32_t& vote_hits,
+                                            unsigned long long& st_lookups, unsigned long long& st_sectors)
+{
+    // rolling state after the first k-1 bases, cut out of the first four containers
+    uint64_t x, rc;
+    {
+        uint64_t v = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)ldc(beg + 1 + j) : 0ull);
+        x = k > 1 ? v >> (64 - s2) : 0ull;
+        rc = revcomp_brev(x, k);
+    }
+    uint32_t cw = 0;
+    int i = k - 1;
+    if (i & 7) cw = ldc(beg + 1 + (i >> 3));
+    uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
+    // up to two rounds; a round = the next two sampled k-mers of the read, looked up together
+    for (int round = 0; round < 2 && ae == ~0ull && i < len; round++) {
+        uint64_t c0 = 0, c1 = 0; int p0 = 0, p1 = 0; uint32_t f0 = 0, f1 = 0; int nc = 0;
+        for (; i < len && nc < 2; i++) {
+            if ((i & 7) == 0) cw = ldc(beg + 1 + (i >> 3));
+            const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
+            x = ((x << 2) | code) & kmsk;
+            rc = (rc >> 2) | ((3ull - code) << s2);
+            const uint64_t cn = x < rc ? x : rc;
+            if (anchor_sampled(cn)) {
+                if (nc == 0) { c0 = cn; p0 = i - (k - 1); f0 = x <= rc ? 1u : 0u; }
+                else         { c1 = cn; p1 = i - (k - 1); f1 = x <= rc ? 1u : 0u; }
+                nc++;
+            }
+        }
+        if (nc == 0) break;
+        const uint64_t h0 = mix2k(c0, k, kmsk), h1 = mix2k(c1, k, kmsk);
+        const uint64_t b0 = mulhi64(h0 << t.hp.shift, av.nb), b1 = mulhi64(h1 << t.hp.shift, av.nb);
+        const uint32_t fp0 = (uint32_t)h0 & 0x7FFFu, fp1 = (uint32_t)h1 & 0x7FFFu;
+        uint64_t e0[4], e1[4];
+        load_bucket64(av.buckets + b0, e0);                      // a full sector overflows into b ^ 1: the same 64 bytes
+        if (nc > 1) load_bucket64(av.buckets + b1, e1);
+        if (STATS) st_sectors += nc;
+        uint64_t m = match_anchor(e0, fp0);
+        if (m == ~0ull && e0[3] != ~0ull) {                       // full sector: its neighbour may hold it
+            load_bucket64(av.buckets + (b0 ^ 1ull), e0);
+            if (STATS) st_sectors++;
+            m = match_anchor(e0, fp0);
+        }
+        if (m != ~0ull) { ae = m; apos = p0; afwd = f0; }
+        else if (nc > 1) {
+            m = match_anchor(e1, fp1);
+            if (m == ~0ull && e1[3] != ~0ull) {
+                load_bucket64(av.buckets + (b1 ^ 1ull), e1);
+                if (STATS) st_sectors++;
+                m = match_anchor(e1, fp1);
+            }
+            if (m != ~0ull) { ae = m; apos = p1; afwd = f1; }
+        }
+    }
+    if (ae != ~0ull) {
+        const uint32_t alab = (uint32_t)(ae >> 32) & 0xFFFFu;
+        const uint64_t tpos = ae & 0xFFFFFFFFull;
+        const bool same = afwd == ((uint32_t)(ae >> 48) & 1u);
+        // text position of read base 0 (F half, or the reverse-complement half)
+        const int64_t g0 = same ? (int64_t)tpos - apos : (int64_t)(2 * av.nF - tpos - (uint64_t)k) - apos;
+        if (g0 >= 0 && (uint64_t)g0 + kLaneMaxBases + 64 <= 2 * av.nF) {
+            const int sft = (int)(g0 & 31);
+            const int ngr = (sft + len + 31) >> 5;                                    // text groups the read spans (<= 7)
+            const uint32_t* tg = av.txt + (size_t)kTextWords * ((uint64_t)g0 >> 5);
+            uint32_t pw0, pw1, pv, pd, po;                                            // group u
+            pw0 = __ldg(tg); pw1 = __ldg(tg + 1); pv = __ldg(tg + 2); pd = __ldg(tg + 3); po = __ldg(tg + 4);
+            Bits192 good, D, O;
+            good.w[0] = good.w[1] = good.w[2] = 0; D = good; O = good;
+            bool span_ok = true;
+#pragma unroll
+            for (int u = 0; u < 6; u++) {
+                uint32_t nw0 = 0, nw1 = 0, nv = 0, nd = 0, no = 0;                    // group u + 1
+                if (u + 1 < ngr) {
+                    const uint32_t* g = tg + kTextWords * (u + 1);
+                    nw0 = __ldg(g); nw1 = __ldg(g + 1); nv = __ldg(g + 2); nd = __ldg(g + 3); no = __ldg(g + 4);
+                }
+                const int here = len - 32 * u;                                        // read bases from 32u on
+                if (here > 0) {
+                    // text bases at read positions 32u .. 32u+31
+                    const uint64_t tcur = ((uint64_t)pw0 << 32) | pw1, tnxt = ((uint64_t)nw0 << 32) | nw1;
+                    const uint64_t tt = sft ? (tcur << (2 * sft)) | (tnxt >> (64 - 2 * sft)) : tcur;
+                    uint64_t rd = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int sl = 1 + 4 * u + j;
+                        rd = (rd << 16) | (sl < nslots ? (uint64_t)ldc(beg + sl) : 0ull);
+                    }
+                    const uint64_t df = tt ^ rd;
+                    const uint32_t mis = mismatch16((uint32_t)(df >> 32)) | (mismatch16((uint32_t)df) << 16);
+                    const uint32_t gv = __funnelshift_r(pv, nv, sft), gd = __funnelshift_r(pd, nd, sft),
+                                   go = __funnelshift_r(po, no, sft);
+                    const uint32_t need = here >= 32 ? 0xFFFFFFFFu : (1u << here) - 1u;
+                    if ((gv & need) != need) span_ok = false;     // a separator inside the span: another record may follow
+                    const uint32_t g32 = ~mis & gv & need;
+                    if (u & 1) { good.w[u >> 1] |= (uint64_t)g32 << 32; D.w[u >> 1] |= (uint64_t)gd << 32; O.w[u >> 1] |= (uint64_t)go << 32; }
+                    else       { good.w[u >> 1] = g32; D.w[u >> 1] = gd; O.w[u >> 1] = go; }
+                }
+                pw0 = nw0; pw1 = nw1; pv = nv; pd = nd; po = no;
+            }
+            if (STATS) st_sectors += (uint32_t)(ngr * kTextWords * 4 + 31) / 32u;
+            if (span_ok) {
+                Bits192 run = good; int have = 1;
+                while (2 * have <= k) { run.and_with(run.shr(have)); have *= 2; }
+                if (have < k) run.and_with(run.shr(k - have));
+                run.w[0] &= ~O.w[0]; run.w[1] &= ~O.w[1]; run.w[2] &= ~O.w[2];       // stored under another label: probe
+                W = run;
+                const uint32_t hits = __popcll(W.w[0] & D.w[0]) + __popcll(W.w[1] & D.w[1]) + __popcll(W.w[2] & D.w[2]);
+                if (hits) { vote_lab = alab; vote_hits = hits; }
+                if (STATS) st_lookups += __popcll(W.w[0]) + __popcll(W.w[1]) + __popcll(W.w[2]);
+            }
+        }
+    }
+}
+
+// what k_anchor_scan leaves for k_query_block<PRE>: per read and part, the windows already answered and their vote
+struct alignas(64) AnchorPre {
+    uint64_t w[2][3];
+    uint32_t vote[2];          // label << 16 | stored windows among the answered ones (0: none)
+    uint32_t pad[2];
+};
+static_assert(sizeof(AnchorPre) == kAnchorPreBytes, "AnchorPre layout");
+
+// The anchor pass as a kernel of its own: a thread per read, no shared memory, no barriers -- a chain of dependent loads
+// (offsets -> containers -> sampled table -> text) that only needs many reads in flight.  The probe kernel that follows
+// (k_query_block<PRE>) then runs at the table-only kernel's occupancy instead of carrying this pass's 125 registers.
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_anchor_scan(const TableView t, const QueryArgs a, const AnchorView av, AnchorPre* __restrict__ pre)
+{
+    const int k = t.hp.k;
+    const uint64_t kmsk = t.hp.mask;
+    const int s2 = 2 * (k - 1);
+    unsigned long long st_lookups = 0, st_sectors = 0;
+    auto ldc = [&](uint32_t idx) -> uint32_t { return (uint32_t)__ldg(a.containers + idx); };
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < a.n_reads; r += gridDim.x * blockDim.x) {
+        const uint32_t rbeg = __ldg(a.offsets + r);
+        const int rslots = (int)(__ldg(a.offsets + r + 1) - rbeg);
+        if (rslots == 0) continue;
+        const int plen0 = (int)ldc(rbeg), pn0 = 1 + ((plen0 + 7) >> 3);
+        int plen1 = 0;
+        bool mine = plen0 >= k && plen0 <= kLaneMaxBases && pn0 <= rslots;
+        if (mine && pn0 < rslots) {
+            plen1 = (int)ldc(rbeg + (uint32_t)pn0);
+            mine = plen1 >= k && plen1 <= kLaneMaxBases && pn0 + 1 + ((plen1 + 7) >> 3) == rslots;
+        }
+        if (!mine) continue;                          // k_query_block hands these reads to k_query and never looks at pre[r]
+        AnchorPre o;
+#pragma unroll
+        for (int part = 0; part < 2; part++) {
+            Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;
+            uint32_t vlab = kLabelNone, vhits = 0;
+            const int len = part ? plen1 : plen0;
+            if (len - k + 1 >= 16)
+                anchor_part<STATS>(t, av, ldc, rbeg + (part ? (uint32_t)pn0 : 0u), len, 1 + ((len + 7) >> 3), k, kmsk, s2, W, vlab, vhits,
+                                   st_lookups, st_sectors);
+            o.w[part][0] = W.w[0]; o.w[part][1] = W.w[1]; o.w[part][2] = W.w[2];
+            o.vote[part] = vhits ? (vlab << 16) | (vhits & 0xFFFFu) : 0u;
+        }
+        o.pad[0] = o.pad[1] = 0;
+        pre[r] = o;
+    }
+    if (STATS) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            st_lookups += __shfl_xor_sync(0xFFFFFFFFu, st_lookups, o);
+            st_sectors += __shfl_xor_sync(0xFFFFFFFFu, st_sectors, o);
+        }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(a.stats + 0, st_lookups); atomicAdd(a.stats + 1, st_sectors); }
+    }
+}
+
+template <int BLK, int MINB, bool ANCHOR, bool STATS, bool STAGE, bool PRE = false>
 __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, const QueryArgs a, const AnchorView av,
                                                           uint32_t* redo_list, uint32_t* redo_count)
 {
+    const AnchorPre* __restrict__ pre = reinterpret_cast<const AnchorPre*>(a.anchor_pre);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BlockSmem<BLK>& sm = *reinterpret_cast<BlockSmem<BLK>*>(smem_raw);
     StageSmem<BLK>& st = *reinterpret_cast<StageSmem<BLK>*>(smem_raw + ((sizeof(BlockSmem<BLK>) + 15) & ~(size_t)15));
@@ -197,118 +376,16 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
                 sm.beg[tid] = beg; sm.len[tid] = (uint16_t)len;
                 const int npos = len - k + 1;
                 Bits192 W; W.w[0] = W.w[1] = W.w[2] = 0;            // windows answered without a table probe
-                if (ANCHOR && npos >= 16) {      // fewer windows: the index's own line fetches (3-4) outweigh what it can save
-                    // rolling state after the first k-1 bases, cut out of the first four containers
-                    uint64_t x, rc;
-                    {
-                        uint64_t v = 0;
-#pragma unroll
-                        for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)ldc(beg + 1 + j) : 0ull);
-                        x = k > 1 ? v >> (64 - s2) : 0ull;
-                        rc = revcomp_brev(x, k);
-                    }
-                    uint32_t cw = 0;
-                    int i = k - 1;
-                    if (i & 7) cw = ldc(beg + 1 + (i >> 3));
-                    uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
-                    // up to two rounds; a round = the next two sampled k-mers of the read, looked up together
-                    for (int round = 0; round < 2 && ae == ~0ull && i < len; round++) {
-                        uint64_t c0 = 0, c1 = 0; int p0 = 0, p1 = 0; uint32_t f0 = 0, f1 = 0; int nc = 0;
-                        for (; i < len && nc < 2; i++) {
-                            if ((i & 7) == 0) cw = ldc(beg + 1 + (i >> 3));
-                            const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
-                            x = ((x << 2) | code) & kmsk;
-                            rc = (rc >> 2) | ((3ull - code) << s2);
-                            const uint64_t cn = x < rc ? x : rc;
-                            if (anchor_sampled(cn)) {
-                                if (nc == 0) { c0 = cn; p0 = i - (k - 1); f0 = x <= rc ? 1u : 0u; }
-                                else         { c1 = cn; p1 = i - (k - 1); f1 = x <= rc ? 1u : 0u; }
-                                nc++;
-                            }
-                        }
-                        if (nc == 0) break;
-                        const uint64_t h0 = mix2k(c0, k, kmsk), h1 = mix2k(c1, k, kmsk);
-                        const uint64_t b0 = mulhi64(h0 << t.hp.shift, av.nb), b1 = mulhi64(h1 << t.hp.shift, av.nb);
-                        const uint32_t fp0 = (uint32_t)h0 & 0x7FFFu, fp1 = (uint32_t)h1 & 0x7FFFu;
-                        uint64_t e0[4], e1[4];
-                        load_bucket64(av.buckets + b0, e0);                      // a full sector overflows into b ^ 1: the same 64 bytes
-                        if (nc > 1) load_bucket64(av.buckets + b1, e1);
-                        if (STATS) st_sectors += nc;
-                        uint64_t m = match_anchor(e0, fp0);
-                        if (m == ~0ull && e0[3] != ~0ull) {                       // full sector: its neighbour may hold it
-                            load_bucket64(av.buckets + (b0 ^ 1ull), e0);
-                            if (STATS) st_sectors++;
-                            m = match_anchor(e0, fp0);
-                        }
-                        if (m != ~0ull) { ae = m; apos = p0; afwd = f0; }
-                        else if (nc > 1) {
-                            m = match_anchor(e1, fp1);
-                            if (m == ~0ull && e1[3] != ~0ull) {
-                                load_bucket64(av.buckets + (b1 ^ 1ull), e1);
-                                if (STATS) st_sectors++;
-                                m = match_anchor(e1, fp1);
-                            }
-                            if (m != ~0ull) { ae = m; apos = p1; afwd = f1; }
-                        }
-                    }
-                    if (ae != ~0ull) {
-                        const uint32_t alab = (uint32_t)(ae >> 32) & 0xFFFFu;
-                        const uint64_t tpos = ae & 0xFFFFFFFFull;
-                        const bool same = afwd == ((uint32_t)(ae >> 48) & 1u);
-                        // text position of read base 0 (F half, or the reverse-complement half)
-                        const int64_t g0 = same ? (int64_t)tpos - apos : (int64_t)(2 * av.nF - tpos - (uint64_t)k) - apos;
-                        if (g0 >= 0 && (uint64_t)g0 + kLaneMaxBases + 64 <= 2 * av.nF) {
-                            const int sft = (int)(g0 & 31);
-                            const int ngr = (sft + len + 31) >> 5;                                    // text groups the read spans (<= 7)
-                            const uint32_t* tg = av.txt + (size_t)kTextWords * ((uint64_t)g0 >> 5);
-                            uint32_t pw0, pw1, pv, pd, po;                                            // group u
-                            pw0 = __ldg(tg); pw1 = __ldg(tg + 1); pv = __ldg(tg + 2); pd = __ldg(tg + 3); po = __ldg(tg + 4);
-                            Bits192 good, D, O;
-                            good.w[0] = good.w[1] = good.w[2] = 0; D = good; O = good;
-                            bool span_ok = true;
-#pragma unroll
-                            for (int u = 0; u < 6; u++) {
-                                uint32_t nw0 = 0, nw1 = 0, nv = 0, nd = 0, no = 0;                    // group u + 1
-                                if (u + 1 < ngr) {
-                                    const uint32_t* g = tg + kTextWords * (u + 1);
-                                    nw0 = __ldg(g); nw1 = __ldg(g + 1); nv = __ldg(g + 2); nd = __ldg(g + 3); no = __ldg(g + 4);
-                                }
-                                const int here = len - 32 * u;                                        // read bases from 32u on
-                                if (here > 0) {
-                                    // text bases at read positions 32u .. 32u+31
-                                    const uint64_t tcur = ((uint64_t)pw0 << 32) | pw1, tnxt = ((uint64_t)nw0 << 32) | nw1;
-                                    const uint64_t tt = sft ? (tcur << (2 * sft)) | (tnxt >> (64 - 2 * sft)) : tcur;
-                                    uint64_t rd = 0;
-#pragma unroll
-                                    for (int j = 0; j < 4; j++) {
-                                        const int sl = 1 + 4 * u + j;
-                                        rd = (rd << 16) | (sl < nslots ? (uint64_t)ldc(beg + sl) : 0ull);
-                                    }
-                                    const uint64_t df = tt ^ rd;
-                                    const uint32_t mis = mismatch16((uint32_t)(df >> 32)) | (mismatch16((uint32_t)df) << 16);
-                                    const uint32_t gv = __funnelshift_r(pv, nv, sft), gd = __funnelshift_r(pd, nd, sft),
-                                                   go = __funnelshift_r(po, no, sft);
-                                    const uint32_t need = here >= 32 ? 0xFFFFFFFFu : (1u << here) - 1u;
-                                    if ((gv & need) != need) span_ok = false;     // a separator inside the span: another record may follow
-                                    const uint32_t g32 = ~mis & gv & need;
-                                    if (u & 1) { good.w[u >> 1] |= (uint64_t)g32 << 32; D.w[u >> 1] |= (uint64_t)gd << 32; O.w[u >> 1] |= (uint64_t)go << 32; }
-                                    else       { good.w[u >> 1] = g32; D.w[u >> 1] = gd; O.w[u >> 1] = go; }
-                                }
-                                pw0 = nw0; pw1 = nw1; pv = nv; pd = nd; po = no;
-                            }
-                            if (STATS) st_sectors += (uint32_t)(ngr * kTextWords * 4 + 31) / 32u;
-                            if (span_ok) {
-                                Bits192 run = good; int have = 1;
-                                while (2 * have <= k) { run.and_with(run.shr(have)); have *= 2; }
-                                if (have < k) run.and_with(run.shr(k - have));
-                                run.w[0] &= ~O.w[0]; run.w[1] &= ~O.w[1]; run.w[2] &= ~O.w[2];       // stored under another label: probe
-                                W = run;
-                                const uint32_t hits = __popcll(W.w[0] & D.w[0]) + __popcll(W.w[1] & D.w[1]) + __popcll(W.w[2] & D.w[2]);
-                                if (hits) vote_smem(sm, (uint32_t)tid, alab, hits);
-                                if (STATS) st_lookups += __popcll(W.w[0]) + __popcll(W.w[1]) + __popcll(W.w[2]);
-                            }
-                        }
-                    }
+                if (ANCHOR && !PRE && npos >= 16) {      // fewer windows: the index's own line fetches (3-4) outweigh what it can save
+                    uint32_t vlab = kLabelNone, vhits = 0;
+                    anchor_part<STATS>(t, av, ldc, beg, len, nslots, k, kmsk, s2, W, vlab, vhits, st_lookups, st_sectors);
+                    if (vhits) vote_smem(sm, (uint32_t)tid, vlab, vhits);
+                }
+                if (PRE) {                               // the anchor pass ran as a kernel of its own (k_anchor_scan)
+                    const AnchorPre& ap = pre[r];
+                    W.w[0] = ap.w[part][0]; W.w[1] = ap.w[part][1]; W.w[2] = ap.w[part][2];
+                    const uint32_t v = ap.vote[part];
+                    if (v & 0xFFFFu) vote_smem(sm, (uint32_t)tid, v >> 16, v & 0xFFFFu);
                 }
                 // ---- the windows still to probe: items of <= 4 windows of one 16-window chunk ----
                 uint32_t nitems = 0;
@@ -457,12 +534,12 @@ __global__ void __launch_bounds__(BLK, MINB) k_query_block(const TableView t, co
 
 namespace {
 
-template <int BLK, int MINB, bool STAGE = false>
+template <int BLK, int MINB, bool STAGE = false, bool PRE = false>
 int launch_block(const TableView& t, const QueryArgs& a, const AnchorView* av, uint32_t* redo_list, uint32_t* redo_count,
                  cudaStream_t s)
 {
     // the staged copy moves 16-byte granules: it needs the batch's containers to start on one
-    if (STAGE && ((uintptr_t)a.containers & 15u)) return launch_block<BLK, MINB, false>(t, a, av, redo_list, redo_count, s);
+    if (STAGE && ((uintptr_t)a.containers & 15u)) return launch_block<BLK, MINB, false, PRE>(t, a, av, redo_list, redo_count, s);
     const size_t smem = ((sizeof(BlockSmem<BLK>) + 15) & ~(size_t)15) + (STAGE ? sizeof(StageSmem<BLK>) : 0);
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
     const uint32_t cap = 148u * 64u * (256u / BLK);
@@ -470,12 +547,13 @@ int launch_block(const TableView& t, const QueryArgs& a, const AnchorView* av, u
     const AnchorView none{};
 #define CCB_LAUNCH_BLOCK(AN, ST, AV)                                                                                   \
     do {   /* the attribute is per device: set it on every launch (microseconds) rather than remember who has it */   \
-        cudaError_t e = cudaFuncSetAttribute(k_query_block<BLK, MINB, AN, ST, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        cudaError_t e = cudaFuncSetAttribute(k_query_block<BLK, MINB, AN, ST, STAGE, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return (int)e;                                                                           \
-        k_query_block<BLK, MINB, AN, ST, STAGE><<<ctas, BLK, smem, s>>>(t, a, AV, redo_list, redo_count);                      \
+        k_query_block<BLK, MINB, AN, ST, STAGE, PRE><<<ctas, BLK, smem, s>>>(t, a, AV, redo_list, redo_count);                      \
     } while (0)
-    if (av) { if (a.stats) CCB_LAUNCH_BLOCK(true, true, *av); else CCB_LAUNCH_BLOCK(true, false, *av); }
-    else    { if (a.stats) CCB_LAUNCH_BLOCK(false, true, none); else CCB_LAUNCH_BLOCK(false, false, none); }
+    if (PRE)     { if (a.stats) CCB_LAUNCH_BLOCK(false, true, none); else CCB_LAUNCH_BLOCK(false, false, none); }
+    else if (av) { if (a.stats) CCB_LAUNCH_BLOCK(true, true, *av); else CCB_LAUNCH_BLOCK(true, false, *av); }
+    else         { if (a.stats) CCB_LAUNCH_BLOCK(false, true, none); else CCB_LAUNCH_BLOCK(false, false, none); }
 #undef CCB_LAUNCH_BLOCK
     return (int)cudaGetLastError();
 }
@@ -501,6 +579,19 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
     if (shape && !strcmp(shape, "64x8")) return launch_block<64, 8>(t, a, av, redo_list, redo_count, s);
     if (shape && !strcmp(shape, "128x5")) return launch_block<128, 5>(t, a, av, redo_list, redo_count, s);
 #endif
+    // With the anchor index and scratch for its results (QueryArgs::anchor_pre): the anchor pass as a kernel of its own,
+    // then the probe kernel at the table-only shape.  CCB_FUSED_ANCHOR=1 (or no scratch) keeps both in one kernel.
+    const char* fe = getenv("CCB_FUSED_ANCHOR");
+    const bool fused = fe && atoi(fe);
+    if (av && a.anchor_pre && !fused) {
+        uint32_t g = (a.n_reads + 127) / 128;
+        if (g > 148u * 64u) g = 148u * 64u;
+        if (a.stats) k_anchor_scan<true><<<g, 128, 0, s>>>(t, a, *av, reinterpret_cast<AnchorPre*>(a.anchor_pre));
+        else         k_anchor_scan<false><<<g, 128, 0, s>>>(t, a, *av, reinterpret_cast<AnchorPre*>(a.anchor_pre));
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return (int)e;
+        return launch_block<256, 3, false, true>(t, a, nullptr, redo_list, redo_count, s);
+    }
     return av ? launch_block<128, 4>(t, a, av, redo_list, redo_count, s) : launch_block<256, 3>(t, a, av, redo_list, redo_count, s);
 }
 

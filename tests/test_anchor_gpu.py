@@ -6,6 +6,17 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["split", "fused"])
+def anchor_flavour(request, monkeypatch):
+    """Every case runs twice: the anchor pass as a kernel of its own in front of the probe kernel (the default:
+    k_anchor_scan + k_query_block<PRE>), and both passes fused in one kernel (CCB_FUSED_ANCHOR=1)."""
+    if request.param == "fused":
+        monkeypatch.setenv("CCB_FUSED_ANCHOR", "1")
+    else:
+        monkeypatch.delenv("CCB_FUSED_ANCHOR", raising=False)
+    yield
+
+
 def _classify(db, d_off, d_cont, n, flags):
     import torch
     out = torch.zeros(n * 5, dtype=torch.int16, device="cuda")
