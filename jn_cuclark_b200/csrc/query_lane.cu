@@ -176,6 +176,9 @@ __device__ __forceinline__ void anchor_part(const TableView& t, const AnchorView
             const uint32_t* tg = av.txt + (size_t)kTextWords * ((uint64_t)g0 >> 5);
             uint32_t pw0, pw1, pv, pd, po;                                            // group u
             pw0 = __ldg(tg); pw1 = __ldg(tg + 1); pv = __ldg(tg + 2); pd = __ldg(tg + 3); po = __ldg(tg + 4);
+            // the span covers two 128-byte lines (seldom three): ask for the last group now, so that the second line is
+            // on its way while the first is compared instead of one more full latency in the middle of the loop
+            const uint32_t last_w0 = ngr > 1 ? __ldg(tg + kTextWords * (ngr - 1)) : 0u;
             Bits192 good, D, O;
             good.w[0] = good.w[1] = good.w[2] = 0; D = good; O = good;
             bool span_ok = true;
@@ -184,7 +187,8 @@ __device__ __forceinline__ void anchor_part(const TableView& t, const AnchorView
                 uint32_t nw0 = 0, nw1 = 0, nv = 0, nd = 0, no = 0;                    // group u + 1
                 if (u + 1 < ngr) {
                     const uint32_t* g = tg + kTextWords * (u + 1);
-                    nw0 = __ldg(g); nw1 = __ldg(g + 1); nv = __ldg(g + 2); nd = __ldg(g + 3); no = __ldg(g + 4);
+                    nw0 = (u + 1 == ngr - 1) ? last_w0 : __ldg(g);
+                    nw1 = __ldg(g + 1); nv = __ldg(g + 2); nd = __ldg(g + 3); no = __ldg(g + 4);
                 }
                 const int here = len - 32 * u;                                        // read bases from 32u on
                 if (here > 0) {
@@ -243,11 +247,22 @@ __global__ void __launch_bounds__(128) k_anchor_scan(const TableView t, const Qu
     const int s2 = 2 * (k - 1);
     unsigned long long st_lookups = 0, st_sectors = 0;
     auto ldc = [&](uint32_t idx) -> uint32_t { return (uint32_t)__ldg(a.containers + idx); };
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < a.n_reads; r += gridDim.x * blockDim.x) {
-        const uint32_t rbeg = __ldg(a.offsets + r);
-        const int rslots = (int)(__ldg(a.offsets + r + 1) - rbeg);
+    // the offsets, the header container and the far end of the NEXT read of this thread are asked for one read ahead:
+    // one dependent trip to memory less in every read's chain
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t nx_beg = 0, nx_end = 0, nx_hdr = 0, keep = 0;
+    if (r < a.n_reads) { nx_beg = __ldg(a.offsets + r); nx_end = __ldg(a.offsets + r + 1); if (nx_end > nx_beg) nx_hdr = ldc(nx_beg); }
+    for (; r < a.n_reads; r += stride) {
+        const uint32_t rbeg = nx_beg;
+        const int rslots = (int)(nx_end - nx_beg);
+        const int plen0 = (int)nx_hdr;
+        if (r + stride < a.n_reads) {
+            nx_beg = __ldg(a.offsets + r + stride); nx_end = __ldg(a.offsets + r + stride + 1);
+            if (nx_end > nx_beg) { nx_hdr = ldc(nx_beg); keep ^= ldc(nx_end - 1); }
+        }
         if (rslots == 0) continue;
-        const int plen0 = (int)ldc(rbeg), pn0 = 1 + ((plen0 + 7) >> 3);
+        const int pn0 = 1 + ((plen0 + 7) >> 3);
         int plen1 = 0;
         bool mine = plen0 >= k && plen0 <= kLaneMaxBases && pn0 <= rslots;
         if (mine && pn0 < rslots) {
@@ -270,6 +285,7 @@ __global__ void __launch_bounds__(128) k_anchor_scan(const TableView t, const Qu
         o.pad[0] = o.pad[1] = 0;
         pre[r] = o;
     }
+    if (keep == 0xABCDu) pre[0].pad[1] = keep;             // (keeps the look-ahead loads alive; pad is never read)
     if (STATS) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) {
