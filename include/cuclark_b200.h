@@ -245,6 +245,24 @@ int  ccb_query_device(ccb_handle* h, const void* d_offsets, const void* d_contai
                       uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
                       int flags, void* stream);
 
+/* ccb_query_device for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, flags and results as ccb_query_device, but the scratch (overflow / redo lists, the anchor pass's
+ * per-read records, the dense path's target counters) is a fixed device array inside the library -- 6.6 MB that every GPU
+ * loading the library holds until exit -- so the call makes no cudaMalloc / cudaFree, at the price of limits:
+ *   n_reads <= CCB_NOALLOC_MAX_READS per call and a handle created with n_targets <= CCB_NOALLOC_MAX_TARGETS;
+ *   beyond either the call fails (-70 / -71, message in ccb_last_error) and nothing is launched.
+ * The array's address is looked up on the first call on each device (a call with n_reads = 0 does only that: make
+ * it once before capturing; the CUDA driver also loads each kernel's code on its first launch, so run one batch of
+ * every kind -- flags, read lengths -- before a region that must not touch the allocator).  ALL calls on one GPU share the array: two calls whose kernels overlap on the GPU (different
+ * streams, or a captured graph replayed beside another call) race on it -- order them.  The array keeps the previous
+ * call's contents; what has to start at zero is cleared on the caller's stream by the call itself. */
+#define CCB_NOALLOC_MAX_READS   65536u
+#define CCB_NOALLOC_MAX_TARGETS 8192u
+int  ccb_query_device_noalloc(ccb_handle* h, const void* d_offsets, const void* d_containers,
+                              uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
+                              int flags, void* stream);
+
 int  ccb_get_stats(const ccb_handle* h, ccb_stats* out);
 
 /* ---- synthetic workload + roofline probe (bench.py and GPU tests; include/ccb_synth.h) ----

@@ -588,3 +588,72 @@ extern "C" int ccb_get_stats(const ccb_handle* h, ccb_stats* out)
     *out = h->stats;
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// ccb_query_device_noalloc: ccb_query_device for callers that must not allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+//
+// ccb_query_device keeps its scratch (overflow + redo lists, their counters, the anchor pass's 64 bytes per read, the
+// dense path's per-block target counters) in buffers it cudaMallocs on first use and regrows.  Here the same scratch is
+// ONE file-scope device array of a fixed size; every GPU that loads the library holds it (6.6 MB) until exit.  In host
+// code `g_noalloc_scratch` is only a stand-in for the symbol: its device address is asked for once per device with
+// cudaGetSymbolAddress (that device current) and kept.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr uint32_t kNoallocMaxReads = CCB_NOALLOC_MAX_READS;
+constexpr uint32_t kNoallocMaxTargets = CCB_NOALLOC_MAX_TARGETS;
+constexpr size_t kNoallocLists = 0;                                               // u32[2 * max reads]: overflow | redo
+constexpr size_t kNoallocCount = kNoallocLists + (size_t)kNoallocMaxReads * 8;    // 2 x u32 counters (own 256 bytes)
+constexpr size_t kNoallocPre = kNoallocCount + 256;                               // AnchorPre[max reads]
+constexpr size_t kNoallocDense = kNoallocPre + (size_t)kNoallocMaxReads * kAnchorPreBytes;
+constexpr size_t kNoallocBytes = kNoallocDense + (size_t)kDenseBlocks * kNoallocMaxTargets * 4;
+constexpr int kNoallocMaxDevices = 64;
+
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocBytes];
+
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[kNoallocMaxDevices];                          // per device: the array's device address
+
+extern "C" int ccb_query_device_noalloc(ccb_handle* h, const void* d_offsets, const void* d_containers,
+                                        uint32_t n_reads, void* d_final5, void* d_rows, void* d_stats,
+                                        int flags, void* stream)
+{
+    if (!h) return -1;
+    if (n_reads > kNoallocMaxReads)
+        return ccb_fail(h, -70, "ccb_query_device_noalloc: %u reads in one call, the fixed scratch holds %u (split the batch, or use ccb_query_device)",
+                        n_reads, kNoallocMaxReads);
+    if ((uint32_t)h->cfg.n_targets > kNoallocMaxTargets)
+        return ccb_fail(h, -71, "ccb_query_device_noalloc: %d targets, the fixed scratch holds %u (use ccb_query_device)",
+                        h->cfg.n_targets, kNoallocMaxTargets);
+    if (!h->db_ready) return ccb_fail(h, -32, "Failed to find the database.");
+    if (h->group) return ccb_fail(h, -63, "this handle leads a device group: use the ccb_batch_* calls");
+    if (h->n_shards > 1) return ccb_fail(h, -63, "this handle holds one shard of the table: use the ccb_shard_* calls");
+    const int dev = h->cfg.device;
+    if (dev < 0 || dev >= kNoallocMaxDevices) return ccb_fail(h, -72, "ccb_query_device_noalloc: device %d out of range", dev);
+    USE_DEV(h);
+    unsigned char* base;
+    {   // set-up, once per device, that device current
+        std::lock_guard<std::mutex> g(g_noalloc_mu);
+        if (!g_noalloc_ptr[dev]) {
+            void* p = nullptr;
+            CU(h, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[dev] = (unsigned char*)p;
+        }
+        base = g_noalloc_ptr[dev];
+    }
+    if (n_reads == 0) return 0;                                                   // (a call that only does the set-up)
+    QueryArgs a{};
+    a.offsets = (const uint32_t*)d_offsets; a.containers = (const uint16_t*)d_containers; a.n_reads = n_reads;
+    a.out5 = (uint16_t*)d_final5; a.rows = (uint16_t*)d_rows; a.row_stride = h->row_stride;
+    a.stats = (flags & CCB_STATS) ? (unsigned long long*)d_stats : nullptr; a.stats_words = (flags & CCB_STATS_EX) ? 4 : 2;
+    a.anchor_pre = base + kNoallocPre;
+    // the array keeps the last call's contents: the two counters are cleared by run_query, the dense counters by the
+    // dense kernel itself, the lists and the anchor records are written before they are read
+    int rc = run_query(h, a, (uint32_t*)(base + kNoallocLists), (uint32_t*)(base + kNoallocCount), kNoallocMaxReads,
+                       (uint32_t*)(base + kNoallocDense), flags, (cudaStream_t)stream);
+    if (rc) return ccb_fail(h, rc, "query launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    return 0;
+}

@@ -114,6 +114,7 @@ SYMBOLS = {
     "ccb_batch_free": (C.c_int, [_H]),
     "ccb_sync": (C.c_int, [_H]),
     "ccb_query_device": (C.c_int, [_H, _VP, _VP, C.c_uint32, _VP, _VP, _VP, C.c_int, _VP]),
+    "ccb_query_device_noalloc": (C.c_int, [_H, _VP, _VP, C.c_uint32, _VP, _VP, _VP, C.c_int, _VP]),
     "ccb_get_stats": (C.c_int, [_H, C.POINTER(Stats)]),
     "ccb_version": (C.c_char_p, []),
     "ccb_l2_fetch_granularity": (C.c_int, [_H]),
@@ -310,6 +311,13 @@ class CuClarkDB:
                      d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
         self._ck(self._lib.ccb_query_device(self._h, d_offsets, d_containers, n_reads, d_final5,
                                             d_rows or None, d_stats or None, flags | default_flags, stream or None))
+
+    def query_device_noalloc(self, d_offsets: int, d_containers: int, n_reads: int, d_final5: int,
+                             d_rows: int = 0, d_stats: int = 0, flags: int = 0, stream: int = 0):
+        """ccb_query_device_noalloc: query_device on the library's fixed scratch array -- no device allocation, at most
+        NOALLOC_MAX_READS reads per call and NOALLOC_MAX_TARGETS targets; calls on one GPU must not overlap."""
+        self._ck(self._lib.ccb_query_device_noalloc(self._h, d_offsets, d_containers, n_reads, d_final5,
+                                                    d_rows or None, d_stats or None, flags | default_flags, stream or None))
 
     # -- sharded table (row E2): raw device pointers, the caller owns buffers and the exchange ----
     def shard_config(self, n_shards: int, shard: int):
