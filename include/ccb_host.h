@@ -38,6 +38,15 @@ int  ccb_host_csv(const ccb_reads* r, size_t first, size_t count, int k, int pai
                   char** out, size_t* len);
 void ccb_host_free(void* p);
 
+/* Pinned batch buffers next to their GPU (csrc/hostnuma.hpp; the reference allocates wherever the thread runs,
+ * src/CuClarkDB.cu:340-365).  Probe for tests and diagnostics: binds the calling thread to the memory node of the PCI device
+ * `pci_bus_id` ("0000:1b:00.0") the way ccb_batch_alloc does around its cudaMallocHost calls, reports the node (-1 = nothing
+ * to do: one node, unknown device, CCB_NUMA=0), the number of CPUs the thread may run on while bound and after the
+ * binding was undone. */
+int  ccb_host_numa_probe(const char* pci_bus_id, int* cpus_while_bound, int* cpus_after);
+/* CPUs of memory node `node` (/sys/devices/system/node/node<N>/cpulist), -1 = no such node */
+int  ccb_host_numa_node_cpus(int node);
+
 #ifdef __cplusplus
 }
 #endif

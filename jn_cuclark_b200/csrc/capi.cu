@@ -386,6 +386,7 @@ static int batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_container
     free_slots(h);
     h->max_reads = max_reads; h->max_cont = max_containers; h->batch_extended = extended != 0;
     h->slots.resize((size_t)h->cfg.n_slots);
+    DeviceNodeBind near_gpu(h->cfg.device);                     // pinned buffers on the memory node the GPU hangs off
     const size_t so = ((size_t)max_reads + 1) * 4, sc = (size_t)(max_containers ? max_containers : 1) * 2,
                  sf = (size_t)(max_reads ? max_reads : 1) * 10, sr = (size_t)(max_reads ? max_reads : 1) * h->row_stride * 2;
     if (index_batches) {

@@ -3,6 +3,7 @@
 #include "../../include/cuclark_b200.h"
 #include "query.cuh"
 #include "table.cuh"
+#include "hostnuma.hpp"
 #include <mutex>
 #include <string>
 #include <vector>
@@ -31,6 +32,19 @@ struct Slot {
 };
 
 constexpr uint32_t kDenseBlocks = 64;
+
+// the calling thread on the CPUs next to `device` while this lives: pinned memory allocated meanwhile is local to the GPU
+struct DeviceNodeBind {
+    char id[32];
+    ccbh::NodeBind bind;
+    static const char* bus_id(int device, char (&buf)[32])
+    {
+        buf[0] = 0;
+        if (cudaDeviceGetPCIBusId(buf, (int)sizeof buf, device) != cudaSuccess) { cudaGetLastError(); buf[0] = 0; }
+        return buf;
+    }
+    explicit DeviceNodeBind(int device) : bind(bus_id(device, id)) {}
+};
 
 // anchor index owner (anchor.cu)
 struct Anchor {

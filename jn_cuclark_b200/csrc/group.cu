@@ -190,6 +190,7 @@ int group_batch_alloc(ccb_handle* h, uint32_t max_reads, uint64_t max_containers
         s.home = si++ % G;
         ccb_handle* hm = g->member[(size_t)s.home];
         cudaError_t e = cudaSetDevice(hm->cfg.device);
+        DeviceNodeBind near_gpu(hm->cfg.device);                  // the slot's pinned buffers next to its home GPU
         auto ok = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
         ok(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         ok(cudaEventCreateWithFlags(&s.routed, cudaEventDisableTiming));

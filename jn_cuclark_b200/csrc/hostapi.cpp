@@ -1,6 +1,7 @@
 // hostapi.cpp -- C ABI (include/ccb_host.h) over hostpipe.cpp
 #include "../../include/ccb_host.h"
 #include "hostpipe.hpp"
+#include "hostnuma.hpp"
 #include <stdlib.h>
 #include <string.h>
 
@@ -62,3 +63,22 @@ extern "C" int ccb_host_csv(const ccb_reads* r, size_t first, size_t count, int 
     return 0;
 }
 extern "C" void ccb_host_free(void* p) { free(p); }
+
+extern "C" int ccb_host_numa_probe(const char* pci_bus_id, int* cpus_while_bound, int* cpus_after)
+{
+    int node;
+    cpu_set_t m;
+    {
+        ccbh::NodeBind b(pci_bus_id);
+        node = b.node();
+        if (cpus_while_bound) *cpus_while_bound = sched_getaffinity(0, sizeof m, &m) == 0 ? CPU_COUNT(&m) : -1;
+    }
+    if (cpus_after) *cpus_after = sched_getaffinity(0, sizeof m, &m) == 0 ? CPU_COUNT(&m) : -1;
+    return node;
+}
+
+extern "C" int ccb_host_numa_node_cpus(int node)
+{
+    cpu_set_t m;
+    return ccbh::node_cpus(node, &m) ? CPU_COUNT(&m) : -1;
+}

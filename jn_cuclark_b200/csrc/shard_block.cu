@@ -38,6 +38,11 @@ struct RouteSmem {
     uint32_t fill[kMaxShards];             // pass 2: slots handed out so far
     unsigned long long base[kMaxShards];   // first slot of the block's segment
     uint32_t queue[BLK * kItems];          // read << 20 | chunk << 16 | mask of <= 4 windows of the chunk
+    // staged pass 2: one round's k-mers (<= 4 per thread) sorted by owner before they leave the SM
+    uint32_t tcnt[2][kMaxShards];          // k-mers of the round per owner (double-buffered: no barrier to clear it)
+    uint32_t sfill[2][kMaxShards];         // slots handed out before the round
+    uint64_t stage_h[BLK * 4];
+    uint8_t  stage_r[BLK * 4];
 };
 
 // the (up to four) mixed k-mers of an item: windows given by the set bits of the item's mask, lowest first
@@ -73,7 +78,11 @@ __device__ __forceinline__ void item_hashes(const RouteSmem<BLK>& sm, const uint
 
 }  // namespace
 
-template <int BLK>
+// STAGED: pass 2 sorts every round's k-mers by owner in shared memory and stores them as contiguous runs, so that one
+// warp instruction writes 256 bytes to one owner.  Unstaged, lanes bound for one owner take consecutive slots straight
+// from the registers: 32 / G lanes x 8 bytes per warp instruction and owner -- 128 bytes at G = 2, but 32 bytes at G = 8,
+// and the fabric between the GPUs then carries 32-byte writes (measured at 8 GPUs: 280 GB/s per GPU).
+template <int BLK, bool STAGED>
 __global__ void __launch_bounds__(BLK, 3) k_route_block(const HashParams hp, const QueryArgs a, const BlockRouteArgs ra)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -151,6 +160,7 @@ __global__ void __launch_bounds__(BLK, 3) k_route_block(const HashParams hp, con
                 const uint32_t c = sm.cnt[tid];
                 const unsigned long long b = c ? atomicAdd(ra.cursor + tid, (unsigned long long)c) : 0ull;
                 sm.base[tid] = b; sm.fill[tid] = 0;
+                sm.tcnt[0][tid] = 0; sm.tcnt[1][tid] = 0; sm.sfill[0][tid] = 0;
                 uint32_t* seg = ra.blkseg + (((size_t)blk * 2 + part) * kMaxShards + tid) * 2;
                 seg[0] = (uint32_t)(b < ra.cap ? b : ra.cap); seg[1] = c;
                 if (b + c > ra.cap) atomicExch(ra.error, 1u);            // the excess is dropped below
@@ -167,17 +177,66 @@ __global__ void __launch_bounds__(BLK, 3) k_route_block(const HashParams hp, con
                     lr = item >> 20;
                     item_hashes(sm, a.containers, item, k, kmsk, h, has);
                 }
+                if (!STAGED) {
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const uint32_t g = has[j] ? owner_of(h[j], hp.shift, G) : 0x100u + (uint32_t)lane;   // idle lanes match nobody
-                    const uint32_t m = __match_any_sync(0xFFFFFFFFu, g);
-                    const int leader = __ffs(m) - 1;
-                    uint32_t start = 0;
-                    if (has[j] && lane == leader) start = atomicAdd(&sm.fill[g], (uint32_t)__popc(m));
-                    start = __shfl_sync(0xFFFFFFFFu, start, leader);
-                    if (has[j]) {
-                        const unsigned long long idx = sm.base[g] + start + (uint32_t)__popc(m & lt);
-                        if (idx < ra.cap) { ra.dst[g][idx] = h[j]; ra.rid[g][idx] = (uint8_t)lr; }
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t g = has[j] ? owner_of(h[j], hp.shift, G) : 0x100u + (uint32_t)lane;   // idle lanes match nobody
+                        const uint32_t m = __match_any_sync(0xFFFFFFFFu, g);
+                        const int leader = __ffs(m) - 1;
+                        uint32_t start = 0;
+                        if (has[j] && lane == leader) start = atomicAdd(&sm.fill[g], (uint32_t)__popc(m));
+                        start = __shfl_sync(0xFFFFFFFFu, start, leader);
+                        if (has[j]) {
+                            const unsigned long long idx = sm.base[g] + start + (uint32_t)__popc(m & lt);
+                            if (idx < ra.cap) { ra.dst[g][idx] = h[j]; ra.rid[g][idx] = (uint8_t)lr; }
+                        }
+                    }
+                } else {
+                    // A: rank inside the round, per owner
+                    const int cur = (int)(rd & 1u);
+                    uint32_t og[4], loc[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t g = has[j] ? owner_of(h[j], hp.shift, G) : 0x100u + (uint32_t)lane;
+                        const uint32_t m = __match_any_sync(0xFFFFFFFFu, g);
+                        const int leader = __ffs(m) - 1;
+                        uint32_t start = 0;
+                        if (has[j] && lane == leader) start = atomicAdd(&sm.tcnt[cur][g], (uint32_t)__popc(m));
+                        start = __shfl_sync(0xFFFFFFFFu, start, leader);
+                        og[j] = g; loc[j] = start + (uint32_t)__popc(m & lt);
+                    }
+                    __syncthreads();
+                    // B: the round's k-mers into shared memory, owner by owner
+                    uint32_t tc[kMaxShards];
+#pragma unroll
+                    for (int gg = 0; gg < kMaxShards; gg++) tc[gg] = gg < (int)G ? sm.tcnt[cur][gg] : 0u;
+                    if (tid < (int)G) {                                        // for the next round (read after its first barrier)
+                        sm.sfill[cur ^ 1][tid] = sm.sfill[cur][tid] + sm.tcnt[cur][tid];
+                        sm.tcnt[cur ^ 1][tid] = 0;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (has[j]) {
+                            uint32_t off = 0;
+#pragma unroll
+                            for (int gg = 0; gg < kMaxShards - 1; gg++) off += gg < (int)og[j] ? tc[gg] : 0u;
+                            sm.stage_h[off + loc[j]] = h[j]; sm.stage_r[off + loc[j]] = (uint8_t)lr;
+                        }
+                    }
+                    __syncthreads();
+                    // C: out, as contiguous runs
+                    uint32_t total = 0;
+#pragma unroll
+                    for (int gg = 0; gg < kMaxShards; gg++) total += tc[gg];
+                    for (uint32_t i = (uint32_t)tid; i < total; i += BLK) {
+                        uint32_t g = 0, o = 0, nxt = 0;
+#pragma unroll
+                        for (int gg = 0; gg < kMaxShards - 1; gg++) {
+                            nxt += tc[gg];
+                            if (i >= nxt) { g = (uint32_t)gg + 1u; o = nxt; }
+                        }
+                        const unsigned long long idx = sm.base[g] + sm.sfill[cur][g] + (i - o);
+                        if (idx < ra.cap) { ra.dst[g][idx] = sm.stage_h[i]; ra.rid[g][idx] = sm.stage_r[i]; }
                     }
                 }
             }
@@ -211,9 +270,13 @@ int launch_route_block(const HashParams& hp, const QueryArgs& a, const BlockRout
     uint32_t ctas = (a.n_reads + BLK - 1) / BLK;
     static const uint32_t per_sm = getenv("CCB_ROUTE_CTAS_PER_SM") ? (uint32_t)atoi(getenv("CCB_ROUTE_CTAS_PER_SM")) : 64u;
     if (ctas > 148u * per_sm) ctas = 148u * per_sm;
-    cudaError_t e = cudaFuncSetAttribute(k_route_block<BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // staged stores pay two barriers per round and win where the runs would otherwise be short (see k_route_block)
+    const char* env = getenv("CCB_ROUTE_STAGED");
+    const bool staged = env ? atoi(env) != 0 : ra.n_shards >= 3;
+    auto kern = staged ? k_route_block<BLK, true> : k_route_block<BLK, false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    k_route_block<BLK><<<ctas, BLK, smem, s>>>(hp, a, ra);
+    kern<<<ctas, BLK, smem, s>>>(hp, a, ra);
     return (int)cudaGetLastError();
 }
 

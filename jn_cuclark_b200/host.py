@@ -22,6 +22,8 @@ HOST_SYMBOLS = {
     "ccb_host_csv": (C.c_int, [_VP, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int,
                                _VP, _VP, C.c_int, C.POINTER(_VP), C.POINTER(C.c_size_t)]),
     "ccb_host_free": (None, [_VP]),
+    "ccb_host_numa_probe": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "ccb_host_numa_node_cpus": (C.c_int, [C.c_int]),
 }
 _bound = False
 
@@ -103,3 +105,15 @@ def join_pairs(f1: str, f2: str) -> bytes:
     s = C.string_at(out.value, n.value)
     L.ccb_host_free(out)
     return s
+
+
+def numa_probe(pci_bus_id: str):
+    """-> (node, cpus while bound, cpus after): what ccb_batch_alloc's binding to the GPU's memory node does to this thread."""
+    L = _lib()
+    a, b = C.c_int(0), C.c_int(0)
+    node = L.ccb_host_numa_probe(pci_bus_id.encode(), C.byref(a), C.byref(b))
+    return node, a.value, b.value
+
+
+def numa_node_cpus(node: int) -> int:
+    return _lib().ccb_host_numa_node_cpus(node)

@@ -170,3 +170,37 @@ def test_pack_random_texts_equal_oracle(oracle, seed):
         oa, ca = a.pack(k)
         ob, cb = b.pack(k)
         assert np.array_equal(oa, ob) and np.array_equal(ca[:int(oa[-1])], cb[:int(ob[-1])]), k
+
+
+def test_numa_binding_is_scoped_and_optional(monkeypatch):
+    """Pinned batch buffers are allocated with the calling thread bound to the memory node of the slot's GPU
+    (csrc/hostnuma.hpp).  An unknown device changes nothing; a known node's CPU list parses to the count the kernel reports;
+    whatever happens while bound, the thread's affinity is what it was afterwards."""
+    import os
+    from jn_cuclark_b200 import host
+    before = len(os.sched_getaffinity(0))
+    node, during, after = host.numa_probe("ffff:ff:1f.7")             # no such device
+    assert node == -1 and during == before and after == before
+    p = "/sys/devices/system/node/node0/cpulist"
+    if os.path.exists(p):
+        want = 0
+        for part in open(p).read().strip().split(","):
+            a, _, b = part.partition("-")
+            want += int(b or a) - int(a) + 1
+        assert host.numa_node_cpus(0) == want
+    assert host.numa_node_cpus(4095) == -1
+    # a real PCI device with a node, if the machine has one: bound to a subset, restored afterwards
+    root = "/sys/bus/pci/devices"
+    for dev in sorted(os.listdir(root)) if os.path.isdir(root) else []:
+        try:
+            n = int(open(os.path.join(root, dev, "numa_node")).read())
+        except (OSError, ValueError):
+            continue
+        if n < 0:
+            continue
+        node, during, after = host.numa_probe(dev.upper())
+        assert after == before and 0 < during <= before
+        assert node in (n, -1)                                         # -1: the node's CPUs are outside this process's cpuset
+        monkeypatch.setenv("CCB_NUMA", "0")
+        assert host.numa_probe(dev)[0] == -1
+        break
