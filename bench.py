@@ -382,7 +382,7 @@ def run_b200(args):
     ms_tab = ms_other if head_anchor else ms
     ms_anc = ms if head_anchor else ms_other
     roof_tab = roofline(c_tab, ms_tab, kname_tab, "k_query_dram_bytes_per_launch" if args.warp else "k_query_block_dram_bytes_per_launch") if ms_tab else None
-    roof_anc = roofline(c_anc, ms_anc, "ccb::k_query_block<anchor>", "k_query_block_anchor_dram_bytes_per_launch") if (c_anc and ms_anc) else None
+    roof_anc = roofline(c_anc, ms_anc, "ccb::k_anchor_scan + ccb::k_query_block<PRE>", "k_query_block_anchor_dram_bytes_per_launch") if (c_anc and ms_anc) else None
     if roof_tab and gather:
         roof_tab.update({"gather32_gbs": gather[32], "gather64_gbs": gather[64], "frac_of_gather32": roof_tab["achieved"] / gather[32]})
 
@@ -531,7 +531,8 @@ def run_b200(args):
                     "reads_per_s": NR * world * args.steps / t_e2e, "ms_per_step": 1e3 * t_e2e / args.steps,
                     "slots": S, "results_equal_resident_path": same, "host_step_ms": pace,
                     "host_feed_gbs": (h2d + d2h) * world * args.steps / t_e2e / 1e9},
-            "gpu_launches": (2 if args.warp else 3) * args.steps,      # k_query_block, k_query (handed-back reads), k_query_dense
+            # per step of the timed region: [k_anchor_scan,] k_query_block, k_query (handed-back reads), k_query_dense
+            "gpu_launches": (2 if args.warp else 4 if head_anchor else 3) * args.steps,
             "roofline": head_roof,
         }
         if other:
