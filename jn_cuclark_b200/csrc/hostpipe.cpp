@@ -120,6 +120,8 @@ void index_sequential(const uint8_t* m, size_t nb, bool fasta, ReadSet& o)
 extern "C" size_t ccbh_count_newlines_avx2(const uint8_t* p, size_t n);
 extern "C" size_t ccbh_newline_offsets_avx2(const uint8_t* p, size_t n, uint32_t* out);
 extern "C" int ccbh_has_bare_marker_avx2(const uint8_t* p, size_t n);
+extern "C" size_t ccbh_pack_bases_avx2(const uint8_t* p, size_t n, uint16_t* out);
+extern "C" int ccbh_survey_avx2(const uint8_t* p, size_t n, uint64_t* newlines);
 
 const bool kAvx2 = __builtin_cpu_supports("avx2") && !getenv("CCB_NO_AVX2");
 
@@ -399,6 +401,26 @@ int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
         if (r.len[i] < (uint64_t)k) continue;       // :1632, reads without a k-mer store nothing
         const uint8_t* p = m + r.seq_s[i]; const uint8_t* e = m + r.seq_e[i];
         while (p < e) {
+            // fastest path (AVX2): the writer sits on a container boundary and whole groups of 32 / 16 / 8 bases follow
+            if (kAvx2 && w.cnt == 0 && p + 32 <= e) {
+                size_t room = (size_t)(e - p);
+                const size_t left = kMaxPart - (w.open ? w.plen : 0u);                  // bases the current part may still take
+                if (room > left) room = left;
+                const size_t slots = w.cap - w.cc - (w.open ? 0u : 1u);                 // (a new part's header comes first)
+                if (w.cc + 1 < w.cap && room / 8 > slots) room = slots * 8;
+                if (room >= 32 && w.cc + 5 <= w.cap) {
+                    const size_t at = w.open ? w.cc : w.cc + 1;
+                    const size_t done = ccbh_pack_bases_avx2(p, room & ~(size_t)7, w.c + at);
+                    if (done) {
+                        if (!w.open) w.begin();
+                        w.cc += done / 8; w.plen += (uint32_t)done;
+                        const uint16_t* l = w.c + w.cc - 4;                             // (done >= 32: at least four containers)
+                        w.hist = ((uint64_t)l[0] << 48) | ((uint64_t)l[1] << 32) | ((uint64_t)l[2] << 16) | l[3];
+                        p += done;
+                        continue;
+                    }
+                }
+            }
             // fast path: the writer sits on a container boundary and the next eight characters are bases
             if (w.cnt == 0 && p + 8 <= e && w.cc < w.cap && (!w.open || w.plen + 8 <= kMaxPart)) {
                 uint16_t q[4];
@@ -514,6 +536,19 @@ struct FmtMemo {
         }
         out.append(x.s, x.len);
     }
+    // the same, written at p (which has room for sizeof E::s bytes); returns the length, -1 when the text did not fit the memo
+    template <typename F> int put_at(char* p, uint64_t key, F&& make)
+    {
+        E& x = e[(size_t)((key * 0x9E3779B97F4A7C15ull) >> 52)];
+        if (x.key != key) {
+            char buf[96];
+            const int m = make(buf, sizeof buf);
+            if (m < 0 || m >= (int)sizeof x.s) return -1;
+            x.key = key; x.len = (uint8_t)m; memcpy(x.s, buf, (size_t)m);
+        }
+        memcpy(p, x.s, sizeof x.s);                      // fixed-size copy (the caller advances by the length)
+        return x.len;
+    }
 };
 }  // namespace
 
@@ -523,6 +558,50 @@ void csv_rows(std::string& out, const ReadSet& r, size_t first, size_t count, in
     char num[96];
     FmtMemo memo_gamma, memo_tail;
     const size_t n_targets = names.size() - 1;
+    if (!extended) {
+        // the common case, row by row into a block of raw memory: name (<= 39) + gamma (<= 38) + target + tail (<= 38)
+        size_t max_name = 0;
+        for (const std::string& s : names) max_name = std::max(max_name, s.size());
+        const size_t row_max = 39 + 39 + max_name + 39 + 39;      // (+ the memo's fixed-size copies overhang by < 39)
+        constexpr size_t kBlock = 256;
+        std::vector<char> buf(kBlock * row_max + 64);
+        size_t j = 0;
+        while (j < count) {
+            const size_t stop = std::min(count, j + kBlock);
+            char* p = buf.data();
+            for (; j < stop; j++) {
+                const size_t i = first + j;
+                const uint16_t* f = final5 + 5 * j;
+                const unsigned total = f[0], ib = f[1], best = f[2], second = f[4];
+                size_t nl = (size_t)(r.name_e[i] - r.name_s[i]);
+                if (nl >= 40) nl = 39;
+                const char* nm = (const char*)r.map + r.name_s[i];
+                const void* z = memchr(nm, 0, nl);
+                if (z) nl = (size_t)((const char*)z - nm);
+                memcpy(p, nm, nl); p += nl;
+                const uint32_t norm = paired ? (uint32_t)r.len[i] - 1u : (uint32_t)r.len[i];
+                auto gamma_text = [&](char* b, size_t cap) {
+                    const double gamma = (double)total / (((double)norm - (double)k) + 1.0);
+                    return snprintf(b, cap, ",%g,", gamma);
+                };
+                int m = memo_gamma.put_at(p, ((uint64_t)total << 32) | norm, gamma_text);
+                if (m < 0) m = gamma_text(p, 39);
+                p += m;
+                const std::string& tn = names[ib < names.size() ? ib : 0];
+                memcpy(p, tn.data(), tn.size()); p += tn.size();
+                auto tail_text = [&](char* b, size_t cap) {
+                    double delta = (double)(best + second);
+                    delta = (delta < 0.001) ? 0 : ((double)best) / delta;
+                    return snprintf(b, cap, ",%u,%g\n", best, delta);
+                };
+                m = memo_tail.put_at(p, ((uint64_t)best << 16) | second, tail_text);
+                if (m < 0) m = tail_text(p, 39);
+                p += m;
+            }
+            out.append(buf.data(), (size_t)(p - buf.data()));
+        }
+        return;
+    }
     for (size_t j = 0; j < count; j++) {
         const size_t i = first + j;
         const uint16_t* f = final5 + 5 * j;
@@ -642,6 +721,14 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
             for (size_t c = next++; c < C && !unusual; c = next++) {
                 const size_t b = c * chunk, e = std::min(nb, b + chunk);
                 const size_t lo = b ? b - 1 : 0, hi = std::min(nb, e + 1);          // patterns that straddle a chunk boundary
+                if (kAvx2 && !fasta) {
+                    // one pass for both questions: the window [lo, hi) overhangs the chunk by a byte on either side
+                    uint64_t c_all = 0;
+                    if (ccbh_survey_avx2(m + lo, hi - lo, &c_all)) { unusual = true; return; }
+                    newlines[c] = c_all - (lo < b && m[lo] == '\n') - (hi > e && m[e] == '\n');
+                    if (newlines[c] < 8 && c + 1 < C) { unusual = true; return; }
+                    continue;
+                }
                 if (kAvx2 ? ccbh_has_bare_marker_avx2(m + lo, hi - lo) : 1) {
                     if (kAvx2) { unusual = true; return; }
                     for (size_t j = lo; j + 2 < hi; j++)
