@@ -413,15 +413,17 @@ int launch_query_dense(const TableView& t, const QueryArgs& a, const uint32_t* r
 // ---------------------------------------------------------------------------
 // A table (or shard) larger than what the TLBs reach is probed range by range: measured with the table-only kernel,
 // 1.2 G random probes take 27.3 ms on a 64 GB table, 60.5 ms on 96 GB and 96.0 ms on 128 GB (profiles/r02_table_size.json)
-// -- beyond 64 GB every probe also misses the translation caches.  A list of k-mers can be walked once per range of
-// <= 48 GB instead (8 more bytes read per k-mer and range, against a probe that costs twice as much).
+// -- beyond 64 GB every probe also misses the translation caches (70 GB: 28.0 ms, 77 GB: 31.5 ms: the cliff starts near
+// 72 GB, profiles/r02_probe_ranges.json).  A list of k-mers can be walked once per range instead; a pass costs 5-7 ms per
+// 1.2 G k-mers whatever it probes, so the ranges are as large as the caches reach: <= 68 GB (a 134 GB table in two
+// ranges of 67 GB: 36.1 ms, in three of 45 GB: 41.1 ms, in one: 105 ms).
 static void probe_passes(const TableView& t, uint64_t& lo, uint64_t& per, int& passes)
 {
     const uint64_t G = t.hp.n_shards > 1 ? t.hp.n_shards : 1;
     const uint64_t held = t.hp.nb / G;                                   // home buckets held here
     lo = held * (t.hp.n_shards > 1 ? t.hp.shard : 0);
     const char* env = getenv("CCB_PROBE_RANGE_MB");                      // (tests: ranges of a few MB on a small table)
-    const uint64_t reach = env && atoll(env) > 0 ? (uint64_t)atoll(env) << 20 : 48ull << 30;
+    const uint64_t reach = env && atoll(env) > 0 ? (uint64_t)atoll(env) << 20 : 68ull << 30;
     passes = (int)((held * 32 + reach - 1) / reach);
     if (passes < 1) passes = 1;
     per = (held + (uint64_t)passes - 1) / (uint64_t)passes;

@@ -14,6 +14,9 @@ ap.add_argument("--anchor", action="store_true", help="one more run with CCB_ANC
 ap.add_argument("--reference", default=None,
                 help="also run the reference GPU binary (oracle/_ref/cuCLARK) with these '-n,-b' pairs, e.g. 1:4,16:32 "
                      "(needs a number of targets that is a multiple of 32, see tests/golden/ref_gpu/README.md)")
+ap.add_argument("--also", default=None,
+                help="more runs of bin/cuCLARK at the largest thread count with extra flags, ';'-separated, e.g. '-d 2;--sharded -d 2' "
+                     "(two GPUs with the table replicated / sharded over them); CSVs compared with the first run's")
 a = ap.parse_args()
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 d = a.dir or tempfile.mkdtemp(prefix="ccb_cli_")
@@ -85,6 +88,22 @@ if a.anchor:
                          "csv_identical_to_table_only": r.returncode == 0 and open(first, "rb").read() == open(os.path.join(d, "res_anchor.csv"), "rb").read(),
                          "phases": [l.strip() for l in r.stderr.splitlines() if "Anchor index" in l or "host pipeline" in l or "Loading time" in l][:6],
                          "stderr_tail": r.stderr[-600:] if (r.returncode or not m) else None}
+if a.also:
+    T = max(int(x) for x in a.threads.split(","))
+    first = os.path.join(d, f"res{a.threads.split(',')[0]}.csv")
+    out["also"] = []
+    for i, extra in enumerate(x.strip() for x in a.also.split(";") if x.strip()):
+        res = os.path.join(d, f"res_also{i}")
+        t0 = time.time()
+        r = subprocess.run([exe, "-T", os.path.join(d, "targets.txt"), "-D", dbdir + "/", "-O", fq, "-R", res, "-n", str(T), "--verbose"] + extra.split(),
+                           capture_output=True, text=True)
+        wall = time.time() - t0
+        m = re.search(r"Done in ([0-9.]+)s \((\d+) reads/min, (\d+) reads\)", r.stderr.replace("\n", " "))
+        out["also"].append({"flags": extra, "threads": T, "rc": r.returncode, "wall_s": wall, "classify_s": float(m.group(1)) if m else None,
+                            "reads_per_min": int(m.group(2)) if m else None,
+                            "csv_identical_to_first_run": r.returncode == 0 and open(first, "rb").read() == open(res + ".csv", "rb").read(),
+                            "phases": [l.strip() for l in r.stderr.splitlines() if "host pipeline" in l or "Loading time" in l or "shard" in l.lower()][:8],
+                            "stderr_tail": r.stderr[-600:] if (r.returncode or not m) else None})
 if a.reference:
     ref = os.path.join(ROOT, "oracle", "_ref", "cuCLARK")
     out["reference_runs"] = []
