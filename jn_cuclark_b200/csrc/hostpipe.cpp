@@ -121,7 +121,6 @@ extern "C" size_t ccbh_count_newlines_avx2(const uint8_t* p, size_t n);
 extern "C" size_t ccbh_newline_offsets_avx2(const uint8_t* p, size_t n, uint32_t* out);
 extern "C" int ccbh_has_bare_marker_avx2(const uint8_t* p, size_t n);
 extern "C" size_t ccbh_pack_bases_avx2(const uint8_t* p, size_t n, uint16_t* out);
-extern "C" int ccbh_survey_avx2(const uint8_t* p, size_t n, uint64_t* newlines);
 
 const bool kAvx2 = __builtin_cpu_supports("avx2") && !getenv("CCB_NO_AVX2");
 
@@ -390,6 +389,54 @@ size_t pack_bound(const ReadSet& r, size_t first, size_t count, int k)
     return tot + 8;
 }
 
+namespace {
+// one read's sequence bytes [p, e) through the writer (the body of pack_reads; also driven record by record by the
+// streaming pipeline, while the bytes the indexer has just walked are still in the first-level cache)
+inline void pack_one(PartWriter& w, const uint8_t* p, const uint8_t* e)
+{
+    while (p < e) {
+        // fastest path (AVX2): the writer sits on a container boundary and whole groups of 32 / 16 / 8 bases follow
+        if (kAvx2 && w.cnt == 0 && p + 32 <= e) {
+            size_t room = (size_t)(e - p);
+            const size_t left = kMaxPart - (w.open ? w.plen : 0u);                  // bases the current part may still take
+            if (room > left) room = left;
+            const size_t slots = w.cap - w.cc - (w.open ? 0u : 1u);                 // (a new part's header comes first)
+            if (w.cc + 1 < w.cap && room / 8 > slots) room = slots * 8;
+            if (room >= 32 && w.cc + 5 <= w.cap) {
+                const size_t at = w.open ? w.cc : w.cc + 1;
+                const size_t done = ccbh_pack_bases_avx2(p, room & ~(size_t)7, w.c + at);
+                if (done) {
+                    if (!w.open) w.begin();
+                    w.cc += done / 8; w.plen += (uint32_t)done;
+                    const uint16_t* l = w.c + w.cc - 4;                             // (done >= 32: at least four containers)
+                    w.hist = ((uint64_t)l[0] << 48) | ((uint64_t)l[1] << 32) | ((uint64_t)l[2] << 16) | l[3];
+                    p += done;
+                    continue;
+                }
+            }
+        }
+        // fast path: the writer sits on a container boundary and the next eight characters are bases
+        if (w.cnt == 0 && p + 8 <= e && w.cc < w.cap && (!w.open || w.plen + 8 <= kMaxPart)) {
+            uint16_t q[4];
+            memcpy(q, p, 8);
+            const uint32_t v0 = kPairs.t[q[0]], v1 = kPairs.t[q[1]], v2 = kPairs.t[q[2]], v3 = kPairs.t[q[3]];
+            if (!((v0 | v1 | v2 | v3) & 0x80u)) {
+                if (!w.open) { w.begin(); if (w.overflow) break; }
+                const uint32_t c16 = (v0 << 12) | (v1 << 8) | (v2 << 4) | v3;
+                if (w.cc < w.cap) w.c[w.cc++] = (uint16_t)c16; else w.overflow = true;
+                w.hist = (w.hist << 16) | c16; w.plen += 8;
+                p += 8;
+                continue;
+            }
+        }
+        const uint32_t code = kCodes.t[*p++];
+        if (code < 4) w.base(code);
+        else if (code == 5) w.end();
+    }
+    w.end();
+}
+}  // namespace
+
 int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
                    uint32_t* offsets, uint16_t* cont, size_t cap)
 {
@@ -399,47 +446,7 @@ int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
         const size_t i = first + j;
         offsets[j] = (uint32_t)w.cc;
         if (r.len[i] < (uint64_t)k) continue;       // :1632, reads without a k-mer store nothing
-        const uint8_t* p = m + r.seq_s[i]; const uint8_t* e = m + r.seq_e[i];
-        while (p < e) {
-            // fastest path (AVX2): the writer sits on a container boundary and whole groups of 32 / 16 / 8 bases follow
-            if (kAvx2 && w.cnt == 0 && p + 32 <= e) {
-                size_t room = (size_t)(e - p);
-                const size_t left = kMaxPart - (w.open ? w.plen : 0u);                  // bases the current part may still take
-                if (room > left) room = left;
-                const size_t slots = w.cap - w.cc - (w.open ? 0u : 1u);                 // (a new part's header comes first)
-                if (w.cc + 1 < w.cap && room / 8 > slots) room = slots * 8;
-                if (room >= 32 && w.cc + 5 <= w.cap) {
-                    const size_t at = w.open ? w.cc : w.cc + 1;
-                    const size_t done = ccbh_pack_bases_avx2(p, room & ~(size_t)7, w.c + at);
-                    if (done) {
-                        if (!w.open) w.begin();
-                        w.cc += done / 8; w.plen += (uint32_t)done;
-                        const uint16_t* l = w.c + w.cc - 4;                             // (done >= 32: at least four containers)
-                        w.hist = ((uint64_t)l[0] << 48) | ((uint64_t)l[1] << 32) | ((uint64_t)l[2] << 16) | l[3];
-                        p += done;
-                        continue;
-                    }
-                }
-            }
-            // fast path: the writer sits on a container boundary and the next eight characters are bases
-            if (w.cnt == 0 && p + 8 <= e && w.cc < w.cap && (!w.open || w.plen + 8 <= kMaxPart)) {
-                uint16_t q[4];
-                memcpy(q, p, 8);
-                const uint32_t v0 = kPairs.t[q[0]], v1 = kPairs.t[q[1]], v2 = kPairs.t[q[2]], v3 = kPairs.t[q[3]];
-                if (!((v0 | v1 | v2 | v3) & 0x80u)) {
-                    if (!w.open) { w.begin(); if (w.overflow) break; }
-                    const uint32_t c16 = (v0 << 12) | (v1 << 8) | (v2 << 4) | v3;
-                    if (w.cc < w.cap) w.c[w.cc++] = (uint16_t)c16; else w.overflow = true;
-                    w.hist = (w.hist << 16) | c16; w.plen += 8;
-                    p += 8;
-                    continue;
-                }
-            }
-            const uint32_t code = kCodes.t[*p++];
-            if (code < 4) w.base(code);
-            else if (code == 5) w.end();
-        }
-        w.end();
+        pack_one(w, m + r.seq_s[i], m + r.seq_e[i]);
         if (w.overflow) return -1;
         if (w.cc > 0xFFFFFFFFull) return -2;        // :1709
     }
@@ -712,34 +719,29 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
     std::thread alloc([&] {
         for (size_t d = 0; d < devs.size(); d++) alloc_rc[d] = ccb_batch_alloc(devs[d], (uint32_t)kMaxBatchReads, spec_containers(opt.k), opt.extended);
     });
-    // survey: newlines per chunk, markers alone on a line, chunks without a record start
-    std::vector<uint64_t> newlines(C, 0);
+    // FASTQ: no survey.  Every worker finds the first record of its chunk by itself (a line that starts with '@' two
+    // lines above a line that starts with '+': in a well-formed file only a header is that) and takes every fourth line
+    // from there, as the reference does; where a chunk's records end and where the next chunk's begin is compared once
+    // all are done -- equal everywhere means the pieces are exactly the sequential parse (induction from byte 0), anything
+    // else (quality lines that look like headers in front of sequences that start with '+', missing lines) gives the
+    // file to the two-phase path.  The text is then walked ONCE: index, 2-bit packing and the copy of the names happen
+    // record by record while the bytes are in the first-level cache.
+    // FASTA: survey (markers alone on a line, chunks without a record start), then index and pack per chunk.
+    constexpr size_t kNoStart = ~(size_t)0;
+    std::vector<size_t> first_start(C, kNoStart), next_start(C, kNoStart);
     std::atomic<bool> unusual(false);
-    {
+    if (fasta) {
         std::atomic<size_t> next(0);
         auto survey = [&] {
             for (size_t c = next++; c < C && !unusual; c = next++) {
                 const size_t b = c * chunk, e = std::min(nb, b + chunk);
                 const size_t lo = b ? b - 1 : 0, hi = std::min(nb, e + 1);          // patterns that straddle a chunk boundary
-                if (kAvx2 && !fasta) {
-                    // one pass for both questions: the window [lo, hi) overhangs the chunk by a byte on either side
-                    uint64_t c_all = 0;
-                    if (ccbh_survey_avx2(m + lo, hi - lo, &c_all)) { unusual = true; return; }
-                    newlines[c] = c_all - (lo < b && m[lo] == '\n') - (hi > e && m[e] == '\n');
-                    if (newlines[c] < 8 && c + 1 < C) { unusual = true; return; }
-                    continue;
-                }
                 if (kAvx2 ? ccbh_has_bare_marker_avx2(m + lo, hi - lo) : 1) {
                     if (kAvx2) { unusual = true; return; }
                     for (size_t j = lo; j + 2 < hi; j++)
                         if (m[j] == '\n' && (m[j + 1] == '@' || m[j + 1] == '>') && m[j + 2] == '\n') { unusual = true; return; }
                 }
-                if (fasta) {
-                    if (c && e - b >= 2 && !memmem(m + b - 1, e - b + 1, "\n>", 2)) { unusual = true; return; }
-                } else {
-                    newlines[c] = count_newlines(m + b, e - b);
-                    if (newlines[c] < 8 && c + 1 < C) { unusual = true; return; }
-                }
+                if (c && e - b >= 2 && !memmem(m + b - 1, e - b + 1, "\n>", 2)) { unusual = true; return; }
             }
         };
         std::vector<std::thread> th;
@@ -751,8 +753,6 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
     for (size_t d = 0; d < devs.size(); d++)
         if (alloc_rc[d]) { err = ccb_last_error(devs[d]); return alloc_rc[d]; }
     if (unusual) return kNotStreamable;
-    std::vector<uint64_t> line0(C, 0);
-    for (size_t c = 1; c < C; c++) line0[c] = line0[c - 1] + newlines[c - 1];
     stats.seconds_index = now() - t0;
     stats.seconds_alloc = 0;
     const size_t max_cont = spec_containers(opt.k);
@@ -784,6 +784,8 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
             fold{stat_mu, stats, c_idx, c_pack, c_wait, c_fmt, c_sink};
         ReadSet rs;
         rs.map = m; rs.nb = nb; rs.fasta = fasta;
+        std::vector<char> name_buf;
+        const std::vector<std::string>& names_of_targets = names;
         DevSlots& d = *ds[(size_t)wid % ds.size()];
         for (;;) {
             const size_t c = next_chunk.fetch_add(1);
@@ -791,7 +793,109 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
             double t1 = now();
             const size_t b = c * chunk, e = std::min(nb, b + chunk);
             rs.clear();
-            const bool ok = fasta ? index_range_fasta(m, nb, b, e, rs) : index_range_fastq(m, nb, b, e, line0[c], c == 0, rs);
+            if (!fasta) {
+                // ---- FASTQ: one walk over the chunk; a batch is packed while it is indexed ----
+                std::string text; std::vector<uint16_t> raw;
+                int slot = -1; uint32_t* off = nullptr; uint16_t *cont = nullptr, *fin = nullptr, *rows = nullptr;
+                PartWriter w{nullptr, 0, 0, opt.k};
+                size_t cnt = 0, bytes = 0, n_chunk = 0;
+                std::vector<char>& names = name_buf;           // (shadows the target names on purpose: csv_rows gets names_of_targets)
+                names.clear();
+                bool bad = false;
+                auto release = [&] { { std::lock_guard<std::mutex> g(d.mu); d.free_slots.push_back(slot); } d.cv.notify_one(); slot = -1; };
+                auto flush = [&]() -> bool {                     // submit what the slot holds, format its rows
+                    if (slot < 0) return true;
+                    if (cnt == 0) { release(); return true; }
+                    c_idx += now() - t1; t1 = now();
+                    if (w.overflow || w.cc > 0xFFFFFFFFull) { release(); give_up = true; return false; }
+                    off[cnt] = (uint32_t)w.cc;
+                    int rc;
+                    {
+                        std::lock_guard<std::mutex> g(d.submit_mu);
+                        rc = ccb_batch_submit(d.h, slot, (uint32_t)cnt, (uint64_t)w.cc, opt.extended ? CCB_EXTENDED : 0);
+                    }
+                    if (!rc) rc = ccb_batch_wait(d.h, slot);
+                    if (rc) { fail(rc, ccb_last_error(d.h)); release(); return false; }
+                    c_wait += now() - t1; t1 = now();
+                    rs.map = (const uint8_t*)names.data();
+                    csv_rows(text, rs, 0, cnt, opt.k, opt.paired, opt.extended, names_of_targets, fin, rows, opt.row_stride);
+                    if (sink.dump) raw.insert(raw.end(), fin, fin + cnt * 5);
+                    release();
+                    n_batches++; n_chunk += cnt;
+                    rs.clear(); names.clear(); cnt = 0; bytes = 0;
+                    c_fmt += now() - t1; t1 = now();
+                    return true;
+                };
+                auto emit = [&](const Rec& r) -> bool {          // one record: its name, its length, its bases into the slot
+                    const size_t sb = (size_t)(r.se - r.ss);
+                    if (sb > kMaxBatchBytes) { give_up = true; return false; }          // one read larger than a slot: two-phase path
+                    if (slot >= 0 && (cnt == kMaxBatchReads || bytes + sb > kMaxBatchBytes) && !flush()) return false;
+                    if (slot < 0) {
+                        c_idx += now() - t1; t1 = now();
+                        {
+                            std::unique_lock<std::mutex> g(d.mu);
+                            d.cv.wait(g, [&] { return !d.free_slots.empty(); });
+                            slot = d.free_slots.back(); d.free_slots.pop_back();
+                        }
+                        ccb_batch_buffers(d.h, slot, &off, &cont, &fin, &rows);
+                        w = PartWriter{cont, 0, max_cont, opt.k};
+                        c_wait += now() - t1; t1 = now();
+                        if (text.capacity() == 0) text.reserve((size_t)(e - b) / 6);
+                    }
+                    size_t nl = (size_t)(r.ne - r.ns);
+                    if (nl > 40) nl = 40;                         // csv_rows prints at most 39 bytes of it
+                    const size_t at = names.size();
+                    names.insert(names.end(), (const char*)m + r.ns, (const char*)m + r.ns + nl);
+                    rs.name_s.push_back(at); rs.name_e.push_back(at + nl); rs.len.push_back(r.len);
+                    off[cnt] = (uint32_t)w.cc;
+                    if (r.len >= (uint64_t)opt.k) pack_one(w, m + r.ss, m + r.se);
+                    cnt++; bytes += sb;
+                    return true;
+                };
+                // where the chunk's first record starts
+                size_t p = kNoStart;
+                if (c == 0) p = 0;
+                else {
+                    NewlineStream nl(m, nb, b);
+                    size_t q0, q1, q2;
+                    if (nl.next(q0) && nl.next(q1) && nl.next(q2)) {
+                        for (;;) {
+                            const size_t st = q0 + 1;             // a line starts here
+                            if (st > e) break;
+                            if (m[st] == '@' && q2 + 1 < nb && m[q2 + 1] == '+') { p = st; break; }
+                            q0 = q1; q1 = q2;
+                            if (!nl.next(q2)) break;
+                        }
+                    }
+                }
+                first_start[c] = p;
+                if (p != kNoStart && p + 1 < nb) {
+                    NewlineStream nl(m, nb, p);
+                    for (;;) {
+                        if (m[p + 1] == '\n') { bad = true; break; }                    // a marker alone on its line: sequential indexer only
+                        size_t q1, q2, q3, q4;
+                        Rec r;
+                        if (!nl.next(q1) || !nl.next(q2) || !nl.next(q3) || !nl.next(q4)) {
+                            fastq_record(m, nb, p, r);            // the text ends inside the record: the plain parser knows every corner
+                            if (!emit(r)) bad = true;
+                            next_start[c] = nb;
+                            break;
+                        }
+                        r.ns = p + 1; r.ne = name_end_before(m, r.ns, q1); r.ss = q1 + 1; r.se = q2; r.len = q2 - r.ss;
+                        if (!emit(r)) { bad = true; break; }
+                        p = q4 + 1;
+                        if (q4 >= e || p + 1 >= nb) { next_start[c] = p; break; }
+                    }
+                } else if (p != kNoStart) next_start[c] = p;
+                if (bad) { if (slot >= 0) release(); if (!failed) give_up = true; sink.put(c, "", {}); return; }
+                if (!flush()) { sink.put(c, "", {}); return; }
+                c_idx += now() - t1; t1 = now();
+                n_reads += n_chunk;
+                sink.put(c, std::move(text), std::move(raw));
+                c_sink += now() - t1;
+                continue;
+            }
+            const bool ok = index_range_fasta(m, nb, b, e, rs);
             c_idx += now() - t1;
             if (!ok) { give_up = true; sink.put(c, "", {}); return; }
             const size_t n = rs.n();
@@ -846,6 +950,16 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
     const bool io_err = sink.io_error || fclose(sink.f) != 0;
     if (sink.dump) fclose(sink.dump);
     if (failed) return failed;
+    if (!fasta && !give_up) {
+        // the pieces are the sequential parse iff every chunk starts where the one before stopped
+        size_t expect = next_start[0];
+        for (size_t c = 1; c < C && !give_up; c++) {
+            const size_t e = std::min(nb, c * chunk + chunk);
+            if (first_start[c] == kNoStart) { if (!(expect > e || expect + 1 >= nb)) give_up = true; }
+            else if (first_start[c] != expect) give_up = true;
+            else expect = next_start[c];
+        }
+    }
     if (give_up) return kNotStreamable;                  // nothing of the partial file is kept: the caller starts over
     stats.reads = n_reads; stats.batches = n_batches;
     stats.seconds_total = now() - t0;

@@ -96,26 +96,3 @@ extern "C" size_t ccbh_pack_bases_avx2(const uint8_t* p, size_t n, uint16_t* out
     }
     return i;
 }
-
-// ccbh_has_bare_marker_avx2 and ccbh_count_newlines_avx2 in one pass over p[0, n): returns 1 when a bare marker was seen
-// (the count is then not meaningful: the caller gives the file to the sequential indexer), else 0 and *newlines
-extern "C" int ccbh_survey_avx2(const uint8_t* p, size_t n, uint64_t* newlines)
-{
-    const __m256i nl = _mm256_set1_epi8('\n'), a = _mm256_set1_epi8('@'), g = _mm256_set1_epi8('>');
-    uint64_t carry_nl = 0, carry_mk = 0, c = 0;
-    size_t i = 0;
-    for (; i + 32 <= n; i += 32) {
-        const __m256i v = _mm256_loadu_si256((const __m256i*)(p + i));
-        const uint64_t mn = (uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(v, nl));
-        const uint64_t mm = (uint32_t)_mm256_movemask_epi8(_mm256_or_si256(_mm256_cmpeq_epi8(v, a), _mm256_cmpeq_epi8(v, g)));
-        const uint64_t NL = (mn << 2) | carry_nl, MK = (mm << 2) | carry_mk;
-        if (NL & (MK >> 1) & (NL >> 2)) return 1;
-        carry_nl = mn >> 30; carry_mk = mm >> 30;
-        c += (uint64_t)__builtin_popcountll(mn);
-    }
-    for (size_t j = i > 2 ? i - 2 : 0; j + 2 < n; j++)
-        if (p[j] == '\n' && (p[j + 1] == '@' || p[j + 1] == '>') && p[j + 2] == '\n') return 1;
-    for (; i < n; i++) c += p[i] == '\n';
-    *newlines = c;
-    return 0;
-}

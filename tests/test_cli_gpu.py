@@ -266,3 +266,19 @@ def test_streaming_pipeline_gives_the_same_csv(setup, tmp_path, chunk):
     _run(s, ["-O", str(odd), "-n", "3"], str(tmp_path / "so"), env)
     _run(s, ["-O", str(odd), "-n", "3"], str(tmp_path / "to"), off)
     assert open(str(tmp_path / "so.csv"), "rb").read() == open(str(tmp_path / "to.csv"), "rb").read()
+    # FASTQ chunks find their first record by themselves (a line starting with '@' two lines above one starting with '+')
+    # and the pieces are checked against each other at the end.  Files that try to fool that: every quality line starts
+    # with '@'; the same with some sequences starting with '+' (then a quality line looks exactly like a header: the check
+    # at the end must catch it and the file must go through the two-phase path); a last record cut short.
+    lines = data.split(b"\n")
+    assert lines[-1] == b"" and (len(lines) - 1) % 4 == 0
+    recs = [lines[i:i + 4] for i in range(0, len(lines) - 1, 4)]
+    at_quals = b"".join(b"\n".join([h, sq, pl, b"@" + q[1:]]) + b"\n" for h, sq, pl, q in recs)
+    fooled = b"".join(b"\n".join([h, (b"+" + sq[1:]) if i % 3 == 1 else sq, pl, b"@" + q[1:]]) + b"\n" for i, (h, sq, pl, q) in enumerate(recs))
+    cut_short = data[: len(data) - len(recs[-1][3]) - 3]
+    for name, text in (("atq", at_quals), ("fooled", fooled), ("short", cut_short)):
+        f = tmp_path / (name + ".fq")
+        f.write_bytes(text)
+        _run(s, ["-O", str(f), "-n", "3", "--extended"], str(tmp_path / ("s_" + name)), env)
+        _run(s, ["-O", str(f), "-n", "3", "--extended"], str(tmp_path / ("t_" + name)), off)
+        assert open(str(tmp_path / ("s_" + name + ".csv")), "rb").read() == open(str(tmp_path / ("t_" + name + ".csv")), "rb").read(), name
