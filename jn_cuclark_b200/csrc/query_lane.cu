@@ -102,8 +102,9 @@ __device__ __forceinline__ uint64_t match_anchor(const uint64_t (&e)[4], uint32_
 
 }  // namespace
 
-// Phase A for one part of a read (with the anchor index): roll over the part until two sampled k-mers are met, look both
-// up in the sampled table at once, compare the part with the target text base by base.  W = the windows answered without
+// Phase A for one part of a read (with the anchor index): mark the sampled k-mers among the part's first 64 windows, look
+// the first two up in the sampled table at once (then, if neither has an entry, the next two), compare the part with the
+// target text base by base.  W = the windows answered without
 // a table probe; vote_lab / vote_hits = the label those windows vote for and how many of them are stored k-mers.
 // ldc(i) = container i of the batch.
 template <bool STATS, typename LDC>
@@ -111,35 +112,51 @@ __device__ __forceinline__ void anchor_part(const TableView& t, const AnchorView
                                             int k, uint64_t kmsk, int s2, Bits192& W, uint32_t& vote_lab, uint32_t& vote_hits,
                                             unsigned long long& st_lookups, unsigned long long& st_sectors)
 {
-    // rolling state after the first k-1 bases, cut out of the first four containers
-    uint64_t x, rc;
+    // Pass 1, in lockstep: which of the part's first 64 windows hold a sampled k-mer?  One bit per window, no branch that
+    // depends on the read -- every lane of the warp runs the same 64 iterations.  (Rolling "until two sampled k-mers were
+    // met" made each warp wait for its unluckiest lane, twice: 80 iterations per warp for 21 per read, 8 of 32 lanes
+    // active, two thirds of the kernel's instructions: profiles/r02_final_ncu_details.csv.)
+    uint64_t smask = 0;
     {
-        uint64_t v = 0;
+        uint64_t x, rc;
+        {
+            uint64_t v = 0;
 #pragma unroll
-        for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)ldc(beg + 1 + j) : 0ull);
-        x = k > 1 ? v >> (64 - s2) : 0ull;
-        rc = revcomp_brev(x, k);
-    }
-    uint32_t cw = 0;
-    int i = k - 1;
-    if (i & 7) cw = ldc(beg + 1 + (i >> 3));
-    uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
-    // up to two rounds; a round = the next two sampled k-mers of the read, looked up together
-    for (int round = 0; round < 2 && ae == ~0ull && i < len; round++) {
-        uint64_t c0 = 0, c1 = 0; int p0 = 0, p1 = 0; uint32_t f0 = 0, f1 = 0; int nc = 0;
-        for (; i < len && nc < 2; i++) {
+            for (int j = 0; j < 4; j++) v = (v << 16) | (1 + j < nslots ? (uint64_t)ldc(beg + 1 + j) : 0ull);
+            x = k > 1 ? v >> (64 - s2) : 0ull;
+            rc = revcomp_brev(x, k);
+        }
+        uint32_t cw = 0;
+        int i = k - 1;
+        if (i & 7) cw = ldc(beg + 1 + (i >> 3));
+        const int stop = min(len, k - 1 + 64);
+        for (; i < stop; i++) {
             if ((i & 7) == 0) cw = ldc(beg + 1 + (i >> 3));
             const uint64_t code = (cw >> (14 - 2 * (i & 7))) & 3u;
             x = ((x << 2) | code) & kmsk;
             rc = (rc >> 2) | ((3ull - code) << s2);
-            const uint64_t cn = x < rc ? x : rc;
-            if (anchor_sampled(cn)) {
-                if (nc == 0) { c0 = cn; p0 = i - (k - 1); f0 = x <= rc ? 1u : 0u; }
-                else         { c1 = cn; p1 = i - (k - 1); f1 = x <= rc ? 1u : 0u; }
-                nc++;
-            }
+            smask |= (uint64_t)(anchor_sampled(x < rc ? x : rc) ? 1u : 0u) << (i - (k - 1));
         }
-        if (nc == 0) break;
+    }
+    // canonical k-mer of window p, cut out of five containers
+    auto window = [&](int p, uint64_t& cn, uint32_t& fwd) {
+        const int c = 1 + (p >> 3), o = p & 7;
+        uint64_t hi = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) hi = (hi << 16) | (c + j < nslots ? (uint64_t)ldc(beg + c + j) : 0ull);
+        const uint64_t lo = c + 4 < nslots ? (uint64_t)ldc(beg + c + 4) : 0ull;
+        const uint64_t w = o ? (hi << (2 * o)) | (lo >> (16 - 2 * o)) : hi;
+        const uint64_t x = w >> (64 - 2 * k);
+        const uint64_t rc = revcomp_brev(x, k);
+        cn = x < rc ? x : rc; fwd = x <= rc ? 1u : 0u;
+    };
+    uint64_t ae = ~0ull; int apos = 0; uint32_t afwd = 0;
+    // up to two rounds; a round = the next two sampled k-mers of the part, looked up together
+    for (int round = 0; round < 2 && ae == ~0ull && smask; round++) {
+        uint64_t c0 = 0, c1 = 0; int p0 = 0, p1 = 0; uint32_t f0 = 0, f1 = 0; int nc = 1;
+        p0 = __ffsll((long long)smask) - 1; smask &= smask - 1;
+        window(p0, c0, f0);
+        if (smask) { p1 = __ffsll((long long)smask) - 1; smask &= smask - 1; window(p1, c1, f1); nc = 2; }
         const uint64_t h0 = mix2k(c0, k, kmsk), h1 = mix2k(c1, k, kmsk);
         const uint64_t b0 = mulhi64(h0 << t.hp.shift, av.nb), b1 = mulhi64(h1 << t.hp.shift, av.nb);
         const uint32_t fp0 = (uint32_t)h0 & 0x7FFFu, fp1 = (uint32_t)h1 & 0x7FFFu;
@@ -239,11 +256,13 @@ static_assert(sizeof(AnchorPre) == kAnchorPreBytes, "AnchorPre layout");
 // The anchor pass as a kernel of its own: a thread per read, no shared memory, no barriers -- a chain of dependent loads
 // (offsets -> containers -> sampled table -> text) that only needs many reads in flight.  The probe kernel that follows
 // (k_query_block<PRE>) then runs at the table-only kernel's occupancy instead of carrying this pass's 125 registers.
-template <bool STATS>
+// K: the k-mer length as a compile-time constant (31 full mode, 27 light mode: every shift of the rolling loop becomes an
+// immediate), 0 = taken from the table at run time.
+template <bool STATS, int K>
 __global__ void __launch_bounds__(128) k_anchor_scan(const TableView t, const QueryArgs a, const AnchorView av, AnchorPre* __restrict__ pre)
 {
-    const int k = t.hp.k;
-    const uint64_t kmsk = t.hp.mask;
+    const int k = K ? K : t.hp.k;
+    const uint64_t kmsk = K ? (K < 32 ? (1ull << (2 * (K & 31))) - 1ull : ~0ull) : t.hp.mask;
     const int s2 = 2 * (k - 1);
     unsigned long long st_lookups = 0, st_sectors = 0;
     auto ldc = [&](uint32_t idx) -> uint32_t { return (uint32_t)__ldg(a.containers + idx); };
@@ -602,8 +621,10 @@ int launch_query_lane(const TableView& t, const QueryArgs& a, const AnchorView* 
     if (av && a.anchor_pre && !fused) {
         uint32_t g = (a.n_reads + 127) / 128;
         if (g > 148u * 64u) g = 148u * 64u;
-        if (a.stats) k_anchor_scan<true><<<g, 128, 0, s>>>(t, a, *av, reinterpret_cast<AnchorPre*>(a.anchor_pre));
-        else         k_anchor_scan<false><<<g, 128, 0, s>>>(t, a, *av, reinterpret_cast<AnchorPre*>(a.anchor_pre));
+        AnchorPre* pre = reinterpret_cast<AnchorPre*>(a.anchor_pre);
+#define CCB_SCAN(K) do { if (a.stats) k_anchor_scan<true, K><<<g, 128, 0, s>>>(t, a, *av, pre); else k_anchor_scan<false, K><<<g, 128, 0, s>>>(t, a, *av, pre); } while (0)
+        if (t.hp.k == 31) CCB_SCAN(31); else if (t.hp.k == 27) CCB_SCAN(27); else CCB_SCAN(0);
+#undef CCB_SCAN
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         return launch_block<256, 3, false, true>(t, a, nullptr, redo_list, redo_count, s);
