@@ -23,6 +23,12 @@ int        ccb_host_reads_is_fasta(const ccb_reads* r);
 /* field: 0 name_s, 1 name_e, 2 seq_s, 3 seq_e, 4 len; array of ccb_host_reads_count u64 */
 const uint64_t* ccb_host_reads_field(const ccb_reads* r, int field);
 
+/* FASTQ only: the index the streaming pipeline of bin/cuCLARK arrives at when it cuts the text into chunks of `chunk` bytes and
+ * lets every chunk find its first record by itself (no counterpart in the reference, which indexes sequentially,
+ * src/CuCLARK_hh.hh:1496-1524; the result must equal ccb_host_index).  *out = the records when the pieces fit together
+ * (return 0); return 1 = not streamable (the pipeline hands such a file to its two-phase path), -1 = not FASTQ. */
+int ccb_host_index_fastq_chunked(const uint8_t* map, size_t nb, size_t chunk, ccb_reads** out);
+
 /* 2-bit packing, src/CuCLARK_hh.hh:1615-1715.  Returns #containers, -1 cap too small, -2 > 2^32. */
 size_t  ccb_host_pack_bound(const ccb_reads* r, size_t first, size_t count, int k);
 int64_t ccb_host_pack(const ccb_reads* r, size_t first, size_t count, int k,

@@ -13,6 +13,16 @@ extern "C" ccb_reads* ccb_host_index(const uint8_t* map, size_t nb, int threads)
     if (ccbh::index_reads(map, nb, threads, r->rs) != 0) { delete r; return nullptr; }
     return r;
 }
+extern "C" int ccb_host_index_fastq_chunked(const uint8_t* map, size_t nb, size_t chunk, ccb_reads** out)
+{
+    if (!out) return -1;
+    *out = nullptr;
+    ccb_reads* r = new ccb_reads();
+    const int rc = ccbh::index_fastq_chunked(map, nb, chunk, r->rs);
+    if (rc) { delete r; return rc; }
+    *out = r;
+    return 0;
+}
 extern "C" void ccb_host_reads_free(ccb_reads* r) { delete r; }
 extern "C" size_t ccb_host_reads_count(const ccb_reads* r) { return r ? r->rs.n() : 0; }
 extern "C" int ccb_host_reads_is_fasta(const ccb_reads* r) { return r && r->rs.fasta; }

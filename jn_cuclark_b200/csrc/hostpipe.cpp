@@ -701,6 +701,85 @@ int reserve_slots(const std::vector<ccb_handle*>& devs, int k, bool extended)
 // path below instead; both produce the same bytes.
 // ---------------------------------------------------------------------------
 namespace {
+// ---- FASTQ in chunks cut at arbitrary bytes (the streaming pipeline; index_fastq_chunked for the tests) -------------
+constexpr size_t kNoStart = ~(size_t)0;
+
+// The records of chunk (b, e]: those whose first byte p satisfies b < p <= e; the record at byte 0 belongs to the chunk
+// that starts there (at_origin).  The chunk's first record is found locally -- the first line in (b, e] that starts with
+// '@' two lines above a line that starts with '+' -- and every fourth line from there is taken as the reference's
+// positional parser does.  first = where the first record starts (kNoStart: none found), next = where the record after
+// the last one taken starts (nb: the text ended inside a record).  emit(rec) per record; false = a marker alone on its
+// line, or emit said stop.
+template <typename Emit>
+bool fastq_chunk_walk(const uint8_t* m, size_t nb, size_t b, size_t e, bool at_origin, size_t& first, size_t& next, Emit&& emit)
+{
+    size_t p = kNoStart;
+    if (at_origin) p = 0;
+    else {
+        NewlineStream nl(m, nb, b);
+        size_t q0, q1, q2;
+        if (nl.next(q0) && nl.next(q1) && nl.next(q2)) {
+            for (;;) {
+                const size_t st = q0 + 1;             // a line starts here
+                if (st > e) break;
+                if (m[st] == '@' && q2 + 1 < nb && m[q2 + 1] == '+') { p = st; break; }
+                q0 = q1; q1 = q2;
+                if (!nl.next(q2)) break;
+            }
+        }
+    }
+    first = p; next = kNoStart;
+    if (p == kNoStart) return true;
+    if (p + 1 >= nb) { next = p; return true; }
+    NewlineStream nl(m, nb, p);
+    for (;;) {
+        if (m[p + 1] == '\n') return false;           // a marker alone on its line: sequential indexer only
+        size_t q1, q2, q3, q4;
+        Rec r;
+        if (!nl.next(q1) || !nl.next(q2) || !nl.next(q3) || !nl.next(q4)) {
+            fastq_record(m, nb, p, r);                // the text ends inside the record: the plain parser knows every corner
+            next = nb;
+            return emit(r);
+        }
+        r.ns = p + 1; r.ne = name_end_before(m, r.ns, q1); r.ss = q1 + 1; r.se = q2; r.len = q2 - r.ss;
+        if (!emit(r)) return false;
+        p = q4 + 1;
+        if (q4 >= e || p + 1 >= nb) { next = p; return true; }
+    }
+}
+
+// the pieces are the sequential parse iff every chunk starts where the one before stopped (induction from byte 0)
+bool fastq_chunks_consistent(const std::vector<size_t>& first, const std::vector<size_t>& next, size_t nb, size_t chunk)
+{
+    if (first.empty()) return true;
+    size_t expect = next[0];
+    for (size_t c = 1; c < first.size(); c++) {
+        const size_t e = std::min(nb, c * chunk + chunk);
+        if (first[c] == kNoStart) { if (!(expect > e || expect + 1 >= nb)) return false; }
+        else if (first[c] != expect) return false;
+        else expect = next[c];
+    }
+    return true;
+}
+}  // namespace
+
+// the same walk without a device: every chunk indexed on its own, the pieces checked, the records in order
+int index_fastq_chunked(const uint8_t* m, size_t nb, size_t chunk, ReadSet& out)
+{
+    out.clear();
+    out.map = m; out.nb = nb; out.fasta = false;
+    if (nb < 2 || m[0] != '@' || chunk == 0) return -1;
+    if (m[1] == '\n') return 1;
+    const size_t C = (nb + chunk - 1) / chunk;
+    std::vector<size_t> first(C, kNoStart), next(C, kNoStart);
+    for (size_t c = 0; c < C; c++) {
+        const size_t b = c * chunk, e = std::min(nb, b + chunk);
+        if (!fastq_chunk_walk(m, nb, b, e, c == 0, first[c], next[c], [&](const Rec& r) { push(out, r); return true; })) return 1;
+    }
+    return fastq_chunks_consistent(first, next, nb, chunk) ? 0 : 1;
+}
+
+namespace {
 constexpr int kNotStreamable = -12345;
 constexpr size_t kStreamMinBytes = (size_t)128 << 20;
 
@@ -727,7 +806,6 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
     // file to the two-phase path.  The text is then walked ONCE: index, 2-bit packing and the copy of the names happen
     // record by record while the bytes are in the first-level cache.
     // FASTA: survey (markers alone on a line, chunks without a record start), then index and pack per chunk.
-    constexpr size_t kNoStart = ~(size_t)0;
     std::vector<size_t> first_start(C, kNoStart), next_start(C, kNoStart);
     std::atomic<bool> unusual(false);
     if (fasta) {
@@ -852,41 +930,7 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
                     cnt++; bytes += sb;
                     return true;
                 };
-                // where the chunk's first record starts
-                size_t p = kNoStart;
-                if (c == 0) p = 0;
-                else {
-                    NewlineStream nl(m, nb, b);
-                    size_t q0, q1, q2;
-                    if (nl.next(q0) && nl.next(q1) && nl.next(q2)) {
-                        for (;;) {
-                            const size_t st = q0 + 1;             // a line starts here
-                            if (st > e) break;
-                            if (m[st] == '@' && q2 + 1 < nb && m[q2 + 1] == '+') { p = st; break; }
-                            q0 = q1; q1 = q2;
-                            if (!nl.next(q2)) break;
-                        }
-                    }
-                }
-                first_start[c] = p;
-                if (p != kNoStart && p + 1 < nb) {
-                    NewlineStream nl(m, nb, p);
-                    for (;;) {
-                        if (m[p + 1] == '\n') { bad = true; break; }                    // a marker alone on its line: sequential indexer only
-                        size_t q1, q2, q3, q4;
-                        Rec r;
-                        if (!nl.next(q1) || !nl.next(q2) || !nl.next(q3) || !nl.next(q4)) {
-                            fastq_record(m, nb, p, r);            // the text ends inside the record: the plain parser knows every corner
-                            if (!emit(r)) bad = true;
-                            next_start[c] = nb;
-                            break;
-                        }
-                        r.ns = p + 1; r.ne = name_end_before(m, r.ns, q1); r.ss = q1 + 1; r.se = q2; r.len = q2 - r.ss;
-                        if (!emit(r)) { bad = true; break; }
-                        p = q4 + 1;
-                        if (q4 >= e || p + 1 >= nb) { next_start[c] = p; break; }
-                    }
-                } else if (p != kNoStart) next_start[c] = p;
+                if (!fastq_chunk_walk(m, nb, b, e, c == 0, first_start[c], next_start[c], emit)) bad = true;
                 if (bad) { if (slot >= 0) release(); if (!failed) give_up = true; sink.put(c, "", {}); return; }
                 if (!flush()) { sink.put(c, "", {}); return; }
                 c_idx += now() - t1; t1 = now();
@@ -950,16 +994,7 @@ int classify_stream(const std::vector<ccb_handle*>& devs, const uint8_t* m, size
     const bool io_err = sink.io_error || fclose(sink.f) != 0;
     if (sink.dump) fclose(sink.dump);
     if (failed) return failed;
-    if (!fasta && !give_up) {
-        // the pieces are the sequential parse iff every chunk starts where the one before stopped
-        size_t expect = next_start[0];
-        for (size_t c = 1; c < C && !give_up; c++) {
-            const size_t e = std::min(nb, c * chunk + chunk);
-            if (first_start[c] == kNoStart) { if (!(expect > e || expect + 1 >= nb)) give_up = true; }
-            else if (first_start[c] != expect) give_up = true;
-            else expect = next_start[c];
-        }
-    }
+    if (!fasta && !give_up && !fastq_chunks_consistent(first_start, next_start, nb, chunk)) give_up = true;
     if (give_up) return kNotStreamable;                  // nothing of the partial file is kept: the caller starts over
     stats.reads = n_reads; stats.batches = n_batches;
     stats.seconds_total = now() - t0;

@@ -49,6 +49,11 @@ struct ReadSet {
 // 0 = ok, -1 = neither '>' nor '@' first ("Failed to recognize the format of the file.")
 int index_reads(const uint8_t* map, size_t nb, int threads, ReadSet& out);
 
+// FASTQ only: the index the streaming pipeline arrives at when the text is cut into chunks of `chunk` bytes, each chunk
+// finding its first record by itself (hostpipe.cpp fastq_chunk_walk).  0 = the pieces fit together, out = the records
+// (equal to index_reads' by construction); 1 = not streamable (the pipeline gives such a file to the two-phase path).
+int index_fastq_chunked(const uint8_t* map, size_t nb, size_t chunk, ReadSet& out);
+
 // upper bound on u16 containers reads [first, first+count) can occupy
 size_t pack_bound(const ReadSet& r, size_t first, size_t count, int k);
 // A2 (src/CuCLARK_hh.hh:1615-1715): returns the number of containers written, -1 if cap is too small.

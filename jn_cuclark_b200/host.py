@@ -12,6 +12,7 @@ from .lib import load_library
 _VP = C.c_void_p
 HOST_SYMBOLS = {
     "ccb_host_index": (_VP, [_VP, C.c_size_t, C.c_int]),
+    "ccb_host_index_fastq_chunked": (C.c_int, [_VP, C.c_size_t, C.c_size_t, C.POINTER(_VP)]),
     "ccb_host_reads_free": (None, [_VP]),
     "ccb_host_reads_count": (C.c_size_t, [_VP]),
     "ccb_host_reads_is_fasta": (C.c_int, [_VP]),
@@ -117,3 +118,26 @@ def numa_probe(pci_bus_id: str):
 
 def numa_node_cpus(node: int) -> int:
     return _lib().ccb_host_numa_node_cpus(node)
+
+
+def index_fastq_chunked(data: bytes, chunk: int):
+    """The FASTQ index as the streaming pipeline finds it with the text cut into chunks of `chunk` bytes
+    (ccb_host_index_fastq_chunked): -> dict of the five field arrays, or None when the pieces do not fit together (such a
+    file goes through the two-phase path)."""
+    L = _lib()
+    buf = np.frombuffer(data, dtype=np.uint8)
+    r = _VP()
+    rc = L.ccb_host_index_fastq_chunked(buf.ctypes.data, buf.size, chunk, C.byref(r))
+    if rc == 1:
+        return None
+    if rc:
+        raise ValueError("not a FASTQ text")
+    try:
+        n = L.ccb_host_reads_count(r)
+        out = {}
+        for i, name in enumerate(FIELDS):
+            p = L.ccb_host_reads_field(r, i)
+            out[name] = np.ctypeslib.as_array(p, shape=(n,)).copy() if n else np.zeros(0, np.uint64)
+        return out
+    finally:
+        L.ccb_host_reads_free(r)

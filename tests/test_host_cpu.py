@@ -204,3 +204,61 @@ def test_numa_binding_is_scoped_and_optional(monkeypatch):
         monkeypatch.setenv("CCB_NUMA", "0")
         assert host.numa_probe(dev)[0] == -1
         break
+
+
+def _fastq(n, rng, at_quals=False, plus_seqs=0):
+    recs = []
+    for i in range(n):
+        L = int(rng.integers(1, 200))
+        seq = bytes(rng.choice(np.frombuffer(b"ACGTN", np.uint8), size=L))
+        if plus_seqs and i % plus_seqs == 1:
+            seq = b"+" + seq[1:]
+        q = bytes(rng.integers(33, 74, L, dtype=np.uint8))
+        if at_quals:
+            q = b"@" + q[1:]
+        recs.append(b"@r%d some text/1\n" % i + seq + b"\n+\n" + q + b"\n")
+    return b"".join(recs)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_fastq_index_in_chunks_equals_sequential_index(seed):
+    """The streaming pipeline cuts a FASTQ text at arbitrary bytes; every chunk finds its first record by itself (a line
+    starting with '@' two lines above a line starting with '+') and takes every fourth line from there; the pieces are
+    checked against each other.  Whatever it accepts must be exactly the sequential index (reference
+    src/CuCLARK_hh.hh:1496-1524) -- for every chunk size, also when every quality line starts with '@', with CRLF-free
+    ragged reads, and with a tail cut short; what tries to fool it must be refused (None), never mis-indexed."""
+    from jn_cuclark_b200 import host
+    rng = np.random.default_rng(seed)
+
+    def same(data, chunk):
+        want = host.HostReads(data)
+        got = host.index_fastq_chunked(data, chunk)
+        if got is None:
+            return False
+        for f in host.FIELDS:
+            assert np.array_equal(got[f], want.arr(f)), (f, chunk)
+        return True
+
+    plain = _fastq(300, rng)
+    atq = _fastq(300, rng, at_quals=True)
+    for chunk in (64, 257, 1000, 4096, 10 ** 6):
+        assert same(plain, chunk), chunk
+        assert same(atq, chunk), chunk                      # quality lines that start with '@' are not headers: line + 2 tells
+        for cut in (1, 7, 40):
+            same(plain[:-cut], chunk)                       # a truncated tail: accepted only if equal (asserted inside)
+    # sequences that start with '+' behind quality lines that start with '@': a quality line then looks exactly like a header.
+    # Some chunk sizes start on the wrong line -- the check at the end must refuse those; none may return a wrong index.
+    fooled = _fastq(300, rng, at_quals=True, plus_seqs=3)
+    refused = 0
+    for chunk in range(50, 1200, 37):
+        refused += 0 if same(fooled, chunk) else 1
+    assert refused > 0
+    # a marker alone on its line is for the sequential indexer
+    odd = plain[:len(plain) // 2]
+    odd = odd[:odd.rindex(b"\n@") + 1] + b"@\nACGT\n+\nIIII\n" + plain[len(plain) // 2:][plain[len(plain) // 2:].index(b"\n@") + 1:]
+    assert host.index_fastq_chunked(odd, 500) is None
+    # missing line: records shifted from there on; either refused or (chunks that never see the damage) equal
+    lines = plain.split(b"\n")
+    broken = b"\n".join(lines[:401] + lines[402:])
+    for chunk in (100, 333, 5000, 10 ** 6):
+        same(broken, chunk)
