@@ -421,12 +421,12 @@ struct Engine {
     void run_pair(const char* f1, const char* f2, const char* result_prefix)
     {   // the reference writes <f1>_ConcatenatedByCLARK.fa, classifies it as FASTA and deletes it
         // (src/CuCLARK_hh.hh:442-452); the same text is built in memory here.
-        vector<char> text; string err;
+        ccbh::TextBuf text; string err;
         if (cli.gzipped) {
             vector<char> a, b;
             if (!inflate_file(f1, a) || !inflate_file(f2, b) || a.empty() || b.empty()) { cerr << "Failed to uncompress input objects." << endl; exit(1); }
-            if (ccbh::join_pairs_streams(fmemopen(a.data(), a.size(), "r"), fmemopen(b.data(), b.size(), "r"), text, err)) { cerr << err << endl; exit(1); }
-        } else if (ccbh::join_pairs(f1, f2, text, err)) { cerr << err << endl; exit(1); }
+            if (ccbh::join_pairs_texts((const uint8_t*)a.data(), a.size(), (const uint8_t*)b.data(), b.size(), text, err, (int)cli.cpu)) { cerr << err << endl; exit(1); }
+        } else if (ccbh::join_pairs(f1, f2, text, err, (int)cli.cpu)) { cerr << err << endl; exit(1); }
         cerr << "Classifying: " << f1 << "_ConcatenatedByCLARK.fa" << "\n";
         if (text.empty()) { cerr << "Failed to open " << f1 << "_ConcatenatedByCLARK.fa" << endl; return; }
         classify(f1, (const uint8_t*)text.data(), text.size(), result_prefix, true);

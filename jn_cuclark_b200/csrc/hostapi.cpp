@@ -50,7 +50,7 @@ extern "C" int64_t ccb_host_pack(const ccb_reads* r, size_t first, size_t count,
 }
 extern "C" int ccb_host_join_pairs(const char* f1, const char* f2, char** out, size_t* len, char* err, size_t errcap)
 {
-    std::vector<char> text; std::string e;
+    ccbh::TextBuf text; std::string e;
     int rc = ccbh::join_pairs(f1, f2, text, e);
     if (rc) { if (err && errcap) { strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; } return rc; }
     *out = (char*)malloc(text.size() ? text.size() : 1);

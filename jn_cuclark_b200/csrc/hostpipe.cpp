@@ -13,6 +13,10 @@
 #include <chrono>
 #include <memory>
 #include <stdlib.h>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #ifndef _GNU_SOURCE
 #define _GNU_SOURCE
@@ -486,14 +490,124 @@ inline void pair_id(const char* s, size_t n, const char*& b, size_t& len)
 
 }  // namespace
 
-int join_pairs(const char* file1, const char* file2, std::vector<char>& out, std::string& err)
+int join_pairs(const char* file1, const char* file2, TextBuf& out, std::string& err, int threads)
 {
+    // small files, and whatever cannot be mapped: line by line
+    size_t min_bytes = (size_t)1 << 20;
+    if (const char* e = getenv("CCB_JOIN_MIN_BYTES")) min_bytes = (size_t)atoll(e);                                         // (tests)
+    struct Map {
+        int fd = -1; void* p = MAP_FAILED; size_t n = 0;
+        explicit Map(const char* f)
+        {
+            struct stat sb;
+            fd = open(f, O_RDONLY);
+            if (fd != -1 && fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0) { n = (size_t)sb.st_size; p = mmap(nullptr, n, PROT_READ, MAP_PRIVATE, fd, 0); }
+        }
+        ~Map() { if (p != MAP_FAILED) munmap(p, n); if (fd != -1) close(fd); }
+        bool ok() const { return p != MAP_FAILED; }
+    };
+    if (!getenv("CCB_JOIN_SEQUENTIAL")) {
+        Map a(file1), b(file2);
+        if (a.ok() && b.ok() && a.n >= min_bytes && b.n >= min_bytes)
+            return join_pairs_texts((const uint8_t*)a.p, a.n, (const uint8_t*)b.p, b.n, out, err, threads);
+    }
     FILE* fa = fopen(file1, "r"); FILE* fb = fopen(file2, "r");
     if (!fa || !fb) { err = std::string("Failed to find/read ") + (!fa ? file1 : file2); if (fa) fclose(fa); if (fb) fclose(fb); return 1; }
     return join_pairs_streams(fa, fb, out, err);
 }
 
-int join_pairs_streams(FILE* fa, FILE* fb, std::vector<char>& out, std::string& err)
+int join_pairs_texts(const uint8_t* a, size_t na, const uint8_t* b, size_t nb, TextBuf& out, std::string& err, int threads)
+{
+    auto sequential = [&]() -> int {
+        FILE* fa = fmemopen((void*)a, na, "r"); FILE* fb = fmemopen((void*)b, nb, "r");
+        if (!fa || !fb) { err = "Failed to find/read the paired-end reads"; if (fa) fclose(fa); if (fb) fclose(fb); return 1; }
+        return join_pairs_streams(fa, fb, out, err);
+    };
+    if (na == 0 || nb == 0 || getenv("CCB_JOIN_SEQUENTIAL")) return sequential();
+    int T = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+    if (T < 1) T = 1;
+    if (T > 64) T = 64;
+    // lines of both texts, counted slice by slice
+    struct Side { const uint8_t* m; size_t n; std::vector<size_t> cut; std::vector<uint64_t> before; uint64_t lines = 0; };
+    Side S[2] = {{a, na, {}, {}}, {b, nb, {}, {}}};
+    for (Side& s : S) {
+        s.cut.resize((size_t)T + 1); s.before.assign((size_t)T + 1, 0);
+        for (int t = 0; t <= T; t++) s.cut[(size_t)t] = s.n / (size_t)T * (size_t)t;
+        s.cut[(size_t)T] = s.n;
+    }
+    {
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; t++) th.emplace_back([&, t] {
+            for (Side& s : S) s.before[(size_t)t + 1] = count_newlines(s.m + s.cut[(size_t)t], s.cut[(size_t)t + 1] - s.cut[(size_t)t]);
+        });
+        for (auto& x : th) x.join();
+    }
+    for (Side& s : S) {
+        for (int t = 0; t < T; t++) s.before[(size_t)t + 1] += s.before[(size_t)t];      // newlines in front of slice t + 1
+        s.lines = s.before[(size_t)T] + (s.m[s.n - 1] != '\n' ? 1u : 0u);
+    }
+    if (S[0].lines != S[1].lines || S[0].lines == 0 || (S[0].lines & 3)) return sequential();
+    const uint64_t R = S[0].lines / 4;
+    const int W = (int)std::min<uint64_t>((uint64_t)T, R);
+    // where line number `line` starts: behind the line-th newline, which lies in the slice with before[t] < line <= before[t+1]
+    auto line_start = [&](const Side& s, uint64_t line) -> size_t {
+        if (line == 0) return 0;
+        size_t t = (size_t)(std::lower_bound(s.before.begin(), s.before.end(), line) - s.before.begin()) - 1;
+        NewlineStream nl(s.m, s.cut[t + 1], s.cut[t]);
+        size_t q = 0;
+        for (uint64_t i = s.before[t]; i < line; i++) nl.next(q);
+        return q + 1;
+    };
+    std::vector<TextBuf> piece((size_t)W);
+    std::atomic<int> odd(0), mismatch(0);
+    {
+        std::vector<std::thread> th;
+        for (int w = 0; w < W; w++) th.emplace_back([&, w] {
+            const uint64_t r0 = R * (uint64_t)w / (uint64_t)W, r1 = R * (uint64_t)(w + 1) / (uint64_t)W;
+            size_t pa = line_start(S[0], 4 * r0), pb = line_start(S[1], 4 * r0);
+            NewlineStream na_(a, na, pa), nb_(b, nb, pb);
+            TextBuf& o = piece[(size_t)w];
+            o.reserve((size_t)((double)(na + nb) / (double)W * 0.56) + 4096);
+            auto next = [](NewlineStream& s, size_t n, size_t& q) { if (!s.next(q)) q = n; };   // the last line may lack its newline
+            for (uint64_t r = r0; r < r1 && !odd && !mismatch; r++) {
+                size_t ha, sa, xa, ya, hb, sb, xb, yb;
+                next(na_, na, ha); next(na_, na, sa); next(na_, na, xa); next(na_, na, ya);
+                next(nb_, nb, hb); next(nb_, nb, sb); next(nb_, nb, xb); next(nb_, nb, yb);
+                // header lines [pa, ha), [pb, hb); sequences [ha + 1, sa), [hb + 1, sb)
+                if (!(ha > pa && hb > pb && a[pa] == '@' && b[pb] == '@')) { odd = 1; break; }
+                const char *ia, *ib; size_t la, lb;
+                pair_id((const char*)a + pa, ha - pa, ia, la); pair_id((const char*)b + pb, hb - pb, ib, lb);
+                if (la != lb || memcmp(ia, ib, la) != 0) { mismatch = 1; break; }
+                const size_t qa = std::min(ha + 1, sa), qb = std::min(hb + 1, sb);
+                const size_t need = 1 + la + 1 + (sa - qa) + 1 + (sb - qb) + 1, at = o.size();
+                o.resize(at + need);
+                char* d = o.data() + at;
+                *d++ = '>'; memcpy(d, ia, la); d += la; *d++ = '\n';
+                memcpy(d, a + qa, sa - qa); d += sa - qa; *d++ = 'N';
+                memcpy(d, b + qb, sb - qb); d += sb - qb; *d++ = '\n';
+                pa = std::min(ya + 1, na); pb = std::min(yb + 1, nb);
+            }
+        });
+        for (auto& x : th) x.join();
+    }
+    if (mismatch) { out.clear(); err = "Error: read id does not match between files!"; return 1; }
+    if (odd) return sequential();                        // a fourth line that is no header: the line-by-line join knows what the reference does
+    std::vector<size_t> at((size_t)W + 1, 0);
+    for (int w = 0; w < W; w++) at[(size_t)w + 1] = at[(size_t)w] + piece[(size_t)w].size();
+    out.clear();
+    out.resize(at[(size_t)W]);
+    {
+        std::vector<std::thread> th;
+        for (int w = 0; w < W; w++) th.emplace_back([&, w] {
+            if (!piece[(size_t)w].empty()) memcpy(out.data() + at[(size_t)w], piece[(size_t)w].data(), piece[(size_t)w].size());
+            TextBuf().swap(piece[(size_t)w]);
+        });
+        for (auto& x : th) x.join();
+    }
+    return 0;
+}
+
+int join_pairs_streams(FILE* fa, FILE* fb, TextBuf& out, std::string& err)
 {
     LineReader a(fa), b(fb);
     if (!a.f || !b.f) { err = "Failed to find/read the paired-end reads"; return 1; }

@@ -33,6 +33,7 @@ struct NoInitAlloc : std::allocator<T> {
     template <typename U, typename... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
 };
 using OffsetVec = std::vector<uint64_t, NoInitAlloc<uint64_t>>;
+using TextBuf = std::vector<char, NoInitAlloc<char>>;      // the joined text of 10 M pairs is 3.3 GB: not to be zero-filled first
 
 // One entry per read, byte offsets into the mapped text (A1, src/CuCLARK_hh.hh:1364-1394, 1496-1524)
 struct ReadSet {
@@ -63,9 +64,14 @@ int64_t pack_reads(const ReadSet& r, size_t first, size_t count, int k,
                    uint32_t* offsets, uint16_t* containers, size_t cap);
 
 // A10 (src/file.cc:205-268): ">id\n<mate1>N<mate2>\n" per pair, in memory.  0 = ok, otherwise err is set.
-int join_pairs(const char* file1, const char* file2, std::vector<char>& out, std::string& err);
-// the same on two open streams (files, or fmemopen over texts inflated in memory); both are closed
-int join_pairs_streams(FILE* a, FILE* b, std::vector<char>& out, std::string& err);
+int join_pairs(const char* file1, const char* file2, TextBuf& out, std::string& err, int threads = 0);
+// the same on two open streams, line by line as the reference reads them; both are closed
+int join_pairs_streams(FILE* a, FILE* b, TextBuf& out, std::string& err);
+// the same on two texts in memory (mapped files, or texts inflated from .gz).  Files that are what they should be -- the
+// same number of lines, a multiple of four, every fourth line of both starting with '@' -- are joined by `threads` workers
+// on ranges of records (0 = one per hardware thread); anything else goes line by line through join_pairs_streams, so
+// every result and every error message is the sequential join's.
+int join_pairs_texts(const uint8_t* a, size_t na, const uint8_t* b, size_t nb, TextBuf& out, std::string& err, int threads = 0);
 
 // A7 (src/CuCLARK_hh.hh:1952-1967, 2096-2118)
 void csv_header(std::string& out, bool extended, const std::vector<std::string>& target_names);

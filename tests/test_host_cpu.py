@@ -262,3 +262,69 @@ def test_fastq_index_in_chunks_equals_sequential_index(seed):
     broken = b"\n".join(lines[:401] + lines[402:])
     for chunk in (100, 333, 5000, 10 ** 6):
         same(broken, chunk)
+
+
+def test_parallel_pair_join_equals_the_line_by_line_join(oracle, tmp_path, monkeypatch):
+    """join_pairs on large files splits the records over threads (hostpipe.cpp join_pairs_texts); small files and anything
+    unusual go line by line as the reference reads them (src/file.cc:205-268).  Forced onto small files here
+    (CCB_JOIN_MIN_BYTES=0): the same bytes as the line-by-line join (CCB_JOIN_SEQUENTIAL=1) and as the oracle's merge, the same
+    error messages, for well-formed files, files without a final newline, CRLF, ids with separators, empty sequences,
+    unequal record counts, a damaged record, a line that is no header where one belongs."""
+    from jn_cuclark_b200 import host
+    rng = np.random.default_rng(5)
+
+    def fq(n, tag, lens=None, crlf=False, ids=None):
+        out = []
+        for i in range(n):
+            L = int(lens[i]) if lens is not None else int(rng.integers(0, 180))
+            s = bytes(rng.choice(np.frombuffer(b"ACGTN", np.uint8), size=L))
+            name = ids[i] if ids else b"read%d" % i
+            eol = b"\r\n" if crlf else b"\n"
+            out.append(b"@" + name + tag + eol + s + eol + b"+" + eol + b"I" * L + eol)
+        return b"".join(out)
+
+    def both(a, b):
+        fa, fb = tmp_path / "a.fq", tmp_path / "b.fq"
+        fa.write_bytes(a); fb.write_bytes(b)
+        res = []
+        for seq in (True, False):
+            if seq:
+                monkeypatch.setenv("CCB_JOIN_SEQUENTIAL", "1")
+            else:
+                monkeypatch.delenv("CCB_JOIN_SEQUENTIAL", raising=False)
+            try:
+                res.append(("ok", host.join_pairs(str(fa), str(fb))))
+            except RuntimeError as e:
+                res.append(("err", str(e)))
+        assert res[0] == res[1], (res[0][0], res[1][0], res[0][1][:200], res[1][1][:200])
+        return res[0], str(fa), str(fb)
+
+    monkeypatch.setenv("CCB_JOIN_MIN_BYTES", "0")
+    ids = [b"r%d" % i if i % 5 else b"weird id %d/x" % i for i in range(1000)]
+    a, b = fq(1000, b"/1", ids=ids), fq(1000, b"/2", ids=ids)
+    (kind, text), fa, fb = both(a, b)
+    assert kind == "ok" and text.count(b"\n") == 2000
+    m = str(tmp_path / "m.fa")
+    assert oracle.merge_paired(fa, fb, m) == 0 and open(m, "rb").read() == text
+    assert both(a[:-1], b[:-1])[0][0] == "ok"                         # no newline at the end of either file
+    assert both(a[:-1], b)[0][0] == "ok"
+    assert both(fq(300, b"/1", crlf=True), fq(300, b"/2", crlf=True))[0][0] == "ok"
+    assert both(fq(50, b" 1"), fq(50, b" 2"))[0][0] == "ok"
+    assert both(fq(3, b"/1"), fq(3, b"/2"))[0][0] == "ok"             # fewer records than threads
+    # unequal counts, a record cut short, a missing line, an id that differs, a non-header where a header belongs
+    assert both(a, fq(900, b"/2", ids=ids))[0][0] in ("ok", "err")
+    assert both(a, b[: len(b) // 2])[0][0] in ("ok", "err")
+    la = a.split(b"\n")
+    assert both(b"\n".join(la[:41] + la[42:]), b)[0][0] in ("ok", "err")
+    bad_id = b.replace(b"@r501/2", b"@q501/2")
+    assert bad_id != b
+    (kind, msg), _, _ = both(a, bad_id)
+    assert kind == "err" and "does not match" in msg
+    shifted = b"\n".join(la[:400] + [b"x" + la[400][1:]] + la[401:])    # line 400 is a header: make it start with 'x'
+    assert both(shifted, b)[0][0] in ("ok", "err")
+    (kind, msg), _, _ = both(b">r0\nACGT\n", b">r0\nACGT\n")
+    assert kind == "err" and "FASTQ" in msg
+    # the golden pair files through the parallel path
+    f1, f2 = os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")
+    assert oracle.merge_paired(f1, f2, m) == 0
+    assert open(m, "rb").read() == host.join_pairs(f1, f2)
