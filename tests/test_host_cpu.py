@@ -328,3 +328,16 @@ def test_parallel_pair_join_equals_the_line_by_line_join(oracle, tmp_path, monke
     f1, f2 = os.path.join(WORLD, "p1.fq"), os.path.join(WORLD, "p2.fq")
     assert oracle.merge_paired(f1, f2, m) == 0
     assert open(m, "rb").read() == host.join_pairs(f1, f2)
+
+
+def test_host_suite_on_the_scalar_paths():
+    """The AVX2 routines (newline events, marker scan, 2-bit packer: csrc/hostscan_avx2.cpp) are chosen once per process;
+    CCB_NO_AVX2=1 takes the scalar code instead.  Every test of this file once more in a process that runs without them."""
+    import subprocess
+    import sys
+    if os.environ.get("CCB_NO_AVX2"):
+        pytest.skip("already the scalar run")
+    env = dict(os.environ, CCB_NO_AVX2="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-x", "-p", "no:cacheprovider"],
+                       env=env, capture_output=True, text=True, timeout=900, cwd=os.path.dirname(HERE))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
